@@ -1,0 +1,153 @@
+// Internal types shared by the host planner and the kernels of the B200 hash groupby.
+// Layout of the group table in HBM (SoA):
+//   keys    : capacity+1 packed keys (64-bit, or 128-bit as ulonglong2), EMPTY = all ones; slot `capacity` is the
+//             reserved home of the one real key whose packed image equals EMPTY
+//   cells[a]: one array per accumulator, capacity+1 cells of 4 or 8 bytes, initialised to the aggregation identity
+// Accumulator semantics follow cudf::detail::update_target_element
+// (/root/reference/cpp/include/cudf/detail/aggregation/device_aggregators.cuh:24-160,309-446).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/bgb.h"
+
+namespace bgb {
+
+constexpr int kMaxKeyCols = 8;
+constexpr int kMaxAccs    = 24;   // accumulator columns per kernel launch
+constexpr int kMaxOuts    = 32;   // output columns per emit launch
+constexpr uint64_t kEmpty = ~0ull;
+
+// physical source element types
+enum Src : uint8_t { S_I8, S_I16, S_I32, S_I64, S_U8, S_U16, S_U32, S_U64, S_F32, S_F64, S_BOOL, S_BAD };
+
+// accumulator ops; cell width is 8 bytes except ACC_COUNT* and *_F32 (4 bytes)
+enum AccOp : uint8_t {
+  ACC_SUM_I64,    // any integral source, wraps like int64 atomic_add
+  ACC_SUM_F64,
+  ACC_SUM_F32,
+  ACC_SUMSQ_I64,
+  ACC_SUMSQ_F64,
+  ACC_SUMSQ_F32,
+  ACC_PROD_I64,
+  ACC_PROD_F64,
+  ACC_PROD_F32,
+  ACC_MIN,        // order-preserving unsigned 64-bit image of the source value, RED.MIN.U64
+  ACC_MAX,
+  ACC_COUNT_VALID,
+  ACC_COUNT_ALL,
+  ACC_ARGMIN,     // (ordered value image << 32 | row) for <= 32-bit sources
+  ACC_ARGMAX
+};
+
+__host__ __device__ inline int acc_cell_bytes(uint8_t op)
+{
+  return (op == ACC_SUM_F32 || op == ACC_SUMSQ_F32 || op == ACC_PROD_F32 || op == ACC_COUNT_VALID || op == ACC_COUNT_ALL) ? 4 : 8;
+}
+
+struct KeyColDesc {
+  const uint8_t* data;
+  const uint32_t* mask;   // nullptr = no nulls
+  int32_t offset;
+  uint8_t width;          // bytes: 1,2,4,8
+  uint8_t fclass;         // 0 integer-like, 1 float32, 2 float64 (normalise -0 / NaN)
+  uint8_t shift;          // bit position of the value field in the packed key (0..127)
+  int8_t null_bit;        // bit position of the "is null" flag (INCLUDE policy), -1 if none
+};
+
+struct AccDesc {
+  const uint8_t* data;
+  const uint32_t* mask;
+  int32_t offset;
+  uint8_t src;            // Src
+  uint8_t op;             // AccOp
+  uint8_t pad[2];
+  void* cells;            // capacity+1 cells
+};
+
+struct TableDesc {
+  uint64_t* keys;         // 64-bit keys, or 128-bit keys as pairs when key_words == 2
+  uint64_t capacity;      // power of two
+  uint32_t* status;       // [0] overflow flag, [1] number of groups (written by compaction)
+  int32_t key_words;      // 1 or 2
+};
+
+struct AggParams {
+  KeyColDesc kc[kMaxKeyCols];
+  AccDesc acc[kMaxAccs];
+  TableDesc table;
+  int64_t num_rows;
+  int32_t num_key_cols;
+  int32_t num_accs;
+  int32_t skip_null_keys;  // null_policy::EXCLUDE and some key column has a mask
+  int32_t init_keys;       // init kernel: also reset keys + status (first accumulator chunk)
+};
+
+// final (output) operations of the emit kernel
+enum OutOp : uint8_t {
+  OUT_KEY,        // unpack key column
+  OUT_COPY_I64,   // 8-byte integer cell -> out type (int64 for sums, narrowed ordered image for MIN/MAX)
+  OUT_COPY_F64,
+  OUT_COPY_F32,
+  OUT_MINMAX,     // decode ordered image to the source type
+  OUT_COUNT,      // int32 cell
+  OUT_MEAN,       // double(sum) / double(count)
+  OUT_MEAN_INT,   // duration / decimal MEAN keeps the source rep: integer division
+  OUT_M2,
+  OUT_VAR,
+  OUT_STD,
+  OUT_ARG         // low 32 bits of the packed (value,row) cell
+};
+
+struct OutDesc {
+  void* out;              // output data
+  uint32_t* out_mask;     // output null mask or nullptr
+  int32_t* null_count;    // device counter (or nullptr)
+  const void* a;          // primary cell array (sum / min / max / count ...)
+  const void* b;          // sum of squares
+  const int32_t* cnt;     // COUNT_VALID cells of the value column (validity + MEAN/VAR), may be nullptr
+  int32_t ddof;
+  uint8_t op;             // OutOp
+  uint8_t src;            // Src of the value (or key) column
+  uint8_t out_width;      // bytes of the output element
+  uint8_t acc_op;         // AccOp that produced `a` (cell width / numeric class)
+  // OUT_KEY only
+  uint8_t shift;
+  int8_t null_bit;
+  uint8_t pad[2];
+};
+
+struct EmitParams {
+  OutDesc out[kMaxOuts];
+  const uint64_t* keys;
+  const uint32_t* group_slots;  // slot index of group j
+  int32_t num_groups;
+  int32_t num_outs;
+  int32_t key_words;
+};
+
+// ------------------------------------------------------------------ device helpers shared by kernels
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t z)
+{
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+// counter-based SplitMix64 x(seed,row) -- identical to oracle/groupby_oracle.c orc_splitmix64
+__host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t seed, uint64_t row)
+{
+  uint64_t z = seed * 0x1000003ull + row + 0x9E3779B97F4A7C15ull;
+  return mix64(z);
+}
+
+// host-side API of the kernel translation units
+cudaError_t launch_init_table(const AggParams& p, cudaStream_t s);
+cudaError_t launch_aggregate_global(const AggParams& p, cudaStream_t s);
+cudaError_t launch_estimate_cardinality(const AggParams& p, int64_t sample_rows, uint64_t* scratch_set, uint64_t set_capacity,
+                                        uint32_t* out_distinct, cudaStream_t s);
+// compaction: fills group_slots[] with occupied slot ids (arbitrary order), status[1] = count
+cudaError_t launch_compact(const TableDesc& t, uint32_t* group_slots, uint32_t* scan_state, cudaStream_t s);
+size_t compact_scan_state_bytes(uint64_t capacity);
+cudaError_t launch_emit(const EmitParams& p, cudaStream_t s);
+
+}  // namespace bgb

@@ -1,0 +1,164 @@
+// Device helpers: element loads, key packing, ordered images, open-addressing probe.
+#pragma once
+#include "bgb_internal.cuh"
+
+namespace bgb {
+
+__device__ __forceinline__ bool bit_is_set(const uint32_t* mask, int64_t i)
+{
+  return (__ldg(mask + (i >> 5)) >> (i & 31)) & 1u;
+}
+
+// raw little-endian bits of one element, zero-extended
+__device__ __forceinline__ uint64_t load_raw(const uint8_t* data, int width, int64_t idx)
+{
+  switch (width) {
+    case 1: return __ldg(data + idx);
+    case 2: return __ldg(reinterpret_cast<const uint16_t*>(data) + idx);
+    case 4: return __ldg(reinterpret_cast<const uint32_t*>(data) + idx);
+    default: return __ldg(reinterpret_cast<const unsigned long long*>(data) + idx);
+  }
+}
+
+// key element canonicalisation: -0 -> +0, any NaN -> one quiet NaN
+// (/root/reference/cpp/include/cudf/hashing/detail/hash_functions.cuh:19-39; equality.cuh nan_equal comparator)
+__device__ __forceinline__ uint64_t canon_key_bits(uint64_t raw, int fclass)
+{
+  if (fclass == 1) {
+    uint32_t u = (uint32_t)raw;
+    if ((u & 0x7fffffffu) == 0) return 0;
+    if ((u & 0x7fffffffu) > 0x7f800000u) return 0x7fc00000u;
+    return u;
+  }
+  if (fclass == 2) {
+    if ((raw & 0x7fffffffffffffffull) == 0) return 0;
+    if ((raw & 0x7fffffffffffffffull) > 0x7ff0000000000000ull) return 0x7ff8000000000000ull;
+  }
+  return raw;
+}
+
+// packs the key columns of `row` into (k0,k1); returns false when the row must be skipped (EXCLUDE + null key)
+__device__ __forceinline__ bool pack_key(const AggParams& p, int64_t row, uint64_t& k0, uint64_t& k1)
+{
+  k0 = 0; k1 = 0;
+#pragma unroll 1
+  for (int c = 0; c < p.num_key_cols; ++c) {
+    const KeyColDesc& kc = p.kc[c];
+    int64_t idx = (int64_t)kc.offset + row;
+    bool valid = kc.mask == nullptr || bit_is_set(kc.mask, idx);
+    if (!valid) {
+      if (p.skip_null_keys) return false;
+      if (kc.null_bit >= 0) { if (kc.null_bit < 64) k0 |= 1ull << kc.null_bit; else k1 |= 1ull << (kc.null_bit - 64); }
+      continue;  // value bits of a null key stay zero: all nulls are equal (null_equality::EQUAL)
+    }
+    uint64_t v = canon_key_bits(load_raw(kc.data, kc.width, idx), kc.fclass);
+    if (kc.shift < 64) k0 |= v << kc.shift; else k1 |= v << (kc.shift - 64);
+  }
+  return true;
+}
+
+__device__ __forceinline__ uint64_t hash_key(uint64_t k0, uint64_t k1, int key_words)
+{
+  uint64_t h = mix64(k0 + 0x9E3779B97F4A7C15ull);
+  if (key_words == 2) h = mix64(h ^ (k1 * 0xD6E8FEB86659FD93ull));
+  return h;
+}
+
+__device__ __forceinline__ void cas128(uint64_t* addr, uint64_t c0, uint64_t c1, uint64_t n0, uint64_t n1, uint64_t& o0, uint64_t& o1)
+{
+  asm volatile(
+    "{\n\t.reg .b128 c, n, o;\n\tmov.b128 c, {%2, %3};\n\tmov.b128 n, {%4, %5};\n\t"
+    "atom.global.relaxed.gpu.cas.b128 o, [%6], c, n;\n\tmov.b128 {%0, %1}, o;\n\t}"
+    : "=l"(o0), "=l"(o1)
+    : "l"(c0), "l"(c1), "l"(n0), "l"(n1), "l"(addr)
+    : "memory");
+}
+
+constexpr uint64_t kNoSlot       = ~0ull;
+constexpr uint32_t kMaxProbes    = 8192;  // beyond this the table is declared overloaded and the host retries bigger
+
+// linear-probing find-or-insert in the HBM table; returns slot or kNoSlot (overflow flag set)
+__device__ __forceinline__ uint64_t find_or_insert(const TableDesc& t, uint64_t k0, uint64_t k1)
+{
+  const uint64_t cap = t.capacity;
+  if (t.key_words == 1) {
+    if (k0 == kEmpty) { t.status[2] = 1; return cap; }
+    uint64_t slot = hash_key(k0, 0, 1) & (cap - 1);
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(t.keys);
+    for (uint32_t probes = 0; probes < kMaxProbes; ++probes) {
+      unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(keys + slot);
+      if (cur == k0) return slot;
+      if (cur == kEmpty) {
+        unsigned long long old = atomicCAS(keys + slot, (unsigned long long)kEmpty, (unsigned long long)k0);
+        if (old == kEmpty || old == k0) return slot;
+      }
+      slot = (slot + 1) & (cap - 1);
+    }
+  } else {
+    if (k0 == kEmpty && k1 == kEmpty) { t.status[2] = 1; return cap; }
+    uint64_t slot = hash_key(k0, k1, 2) & (cap - 1);
+    for (uint32_t probes = 0; probes < kMaxProbes; ++probes) {
+      const volatile uint64_t* e = t.keys + 2 * slot;
+      uint64_t c0 = e[0], c1 = e[1];
+      // a torn read can only mix EMPTY words with final words (slots go EMPTY -> key exactly once, atomically);
+      // keys that themselves contain an all-ones word never trust the two-load fast path and always take the CAS
+      const bool odd_key = (k0 == kEmpty) || (k1 == kEmpty);
+      if (!odd_key && c0 == k0 && c1 == k1) return slot;
+      if (odd_key || c0 == kEmpty || c1 == kEmpty) {
+        uint64_t o0, o1;
+        cas128(t.keys + 2 * slot, kEmpty, kEmpty, k0, k1, o0, o1);
+        if ((o0 == kEmpty && o1 == kEmpty) || (o0 == k0 && o1 == k1)) return slot;
+      }
+      slot = (slot + 1) & (cap - 1);
+    }
+  }
+  t.status[0] = 1;
+  return kNoSlot;
+}
+
+// ---- order-preserving unsigned images (so that MIN/MAX are one RED.MIN/MAX.U64 for every type)
+__device__ __forceinline__ uint64_t ordered_image(uint64_t raw, int src)
+{
+  switch (src) {
+    case S_I8: return (uint64_t)((int64_t)(int8_t)raw) ^ 0x8000000000000000ull;
+    case S_I16: return (uint64_t)((int64_t)(int16_t)raw) ^ 0x8000000000000000ull;
+    case S_I32: return (uint64_t)((int64_t)(int32_t)raw) ^ 0x8000000000000000ull;
+    case S_I64: return raw ^ 0x8000000000000000ull;
+    case S_F32: { uint32_t u = (uint32_t)raw; return (u & 0x80000000u) ? (uint32_t)~u : (u | 0x80000000u); }
+    case S_F64: return (raw >> 63) ? ~raw : (raw | 0x8000000000000000ull);
+    case S_BOOL: return raw != 0;
+    default: return raw;  // unsigned
+  }
+}
+__device__ __forceinline__ uint64_t ordered_decode(uint64_t img, int src)
+{
+  switch (src) {
+    case S_I8: case S_I16: case S_I32: case S_I64: return img ^ 0x8000000000000000ull;
+    case S_F32: { uint32_t u = (uint32_t)img; return (u & 0x80000000u) ? (u & 0x7fffffffu) : (uint32_t)~u; }
+    case S_F64: return (img >> 63) ? (img & 0x7fffffffffffffffull) : ~img;
+    default: return img;
+  }
+}
+
+__device__ __forceinline__ int src_width(int src)
+{
+  switch (src) {
+    case S_I8: case S_U8: case S_BOOL: return 1;
+    case S_I16: case S_U16: return 2;
+    case S_I32: case S_U32: case S_F32: return 4;
+    default: return 8;
+  }
+}
+// integral source -> int64 (static_cast<int64_t>(Source) in update_target_element<Source, SUM>)
+__device__ __forceinline__ int64_t raw_to_i64(uint64_t raw, int src)
+{
+  switch (src) {
+    case S_I8: return (int8_t)raw;
+    case S_I16: return (int16_t)raw;
+    case S_I32: return (int32_t)raw;
+    case S_BOOL: return raw != 0;
+    default: return (int64_t)raw;  // I64, U8..U64 (uint64 reinterpreted, like the reference's static_cast)
+  }
+}
+
+}  // namespace bgb

@@ -1,0 +1,27 @@
+#include "errors.h"
+
+#include <cstdarg>
+#include <cstdio>
+
+namespace bgb {
+static thread_local char g_msg[512] = "";
+
+int set_error(int status, const char* fmt, ...)
+{
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_msg, sizeof g_msg, fmt, ap);
+  va_end(ap);
+  return status;
+}
+int check_cuda(cudaError_t e, const char* what)
+{
+  if (e == cudaSuccess) return BGB_OK;
+  snprintf(g_msg, sizeof g_msg, "CUDA error in %s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+  return e == cudaErrorMemoryAllocation ? BGB_OUT_OF_MEMORY : BGB_CUDA_ERROR;
+}
+const char* last_error() { return g_msg; }
+}  // namespace bgb
+
+extern "C" const char* bgb_last_error(void) { return bgb::last_error(); }
+extern "C" int bgb_version(void) { return BGB_VERSION; }

@@ -1,0 +1,309 @@
+// C ABI: bgb_groupby_build / _emit / _result_info / _destroy.  See include/bgb.h for the contract.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "errors.h"
+#include "fastpaths.h"
+#include "plan.h"
+
+using namespace bgb;
+
+struct bgb_groupby {
+  Plan plan;
+  bgb_allocator alloc{};
+  bool has_alloc = false;
+  cudaStream_t stream = nullptr;
+  struct Block { void* p; size_t bytes; };
+  std::vector<Block> blocks;
+  // device state
+  TableDesc table{};
+  uint32_t* group_slots = nullptr;
+  int32_t num_groups = 0;
+  std::string path = "empty";
+
+  void* dalloc(size_t bytes)
+  {
+    if (bytes == 0) bytes = 16;
+    void* p = nullptr;
+    if (has_alloc) p = alloc.allocate(bytes, (void*)stream, alloc.ctx);
+    else if (cudaMallocAsync(&p, bytes, stream) != cudaSuccess) { cudaGetLastError(); p = nullptr; }
+    if (p) blocks.push_back({p, bytes});
+    return p;
+  }
+  void dfree(void* p)
+  {
+    for (size_t i = 0; i < blocks.size(); ++i)
+      if (blocks[i].p == p) {
+        if (has_alloc) alloc.deallocate(p, blocks[i].bytes, (void*)stream, alloc.ctx);
+        else cudaFreeAsync(p, stream);
+        blocks.erase(blocks.begin() + i);
+        return;
+      }
+  }
+  void free_all()
+  {
+    while (!blocks.empty()) dfree(blocks.back().p);
+  }
+};
+
+namespace {
+
+uint64_t next_pow2(uint64_t x) { uint64_t p = 1; while (p < x) p <<= 1; return p; }
+
+void fill_agg_params(const bgb_groupby& h, AggParams& p, size_t acc_begin, size_t acc_end)
+{
+  const Plan& pl = h.plan;
+  memset(&p, 0, sizeof p);
+  p.num_rows       = pl.num_rows;
+  p.num_key_cols   = (int)pl.keys.size();
+  p.skip_null_keys = pl.skip_null_keys;
+  for (size_t c = 0; c < pl.keys.size(); ++c) {
+    const KeyPlan& k = pl.keys[c];
+    p.kc[c] = KeyColDesc{(const uint8_t*)k.v.data, k.v.null_mask, k.v.offset, k.width, k.fclass, k.shift, k.null_bit};
+  }
+  p.num_accs = (int)(acc_end - acc_begin);
+  for (size_t a = acc_begin; a < acc_end; ++a) {
+    const AccPlan& ap = pl.accs[a];
+    AccDesc& d        = p.acc[a - acc_begin];
+    if (ap.value_col >= 0) {
+      const ValuePlan& v = pl.values[ap.value_col];
+      d.data = (const uint8_t*)v.v.data; d.mask = v.v.null_mask; d.offset = v.v.offset; d.src = v.src;
+    } else { d.data = nullptr; d.mask = nullptr; d.offset = 0; d.src = S_I32; }
+    d.op    = ap.op;
+    d.cells = ap.cells;
+  }
+  p.table = h.table;
+}
+
+// solve d = G (1 - exp(-m/G)) for G: expected distinct values among m uniform draws from G groups
+double solve_cardinality(double d, double m)
+{
+  if (d >= m) return 1e18;
+  double lo = d, hi = 1e15;
+  for (int it = 0; it < 200; ++it) {
+    double mid = std::sqrt(lo * hi);
+    double e   = mid * (1.0 - std::exp(-m / mid));
+    if (e < d) lo = mid; else hi = mid;
+    if (hi / lo < 1.0001) break;
+  }
+  return hi;
+}
+
+}  // namespace
+
+extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
+                                 const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
+                                 const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups)
+{
+  if (!out_handle || !num_groups) return set_error(BGB_INVALID_ARGUMENT, "null output pointer");
+  *out_handle = nullptr;
+  *num_groups = 0;
+  bgb_groupby* h = new bgb_groupby();
+  int rc = make_plan(keys, num_keys, include_null_keys, requests, num_requests, h->plan);
+  if (rc != BGB_OK) { delete h; return rc; }
+  h->stream = (cudaStream_t)stream;
+  if (alloc && alloc->allocate && alloc->deallocate) { h->alloc = *alloc; h->has_alloc = true; }
+  bgb_options opt{};
+  if (options) opt = *options;
+  Plan& pl = h->plan;
+  const int64_t N = pl.num_rows;
+  if (N == 0) { *out_handle = h; return BGB_OK; }  // groupby.cu:233: empty input -> empty outputs
+  cudaStream_t s = h->stream;
+
+#define FAIL_RC(expr)            \
+  do {                           \
+    int rc_ = (expr);            \
+    if (rc_ != BGB_OK) { h->free_all(); delete h; return rc_; } \
+  } while (0)
+
+  uint32_t* status = (uint32_t*)h->dalloc(8 * sizeof(uint32_t));
+  if (!status) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "status alloc"));
+  h->table.status    = status;
+  h->table.key_words = pl.key_words;
+
+  // ---- capacity: explicit, or from the sampled cardinality estimate (one small kernel + one read-back)
+  const uint64_t cap_max = next_pow2((uint64_t)(2 * N < 1024 ? 1024 : 2 * N));
+  uint64_t capacity      = 0;
+  double g_est           = (double)N;
+  if (opt.capacity_log2 > 0) capacity = 1ull << opt.capacity_log2;
+  else if (N <= 4096) capacity = next_pow2(2 * (uint64_t)N < 1024 ? 1024 : 2 * (uint64_t)N);
+  else {
+    const int64_t sample  = opt.sample_rows > 0 ? opt.sample_rows : 65536;
+    const uint64_t setcap = next_pow2((uint64_t)sample * 4);
+    uint64_t* set   = (uint64_t*)h->dalloc(setcap * sizeof(uint64_t));
+    if (!set) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "estimator scratch"));
+    AggParams ep;
+    fill_agg_params(*h, ep, 0, 0);
+    FAIL_RC(check_cuda(launch_estimate_cardinality(ep, sample, set, setcap, status + 4, s), "estimate"));
+    uint32_t est[2] = {0, 0};
+    FAIL_RC(check_cuda(cudaMemcpyAsync(est, status + 4, sizeof est, cudaMemcpyDeviceToHost, s), "estimate copy"));
+    FAIL_RC(check_cuda(cudaStreamSynchronize(s), "estimate sync"));
+    h->dfree(set);
+    const double d = est[0], m = est[1];
+    if (m == 0) g_est = 1;
+    else if (d > 0.9 * m) g_est = (double)N;  // nearly all sampled keys distinct: cardinality unknown, assume the worst
+    else g_est = std::min((double)N, 1.5 * solve_cardinality(d, m));
+    capacity = next_pow2((uint64_t)std::max(1024.0, 2.0 * g_est));
+    if (capacity > cap_max) capacity = cap_max;
+  }
+
+  for (int attempt = 0;; ++attempt) {
+    h->table.capacity = capacity;
+    const uint64_t slots = capacity + 1;
+    h->table.keys = (uint64_t*)h->dalloc(slots * 8 * pl.key_words);
+    if (!h->table.keys) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "group table keys (%llu slots)", (unsigned long long)slots));
+    for (AccPlan& a : pl.accs) {
+      a.cells = h->dalloc(slots * acc_cell_bytes(a.op));
+      if (!a.cells) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "group table accumulators"));
+    }
+    // init + aggregate, kMaxAccs accumulators per launch (the first launch also initialises the keys)
+    std::string path;
+    bool done = false;
+    FAIL_RC(try_fast_paths(pl, h->table, opt, g_est, s, done, path));
+    if (!done) {
+      size_t na = pl.accs.size();
+      for (size_t b = 0; b == 0 || b < na; b += kMaxAccs) {
+        AggParams p;
+        fill_agg_params(*h, p, b, std::min(na, b + kMaxAccs));
+        p.init_keys = (b == 0);  // later chunks only initialise their own cells
+        FAIL_RC(check_cuda(launch_init_table(p, s), "init_table"));
+      }
+      for (size_t b = 0; b == 0 || b < na; b += kMaxAccs) {
+        AggParams p;
+        fill_agg_params(*h, p, b, std::min(na, b + kMaxAccs));
+        FAIL_RC(check_cuda(launch_aggregate_global(p, s), "aggregate_global"));
+      }
+      path = "global";
+    }
+    h->path = path;
+    // compaction: occupied slots -> dense group list (+ group count)
+    const uint64_t max_groups = std::min<uint64_t>(slots, (uint64_t)N);
+    h->group_slots            = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
+    uint32_t* scan_state      = (uint32_t*)h->dalloc(compact_scan_state_bytes(capacity));
+    if (!h->group_slots || !scan_state) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "compaction scratch"));
+    FAIL_RC(check_cuda(launch_compact(h->table, h->group_slots, scan_state, s), "compact"));
+    uint32_t st[4] = {0, 0, 0, 0};
+    FAIL_RC(check_cuda(cudaMemcpyAsync(st, status, sizeof st, cudaMemcpyDeviceToHost, s), "status copy"));
+    FAIL_RC(check_cuda(cudaStreamSynchronize(s), "build sync"));
+    h->dfree(scan_state);
+    if (st[0] == 0) { h->num_groups = (int32_t)st[1]; break; }
+    // table overloaded: free it and retry at the size that fits every row as its own group
+    if (capacity >= cap_max || attempt >= 2) FAIL_RC(set_error(BGB_CUDA_ERROR, "group table overflow at maximum capacity"));
+    h->dfree(h->group_slots); h->group_slots = nullptr;
+    h->dfree(h->table.keys); h->table.keys = nullptr;
+    for (AccPlan& a : pl.accs) { h->dfree(a.cells); a.cells = nullptr; }
+    capacity = cap_max;
+    g_est    = (double)N;
+  }
+#undef FAIL_RC
+  *num_groups = h->num_groups;
+  *out_handle = h;
+  return BGB_OK;
+}
+
+extern "C" int bgb_groupby_result_info(const bgb_groupby* h, int32_t request, int32_t aggregation, int32_t* type_id,
+                                       int32_t* scale, int32_t* nullable)
+{
+  if (!h) return set_error(BGB_INVALID_ARGUMENT, "null handle");
+  const Plan& pl = h->plan;
+  if (request < 0 || request >= (int)pl.request_first_out.size() || aggregation < 0 || aggregation >= pl.request_num_aggs[request])
+    return set_error(BGB_INVALID_ARGUMENT, "no result (%d,%d)", request, aggregation);
+  const OutPlan& o = pl.outs[pl.request_first_out[request] + aggregation];
+  if (type_id) *type_id = o.type_id;
+  if (scale) *scale = o.scale;
+  if (nullable) *nullable = o.nullable;
+  return BGB_OK;
+}
+
+extern "C" int bgb_groupby_key_info(const bgb_groupby* h, int32_t key, int32_t* type_id, int32_t* scale, int32_t* nullable)
+{
+  if (!h || key < 0 || key >= (int)h->plan.keys.size()) return set_error(BGB_INVALID_ARGUMENT, "no key column %d", key);
+  const KeyPlan& k = h->plan.keys[key];
+  if (type_id) *type_id = k.v.type_id;
+  if (scale) *scale = k.v.scale;
+  if (nullable) *nullable = k.nullable_out;
+  return BGB_OK;
+}
+
+extern "C" const char* bgb_groupby_path(const bgb_groupby* h) { return h ? h->path.c_str() : ""; }
+
+extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bgb_mutable_column* out_results, void* stream)
+{
+  if (!h) return set_error(BGB_INVALID_ARGUMENT, "null handle");
+  const Plan& pl = h->plan;
+  const int nk = (int)pl.keys.size(), nr = (int)pl.outs.size();
+  if ((nk > 0 && !out_keys) || (nr > 0 && !out_results)) return set_error(BGB_INVALID_ARGUMENT, "null output arrays");
+  for (int i = 0; i < nk; ++i) out_keys[i].null_count = 0;
+  for (int i = 0; i < nr; ++i) out_results[i].null_count = 0;
+  const int32_t G = h->num_groups;
+  if (G == 0) return BGB_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  h->stream      = s;
+
+  // validate caller buffers
+  for (int i = 0; i < nk; ++i) {
+    if (out_keys[i].size < G || !out_keys[i].data) return set_error(BGB_INVALID_ARGUMENT, "out_keys[%d] too small", i);
+    if (pl.keys[i].nullable_out && !out_keys[i].null_mask) return set_error(BGB_INVALID_ARGUMENT, "out_keys[%d] needs a null mask", i);
+  }
+  for (int i = 0; i < nr; ++i) {
+    if (out_results[i].size < G || !out_results[i].data) return set_error(BGB_INVALID_ARGUMENT, "out_results[%d] too small", i);
+    if (pl.outs[i].nullable && !out_results[i].null_mask) return set_error(BGB_INVALID_ARGUMENT, "out_results[%d] needs a null mask", i);
+  }
+  const int total = nk + nr;
+  int32_t* d_nulls = (int32_t*)h->dalloc(sizeof(int32_t) * total);
+  if (!d_nulls) return set_error(BGB_OUT_OF_MEMORY, "null counters");
+  int rc = check_cuda(cudaMemsetAsync(d_nulls, 0, sizeof(int32_t) * total, s), "memset");
+  if (rc) return rc;
+  bool any_nullable = false;
+
+  std::vector<OutDesc> descs;
+  for (int i = 0; i < nk; ++i) {
+    const KeyPlan& k = pl.keys[i];
+    OutDesc d{};
+    d.out = out_keys[i].data; d.out_mask = k.nullable_out ? out_keys[i].null_mask : nullptr; d.null_count = d_nulls + i;
+    d.op = OUT_KEY; d.src = type_src(k.v.type_id); d.out_width = k.width; d.shift = k.shift; d.null_bit = k.null_bit;
+    any_nullable |= k.nullable_out;
+    descs.push_back(d);
+  }
+  for (int i = 0; i < nr; ++i) {
+    const OutPlan& o = pl.outs[i];
+    OutDesc d{};
+    d.out = out_results[i].data; d.out_mask = o.nullable ? out_results[i].null_mask : nullptr; d.null_count = d_nulls + nk + i;
+    d.a   = o.acc_a >= 0 ? pl.accs[o.acc_a].cells : nullptr;
+    d.b   = o.acc_b >= 0 ? pl.accs[o.acc_b].cells : nullptr;
+    d.cnt = o.acc_cnt >= 0 ? (const int32_t*)pl.accs[o.acc_cnt].cells : nullptr;
+    d.ddof = o.ddof; d.op = o.op; d.src = o.src; d.out_width = o.out_width; d.acc_op = o.acc_op; d.null_bit = -1;
+    any_nullable |= o.nullable;
+    descs.push_back(d);
+  }
+  for (size_t b = 0; b < descs.size(); b += kMaxOuts) {
+    EmitParams ep;
+    memset(&ep, 0, sizeof ep);
+    ep.keys = h->table.keys; ep.group_slots = h->group_slots; ep.num_groups = G; ep.key_words = pl.key_words;
+    ep.num_outs = (int)std::min<size_t>(kMaxOuts, descs.size() - b);
+    for (int i = 0; i < ep.num_outs; ++i) ep.out[i] = descs[b + i];
+    rc = check_cuda(launch_emit(ep, s), "emit");
+    if (rc) return rc;
+  }
+  if (any_nullable) {
+    std::vector<int32_t> hn(total);
+    rc = check_cuda(cudaMemcpyAsync(hn.data(), d_nulls, sizeof(int32_t) * total, cudaMemcpyDeviceToHost, s), "null counts");
+    if (rc) return rc;
+    rc = check_cuda(cudaStreamSynchronize(s), "emit sync");
+    if (rc) return rc;
+    for (int i = 0; i < nk; ++i) out_keys[i].null_count = hn[i];
+    for (int i = 0; i < nr; ++i) out_results[i].null_count = hn[nk + i];
+  }
+  h->dfree(d_nulls);
+  return BGB_OK;
+}
+
+extern "C" void bgb_groupby_destroy(bgb_groupby* h)
+{
+  if (!h) return;
+  h->free_all();
+  delete h;
+}

@@ -1,0 +1,166 @@
+// Generic (descriptor-driven) kernels: table init, fused hash+probe+aggregate into the HBM group table,
+// cardinality estimator. They serve every supported type/aggregation combination; the specialised
+// shared-memory and partitioned kernels (kernels_smem.cu, kernels_partition.cu) are fast paths in front of them.
+//
+// Replaces, as ONE pass over the rows with no N-sized temporaries:
+//   cuco::static_set insert_and_find + compute_aggs_* (/root/reference/cpp/src/groupby/hash/compute_global_memory_aggs.cuh:41-157,
+//   /root/reference/cpp/src/groupby/hash/single_pass_functors.cuh:86-157) and initialize_with_identity
+//   (/root/reference/cpp/src/aggregation/aggregation.cu:39-97).
+#include "device_utils.cuh"
+
+namespace bgb {
+
+// ------------------------------------------------------------------ identities
+__device__ __forceinline__ uint64_t acc_identity64(uint8_t op)
+{
+  switch (op) {
+    case ACC_PROD_I64: return 1ull;
+    case ACC_PROD_F64: return 0x3ff0000000000000ull;  // 1.0
+    case ACC_MIN: case ACC_ARGMIN: return ~0ull;
+    default: return 0ull;  // sums, MAX (smallest ordered image), ARGMAX
+  }
+}
+__device__ __forceinline__ uint32_t acc_identity32(uint8_t op) { return op == ACC_PROD_F32 ? 0x3f800000u : 0u; }
+
+__global__ void __launch_bounds__(256) init_table_kernel(const __grid_constant__ AggParams p)
+{
+  const uint64_t n      = p.table.capacity + 1;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    if (p.init_keys) {
+      if (p.table.key_words == 1) p.table.keys[i] = kEmpty;
+      else { reinterpret_cast<ulonglong2*>(p.table.keys)[i] = make_ulonglong2(kEmpty, kEmpty); }
+    }
+    for (int a = 0; a < p.num_accs; ++a) {
+      const uint8_t op = p.acc[a].op;
+      if (acc_cell_bytes(op) == 8) reinterpret_cast<uint64_t*>(p.acc[a].cells)[i] = acc_identity64(op);
+      else reinterpret_cast<uint32_t*>(p.acc[a].cells)[i] = acc_identity32(op);
+    }
+  }
+  if (p.init_keys && blockIdx.x == 0 && threadIdx.x < 4) p.table.status[threadIdx.x] = 0;
+}
+
+cudaError_t launch_init_table(const AggParams& p, cudaStream_t s)
+{
+  uint64_t n = p.table.capacity + 1;
+  int blocks = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
+  init_table_kernel<<<blocks, 256, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ one row into one accumulator
+__device__ __forceinline__ void atomic_mul_i64(unsigned long long* addr, int64_t v)
+{
+  unsigned long long old = *addr, assumed;
+  do { assumed = old; old = atomicCAS(addr, assumed, (unsigned long long)((int64_t)assumed * v)); } while (old != assumed);
+}
+__device__ __forceinline__ void atomic_mul_f64(unsigned long long* addr, double v)
+{
+  unsigned long long old = *addr, assumed;
+  do {
+    assumed = old;
+    old     = atomicCAS(addr, assumed, (unsigned long long)__double_as_longlong(__longlong_as_double((long long)assumed) * v));
+  } while (old != assumed);
+}
+__device__ __forceinline__ void atomic_mul_f32(unsigned int* addr, float v)
+{
+  unsigned int old = *addr, assumed;
+  do { assumed = old; old = atomicCAS(addr, assumed, __float_as_uint(__uint_as_float(assumed) * v)); } while (old != assumed);
+}
+
+__device__ __forceinline__ void apply_acc(const AccDesc& a, int64_t row, uint64_t slot)
+{
+  const int64_t idx = (int64_t)a.offset + row;
+  if (a.op == ACC_COUNT_ALL) { atomicAdd(reinterpret_cast<int*>(a.cells) + slot, 1); return; }
+  if (a.mask != nullptr && !bit_is_set(a.mask, idx)) return;  // null source skipped (device_aggregators.cuh:434-436)
+  if (a.op == ACC_COUNT_VALID) { atomicAdd(reinterpret_cast<int*>(a.cells) + slot, 1); return; }
+  const uint64_t raw = load_raw(a.data, src_width(a.src), idx);
+  unsigned long long* c64 = reinterpret_cast<unsigned long long*>(a.cells) + slot;
+  unsigned int* c32       = reinterpret_cast<unsigned int*>(a.cells) + slot;
+  switch (a.op) {
+    case ACC_SUM_I64: atomicAdd(c64, (unsigned long long)raw_to_i64(raw, a.src)); break;
+    case ACC_SUM_F64: atomicAdd(reinterpret_cast<double*>(c64), __longlong_as_double((long long)raw)); break;
+    case ACC_SUM_F32: atomicAdd(reinterpret_cast<float*>(c32), __uint_as_float((uint32_t)raw)); break;
+    case ACC_SUMSQ_I64: { uint64_t v = (uint64_t)raw_to_i64(raw, a.src); atomicAdd(c64, (unsigned long long)(v * v)); break; }
+    case ACC_SUMSQ_F64: { double v = __longlong_as_double((long long)raw); atomicAdd(reinterpret_cast<double*>(c64), v * v); break; }
+    case ACC_SUMSQ_F32: { float v = __uint_as_float((uint32_t)raw); atomicAdd(reinterpret_cast<float*>(c32), v * v); break; }
+    case ACC_PROD_I64: atomic_mul_i64(c64, raw_to_i64(raw, a.src)); break;
+    case ACC_PROD_F64: atomic_mul_f64(c64, __longlong_as_double((long long)raw)); break;
+    case ACC_PROD_F32: atomic_mul_f32(c32, __uint_as_float((uint32_t)raw)); break;
+    case ACC_MIN: { unsigned long long v = ordered_image(raw, a.src); if (v < *reinterpret_cast<volatile unsigned long long*>(c64)) atomicMin(c64, v); break; }
+    case ACC_MAX: { unsigned long long v = ordered_image(raw, a.src); if (v > *reinterpret_cast<volatile unsigned long long*>(c64)) atomicMax(c64, v); break; }
+    case ACC_ARGMIN: atomicMin(c64, (unsigned long long)((ordered_image(raw, a.src) << 32) | (uint32_t)row)); break;
+    case ACC_ARGMAX: atomicMax(c64, (unsigned long long)((ordered_image(raw, a.src) << 32) | (0xFFFFFFFFu - (uint32_t)row))); break;
+    default: break;
+  }
+}
+
+// ------------------------------------------------------------------ fused hash + probe + aggregate (HBM table)
+__global__ void __launch_bounds__(256) aggregate_global_kernel(const __grid_constant__ AggParams p)
+{
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < p.num_rows; row += stride) {
+    uint64_t k0, k1;
+    if (!pack_key(p, row, k0, k1)) continue;
+    const uint64_t slot = find_or_insert(p.table, k0, k1);
+    if (slot == kNoSlot) return;
+#pragma unroll 1
+    for (int a = 0; a < p.num_accs; ++a) apply_acc(p.acc[a], row, slot);
+  }
+}
+
+cudaError_t launch_aggregate_global(const AggParams& p, cudaStream_t s)
+{
+  if (p.num_rows == 0) return cudaSuccess;
+  int64_t want = (p.num_rows + 255) / 256;
+  int blocks   = (int)(want < 148 * 8 ? want : 148 * 8);
+  aggregate_global_kernel<<<blocks, 256, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ cardinality estimator
+// Inserts the packed keys of `sample_rows` evenly spaced rows into a scratch set; out[0] = distinct, out[1] = sampled
+// rows that were not skipped. Only a regime hint: correctness never depends on it (overflow -> host retries bigger).
+__global__ void __launch_bounds__(256) estimate_kernel(const __grid_constant__ AggParams p, int64_t sample_rows, int64_t step,
+                                                       uint64_t* set, uint64_t set_capacity, uint32_t* out)
+{
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= sample_rows) return;
+  int64_t row = t * step;
+  if (row >= p.num_rows) return;
+  uint64_t k0, k1;
+  if (!pack_key(p, row, k0, k1)) return;
+  atomicAdd(out + 1, 1u);
+  uint64_t f = hash_key(k0, k1, p.table.key_words);
+  if (f == kEmpty) f = 0;
+  uint64_t slot = mix64(f) & (set_capacity - 1);
+  unsigned long long* s = reinterpret_cast<unsigned long long*>(set);
+  for (uint64_t probes = 0; probes < set_capacity; ++probes) {
+    unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(s + slot);
+    if (cur == f) return;
+    if (cur == kEmpty) {
+      unsigned long long old = atomicCAS(s + slot, (unsigned long long)kEmpty, (unsigned long long)f);
+      if (old == kEmpty) { atomicAdd(out, 1u); return; }
+      if (old == f) return;
+    }
+    slot = (slot + 1) & (set_capacity - 1);
+  }
+}
+
+cudaError_t launch_estimate_cardinality(const AggParams& p, int64_t sample_rows, uint64_t* scratch_set, uint64_t set_capacity,
+                                        uint32_t* out_distinct, cudaStream_t s)
+{
+  cudaError_t e = cudaMemsetAsync(scratch_set, 0xff, set_capacity * sizeof(uint64_t), s);
+  if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(out_distinct, 0, 2 * sizeof(uint32_t), s);
+  if (e != cudaSuccess) return e;
+  if (sample_rows > p.num_rows) sample_rows = p.num_rows;
+  if (sample_rows <= 0) return cudaSuccess;
+  int64_t step = p.num_rows / sample_rows;
+  if (step < 1) step = 1;
+  int blocks = (int)((sample_rows + 255) / 256);
+  estimate_kernel<<<blocks, 256, 0, s>>>(p, sample_rows, step, scratch_set, set_capacity, out_distinct);
+  return cudaGetLastError();
+}
+
+}  // namespace bgb

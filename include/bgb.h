@@ -1,0 +1,207 @@
+/*
+ * bgb.h -- C ABI of the B200-native hash groupby-aggregate ("bgb" = B200 group-by).
+ *
+ * This is the drop-in boundary for libcudf's hash groupby path. The reference has no C ABI on this path
+ * (pylibcudf binds the C++ class directly); these entry points are what a cgo / JNI / ctypes / Cython
+ * binding would call in place of
+ *     cudf::groupby::detail::hash::groupby(keys, requests, null_policy, stream, mr)
+ *                                              /root/reference/cpp/src/groupby/hash/groupby.cu:134-147
+ *     cudf::groupby::detail::hash::can_use_hash_groupby(requests)
+ *                                              /root/reference/cpp/src/groupby/hash/groupby.cu:115-131
+ * declared in /root/reference/cpp/include/cudf/detail/groupby.hpp:18-37 and reached from
+ * cudf::groupby::groupby::aggregate (/root/reference/cpp/src/groupby/groupby.cu:219-236).
+ * The C++ class with the reference's exact signatures sits on top of this ABI in include/cudf/groupby.hpp.
+ *
+ * Rules of the boundary
+ *  - plain pointers and sizes only; every pointer in a bgb_column_view / bgb_mutable_column is DEVICE memory
+ *    (except where a function name says _host);
+ *  - stream-ordered on the caller's CUDA stream (passed as void* = cudaStream_t); never touches the default stream
+ *    unless the caller passes it; the only host waits are on that stream (group count read-back);
+ *  - output memory is allocated by the CALLER (two-phase build -> emit), scratch comes from the caller's
+ *    bgb_allocator (or cudaMallocAsync on the stream when NULL); the library never frees caller memory;
+ *  - no exception crosses the boundary: status codes + bgb_last_error() (thread-local message);
+ *  - re-entrant: no global mutable state besides an immutable device-property cache.
+ */
+#ifndef BGB_H
+#define BGB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BGB_VERSION 100
+
+typedef enum bgb_status {
+  BGB_OK = 0,
+  BGB_INVALID_ARGUMENT = 1, /* what the reference reports as cudf::logic_error (groupby.cu:186-229) */
+  BGB_UNSUPPORTED = 2,      /* can_use_hash_groupby() == false: caller takes its sort fallback */
+  BGB_CUDA_ERROR = 3,       /* cudf::cuda_error */
+  BGB_NCCL_ERROR = 4,
+  BGB_OUT_OF_MEMORY = 5
+} bgb_status;
+
+/* cudf::type_id, same numeric values (/root/reference/cpp/include/cudf/types.hpp:185-217) */
+typedef enum bgb_type_id {
+  BGB_EMPTY = 0, BGB_INT8 = 1, BGB_INT16 = 2, BGB_INT32 = 3, BGB_INT64 = 4, BGB_UINT8 = 5, BGB_UINT16 = 6,
+  BGB_UINT32 = 7, BGB_UINT64 = 8, BGB_FLOAT32 = 9, BGB_FLOAT64 = 10, BGB_BOOL8 = 11, BGB_TIMESTAMP_DAYS = 12,
+  BGB_TIMESTAMP_SECONDS = 13, BGB_TIMESTAMP_MILLISECONDS = 14, BGB_TIMESTAMP_MICROSECONDS = 15,
+  BGB_TIMESTAMP_NANOSECONDS = 16, BGB_DURATION_DAYS = 17, BGB_DURATION_SECONDS = 18, BGB_DURATION_MILLISECONDS = 19,
+  BGB_DURATION_MICROSECONDS = 20, BGB_DURATION_NANOSECONDS = 21, BGB_DICTIONARY32 = 22, BGB_STRING = 23, BGB_LIST = 24,
+  BGB_DECIMAL32 = 25, BGB_DECIMAL64 = 26, BGB_DECIMAL128 = 27, BGB_STRUCT = 28
+} bgb_type_id;
+
+/* cudf::aggregation::Kind, same numeric values (/root/reference/cpp/include/cudf/aggregation.hpp:78-121) */
+typedef enum bgb_agg_kind {
+  BGB_SUM = 0, BGB_SUM_OVERFLOW = 1, BGB_PRODUCT = 2, BGB_MIN = 3, BGB_MAX = 4, BGB_COUNT_VALID = 5, BGB_COUNT_ALL = 6,
+  BGB_ANY = 7, BGB_ALL = 8, BGB_SUM_OF_SQUARES = 9, BGB_MEAN = 10, BGB_M2 = 11, BGB_VARIANCE = 12, BGB_STD = 13,
+  BGB_MEDIAN = 14, BGB_QUANTILE = 15, BGB_ARGMAX = 16, BGB_ARGMIN = 17, BGB_NUNIQUE = 18, BGB_NTH_ELEMENT = 19
+} bgb_agg_kind;
+
+/* POD mirror of cudf::column_view's fields (/root/reference/cpp/include/cudf/column/column_view.hpp:236-243):
+ * element i lives at data + (offset + i) * sizeof(T); validity bit (offset + i) of the 32-bit mask words, 1 = valid
+ * (/root/reference/cpp/include/cudf/utilities/bit.hpp:47-60). null_mask == NULL means "no nulls". */
+typedef struct bgb_column_view {
+  int32_t type_id;    /* bgb_type_id */
+  int32_t scale;      /* fixed_point scale, carried through untouched */
+  int32_t size;       /* rows (cudf::size_type = int32) */
+  int32_t null_count; /* as column_view::null_count(); has_nulls() == null_count > 0 */
+  int32_t offset;
+  int32_t reserved;
+  const void* data;
+  const uint32_t* null_mask;
+} bgb_column_view;
+
+/* one cudf::groupby_aggregation (kind + the ddof of VARIANCE/STD, cudf/aggregation.hpp:293,305) */
+typedef struct bgb_aggregation {
+  int32_t kind; /* bgb_agg_kind */
+  int32_t ddof;
+} bgb_aggregation;
+
+/* cudf::groupby::aggregation_request (/root/reference/cpp/include/cudf/groupby.hpp:54-57) */
+typedef struct bgb_request {
+  bgb_column_view values;
+  const bgb_aggregation* aggregations;
+  int32_t num_aggregations;
+  int32_t reserved;
+} bgb_request;
+
+/* caller-owned output column: data/null_mask sized for `size` rows (mask words = (size+31)/32, zero-filled not required).
+ * null_mask may be NULL when bgb_groupby_result_info said nullable == 0. null_count is written by emit. */
+typedef struct bgb_mutable_column {
+  int32_t type_id;
+  int32_t size;
+  void* data;
+  uint32_t* null_mask;
+  int32_t null_count; /* out */
+  int32_t reserved;
+} bgb_mutable_column;
+
+/* stream-ordered scratch allocator = the role of rmm::device_async_resource_ref on the reference path.
+ * NULL allocator => cudaMallocAsync / cudaFreeAsync on the call's stream. */
+typedef struct bgb_allocator {
+  void* (*allocate)(size_t bytes, void* stream, void* ctx);
+  void (*deallocate)(void* ptr, size_t bytes, void* stream, void* ctx);
+  void* ctx;
+} bgb_allocator;
+
+/* tunables; zero-initialise for defaults. Mirrors the reference's compile-time constants
+ * (/root/reference/cpp/src/groupby/hash/helpers.cuh:19-40) but selectable for tests. */
+typedef struct bgb_options {
+  int32_t force_path;        /* 0 auto, 1 global-table kernel only, 2 shared-memory pre-aggregation, 3 partitioned */
+  int32_t capacity_log2;     /* 0 auto; else global table has 2^capacity_log2 slots */
+  int32_t sample_rows;       /* 0 auto (65536) rows sampled by the cardinality estimator */
+  int32_t reserved[5];
+} bgb_options;
+
+typedef struct bgb_groupby bgb_groupby; /* opaque handle between build and emit */
+
+/* ---- capability + type rules ---------------------------------------------------------------------------- */
+
+/* mirrors can_use_hash_groupby (hash/groupby.cu:115-131) restricted to what this library implements:
+ * *out = 1 when every (value type, aggregation) pair is served by the hash path, else 0 (caller uses sort path). */
+int bgb_can_use_hash_groupby(const bgb_column_view* keys, int32_t num_keys, const bgb_request* requests,
+                             int32_t num_requests, int32_t* out);
+
+/* cudf::detail::target_type(values_type, kind) (detail/aggregation/aggregation.hpp:878-1012); -1 when invalid */
+int32_t bgb_target_type(int32_t values_type_id, int32_t kind);
+
+/* ---- the groupby call, two-phase --------------------------------------------------------------------------- */
+
+/* Phase 1: hash rows, aggregate into the group table, compact, count groups.
+ * Waits on `stream` once to read *num_groups back (the reference also learns the group count on the host,
+ * hash/output_utils.cu:145-147). keys/requests must stay alive until emit. */
+int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
+                      const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
+                      const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups);
+
+/* result column (request r, aggregation a): type, scale and whether a null mask must be supplied */
+int bgb_groupby_result_info(const bgb_groupby* handle, int32_t request, int32_t aggregation, int32_t* type_id,
+                            int32_t* scale, int32_t* nullable);
+/* key column k of the unique-keys table: nullable iff include_null_keys and the input key column has a mask */
+int bgb_groupby_key_info(const bgb_groupby* handle, int32_t key, int32_t* type_id, int32_t* scale, int32_t* nullable);
+
+/* Phase 2: gather unique keys and finalise every requested aggregation into caller-allocated columns.
+ * out_keys[num_keys]; out_results flattened request-major (all aggregations of request 0, then request 1, ...).
+ * Asynchronous on `stream` except that null_count fields are valid only after the stream is synchronised
+ * by this call (it synchronises when any output is nullable). */
+int bgb_groupby_emit(bgb_groupby* handle, bgb_mutable_column* out_keys, bgb_mutable_column* out_results, void* stream);
+
+/* which kernels the last build used: "global", "smem", "partitioned", ... (diagnostics, tests) */
+const char* bgb_groupby_path(const bgb_groupby* handle);
+
+void bgb_groupby_destroy(bgb_groupby* handle);
+
+/* ---- host-buffer convenience (end-to-end measurement and simple callers) ------------------------------------- */
+
+/* Same call with HOST columns (pinned or pageable): copies inputs H2D in chunks overlapped with aggregation,
+ * runs build+emit, copies the results D2H into host buffers the library allocates with malloc
+ * (*out_keys / *out_results, release with bgb_free_host_result). */
+typedef struct bgb_host_column {
+  int32_t type_id;
+  int32_t size;
+  void* data;          /* malloc'ed, size elements */
+  uint32_t* null_mask; /* malloc'ed or NULL */
+  int32_t null_count;
+  int32_t reserved;
+} bgb_host_column;
+int bgb_groupby_host(const bgb_column_view* host_keys, int32_t num_keys, int32_t include_null_keys,
+                     const bgb_request* host_requests, int32_t num_requests, const bgb_options* options,
+                     int32_t* num_groups, bgb_host_column** out_keys, bgb_host_column** out_results,
+                     int32_t* num_results);
+void bgb_free_host_result(bgb_host_column* cols, int32_t n);
+
+/* ---- multi-GPU building blocks (one process per GPU; the exchange itself is an NCCL all-to-all run by the host
+ *      layer, see cudf_b200/distributed.py and SURVEY.md 8e) ------------------------------------------------------ */
+
+/* Partition the rows of (keys, partial columns) by hash2(key) % num_parts into contiguous per-destination runs.
+ * All columns are permuted identically; part_offsets[num_parts+1] (device) receives the run boundaries. */
+int bgb_partition_by_key_hash(const bgb_column_view* keys, int32_t num_keys, const bgb_column_view* cols,
+                              int32_t num_cols, int32_t num_parts, bgb_mutable_column* out_keys,
+                              bgb_mutable_column* out_cols, int32_t* part_offsets_device, void* stream,
+                              const bgb_allocator* alloc);
+
+/* ---- synthetic inputs (SURVEY.md 8d generators; bench + tests only) --------------------------------------------- */
+
+/* out[i] = splitmix64(seed, first_row + i) % modulus (modulus 0: raw 64 bits), cast to type_id (ints) */
+int bgb_gen_uniform_int(void* out, int32_t type_id, int64_t n, uint64_t seed, uint64_t first_row, uint64_t modulus,
+                        int64_t add, void* stream);
+/* out[i] = (double|float)(splitmix64 % modulus) + add */
+int bgb_gen_uniform_real(void* out, int32_t type_id, int64_t n, uint64_t seed, uint64_t first_row, uint64_t modulus,
+                         double add, void* stream);
+/* validity bit i cleared when splitmix64(seed, first_row+i) % null_every == 0; returns null count in *null_count (host) */
+int bgb_gen_null_mask(uint32_t* mask_words, int64_t n, uint64_t seed, uint64_t first_row, uint32_t null_every,
+                      int32_t* null_count, void* stream);
+/* categorical by cumulative thresholds out of 65536: out[i] = values[first j with (x & 0xFFFF) < cum[j]] (int8) */
+int bgb_gen_categorical_i8(int8_t* out, int64_t n, uint64_t seed, uint64_t first_row, const int32_t* cum_host,
+                           const int8_t* values_host, int32_t num_categories, void* stream);
+
+const char* bgb_last_error(void);
+int bgb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BGB_H */
