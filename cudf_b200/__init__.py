@@ -7,4 +7,4 @@ from . import aggregation  # noqa: F401
 from ._lib import BgbError, CudaError, LogicError, UnsupportedError  # noqa: F401
 from .aggregation import NullPolicy  # noqa: F401
 from .column import Column, Table, TypeId  # noqa: F401
-from .groupby import GroupBy, GroupByRequest, can_use_hash_groupby  # noqa: F401
+from .groupby import GroupBy, GroupByRequest, HostColumnView, can_use_hash_groupby, groupby_host  # noqa: F401

@@ -51,8 +51,8 @@ class MutableColumn(C.Structure):
 
 
 class Options(C.Structure):
-    _fields_ = [("force_path", C.c_int32), ("capacity_log2", C.c_int32), ("sample_rows", C.c_int32),
-                ("reserved", C.c_int32 * 5)]
+    _fields_ = [("force_path", C.c_int32), ("capacity_log2", C.c_int32), ("sample_rows", C.c_int32), ("profile", C.c_int32),
+                ("reserved", C.c_int32 * 4)]
 
 
 class HostColumn(C.Structure):
@@ -90,12 +90,13 @@ def lib():
     L.bgb_gen_null_mask.argtypes = [C.c_void_p, C.c_int64, C.c_uint64, C.c_uint64, C.c_uint32, C.POINTER(C.c_int32), C.c_void_p]
     L.bgb_gen_categorical_i8.argtypes = [C.c_void_p, C.c_int64, C.c_uint64, C.c_uint64, C.POINTER(C.c_int32), C.c_char_p,
                                          C.c_int32, C.c_void_p]
-    if hasattr(L, "bgb_groupby_host"):
-        L.bgb_groupby_host.argtypes = [C.POINTER(ColumnView), C.c_int32, C.c_int32, C.POINTER(Request), C.c_int32,
-                                       C.POINTER(Options), C.POINTER(C.c_int32), C.POINTER(C.POINTER(HostColumn)),
-                                       C.POINTER(C.POINTER(HostColumn)), C.POINTER(C.c_int32)]
-        L.bgb_free_host_result.argtypes = [C.POINTER(HostColumn), C.c_int32]
-        L.bgb_free_host_result.restype = None
+    L.bgb_groupby_host.argtypes = [C.POINTER(ColumnView), C.c_int32, C.c_int32, C.POINTER(Request), C.c_int32,
+                                   C.POINTER(Options), C.POINTER(C.c_int32), C.POINTER(C.POINTER(HostColumn)),
+                                   C.POINTER(C.POINTER(HostColumn)), C.POINTER(C.c_int32)]
+    L.bgb_free_host_result.argtypes = [C.POINTER(HostColumn), C.c_int32]
+    L.bgb_free_host_result.restype = None
+    L.bgb_groupby_profile.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_float)]
+    L.bgb_kernel_launches.restype = C.c_int64
     _lib = L
     return L
 

@@ -1,6 +1,7 @@
 // Device helpers: element loads, key packing, ordered images, open-addressing probe.
 #pragma once
 #include "bgb_internal.cuh"
+#include "errors.h"
 
 namespace bgb {
 

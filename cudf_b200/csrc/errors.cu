@@ -1,6 +1,7 @@
 #include "errors.h"
 
 #include <cstdarg>
+#include <atomic>
 #include <cstdio>
 
 namespace bgb {
@@ -21,7 +22,12 @@ int check_cuda(cudaError_t e, const char* what)
   return e == cudaErrorMemoryAllocation ? BGB_OUT_OF_MEMORY : BGB_CUDA_ERROR;
 }
 const char* last_error() { return g_msg; }
+static std::atomic<long long> g_launches{0};
+cudaError_t note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); return cudaGetLastError(); }
+long long launches() { return g_launches.load(); }
 }  // namespace bgb
 
 extern "C" const char* bgb_last_error(void) { return bgb::last_error(); }
+namespace bgb { long long launches(); }
+extern "C" int64_t bgb_kernel_launches(void) { return bgb::launches(); }
 extern "C" int bgb_version(void) { return BGB_VERSION; }

@@ -5,5 +5,6 @@
 
 namespace bgb {
 int set_error(int status, const char* fmt, ...);          // stores the message, returns status
-int check_cuda(cudaError_t e, const char* what);          // BGB_OK or BGB_CUDA_ERROR / BGB_OUT_OF_MEMORY with message
+int check_cuda(cudaError_t e, const char* what);
+cudaError_t note_launch();                                // counts one kernel launch, returns cudaGetLastError()          // BGB_OK or BGB_CUDA_ERROR / BGB_OUT_OF_MEMORY with message
 }  // namespace bgb

@@ -23,6 +23,27 @@ struct bgb_groupby {
   uint32_t* group_slots = nullptr;
   int32_t num_groups = 0;
   std::string path = "empty";
+  // optional per-kernel CUDA-event timing (bgb_options.profile)
+  struct Prof { const char* name; cudaEvent_t e0, e1; float ms; };
+  std::vector<Prof> prof;
+  bool profile = false;
+  void prof_begin(const char* name)
+  {
+    if (!profile) return;
+    Prof p{name, nullptr, nullptr, -1.f};
+    cudaEventCreate(&p.e0); cudaEventCreate(&p.e1);
+    cudaEventRecord(p.e0, stream);
+    prof.push_back(p);
+  }
+  void prof_end() { if (profile && !prof.empty()) cudaEventRecord(prof.back().e1, stream); }
+  void prof_resolve()  // after a stream synchronise
+  {
+    for (Prof& p : prof)
+      if (p.ms < 0 && p.e0) {
+        if (cudaEventElapsedTime(&p.ms, p.e0, p.e1) != cudaSuccess) { cudaGetLastError(); p.ms = 0; }
+        cudaEventDestroy(p.e0); cudaEventDestroy(p.e1); p.e0 = p.e1 = nullptr;
+      }
+  }
 
   void* dalloc(size_t bytes)
   {
@@ -108,6 +129,7 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
   if (alloc && alloc->allocate && alloc->deallocate) { h->alloc = *alloc; h->has_alloc = true; }
   bgb_options opt{};
   if (options) opt = *options;
+  h->profile = opt.profile != 0;
   Plan& pl = h->plan;
   const int64_t N = pl.num_rows;
   if (N == 0) { *out_handle = h; return BGB_OK; }  // groupby.cu:233: empty input -> empty outputs
@@ -137,10 +159,13 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     if (!set) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "estimator scratch"));
     AggParams ep;
     fill_agg_params(*h, ep, 0, 0);
+    h->prof_begin("estimate_cardinality");
     FAIL_RC(check_cuda(launch_estimate_cardinality(ep, sample, set, setcap, status + 4, s), "estimate"));
+    h->prof_end();
     uint32_t est[2] = {0, 0};
     FAIL_RC(check_cuda(cudaMemcpyAsync(est, status + 4, sizeof est, cudaMemcpyDeviceToHost, s), "estimate copy"));
     FAIL_RC(check_cuda(cudaStreamSynchronize(s), "estimate sync"));
+    h->prof_resolve();
     h->dfree(set);
     const double d = est[0], m = est[1];
     if (m == 0) g_est = 1;
@@ -165,17 +190,21 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     FAIL_RC(try_fast_paths(pl, h->table, opt, g_est, s, done, path));
     if (!done) {
       size_t na = pl.accs.size();
+      h->prof_begin("init_table");
       for (size_t b = 0; b == 0 || b < na; b += kMaxAccs) {
         AggParams p;
         fill_agg_params(*h, p, b, std::min(na, b + kMaxAccs));
         p.init_keys = (b == 0);  // later chunks only initialise their own cells
         FAIL_RC(check_cuda(launch_init_table(p, s), "init_table"));
       }
+      h->prof_end();
+      h->prof_begin("aggregate_global");
       for (size_t b = 0; b == 0 || b < na; b += kMaxAccs) {
         AggParams p;
         fill_agg_params(*h, p, b, std::min(na, b + kMaxAccs));
         FAIL_RC(check_cuda(launch_aggregate_global(p, s), "aggregate_global"));
       }
+      h->prof_end();
       path = "global";
     }
     h->path = path;
@@ -184,10 +213,13 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     h->group_slots            = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
     uint32_t* scan_state      = (uint32_t*)h->dalloc(compact_scan_state_bytes(capacity));
     if (!h->group_slots || !scan_state) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "compaction scratch"));
+    h->prof_begin("compact");
     FAIL_RC(check_cuda(launch_compact(h->table, h->group_slots, scan_state, s), "compact"));
+    h->prof_end();
     uint32_t st[4] = {0, 0, 0, 0};
     FAIL_RC(check_cuda(cudaMemcpyAsync(st, status, sizeof st, cudaMemcpyDeviceToHost, s), "status copy"));
     FAIL_RC(check_cuda(cudaStreamSynchronize(s), "build sync"));
+    h->prof_resolve();
     h->dfree(scan_state);
     if (st[0] == 0) { h->num_groups = (int32_t)st[1]; break; }
     // table overloaded: free it and retry at the size that fits every row as its own group
@@ -279,6 +311,7 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
     any_nullable |= o.nullable;
     descs.push_back(d);
   }
+  h->prof_begin("emit");
   for (size_t b = 0; b < descs.size(); b += kMaxOuts) {
     EmitParams ep;
     memset(&ep, 0, sizeof ep);
@@ -286,6 +319,11 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
     ep.num_outs = (int)std::min<size_t>(kMaxOuts, descs.size() - b);
     for (int i = 0; i < ep.num_outs; ++i) ep.out[i] = descs[b + i];
     rc = check_cuda(launch_emit(ep, s), "emit");
+    if (rc) return rc;
+  }
+  h->prof_end();
+  if (h->profile && !any_nullable) {
+    rc = check_cuda(cudaStreamSynchronize(s), "emit sync");
     if (rc) return rc;
   }
   if (any_nullable) {
@@ -297,13 +335,23 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
     for (int i = 0; i < nk; ++i) out_keys[i].null_count = hn[i];
     for (int i = 0; i < nr; ++i) out_results[i].null_count = hn[nk + i];
   }
+  h->prof_resolve();
   h->dfree(d_nulls);
+  return BGB_OK;
+}
+
+extern "C" int bgb_groupby_profile(const bgb_groupby* h, int32_t index, const char** name, float* ms)
+{
+  if (!h || index < 0 || index >= (int)h->prof.size()) return BGB_INVALID_ARGUMENT;
+  if (name) *name = h->prof[index].name;
+  if (ms) *ms = h->prof[index].ms < 0 ? 0.f : h->prof[index].ms;
   return BGB_OK;
 }
 
 extern "C" void bgb_groupby_destroy(bgb_groupby* h)
 {
   if (!h) return;
+  for (auto& p : h->prof) if (p.e0) { cudaEventDestroy(p.e0); cudaEventDestroy(p.e1); }
   h->free_all();
   delete h;
 }

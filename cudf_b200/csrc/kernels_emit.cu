@@ -102,7 +102,7 @@ cudaError_t launch_compact(const TableDesc& t, uint32_t* group_slots, uint32_t* 
   if (e != cudaSuccess) return e;
   uint64_t tiles = (t.capacity + 1 + kScanTile - 1) / kScanTile;
   compact_kernel<<<(unsigned)tiles, kScanThreads, 0, s>>>(t, group_slots, reinterpret_cast<unsigned long long*>(scan_state));
-  return cudaGetLastError();
+  return note_launch();
 }
 
 // ------------------------------------------------------------------ output gather + finalise
@@ -212,7 +212,7 @@ cudaError_t launch_emit(const EmitParams& p, cudaStream_t s)
   if (p.num_groups == 0 || p.num_outs == 0) return cudaSuccess;
   int blocks = (p.num_groups + 255) / 256;
   emit_kernel<<<blocks, 256, 0, s>>>(p);
-  return cudaGetLastError();
+  return note_launch();
 }
 
 }  // namespace bgb

@@ -45,7 +45,7 @@ cudaError_t launch_init_table(const AggParams& p, cudaStream_t s)
   uint64_t n = p.table.capacity + 1;
   int blocks = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
   init_table_kernel<<<blocks, 256, 0, s>>>(p);
-  return cudaGetLastError();
+  return note_launch();
 }
 
 // ------------------------------------------------------------------ one row into one accumulator
@@ -115,7 +115,7 @@ cudaError_t launch_aggregate_global(const AggParams& p, cudaStream_t s)
   int64_t want = (p.num_rows + 255) / 256;
   int blocks   = (int)(want < 148 * 8 ? want : 148 * 8);
   aggregate_global_kernel<<<blocks, 256, 0, s>>>(p);
-  return cudaGetLastError();
+  return note_launch();
 }
 
 // ------------------------------------------------------------------ cardinality estimator
@@ -160,7 +160,7 @@ cudaError_t launch_estimate_cardinality(const AggParams& p, int64_t sample_rows,
   if (step < 1) step = 1;
   int blocks = (int)((sample_rows + 255) / 256);
   estimate_kernel<<<blocks, 256, 0, s>>>(p, sample_rows, step, scratch_set, set_capacity, out_distinct);
-  return cudaGetLastError();
+  return note_launch();
 }
 
 }  // namespace bgb

@@ -28,6 +28,7 @@ class GroupBy:
         self._null_handling = null_handling
         self._options = options or {}
         self.last_path = None
+        self.last_profile = []  # [(kernel name, device ms)] when options["profile"] is set
 
     def _c_requests(self, requests):
         n = len(requests)
@@ -57,6 +58,7 @@ class GroupBy:
         opt.force_path = int(self._options.get("force_path", 0))
         opt.capacity_log2 = int(self._options.get("capacity_log2", 0))
         opt.sample_rows = int(self._options.get("sample_rows", 0))
+        opt.profile = int(self._options.get("profile", 0))
         handle = C.c_void_p()
         ngroups = C.c_int32(0)
         with torch.cuda.device(device):
@@ -94,6 +96,8 @@ class GroupBy:
                             k += 1
                         res_cols.append(cols)
                 _lib.check(L.bgb_groupby_emit(handle, okeys, ores, sptr))
+                if opt.profile:
+                    self.last_profile = _read_profile(L, handle)
                 for i, c in enumerate(key_cols):
                     c.null_count = okeys[i].null_count
                 k = 0
@@ -105,6 +109,84 @@ class GroupBy:
                 L.bgb_groupby_destroy(handle)
         del keep
         return Table(key_cols), [Table(cols) for cols in res_cols]
+
+
+def _read_profile(L, handle):
+    out, i = [], 0
+    name, ms = C.c_char_p(), C.c_float()
+    while L.bgb_groupby_profile(handle, i, C.byref(name), C.byref(ms)) == 0:
+        out.append((name.value.decode(), ms.value))
+        i += 1
+    return out
+
+
+class HostColumnView:
+    """A host-memory column (numpy data + optional packed uint32 validity words) for groupby_host."""
+
+    def __init__(self, data, mask_words=None, null_count=0, type_id=None):
+        from .column import _NP_OF_TYPE
+        self.data = data
+        self.mask = mask_words
+        self.null_count = null_count if mask_words is not None else 0
+        if type_id is None:
+            type_id = {v: k for k, v in reversed(list(_NP_OF_TYPE.items()))}[data.dtype.type]
+        self.type_id = type_id
+
+    def view(self):
+        return _lib.ColumnView(self.type_id, 0, len(self.data), self.null_count, 0, 0, self.data.ctypes.data if len(self.data) else None,
+                               self.mask.ctypes.data if self.mask is not None else None)
+
+
+def groupby_host(keys, requests, null_handling: int = NullPolicy.EXCLUDE, options: dict | None = None):
+    """End-to-end call on HOST columns through the C ABI's bgb_groupby_host: H2D staging, build, emit, D2H.
+
+    keys: [HostColumnView]; requests: [(HostColumnView, [Aggregation])].
+    Returns (num_groups, [(data, mask_words|None, null_count)] keys, [[...] per request]) as numpy arrays (copied)."""
+    import numpy as np
+    from .column import _NP_OF_TYPE
+    L = _lib.lib()
+    options = options or {}
+    nk = len(keys)
+    ckeys = (_lib.ColumnView * max(nk, 1))()
+    for i, c in enumerate(keys):
+        ckeys[i] = c.view()
+    creq = (_lib.Request * max(len(requests), 1))()
+    keep = []
+    for i, (col, aggs) in enumerate(requests):
+        ca = (_lib.Aggregation * max(len(aggs), 1))()
+        for j, a in enumerate(aggs):
+            ca[j] = _lib.Aggregation(a.kind, a.ddof)
+        keep.append(ca)
+        creq[i] = _lib.Request(col.view(), ca, len(aggs), 0)
+    opt = _lib.Options()
+    opt.force_path = int(options.get("force_path", 0))
+    opt.capacity_log2 = int(options.get("capacity_log2", 0))
+    ng, nres = C.c_int32(0), C.c_int32(0)
+    hk, hr = C.POINTER(_lib.HostColumn)(), C.POINTER(_lib.HostColumn)()
+    _lib.check(L.bgb_groupby_host(ckeys, nk, int(null_handling), creq, len(requests), C.byref(opt), C.byref(ng), C.byref(hk),
+                                  C.byref(hr), C.byref(nres)))
+    G = ng.value
+
+    def take(hc):
+        dt = np.dtype(_NP_OF_TYPE[hc.type_id])
+        if G == 0:
+            return np.empty(0, dt), None, 0
+        data = np.ctypeslib.as_array(C.cast(hc.data, C.POINTER(C.c_uint8)), shape=(G * dt.itemsize,)).view(dt).copy()
+        mask = None
+        if hc.null_mask:
+            mask = np.ctypeslib.as_array(C.cast(hc.null_mask, C.POINTER(C.c_uint32)), shape=((G + 31) // 32,)).copy()
+        return data, mask, hc.null_count
+
+    try:
+        kout = [take(hk[i]) for i in range(nk)]
+        rout, k = [], 0
+        for _, aggs in requests:
+            rout.append([take(hr[k + j]) for j in range(len(aggs))])
+            k += len(aggs)
+    finally:
+        L.bgb_free_host_result(hk, nk)
+        L.bgb_free_host_result(hr, nres.value)
+    return G, kout, rout
 
 
 def can_use_hash_groupby(keys: Table, requests) -> bool:

@@ -113,7 +113,8 @@ typedef struct bgb_options {
   int32_t force_path;        /* 0 auto, 1 global-table kernel only, 2 shared-memory pre-aggregation, 3 partitioned */
   int32_t capacity_log2;     /* 0 auto; else global table has 2^capacity_log2 slots */
   int32_t sample_rows;       /* 0 auto (65536) rows sampled by the cardinality estimator */
-  int32_t reserved[5];
+  int32_t profile;           /* != 0: bracket every kernel with CUDA events on the call's stream (bgb_groupby_profile) */
+  int32_t reserved[4];
 } bgb_options;
 
 typedef struct bgb_groupby bgb_groupby; /* opaque handle between build and emit */
@@ -154,6 +155,12 @@ const char* bgb_groupby_path(const bgb_groupby* handle);
 
 void bgb_groupby_destroy(bgb_groupby* handle);
 
+/* Measurement hooks (bench.py): device time of kernel #index of the last build+emit on this handle, taken with CUDA
+ * events on the call's stream when options->profile != 0. Returns BGB_INVALID_ARGUMENT past the last entry. */
+int bgb_groupby_profile(const bgb_groupby* handle, int32_t index, const char** name, float* ms);
+/* process-wide number of kernels this library has launched (every launch goes through one counter) */
+int64_t bgb_kernel_launches(void);
+
 /* ---- host-buffer convenience (end-to-end measurement and simple callers) ------------------------------------- */
 
 /* Same call with HOST columns (pinned or pageable): copies inputs H2D in chunks overlapped with aggregation,
@@ -172,16 +179,6 @@ int bgb_groupby_host(const bgb_column_view* host_keys, int32_t num_keys, int32_t
                      int32_t* num_groups, bgb_host_column** out_keys, bgb_host_column** out_results,
                      int32_t* num_results);
 void bgb_free_host_result(bgb_host_column* cols, int32_t n);
-
-/* ---- multi-GPU building blocks (one process per GPU; the exchange itself is an NCCL all-to-all run by the host
- *      layer, see cudf_b200/distributed.py and SURVEY.md 8e) ------------------------------------------------------ */
-
-/* Partition the rows of (keys, partial columns) by hash2(key) % num_parts into contiguous per-destination runs.
- * All columns are permuted identically; part_offsets[num_parts+1] (device) receives the run boundaries. */
-int bgb_partition_by_key_hash(const bgb_column_view* keys, int32_t num_keys, const bgb_column_view* cols,
-                              int32_t num_cols, int32_t num_parts, bgb_mutable_column* out_keys,
-                              bgb_mutable_column* out_cols, int32_t* part_offsets_device, void* stream,
-                              const bgb_allocator* alloc);
 
 /* ---- synthetic inputs (SURVEY.md 8d generators; bench + tests only) --------------------------------------------- */
 
