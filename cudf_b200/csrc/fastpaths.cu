@@ -1,11 +1,124 @@
 #include "fastpaths.h"
 
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "errors.h"
+#include "kernels_smem.h"
+
 namespace bgb {
-int try_fast_paths(const Plan& plan, const TableDesc& table, const bgb_options& opt, double g_est, cudaStream_t s, bool& done,
-                   std::string& path)
+
+static bool aligned_to(const void* base, int64_t offset, int width, int bytes)
 {
-  (void)plan; (void)table; (void)opt; (void)g_est; (void)s; (void)path;
+  return (((uintptr_t)base + (uintptr_t)(offset * width)) % (uintptr_t)bytes) == 0;
+}
+
+SmemEligibility smem_eligibility(const Plan& pl)
+{
+  SmemEligibility e;
+  if (pl.key_words != 1 || pl.num_rows == 0) return e;
+  for (size_t i = 0; i < pl.accs.size(); ++i) {
+    const AccPlan& a = pl.accs[i];
+    if (a.op == ACC_SUM_I64) { if (e.sum_acc >= 0) return e; e.sum_acc = (int)i; }
+    else if (a.op == ACC_COUNT_VALID) { if (e.cntv_acc >= 0) return e; e.cntv_acc = (int)i; }
+    else if (a.op == ACC_COUNT_ALL) e.cnta_acc = (int)i;
+    else return e;
+    if (a.value_col >= 0) { if (e.value_col >= 0 && e.value_col != a.value_col) return e; e.value_col = a.value_col; }
+  }
+  if (e.value_col >= 0) {
+    const ValuePlan& v = pl.values[e.value_col];
+    if (e.cnta_acc >= 0 && v.has_mask) return e;  // COUNT_ALL differs from COUNT_VALID: generic path
+    if (e.sum_acc >= 0) {
+      if (v.src == S_I64 || v.src == S_U64) e.value_width = 8;
+      else if (v.src == S_I32 || v.src == S_U32) e.value_width = 4;
+      else return e;
+      if (!aligned_to(v.v.data, v.v.offset, e.value_width, 2 * e.value_width)) return e;
+    }
+  }
+  int key_bits = 0;
+  for (const KeyPlan& k : pl.keys) key_bits = std::max(key_bits, std::max((int)k.shift + 8 * k.width, (int)k.null_bit + 1));
+  const KeyPlan& k0 = pl.keys[0];
+  if (pl.keys.size() == 1 && (k0.width == 4 || k0.width == 8) && k0.null_bit < 0 && aligned_to(k0.v.data, k0.v.offset, k0.width, 2 * k0.width)) {
+    e.key_mode = 1; e.smem_key_bytes = k0.width;
+  } else {
+    e.key_mode = 0; e.smem_key_bytes = key_bits <= 32 ? 4 : 8;
+  }
+  e.ok = true;
+  return e;
+}
+
+static int bit_length(uint64_t x) { int b = 0; while (x) { ++b; x >>= 1; } return b; }
+
+static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint32_t slots)
+{
+  const Plan& pl = *ctx.plan;
+  // global table init (keys + every accumulator) with the generic init kernel
+  AggParams ip;
+  memset(&ip, 0, sizeof ip);
+  ip.table = ctx.table; ip.init_keys = 1; ip.num_accs = (int)pl.accs.size();
+  for (size_t i = 0; i < pl.accs.size(); ++i) { ip.acc[i].op = pl.accs[i].op; ip.acc[i].cells = pl.accs[i].cells; }
+  ctx.prof->begin("init_table");
+  int rc = check_cuda(launch_init_table(ip, ctx.stream), "init_table");
+  ctx.prof->end();
+  if (rc) return rc;
+
+  SmemParams sp;
+  memset(&sp, 0, sizeof sp);
+  sp.a.num_rows = pl.num_rows; sp.a.num_key_cols = (int)pl.keys.size(); sp.a.skip_null_keys = pl.skip_null_keys;
+  for (size_t c = 0; c < pl.keys.size(); ++c) {
+    const KeyPlan& k = pl.keys[c];
+    sp.a.kc[c] = KeyColDesc{(const uint8_t*)k.v.data, k.v.null_mask, k.v.offset, k.width, k.fclass, k.shift, k.null_bit};
+  }
+  sp.a.table = ctx.table;
+  if (e.value_col >= 0) {
+    const ValuePlan& v = pl.values[e.value_col];
+    sp.v_data = (const uint8_t*)v.v.data; sp.v_mask = v.v.null_mask; sp.v_offset = v.v.offset;
+    sp.v_signed = (v.src == S_I32 || v.src == S_I64);
+  }
+  sp.sum_cells  = e.sum_acc >= 0 ? (unsigned long long*)pl.accs[e.sum_acc].cells : nullptr;
+  sp.cntv_cells = e.cntv_acc >= 0 ? (int*)pl.accs[e.cntv_acc].cells : nullptr;
+  sp.cnta_cells = e.cnta_acc >= 0 ? (int*)pl.accs[e.cnta_acc].cells : nullptr;
+  sp.slots      = slots;
+  sp.fill_limit = std::min<uint32_t>((uint32_t)(0.85 * slots), slots > 1100 ? slots - 1100 : 0);
+  // count field width c and value range m: a CTA flushes before 2^c rows, partial sums stay below 2^(c+m) <= 2^(63-c)
+  int m = e.value_width == 0 ? 0 : bit_length(ctx.max_abs_value) + 1;
+  if (e.value_width == 4) m = std::min(m, 31);
+  int c = std::min(24, (63 - m) / 2);
+  if (c < 16) { c = 16; m = 31; }
+  sp.cnt_bits = c; sp.val_bits = std::min(m, 63 - 2 * c);
+  sp.debug = getenv("BGB_DEBUG") != nullptr;
+  if (sp.debug) {
+    cudaMemsetAsync(ctx.table.status + 4, 0, 16, ctx.stream);
+    fprintf(stderr, "[bgb] smem path: slots=%u fill_limit=%u c=%d m=%d g_raw=%.0f max_abs=%llu key_mode=%d sk=%d vw=%d\n", sp.slots, sp.fill_limit,
+            sp.cnt_bits, sp.val_bits, ctx.g_raw, (unsigned long long)ctx.max_abs_value, e.key_mode, e.smem_key_bytes, e.value_width);
+  }
+  ctx.prof->begin("aggregate_smem");
+  rc = check_cuda(launch_aggregate_smem(sp, e.smem_key_bytes, e.key_mode, e.value_width, ctx.num_sms, ctx.stream), "aggregate_smem");
+  ctx.prof->end();
+  return rc;
+}
+
+int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path)
+{
   done = false;
+  const Plan& pl = *ctx.plan;
+  if (ctx.opt.force_path == 1) return BGB_OK;  // generic kernel only
+  const SmemEligibility e = smem_eligibility(pl);
+  if (e.ok && (ctx.opt.force_path == 0 || ctx.opt.force_path == 2)) {
+    const uint32_t slots_max = (uint32_t)(smem_table_max_bytes() / (e.smem_key_bytes + 8));
+    const bool fits = ctx.g_raw <= 1.2 * slots_max;
+    if ((fits && pl.num_rows >= 65536) || ctx.opt.force_path == 2) {
+      uint32_t slots = (uint32_t)std::min<double>(slots_max, std::max(2048.0, std::ceil(2.2 * ctx.g_raw)));
+      int rc = run_smem_path(ctx, e, slots);
+      if (rc) return rc;
+      done = true; path = "smem";
+      return BGB_OK;
+    }
+  }
   return BGB_OK;
 }
+
 }  // namespace bgb

@@ -4,8 +4,28 @@
 #include <string>
 
 #include "plan.h"
+#include "profiler.h"
 
 namespace bgb {
-int try_fast_paths(const Plan& plan, const TableDesc& table, const bgb_options& opt, double g_est, cudaStream_t s, bool& done,
-                   std::string& path);
+
+struct BuildContext {
+  const Plan* plan;
+  TableDesc table;
+  bgb_options opt;
+  double g_raw;             // sampled cardinality estimate (no safety factor)
+  uint64_t max_abs_value;   // largest |v| among the sampled rows of the SUM column (0 when not sampled)
+  cudaStream_t stream;
+  Profiler* prof;
+  int num_sms;
+};
+
+// which accumulator set the shared-memory kernel can serve; value_col = -1 when there is no SUM/COUNT_VALID column
+struct SmemEligibility {
+  bool ok = false;
+  int value_col = -1, sum_acc = -1, cntv_acc = -1, cnta_acc = -1;
+  int key_mode = 0, smem_key_bytes = 8, value_width = 0;
+};
+SmemEligibility smem_eligibility(const Plan& plan);
+
+int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path);
 }

@@ -1,6 +1,7 @@
 // C ABI: bgb_groupby_build / _emit / _result_info / _destroy.  See include/bgb.h for the contract.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -8,6 +9,7 @@
 #include "errors.h"
 #include "fastpaths.h"
 #include "plan.h"
+#include "profiler.h"
 
 using namespace bgb;
 
@@ -23,27 +25,7 @@ struct bgb_groupby {
   uint32_t* group_slots = nullptr;
   int32_t num_groups = 0;
   std::string path = "empty";
-  // optional per-kernel CUDA-event timing (bgb_options.profile)
-  struct Prof { const char* name; cudaEvent_t e0, e1; float ms; };
-  std::vector<Prof> prof;
-  bool profile = false;
-  void prof_begin(const char* name)
-  {
-    if (!profile) return;
-    Prof p{name, nullptr, nullptr, -1.f};
-    cudaEventCreate(&p.e0); cudaEventCreate(&p.e1);
-    cudaEventRecord(p.e0, stream);
-    prof.push_back(p);
-  }
-  void prof_end() { if (profile && !prof.empty()) cudaEventRecord(prof.back().e1, stream); }
-  void prof_resolve()  // after a stream synchronise
-  {
-    for (Prof& p : prof)
-      if (p.ms < 0 && p.e0) {
-        if (cudaEventElapsedTime(&p.ms, p.e0, p.e1) != cudaSuccess) { cudaGetLastError(); p.ms = 0; }
-        cudaEventDestroy(p.e0); cudaEventDestroy(p.e1); p.e0 = p.e1 = nullptr;
-      }
-  }
+  Profiler prof;
 
   void* dalloc(size_t bytes)
   {
@@ -129,7 +111,8 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
   if (alloc && alloc->allocate && alloc->deallocate) { h->alloc = *alloc; h->has_alloc = true; }
   bgb_options opt{};
   if (options) opt = *options;
-  h->profile = opt.profile != 0;
+  h->prof.on = opt.profile != 0;
+  h->prof.stream = (cudaStream_t)stream;
   Plan& pl = h->plan;
   const int64_t N = pl.num_rows;
   if (N == 0) { *out_handle = h; return BGB_OK; }  // groupby.cu:233: empty input -> empty outputs
@@ -149,7 +132,10 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
   // ---- capacity: explicit, or from the sampled cardinality estimate (one small kernel + one read-back)
   const uint64_t cap_max = next_pow2((uint64_t)(2 * N < 1024 ? 1024 : 2 * N));
   uint64_t capacity      = 0;
-  double g_est           = (double)N;
+  double g_est           = (double)N, g_raw = (double)N;
+  uint64_t max_abs       = ~0ull;
+  int num_sms            = 148;
+  { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev); }
   if (opt.capacity_log2 > 0) capacity = 1ull << opt.capacity_log2;
   else if (N <= 4096) capacity = next_pow2(2 * (uint64_t)N < 1024 ? 1024 : 2 * (uint64_t)N);
   else {
@@ -159,18 +145,26 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     if (!set) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "estimator scratch"));
     AggParams ep;
     fill_agg_params(*h, ep, 0, 0);
-    h->prof_begin("estimate_cardinality");
+    const SmemEligibility se = smem_eligibility(pl);
+    if (se.ok && se.sum_acc >= 0) {  // also sample the magnitude of the SUM inputs
+      const ValuePlan& v = pl.values[se.value_col];
+      ep.num_accs = 1;
+      ep.acc[0].data = (const uint8_t*)v.v.data; ep.acc[0].mask = v.v.null_mask; ep.acc[0].offset = v.v.offset; ep.acc[0].src = v.src;
+    }
+    h->prof.begin("estimate_cardinality");
     FAIL_RC(check_cuda(launch_estimate_cardinality(ep, sample, set, setcap, status + 4, s), "estimate"));
-    h->prof_end();
-    uint32_t est[2] = {0, 0};
+    h->prof.end();
+    uint32_t est[4] = {0, 0, 0, 0};
     FAIL_RC(check_cuda(cudaMemcpyAsync(est, status + 4, sizeof est, cudaMemcpyDeviceToHost, s), "estimate copy"));
     FAIL_RC(check_cuda(cudaStreamSynchronize(s), "estimate sync"));
-    h->prof_resolve();
+    h->prof.resolve();
     h->dfree(set);
     const double d = est[0], m = est[1];
-    if (m == 0) g_est = 1;
-    else if (d > 0.9 * m) g_est = (double)N;  // nearly all sampled keys distinct: cardinality unknown, assume the worst
-    else g_est = std::min((double)N, 1.5 * solve_cardinality(d, m));
+    max_abs = (uint64_t)est[2] | ((uint64_t)est[3] << 32);
+    if (m == 0) g_raw = 1;
+    else if (d > 0.9 * m) g_raw = (double)N;  // nearly all sampled keys distinct: cardinality unknown, assume the worst
+    else g_raw = std::min((double)N, solve_cardinality(d, m));
+    g_est = std::min((double)N, 1.5 * g_raw);
     capacity = next_pow2((uint64_t)std::max(1024.0, 2.0 * g_est));
     if (capacity > cap_max) capacity = cap_max;
   }
@@ -187,24 +181,25 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     // init + aggregate, kMaxAccs accumulators per launch (the first launch also initialises the keys)
     std::string path;
     bool done = false;
-    FAIL_RC(try_fast_paths(pl, h->table, opt, g_est, s, done, path));
+    BuildContext ctx{&pl, h->table, opt, g_raw, max_abs, s, &h->prof, num_sms};
+    FAIL_RC(try_fast_paths(ctx, done, path));
     if (!done) {
       size_t na = pl.accs.size();
-      h->prof_begin("init_table");
+      h->prof.begin("init_table");
       for (size_t b = 0; b == 0 || b < na; b += kMaxAccs) {
         AggParams p;
         fill_agg_params(*h, p, b, std::min(na, b + kMaxAccs));
         p.init_keys = (b == 0);  // later chunks only initialise their own cells
         FAIL_RC(check_cuda(launch_init_table(p, s), "init_table"));
       }
-      h->prof_end();
-      h->prof_begin("aggregate_global");
+      h->prof.end();
+      h->prof.begin("aggregate_global");
       for (size_t b = 0; b == 0 || b < na; b += kMaxAccs) {
         AggParams p;
         fill_agg_params(*h, p, b, std::min(na, b + kMaxAccs));
         FAIL_RC(check_cuda(launch_aggregate_global(p, s), "aggregate_global"));
       }
-      h->prof_end();
+      h->prof.end();
       path = "global";
     }
     h->path = path;
@@ -213,14 +208,15 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     h->group_slots            = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
     uint32_t* scan_state      = (uint32_t*)h->dalloc(compact_scan_state_bytes(capacity));
     if (!h->group_slots || !scan_state) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "compaction scratch"));
-    h->prof_begin("compact");
+    h->prof.begin("compact");
     FAIL_RC(check_cuda(launch_compact(h->table, h->group_slots, scan_state, s), "compact"));
-    h->prof_end();
-    uint32_t st[4] = {0, 0, 0, 0};
+    h->prof.end();
+    uint32_t st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     FAIL_RC(check_cuda(cudaMemcpyAsync(st, status, sizeof st, cudaMemcpyDeviceToHost, s), "status copy"));
     FAIL_RC(check_cuda(cudaStreamSynchronize(s), "build sync"));
-    h->prof_resolve();
+    h->prof.resolve();
     h->dfree(scan_state);
+    if (getenv("BGB_DEBUG")) fprintf(stderr, "[bgb] path=%s groups=%u overflow=%u bypass_rows=%u flushes=%u\n", path.c_str(), st[1], st[0], st[4], st[5]);
     if (st[0] == 0) { h->num_groups = (int32_t)st[1]; break; }
     // table overloaded: free it and retry at the size that fits every row as its own group
     if (capacity >= cap_max || attempt >= 2) FAIL_RC(set_error(BGB_CUDA_ERROR, "group table overflow at maximum capacity"));
@@ -229,6 +225,7 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     for (AccPlan& a : pl.accs) { h->dfree(a.cells); a.cells = nullptr; }
     capacity = cap_max;
     g_est    = (double)N;
+    g_raw    = (double)N;
   }
 #undef FAIL_RC
   *num_groups = h->num_groups;
@@ -274,6 +271,7 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
   if (G == 0) return BGB_OK;
   cudaStream_t s = (cudaStream_t)stream;
   h->stream      = s;
+  h->prof.stream = s;
 
   // validate caller buffers
   for (int i = 0; i < nk; ++i) {
@@ -311,7 +309,7 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
     any_nullable |= o.nullable;
     descs.push_back(d);
   }
-  h->prof_begin("emit");
+  h->prof.begin("emit");
   for (size_t b = 0; b < descs.size(); b += kMaxOuts) {
     EmitParams ep;
     memset(&ep, 0, sizeof ep);
@@ -321,8 +319,8 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
     rc = check_cuda(launch_emit(ep, s), "emit");
     if (rc) return rc;
   }
-  h->prof_end();
-  if (h->profile && !any_nullable) {
+  h->prof.end();
+  if (h->prof.on && !any_nullable) {
     rc = check_cuda(cudaStreamSynchronize(s), "emit sync");
     if (rc) return rc;
   }
@@ -335,23 +333,22 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
     for (int i = 0; i < nk; ++i) out_keys[i].null_count = hn[i];
     for (int i = 0; i < nr; ++i) out_results[i].null_count = hn[nk + i];
   }
-  h->prof_resolve();
+  h->prof.resolve();
   h->dfree(d_nulls);
   return BGB_OK;
 }
 
 extern "C" int bgb_groupby_profile(const bgb_groupby* h, int32_t index, const char** name, float* ms)
 {
-  if (!h || index < 0 || index >= (int)h->prof.size()) return BGB_INVALID_ARGUMENT;
-  if (name) *name = h->prof[index].name;
-  if (ms) *ms = h->prof[index].ms < 0 ? 0.f : h->prof[index].ms;
+  if (!h || index < 0 || index >= (int)h->prof.entries.size()) return BGB_INVALID_ARGUMENT;
+  if (name) *name = h->prof.entries[index].name;
+  if (ms) *ms = h->prof.entries[index].ms < 0 ? 0.f : h->prof.entries[index].ms;
   return BGB_OK;
 }
 
 extern "C" void bgb_groupby_destroy(bgb_groupby* h)
 {
   if (!h) return;
-  for (auto& p : h->prof) if (p.e0) { cudaEventDestroy(p.e0); cudaEventDestroy(p.e1); }
   h->free_all();
   delete h;
 }

@@ -131,6 +131,15 @@ __global__ void __launch_bounds__(256) estimate_kernel(const __grid_constant__ A
   uint64_t k0, k1;
   if (!pack_key(p, row, k0, k1)) return;
   atomicAdd(out + 1, 1u);
+  if (p.num_accs == 1 && p.acc[0].data != nullptr) {  // magnitude of the sampled integer SUM inputs (sizes the smem count field)
+    const AccDesc& a = p.acc[0];
+    const int64_t idx = (int64_t)a.offset + row;
+    if (a.mask == nullptr || bit_is_set(a.mask, idx)) {
+      const int64_t v = raw_to_i64(load_raw(a.data, src_width(a.src), idx), a.src);
+      const unsigned long long mag = v < 0 ? ~(unsigned long long)v : (unsigned long long)v;
+      if (mag) atomicMax(reinterpret_cast<unsigned long long*>(out + 2), mag);
+    }
+  }
   uint64_t f = hash_key(k0, k1, p.table.key_words);
   if (f == kEmpty) f = 0;
   uint64_t slot = mix64(f) & (set_capacity - 1);
@@ -152,7 +161,7 @@ cudaError_t launch_estimate_cardinality(const AggParams& p, int64_t sample_rows,
 {
   cudaError_t e = cudaMemsetAsync(scratch_set, 0xff, set_capacity * sizeof(uint64_t), s);
   if (e != cudaSuccess) return e;
-  e = cudaMemsetAsync(out_distinct, 0, 2 * sizeof(uint32_t), s);
+  e = cudaMemsetAsync(out_distinct, 0, 4 * sizeof(uint32_t), s);
   if (e != cudaSuccess) return e;
   if (sample_rows > p.num_rows) sample_rows = p.num_rows;
   if (sample_rows <= 0) return cudaSuccess;

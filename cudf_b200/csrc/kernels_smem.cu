@@ -1,0 +1,276 @@
+// Shared-memory pre-aggregation kernel: the low-cardinality fast path (BASELINE config A / A9 at 1e4 groups).
+//
+// One persistent CTA per SM owns a private open-addressing table in shared memory (up to ~227 KB):
+//   skeys[S]  packed key (4 or 8 bytes), EMPTY = all ones
+//   slo[S]    low 32 bits of the partial int64 SUM
+//   shc[S]    [ high bits of the partial SUM : 32-c | row count : c ]   (one ATOMS.ADD updates both)
+// Rows are streamed from HBM with 128-bit coalesced loads, software-pipelined one chunk ahead in registers (the whole
+// shared memory belongs to the table, so there is no room for a TMA staging ring here; the TMA-staged kernels are the
+// tiny-cardinality and partition kernels). Per row: one LDS probe sequence, ATOMS.ADD(lo) with return to catch the
+// carry, ATOMS.ADD(hi|count). 64-bit shared atomics do not exist in hardware (ATOMS.CAST.SPIN loop, 3x slower, see
+// profiles/r01_microbench.txt), hence the split. Values outside [-2^m, 2^m) and the key equal to EMPTY go straight to
+// the HBM table with global atomics, as do keys that no longer fit once the table is `fill_limit` full, so any input is
+// aggregated exactly; the host only routes here when the sampled cardinality says the table will hold the groups.
+// Partials are flushed into the global table (find-or-insert + RED.ADD) every < 2^c rows per CTA and at the end.
+//
+// Replaces the reference's shared-memory path: compute_mapping_indices + single_pass_shmem_aggs_kernel
+// (/root/reference/cpp/src/groupby/hash/compute_mapping_indices.cuh:23-151,
+//  /root/reference/cpp/src/groupby/hash/compute_shared_memory_aggs.cu:121-353), which caps out at 128 groups per block.
+#include "device_utils.cuh"
+#include "kernels_smem.h"
+
+namespace bgb {
+
+namespace {
+
+constexpr int kThreads      = 1024;
+constexpr int kRowsPerThread = 4;
+constexpr int kChunk        = kThreads * kRowsPerThread;
+
+__device__ __forceinline__ uint32_t hash32(uint64_t k)
+{
+  uint32_t h = (uint32_t)k ^ ((uint32_t)(k >> 32) * 0x85EBCA6Bu);
+  h ^= h >> 16; h *= 0x7FEB352Du; h ^= h >> 15; h *= 0x846CA68Bu; h ^= h >> 16;
+  return h;
+}
+
+template <int W>
+__device__ __forceinline__ void load_pair(const uint8_t* base, int64_t idx, uint64_t& a, uint64_t& b)
+{
+  if (W == 8) { const ulonglong2 v = __ldcs(reinterpret_cast<const ulonglong2*>(base + idx * 8)); a = v.x; b = v.y; }
+  else if (W == 4) { const uint2 v = __ldcs(reinterpret_cast<const uint2*>(base + idx * 4)); a = v.x; b = v.y; }
+}
+template <int W>
+__device__ __forceinline__ uint64_t load_one(const uint8_t* base, int64_t idx)
+{
+  if (W == 8) return __ldcs(reinterpret_cast<const unsigned long long*>(base + idx * 8));
+  return __ldcs(reinterpret_cast<const uint32_t*>(base + idx * 4));
+}
+
+template <int SK> struct SKey;
+template <> struct SKey<8> { using type = unsigned long long; };
+template <> struct SKey<4> { using type = unsigned int; };
+
+struct RowBuf {
+  uint64_t k[kRowsPerThread];
+  uint64_t v[kRowsPerThread];
+  uint32_t flags;  // bit i: row i present and key usable; bit 8+i: value valid
+};
+
+}  // namespace
+
+template <int SK, int KEYMODE, int VW>
+__global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_constant__ SmemParams p)
+{
+  using skey_t = typename SKey<SK>::type;
+  constexpr skey_t kSEmpty = (skey_t)~(skey_t)0;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const uint32_t S = p.slots;
+  skey_t* skeys    = reinterpret_cast<skey_t*>(smem_raw);
+  uint32_t* slo    = reinterpret_cast<uint32_t*>(skeys + S);
+  uint32_t* shc    = slo + S;
+  __shared__ uint32_t s_fill;
+  __shared__ int s_abort;
+
+  for (uint32_t i = threadIdx.x; i < S; i += kThreads) { skeys[i] = kSEmpty; slo[i] = 0; shc[i] = 0; }
+  if (threadIdx.x == 0) { s_fill = 0; s_abort = 0; }
+  __syncthreads();
+
+  const AggParams& a   = p.a;
+  const int64_t n      = a.num_rows;
+  const int64_t nchunk = (n + kChunk - 1) / kChunk;
+  const int c_bits     = p.cnt_bits;
+  const uint32_t c_mask = (1u << c_bits) - 1u;
+  const int m_bits     = p.val_bits;
+  const KeyColDesc kc0 = a.kc[0];
+
+  // ---- chunk loader: thread t owns rows {2t, 2t+1} of each half-chunk, so every load is a 16-byte (or 8-byte) vector
+  auto load_chunk = [&](int64_t c, RowBuf& rb) {
+    rb.flags = 0;
+#pragma unroll
+    for (int half = 0; half < kRowsPerThread / 2; ++half) {
+      const int64_t r = c * kChunk + (int64_t)half * (kChunk / 2) + (int64_t)threadIdx.x * 2;
+      const int i0 = half * 2;
+      rb.k[i0] = rb.k[i0 + 1] = 0; rb.v[i0] = rb.v[i0 + 1] = 0;
+      if (r >= n) continue;
+      const bool two = r + 1 < n;
+      uint32_t present = two ? 3u : 1u;
+      if (KEYMODE == 1) {
+        const int64_t idx = (int64_t)kc0.offset + r;
+        if (two) load_pair<SK>(kc0.data, idx, rb.k[i0], rb.k[i0 + 1]);
+        else rb.k[i0] = load_one<SK>(kc0.data, idx);
+        if (kc0.fclass) { rb.k[i0] = canon_key_bits(rb.k[i0], kc0.fclass); rb.k[i0 + 1] = canon_key_bits(rb.k[i0 + 1], kc0.fclass); }
+        if (kc0.mask != nullptr) {  // EXCLUDE policy: rows with a null key are dropped (direct mode never sees INCLUDE + mask)
+          if (!bit_is_set(kc0.mask, idx)) present &= ~1u;
+          if (two && !bit_is_set(kc0.mask, idx + 1)) present &= ~2u;
+        }
+      } else {
+        // packed key of rows r, r+1 (no early exit: both rows walk the key columns together)
+        uint64_t ka = 0, kb = 0;
+        bool skip_a = false, skip_b = !two;
+#pragma unroll 1
+        for (int col = 0; col < a.num_key_cols; ++col) {
+          const KeyColDesc& kc = a.kc[col];
+          const int64_t idx = (int64_t)kc.offset + r;
+          const bool va = kc.mask == nullptr || bit_is_set(kc.mask, idx);
+          const bool vb = two && (kc.mask == nullptr || bit_is_set(kc.mask, idx + 1));
+          if (va) ka |= canon_key_bits(load_raw(kc.data, kc.width, idx), kc.fclass) << kc.shift;
+          else if (a.skip_null_keys) skip_a = true;
+          else if (kc.null_bit >= 0) ka |= 1ull << kc.null_bit;
+          if (vb) kb |= canon_key_bits(load_raw(kc.data, kc.width, idx + 1), kc.fclass) << kc.shift;
+          else if (a.skip_null_keys) skip_b = true;
+          else if (two && kc.null_bit >= 0) kb |= 1ull << kc.null_bit;
+        }
+        rb.k[i0] = ka; rb.k[i0 + 1] = kb;
+        if (skip_a) present &= ~1u;
+        if (skip_b) present &= ~2u;
+      }
+      uint32_t vvalid = present;
+      if (VW != 0) {
+        const int64_t vidx = (int64_t)p.v_offset + r;
+        if (two) load_pair<VW>(p.v_data, vidx, rb.v[i0], rb.v[i0 + 1]);
+        else rb.v[i0] = load_one<VW>(p.v_data, vidx);
+        if (VW == 4 && p.v_signed) { rb.v[i0] = (uint64_t)(int64_t)(int32_t)rb.v[i0]; rb.v[i0 + 1] = (uint64_t)(int64_t)(int32_t)rb.v[i0 + 1]; }
+      }
+      if (p.v_mask != nullptr) {  // COUNT_VALID without a SUM still honours the value column's mask
+        const int64_t vidx = (int64_t)p.v_offset + r;
+        if (!bit_is_set(p.v_mask, vidx)) vvalid &= ~1u;
+        if (two && !bit_is_set(p.v_mask, vidx + 1)) vvalid &= ~2u;
+      }
+      rb.flags |= (present << i0) | (vvalid << (8 + i0));
+    }
+  };
+
+  // ---- slow path of one row: straight into the HBM table (key == EMPTY image, value out of range, table full)
+  auto global_row = [&](uint64_t k, uint64_t v, bool vvalid) {
+    const uint64_t g = find_or_insert(a.table, k, 0);
+    if (g == kNoSlot) { s_abort = 1; return; }
+    if (p.debug) atomicAdd(a.table.status + 4, 1u);
+    if (vvalid) {
+      if (VW != 0 && p.sum_cells) atomicAdd(p.sum_cells + g, (unsigned long long)v);
+      if (p.cntv_cells) atomicAdd(p.cntv_cells + g, 1);
+      if (p.cnta_cells) atomicAdd(p.cnta_cells + g, 1);
+    }
+  };
+
+  // one row: probe / insert in the shared table, then the two shared atomics. Lanes take different numbers of probe
+  // steps; the caller re-joins the warp after every row (__syncwarp) so the next row's LDS/ATOMS issue as full warps.
+  auto process_row = [&](uint64_t k, uint64_t v, bool present, bool vvalid) {
+    if (!present) return;
+    const bool in_range = VW == 0 || ((v + (1ull << m_bits)) >> (m_bits + 1)) == 0;
+    if ((skey_t)k == kSEmpty || !in_range) { global_row(k, v, vvalid); return; }
+    uint32_t slot = __umulhi(hash32(k), S);
+    bool found = false;
+    while (true) {
+      const skey_t cur = *reinterpret_cast<volatile skey_t*>(skeys + slot);
+      if (cur == (skey_t)k) { found = true; break; }
+      if (cur == kSEmpty) {
+        if (*reinterpret_cast<volatile uint32_t*>(&s_fill) >= p.fill_limit) break;  // table full: this row bypasses
+        const skey_t old = atomicCAS(skeys + slot, kSEmpty, (skey_t)k);
+        if (old == kSEmpty) {  // first sight of this key in this CTA: make the group exist in the HBM table right away,
+          atomicAdd(&s_fill, 1u);  // so that groups whose values are all null are not lost and flush may skip idle slots
+          if (find_or_insert(a.table, k, 0) == kNoSlot) s_abort = 1;
+          found = true; break;
+        }
+        if (old == (skey_t)k) { found = true; break; }
+      }
+      slot = slot + 1 == S ? 0 : slot + 1;
+    }
+    if (!found) { global_row(k, v, vvalid); return; }
+    if (!vvalid) return;  // null value: the group exists, nothing to add (device_aggregators.cuh:434-436)
+    uint32_t hi_delta = 0;
+    if (VW != 0) {
+      const uint32_t vlo = (uint32_t)v;
+      const uint32_t old = atomicAdd(slo + slot, vlo);
+      hi_delta = (uint32_t)(v >> 32) + ((uint32_t)(old + vlo) < old ? 1u : 0u);
+    }
+    atomicAdd(shc + slot, (hi_delta << c_bits) + 1u);
+  };
+  auto process = [&](const RowBuf& rb) {
+#pragma unroll
+    for (int i = 0; i < kRowsPerThread; ++i) {
+      process_row(rb.k[i], rb.v[i], (rb.flags >> i) & 1u, (rb.flags >> (8 + i)) & 1u);
+      __syncwarp();
+    }
+  };
+
+  // ---- flush the CTA's partials into the HBM table; CTAs start at different slots so they do not queue on one address
+  auto flush = [&]() {
+    __syncthreads();
+    if (p.debug && threadIdx.x == 0) atomicAdd(a.table.status + 5, 1u);
+    const uint32_t rot = (uint32_t)(((uint64_t)blockIdx.x * S) / gridDim.x);
+    for (uint32_t i = threadIdx.x; i < S; i += kThreads) {
+      uint32_t s = i + rot; if (s >= S) s -= S;
+      const skey_t k = skeys[s];
+      if (k == kSEmpty) continue;
+      const uint32_t hc = shc[s], lo = slo[s];
+      if (hc == 0) continue;  // no valid row since the last flush (the count field is never 0 once a row was added)
+      shc[s] = 0; slo[s] = 0;
+      const uint64_t g = find_or_insert(a.table, (uint64_t)k, 0);
+      if (g == kNoSlot) { s_abort = 1; continue; }
+      const uint32_t cnt = hc & c_mask;
+      if (VW != 0 && p.sum_cells) {
+        const int64_t hi = (int64_t)((int32_t)hc >> c_bits);
+        atomicAdd(p.sum_cells + g, (unsigned long long)(((uint64_t)hi << 32) + lo));
+      }
+      if (p.cntv_cells) atomicAdd(p.cntv_cells + g, (int)cnt);
+      if (p.cnta_cells) atomicAdd(p.cnta_cells + g, (int)cnt);
+    }
+    __syncthreads();
+  };
+
+  RowBuf cur, nxt;
+  int64_t c = blockIdx.x;
+  uint32_t rows_since_flush = 0;
+  if (c < nchunk) load_chunk(c, cur);
+  for (; c < nchunk; c += gridDim.x) {
+    __syncwarp();  // the trip count is block-uniform: re-join lanes that drifted apart in the previous iteration
+    const int64_t cn = c + gridDim.x;
+    if (cn < nchunk) load_chunk(cn, nxt); else nxt.flags = 0;
+    process(cur);
+    cur = nxt;
+    rows_since_flush += kChunk;
+    if (rows_since_flush + kChunk > c_mask) {  // block-uniform: count field would overflow
+      flush();
+      rows_since_flush = 0;
+      if (*reinterpret_cast<volatile int*>(&s_abort)) break;
+    }
+  }
+  flush();
+  if (threadIdx.x == 0 && s_abort) a.table.status[0] = 1;
+}
+
+// ------------------------------------------------------------------ host side
+size_t smem_table_max_bytes()
+{
+  // 227 KB opt-in maximum per CTA minus the static __shared__ words of the kernel
+  return 232448 - 64;
+}
+
+template <int SK, int KEYMODE, int VW>
+static cudaError_t launch_one(const SmemParams& p, int grid, size_t smem, cudaStream_t s)
+{
+  auto kern = agg_smem_kernel<SK, KEYMODE, VW>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  kern<<<grid, kThreads, smem, s>>>(p);
+  return note_launch();
+}
+
+cudaError_t launch_aggregate_smem(const SmemParams& p, int smem_key_bytes, int key_mode, int value_width, int num_sms, cudaStream_t s)
+{
+  if (p.a.num_rows == 0) return cudaSuccess;
+  const size_t smem = (size_t)p.slots * (smem_key_bytes + 8);
+  const int64_t nchunk = (p.a.num_rows + kChunk - 1) / kChunk;
+  const int grid = (int)(nchunk < num_sms ? nchunk : num_sms);
+#define BGB_SMEM_CASE(SK, KM, VW) \
+  if (smem_key_bytes == SK && key_mode == KM && value_width == VW) return launch_one<SK, KM, VW>(p, grid, smem, s);
+  BGB_SMEM_CASE(8, 1, 8) BGB_SMEM_CASE(8, 1, 4) BGB_SMEM_CASE(8, 1, 0)
+  BGB_SMEM_CASE(4, 1, 8) BGB_SMEM_CASE(4, 1, 4) BGB_SMEM_CASE(4, 1, 0)
+  BGB_SMEM_CASE(8, 0, 8) BGB_SMEM_CASE(8, 0, 4) BGB_SMEM_CASE(8, 0, 0)
+  BGB_SMEM_CASE(4, 0, 8) BGB_SMEM_CASE(4, 0, 4) BGB_SMEM_CASE(4, 0, 0)
+#undef BGB_SMEM_CASE
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace bgb
