@@ -52,7 +52,7 @@ SmemEligibility smem_eligibility(const Plan& pl)
 
 static int bit_length(uint64_t x) { int b = 0; while (x) { ++b; x >>= 1; } return b; }
 
-static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint32_t slots)
+static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint32_t slots, uint32_t dense)
 {
   const Plan& pl = *ctx.plan;
   // global table init (keys + every accumulator) with the generic init kernel
@@ -82,7 +82,7 @@ static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint
   sp.cntv_cells = e.cntv_acc >= 0 ? (int*)pl.accs[e.cntv_acc].cells : nullptr;
   sp.cnta_cells = e.cnta_acc >= 0 ? (int*)pl.accs[e.cnta_acc].cells : nullptr;
   sp.slots      = slots;
-  sp.fill_limit = std::min<uint32_t>((uint32_t)(0.85 * slots), slots > 1100 ? slots - 1100 : 0);
+  sp.dense      = dense;
   // count field width c and value range m: a CTA flushes before 2^c rows, partial sums stay below 2^(c+m) <= 2^(63-c)
   int m = e.value_width == 0 ? 0 : bit_length(ctx.max_abs_value) + 1;
   if (e.value_width == 4) m = std::min(m, 31);
@@ -92,7 +92,7 @@ static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint
   sp.debug = getenv("BGB_DEBUG") != nullptr;
   if (sp.debug) {
     cudaMemsetAsync(ctx.table.status + 4, 0, 16, ctx.stream);
-    fprintf(stderr, "[bgb] smem path: slots=%u fill_limit=%u c=%d m=%d g_raw=%.0f max_abs=%llu key_mode=%d sk=%d vw=%d\n", sp.slots, sp.fill_limit,
+    fprintf(stderr, "[bgb] smem path: slots=%u dense=%u c=%d m=%d g_raw=%.0f max_abs=%llu key_mode=%d sk=%d vw=%d\n", sp.slots, sp.dense,
             sp.cnt_bits, sp.val_bits, ctx.g_raw, (unsigned long long)ctx.max_abs_value, e.key_mode, e.smem_key_bytes, e.value_width);
   }
   ctx.prof->begin("aggregate_smem");
@@ -108,11 +108,23 @@ int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path)
   if (ctx.opt.force_path == 1) return BGB_OK;  // generic kernel only
   const SmemEligibility e = smem_eligibility(pl);
   if (e.ok && (ctx.opt.force_path == 0 || ctx.opt.force_path == 2)) {
-    const uint32_t slots_max = (uint32_t)(smem_table_max_bytes() / (e.smem_key_bytes + 8));
-    const bool fits = ctx.g_raw <= 1.2 * slots_max;
+    // split the shared memory between dense group rows (key + 8 B of accumulators) and the 2-byte index slots:
+    // rows for the estimated groups plus slack for insert races, then as many index slots as fit (load factor <= 0.5
+    // whenever the memory allows it)
+    const size_t bytes    = smem_table_max_bytes();
+    const int row_bytes   = e.smem_key_bytes + 8;
+    const double g        = std::max(64.0, ctx.g_raw);
+    const uint32_t d_max  = (uint32_t)std::min<size_t>(65000, (bytes - 2 * 1024) / row_bytes);
+    const bool fits       = 1.02 * g + 256 <= d_max;
     if ((fits && pl.num_rows >= 65536) || ctx.opt.force_path == 2) {
-      uint32_t slots = (uint32_t)std::min<double>(slots_max, std::max(2048.0, std::ceil(2.2 * ctx.g_raw)));
-      int rc = run_smem_path(ctx, e, slots);
+      uint32_t dense = (uint32_t)std::min<double>(d_max, std::ceil(1.08 * g) + 384);
+      uint32_t slots = (uint32_t)std::min<double>((double)((bytes - (size_t)dense * row_bytes) / 2), std::max(4096.0, 4.0 * g));
+      if (slots < 1.25 * dense) {  // cardinality above what one CTA can hold: keep the index sparse enough to terminate
+        dense = (uint32_t)(bytes / (row_bytes + 2.5));
+        slots = (uint32_t)((bytes - (size_t)dense * row_bytes) / 2);
+      }
+      slots &= ~1u;
+      int rc = run_smem_path(ctx, e, slots, dense);
       if (rc) return rc;
       done = true; path = "smem";
       return BGB_OK;

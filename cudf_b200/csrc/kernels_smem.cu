@@ -1,16 +1,21 @@
 // Shared-memory pre-aggregation kernel: the low-cardinality fast path (BASELINE config A / A9 at 1e4 groups).
 //
-// One persistent CTA per SM owns a private open-addressing table in shared memory (up to ~227 KB):
-//   skeys[S]  packed key (4 or 8 bytes), EMPTY = all ones
-//   slo[S]    low 32 bits of the partial int64 SUM
-//   shc[S]    [ high bits of the partial SUM : 32-c | row count : c ]   (one ATOMS.ADD updates both)
+// One persistent CTA per SM owns a private group table in shared memory (up to ~227 KB), laid out for a LOW load factor
+// of the probed structure and DENSE accumulators:
+//   sidx[S]   16-bit open-addressing index (linear probing), entry = dense group id, 0xFFFF = empty   (2 B per slot)
+//   skd[D]    packed key of dense group id (4 or 8 bytes)
+//   slo[D]    low 32 bits of the partial int64 SUM
+//   shc[D]    [ high bits of the partial SUM : 32-c | row count : c ]   (one ATOMS.ADD updates both)
+// With 1e4 groups this gives S = 24K index slots (load 0.41) + 11K dense rows in 227 KB; storing keys and accumulators
+// in the probed slots (16 B each) would cap the table at 14.5K slots (load 0.69), where the longest of a warp's 32
+// linear-probe sequences is ~11 steps (measured with ncu: profiles/r01_smem_kernel_v2_notes.txt).
 // Rows are streamed from HBM with 128-bit coalesced loads, software-pipelined one chunk ahead in registers (the whole
 // shared memory belongs to the table, so there is no room for a TMA staging ring here; the TMA-staged kernels are the
-// tiny-cardinality and partition kernels). Per row: one LDS probe sequence, ATOMS.ADD(lo) with return to catch the
-// carry, ATOMS.ADD(hi|count). 64-bit shared atomics do not exist in hardware (ATOMS.CAST.SPIN loop, 3x slower, see
-// profiles/r01_microbench.txt), hence the split. Values outside [-2^m, 2^m) and the key equal to EMPTY go straight to
-// the HBM table with global atomics, as do keys that no longer fit once the table is `fill_limit` full, so any input is
-// aggregated exactly; the host only routes here when the sampled cardinality says the table will hold the groups.
+// tiny-cardinality and partition kernels). Per row: LDS.U16 index probe + LDS key compare, ATOMS.ADD(lo) with return to
+// catch the carry, ATOMS.ADD(hi|count). 64-bit shared atomics do not exist in hardware (ATOMS.CAST.SPIN loop, 3x
+// slower, see profiles/r01_microbench.txt), hence the split. Values outside [-2^m, 2^m) go straight to the HBM table
+// with global atomics, as do keys that no longer fit once the dense rows are used up, so any input is aggregated
+// exactly; the host only routes here when the sampled cardinality says the table will hold the groups.
 // Partials are flushed into the global table (find-or-insert + RED.ADD) every < 2^c rows per CTA and at the end.
 //
 // Replaces the reference's shared-memory path: compute_mapping_indices + single_pass_shmem_aggs_kernel
@@ -63,17 +68,20 @@ template <int SK, int KEYMODE, int VW>
 __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_constant__ SmemParams p)
 {
   using skey_t = typename SKey<SK>::type;
-  constexpr skey_t kSEmpty = (skey_t)~(skey_t)0;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const uint32_t S = p.slots;
-  skey_t* skeys    = reinterpret_cast<skey_t*>(smem_raw);
-  uint32_t* slo    = reinterpret_cast<uint32_t*>(skeys + S);
-  uint32_t* shc    = slo + S;
-  __shared__ uint32_t s_fill;
+  const uint32_t S = p.slots;   // index slots (even)
+  const uint32_t D = p.dense;   // dense group rows
+  skey_t* skd        = reinterpret_cast<skey_t*>(smem_raw);
+  uint32_t* slo      = reinterpret_cast<uint32_t*>(skd + D);
+  uint32_t* shc      = slo + D;
+  uint32_t* sidx32   = shc + D;  // S/2 words, two 16-bit entries each
+  const uint16_t* sidx16 = reinterpret_cast<const uint16_t*>(sidx32);
+  __shared__ uint32_t s_count;  // dense rows handed out (may exceed D: those inserts bypass)
   __shared__ int s_abort;
 
-  for (uint32_t i = threadIdx.x; i < S; i += kThreads) { skeys[i] = kSEmpty; slo[i] = 0; shc[i] = 0; }
-  if (threadIdx.x == 0) { s_fill = 0; s_abort = 0; }
+  for (uint32_t i = threadIdx.x; i < D; i += kThreads) { slo[i] = 0; shc[i] = 0; }
+  for (uint32_t i = threadIdx.x; i < S / 2; i += kThreads) sidx32[i] = 0xFFFFFFFFu;
+  if (threadIdx.x == 0) { s_count = 0; s_abort = 0; }
   __syncthreads();
 
   const AggParams& a   = p.a;
@@ -158,33 +166,48 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
   auto process_row = [&](uint64_t k, uint64_t v, bool present, bool vvalid) {
     if (!present) return;
     const bool in_range = VW == 0 || ((v + (1ull << m_bits)) >> (m_bits + 1)) == 0;
-    if ((skey_t)k == kSEmpty || !in_range) { global_row(k, v, vvalid); return; }
+    if (!in_range) { global_row(k, v, vvalid); return; }
     uint32_t slot = __umulhi(hash32(k), S);
-    bool found = false;
+    uint32_t id;
     while (true) {
-      const skey_t cur = *reinterpret_cast<volatile skey_t*>(skeys + slot);
-      if (cur == (skey_t)k) { found = true; break; }
-      if (cur == kSEmpty) {
-        if (*reinterpret_cast<volatile uint32_t*>(&s_fill) >= p.fill_limit) break;  // table full: this row bypasses
-        const skey_t old = atomicCAS(skeys + slot, kSEmpty, (skey_t)k);
-        if (old == kSEmpty) {  // first sight of this key in this CTA: make the group exist in the HBM table right away,
-          atomicAdd(&s_fill, 1u);  // so that groups whose values are all null are not lost and flush may skip idle slots
-          if (find_or_insert(a.table, k, 0) == kNoSlot) s_abort = 1;
-          found = true; break;
-        }
-        if (old == (skey_t)k) { found = true; break; }
+      id = *reinterpret_cast<const volatile uint16_t*>(sidx16 + slot);
+      if (id != 0xFFFFu) {
+        if (*reinterpret_cast<volatile skey_t*>(skd + id) == (skey_t)k) break;
+        slot = slot + 1 == S ? 0 : slot + 1;
+        continue;
       }
-      slot = slot + 1 == S ? 0 : slot + 1;
+      // empty index slot: take a dense row, publish the key, then try to claim the slot (16-bit CAS on its 32-bit word)
+      if (*reinterpret_cast<volatile uint32_t*>(&s_count) >= D) { id = 0xFFFFu; break; }  // table full: bypass
+      const uint32_t mine = atomicAdd(&s_count, 1u);
+      if (mine >= D) { id = 0xFFFFu; break; }
+      skd[mine] = (skey_t)k;
+      __threadfence_block();
+      const uint32_t sh = (slot & 1u) * 16u;
+      uint32_t* w  = sidx32 + (slot >> 1);
+      uint32_t cur = *reinterpret_cast<volatile uint32_t*>(w);
+      bool won = false;
+      while (((cur >> sh) & 0xFFFFu) == 0xFFFFu) {
+        const uint32_t want = (cur & ~(0xFFFFu << sh)) | (mine << sh);
+        const uint32_t prev = atomicCAS(w, cur, want);
+        if (prev == cur) { won = true; break; }
+        cur = prev;
+      }
+      if (won) {  // first sight of this key in this CTA: make the group exist in the HBM table right away, so that
+        id = mine;  // groups whose values are all null are not lost and flush may skip idle rows
+        if (find_or_insert(a.table, k, 0) == kNoSlot) s_abort = 1;
+        break;
+      }
+      // lost the slot to another thread (dense row `mine` stays unused: its count is 0, flush skips it); look again
     }
-    if (!found) { global_row(k, v, vvalid); return; }
+    if (id == 0xFFFFu) { global_row(k, v, vvalid); return; }
     if (!vvalid) return;  // null value: the group exists, nothing to add (device_aggregators.cuh:434-436)
     uint32_t hi_delta = 0;
     if (VW != 0) {
       const uint32_t vlo = (uint32_t)v;
-      const uint32_t old = atomicAdd(slo + slot, vlo);
+      const uint32_t old = atomicAdd(slo + id, vlo);
       hi_delta = (uint32_t)(v >> 32) + ((uint32_t)(old + vlo) < old ? 1u : 0u);
     }
-    atomicAdd(shc + slot, (hi_delta << c_bits) + 1u);
+    atomicAdd(shc + id, (hi_delta << c_bits) + 1u);
   };
   auto process = [&](const RowBuf& rb) {
 #pragma unroll
@@ -198,15 +221,14 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
   auto flush = [&]() {
     __syncthreads();
     if (p.debug && threadIdx.x == 0) atomicAdd(a.table.status + 5, 1u);
-    const uint32_t rot = (uint32_t)(((uint64_t)blockIdx.x * S) / gridDim.x);
-    for (uint32_t i = threadIdx.x; i < S; i += kThreads) {
-      uint32_t s = i + rot; if (s >= S) s -= S;
-      const skey_t k = skeys[s];
-      if (k == kSEmpty) continue;
+    const uint32_t used = min(*reinterpret_cast<volatile uint32_t*>(&s_count), D);
+    const uint32_t rot  = used ? (uint32_t)(((uint64_t)blockIdx.x * used) / gridDim.x) : 0;
+    for (uint32_t i = threadIdx.x; i < used; i += kThreads) {
+      uint32_t s = i + rot; if (s >= used) s -= used;
       const uint32_t hc = shc[s], lo = slo[s];
       if (hc == 0) continue;  // no valid row since the last flush (the count field is never 0 once a row was added)
       shc[s] = 0; slo[s] = 0;
-      const uint64_t g = find_or_insert(a.table, (uint64_t)k, 0);
+      const uint64_t g = find_or_insert(a.table, (uint64_t)skd[s], 0);
       if (g == kNoSlot) { s_abort = 1; continue; }
       const uint32_t cnt = hc & c_mask;
       if (VW != 0 && p.sum_cells) {
@@ -241,6 +263,11 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
 }
 
 // ------------------------------------------------------------------ host side
+size_t smem_table_bytes(uint32_t slots, uint32_t dense, int smem_key_bytes)
+{
+  return (size_t)dense * (smem_key_bytes + 8) + (size_t)slots * 2;
+}
+
 size_t smem_table_max_bytes()
 {
   // 227 KB opt-in maximum per CTA minus the static __shared__ words of the kernel
@@ -260,7 +287,7 @@ static cudaError_t launch_one(const SmemParams& p, int grid, size_t smem, cudaSt
 cudaError_t launch_aggregate_smem(const SmemParams& p, int smem_key_bytes, int key_mode, int value_width, int num_sms, cudaStream_t s)
 {
   if (p.a.num_rows == 0) return cudaSuccess;
-  const size_t smem = (size_t)p.slots * (smem_key_bytes + 8);
+  const size_t smem = smem_table_bytes(p.slots, p.dense, smem_key_bytes);
   const int64_t nchunk = (p.a.num_rows + kChunk - 1) / kChunk;
   const int grid = (int)(nchunk < num_sms ? nchunk : num_sms);
 #define BGB_SMEM_CASE(SK, KM, VW) \
