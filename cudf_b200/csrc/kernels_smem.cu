@@ -62,6 +62,89 @@ struct RowBuf {
   uint32_t flags;  // bit i: row i present and key usable; bit 8+i: value valid
 };
 
+
+// ---- shared-window accessors on 32-bit addresses (keeps the probe loop free of generic->shared address arithmetic)
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr)
+{
+  uint32_t v;
+  asm volatile("ld.volatile.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr)
+{
+  uint32_t v;
+  asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t lds_u64(uint32_t addr)
+{
+  uint64_t v;
+  asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(v) : "r"(addr) : "memory");
+  return v;
+}
+template <int SK>
+__device__ __forceinline__ uint64_t lds_key(uint32_t addr) { return SK == 8 ? lds_u64(addr) : (uint64_t)lds_u32(addr); }
+__device__ __forceinline__ uint32_t atoms_add_ret(uint32_t addr, uint32_t v)
+{
+  uint32_t old;
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(addr), "r"(v) : "memory");
+  return old;
+}
+__device__ __forceinline__ void atoms_add(uint32_t addr, uint32_t v)
+{
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+constexpr uint32_t kIdEmpty  = 0xFFFFu;   // index entry: slot free
+constexpr uint32_t kIdBypass = 0x10000u;  // row result: handled through the HBM table
+constexpr uint32_t kIdSkip   = 0x10001u;  // row result: nothing to do
+
+// slow path of one row: straight into the HBM table (value out of range, table full)
+__device__ __noinline__ void smem_global_row(const SmemParams& p, uint64_t k, uint64_t v, bool vvalid, bool has_sum, int* s_abort)
+{
+  const uint64_t g = find_or_insert(p.a.table, k, 0);
+  if (g == kNoSlot) { *s_abort = 1; return; }
+  if (p.debug) atomicAdd(p.a.table.status + 4, 1u);
+  if (vvalid) {
+    if (has_sum && p.sum_cells) atomicAdd(p.sum_cells + g, (unsigned long long)v);
+    if (p.cntv_cells) atomicAdd(p.cntv_cells + g, 1);
+    if (p.cnta_cells) atomicAdd(p.cnta_cells + g, 1);
+  }
+}
+
+// empty index slot seen while probing for k: take a dense row, publish the key, then try to claim the slot (16-bit CAS
+// on its 32-bit word). Returns the dense id, kIdBypass when the table is full, or kIdEmpty when the slot was lost to
+// another thread (the caller looks at the slot again; dense row `mine` stays unused, its count is 0, flush skips it).
+template <int SK>
+__device__ __noinline__ uint32_t smem_insert_key(const SmemParams& p, uint64_t k, uint32_t slot_addr, uint32_t kd_a, uint32_t* s_count,
+                                                 int* s_abort)
+{
+  const uint32_t D = p.dense;
+  if (*reinterpret_cast<volatile uint32_t*>(s_count) >= D) return kIdBypass;
+  const uint32_t mine = atomicAdd(s_count, 1u);
+  if (mine >= D) return kIdBypass;
+  if (SK == 8) asm volatile("st.shared.u64 [%0], %1;" ::"r"(kd_a + mine * 8), "l"(k) : "memory");
+  else asm volatile("st.shared.u32 [%0], %1;" ::"r"(kd_a + mine * 4), "r"((uint32_t)k) : "memory");
+  __threadfence_block();
+  const uint32_t sh = (slot_addr & 2u) * 8u;
+  const uint32_t w  = slot_addr & ~3u;
+  uint32_t cur = lds_u32(w);
+  while (((cur >> sh) & 0xFFFFu) == kIdEmpty) {
+    const uint32_t want = (cur & ~(0xFFFFu << sh)) | (mine << sh);
+    uint32_t prev;
+    asm volatile("atom.shared.cas.b32 %0, [%1], %2, %3;" : "=r"(prev) : "r"(w), "r"(cur), "r"(want) : "memory");
+    if (prev == cur) {
+      // first sight of this key in this CTA: make the group exist in the HBM table right away, so that groups whose
+      // values are all null are not lost and flush may skip idle rows
+      if (find_or_insert(p.a.table, k, 0) == kNoSlot) *s_abort = 1;
+      return mine;
+    }
+    cur = prev;
+  }
+  return kIdEmpty;
+}
+
 }  // namespace
 
 template <int SK, int KEYMODE, int VW>
@@ -75,7 +158,6 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
   uint32_t* slo      = reinterpret_cast<uint32_t*>(skd + D);
   uint32_t* shc      = slo + D;
   uint32_t* sidx32   = shc + D;  // S/2 words, two 16-bit entries each
-  const uint16_t* sidx16 = reinterpret_cast<const uint16_t*>(sidx32);
   __shared__ uint32_t s_count;  // dense rows handed out (may exceed D: those inserts bypass)
   __shared__ int s_abort;
 
@@ -149,71 +231,55 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
     }
   };
 
-  // ---- slow path of one row: straight into the HBM table (key == EMPTY image, value out of range, table full)
-  auto global_row = [&](uint64_t k, uint64_t v, bool vvalid) {
-    const uint64_t g = find_or_insert(a.table, k, 0);
-    if (g == kNoSlot) { s_abort = 1; return; }
-    if (p.debug) atomicAdd(a.table.status + 4, 1u);
-    if (vvalid) {
-      if (VW != 0 && p.sum_cells) atomicAdd(p.sum_cells + g, (unsigned long long)v);
-      if (p.cntv_cells) atomicAdd(p.cntv_cells + g, 1);
-      if (p.cnta_cells) atomicAdd(p.cnta_cells + g, 1);
-    }
-  };
+  uint32_t kd_a = smem_addr(skd), lo_a = smem_addr(slo), hc_a = smem_addr(shc), idx_a = smem_addr(sidx32);
+  uint32_t idx_end = idx_a + 2 * S;
+  // pin the window addresses in registers (otherwise they are re-derived from SR_CgaCtaId inside the probe loop)
+  asm volatile("" : "+r"(kd_a), "+r"(lo_a), "+r"(hc_a), "+r"(idx_a), "+r"(idx_end));
+  const uint64_t m_bias  = 1ull << m_bits;
 
-  // one row: probe / insert in the shared table, then the two shared atomics. Lanes take different numbers of probe
-  // steps; the caller re-joins the warp after every row (__syncwarp) so the next row's LDS/ATOMS issue as full warps.
-  auto process_row = [&](uint64_t k, uint64_t v, bool present, bool vvalid) {
-    if (!present) return;
-    const bool in_range = VW == 0 || ((v + (1ull << m_bits)) >> (m_bits + 1)) == 0;
-    if (!in_range) { global_row(k, v, vvalid); return; }
-    uint32_t slot = __umulhi(hash32(k), S);
-    uint32_t id;
-    while (true) {
-      id = *reinterpret_cast<const volatile uint16_t*>(sidx16 + slot);
-      if (id != 0xFFFFu) {
-        if (*reinterpret_cast<volatile skey_t*>(skd + id) == (skey_t)k) break;
-        slot = slot + 1 == S ? 0 : slot + 1;
-        continue;
-      }
-      // empty index slot: take a dense row, publish the key, then try to claim the slot (16-bit CAS on its 32-bit word)
-      if (*reinterpret_cast<volatile uint32_t*>(&s_count) >= D) { id = 0xFFFFu; break; }  // table full: bypass
-      const uint32_t mine = atomicAdd(&s_count, 1u);
-      if (mine >= D) { id = 0xFFFFu; break; }
-      skd[mine] = (skey_t)k;
-      __threadfence_block();
-      const uint32_t sh = (slot & 1u) * 16u;
-      uint32_t* w  = sidx32 + (slot >> 1);
-      uint32_t cur = *reinterpret_cast<volatile uint32_t*>(w);
-      bool won = false;
-      while (((cur >> sh) & 0xFFFFu) == 0xFFFFu) {
-        const uint32_t want = (cur & ~(0xFFFFu << sh)) | (mine << sh);
-        const uint32_t prev = atomicCAS(w, cur, want);
-        if (prev == cur) { won = true; break; }
-        cur = prev;
-      }
-      if (won) {  // first sight of this key in this CTA: make the group exist in the HBM table right away, so that
-        id = mine;  // groups whose values are all null are not lost and flush may skip idle rows
-        if (find_or_insert(a.table, k, 0) == kNoSlot) s_abort = 1;
-        break;
-      }
-      // lost the slot to another thread (dense row `mine` stays unused: its count is 0, flush skips it); look again
-    }
-    if (id == 0xFFFFu) { global_row(k, v, vvalid); return; }
-    if (!vvalid) return;  // null value: the group exists, nothing to add (device_aggregators.cuh:434-436)
-    uint32_t hi_delta = 0;
-    if (VW != 0) {
-      const uint32_t vlo = (uint32_t)v;
-      const uint32_t old = atomicAdd(slo + id, vlo);
-      hi_delta = (uint32_t)(v >> 32) + ((uint32_t)(old + vlo) < old ? 1u : 0u);
-    }
-    atomicAdd(shc + id, (hi_delta << c_bits) + 1u);
-  };
+  // ---- one chunk: (1) every lane finds the dense id of each of its rows (divergent probe loops, inserts and bypasses
+  // are rare), (2) the warp re-joins, (3) the shared atomics of all rows issue as full warps
   auto process = [&](const RowBuf& rb) {
+    uint32_t id[kRowsPerThread];
 #pragma unroll
     for (int i = 0; i < kRowsPerThread; ++i) {
-      process_row(rb.k[i], rb.v[i], (rb.flags >> i) & 1u, (rb.flags >> (8 + i)) & 1u);
-      __syncwarp();
+      const uint64_t k = rb.k[i], v = rb.v[i];
+      const bool present = (rb.flags >> i) & 1u, vvalid = (rb.flags >> (8 + i)) & 1u;
+      id[i] = kIdSkip;
+      if (present) {
+        const bool in_range = VW == 0 || ((v + m_bias) >> (m_bits + 1)) == 0;
+        if (!in_range) { smem_global_row(p, k, v, vvalid, VW != 0, &s_abort); }
+        else {
+          uint32_t sa = idx_a + 2 * __umulhi(hash32(k), S);
+          uint32_t e;
+          while (true) {
+            e = lds_u16(sa);
+            if (e == kIdEmpty) {
+              e = smem_insert_key<SK>(p, k, sa, kd_a, &s_count, &s_abort);
+              if (e == kIdEmpty) continue;  // slot taken meanwhile: look at it again
+              break;
+            }
+            if (lds_key<SK>(kd_a + e * SK) == (SK == 8 ? k : (uint64_t)(uint32_t)k)) break;
+            sa += 2;
+            if (sa == idx_end) sa = idx_a;
+          }
+          if (e == kIdBypass) smem_global_row(p, k, v, vvalid, VW != 0, &s_abort);
+          else if (vvalid) id[i] = e;  // null value: the group exists, nothing to add (device_aggregators.cuh:434-436)
+        }
+      }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < kRowsPerThread; ++i) {
+      if (id[i] < kIdEmpty) {
+        uint32_t hi_delta = 0;
+        if (VW != 0) {
+          const uint32_t vlo = (uint32_t)rb.v[i];
+          const uint32_t old = atoms_add_ret(lo_a + id[i] * 4, vlo);
+          hi_delta = (uint32_t)(rb.v[i] >> 32) + ((uint32_t)(old + vlo) < old ? 1u : 0u);
+        }
+        atoms_add(hc_a + id[i] * 4, (hi_delta << c_bits) + 1u);
+      }
     }
   };
 
