@@ -220,37 +220,40 @@ def run_reference_arm(args):
 
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
+    """One long-running `nvidia-smi -lms` child started BEFORE the timed region (spawning a process inside it would
+    steal host time from the steps); its output is parsed after the region ends."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
         self.index = index
-        self.samples = []
-        self._stop = threading.Event()
-        self._t = None
-
-    def _run(self):
-        while not self._stop.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.splitlines()[0].split(",")])
-            except Exception:
-                pass
-            self._stop.wait(0.1)
+        self.proc = None
+        self.t_start = None
 
     def start(self):
-        self._t = threading.Thread(target=self._run, daemon=True)
-        self._t.start()
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            time.sleep(0.3)  # let it print its first sample before the timed region starts
+        except Exception:
+            self.proc = None
+
+    def mark(self):
+        self.t_start = time.time()
 
     def stop(self):
-        self._stop.set()
-        if self._t:
-            self._t.join(timeout=6)
+        out = ""
+        if self.proc is not None:
+            time.sleep(0.12)
+            self.proc.terminate()
+            try:
+                out, _ = self.proc.communicate(timeout=5)
+            except Exception:
+                self.proc.kill()
         sm, mx, reasons = [], 0.0, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for smp in self.samples:
+        for line in out.splitlines():
+            smp = [x.strip() for x in line.split(",")]
             try:
                 sm.append(float(smp[0])); mx = max(mx, float(smp[1]))
                 for nm, val in zip(names, smp[3:7]):
@@ -258,6 +261,7 @@ class ClockSampler:
                         reasons.add(nm)
             except Exception:
                 continue
+        # the samples span a little more than the timed region (start-up + tail): the maximum-load ones are what matter
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
                 "samples": len(sm)}
 

@@ -68,7 +68,8 @@ struct AccDesc {
 struct TableDesc {
   uint64_t* keys;         // 64-bit keys, or 128-bit keys as pairs when key_words == 2
   uint64_t capacity;      // power of two
-  uint32_t* status;       // [0] overflow flag, [1] number of groups (written by compaction)
+  uint32_t* status;       // 16 words: [0] overflow flag, [1] number of groups (written by compaction), [2] reserved slot used,
+                          // [4..5] debug counters, [8..15] cardinality estimator outputs
   int32_t key_words;      // 1 or 2
 };
 
@@ -144,7 +145,7 @@ __host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t seed, uint64_t 
 cudaError_t launch_init_table(const AggParams& p, cudaStream_t s);
 cudaError_t launch_aggregate_global(const AggParams& p, cudaStream_t s);
 cudaError_t launch_estimate_cardinality(const AggParams& p, int64_t sample_rows, uint64_t* scratch_set, uint64_t set_capacity,
-                                        uint32_t* out_distinct, cudaStream_t s);
+                                        uint32_t* out_distinct /* 8 words */, uint64_t key_flip, cudaStream_t s);
 // compaction: fills group_slots[] with occupied slot ids (arbitrary order), status[1] = count
 cudaError_t launch_compact(const TableDesc& t, uint32_t* group_slots, uint32_t* scan_state, cudaStream_t s);
 size_t compact_scan_state_bytes(uint64_t capacity);

@@ -46,13 +46,19 @@ SmemEligibility smem_eligibility(const Plan& pl)
   } else {
     e.key_mode = 0; e.smem_key_bytes = key_bits <= 32 ? 4 : 8;
   }
+  e.integer_keys = true;
+  for (const KeyPlan& k : pl.keys) if (k.fclass != 0) e.integer_keys = false;
+  if (pl.keys.size() == 1 && k0.null_bit < 0) {
+    const uint8_t src = type_src(k0.v.type_id);
+    if (src == S_I8 || src == S_I16 || src == S_I32 || src == S_I64) e.key_flip = 1ull << (8 * k0.width - 1);
+  }
   e.ok = true;
   return e;
 }
 
 static int bit_length(uint64_t x) { int b = 0; while (x) { ++b; x >>= 1; } return b; }
 
-static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint32_t slots, uint32_t dense)
+static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint32_t slots, uint32_t dense, bool direct, uint64_t key_base)
 {
   const Plan& pl = *ctx.plan;
   // global table init (keys + every accumulator) with the generic init kernel
@@ -83,6 +89,9 @@ static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint
   sp.cnta_cells = e.cnta_acc >= 0 ? (int*)pl.accs[e.cnta_acc].cells : nullptr;
   sp.slots      = slots;
   sp.dense      = dense;
+  sp.direct     = direct;
+  sp.key_flip   = e.key_flip;
+  sp.key_base   = key_base;
   // count field width c and value range m: a CTA flushes before 2^c rows, partial sums stay below 2^(c+m) <= 2^(63-c)
   int m = e.value_width == 0 ? 0 : bit_length(ctx.max_abs_value) + 1;
   if (e.value_width == 4) m = std::min(m, 31);
@@ -92,7 +101,7 @@ static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint
   sp.debug = getenv("BGB_DEBUG") != nullptr;
   if (sp.debug) {
     cudaMemsetAsync(ctx.table.status + 4, 0, 16, ctx.stream);
-    fprintf(stderr, "[bgb] smem path: slots=%u dense=%u c=%d m=%d g_raw=%.0f max_abs=%llu key_mode=%d sk=%d vw=%d\n", sp.slots, sp.dense,
+    fprintf(stderr, "[bgb] smem path: direct=%d slots=%u dense=%u c=%d m=%d g_raw=%.0f max_abs=%llu key_mode=%d sk=%d vw=%d\n", (int)direct, sp.slots, sp.dense,
             sp.cnt_bits, sp.val_bits, ctx.g_raw, (unsigned long long)ctx.max_abs_value, e.key_mode, e.smem_key_bytes, e.value_width);
   }
   ctx.prof->begin("aggregate_smem");
@@ -107,11 +116,25 @@ int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path)
   const Plan& pl = *ctx.plan;
   if (ctx.opt.force_path == 1) return BGB_OK;  // generic kernel only
   const SmemEligibility e = smem_eligibility(pl);
-  if (e.ok && (ctx.opt.force_path == 0 || ctx.opt.force_path == 2)) {
-    // split the shared memory between dense group rows (key + 8 B of accumulators) and the 2-byte index slots:
-    // rows for the estimated groups plus slack for insert races, then as many index slots as fit (load factor <= 0.5
-    // whenever the memory allows it)
-    const size_t bytes    = smem_table_max_bytes();
+  if (e.ok && (ctx.opt.force_path == 0 || ctx.opt.force_path == 2 || ctx.opt.force_path == 4)) {
+    const size_t bytes = smem_table_max_bytes();
+    // (a) direct addressing: integer keys whose sampled range fits -> dense id = key - min, no probing at all. Keys
+    //     outside [min - pad, min - pad + rows) (the sample can miss the extremes) take the global-atomic bypass.
+    const uint32_t direct_rows_max = (uint32_t)((bytes - 1024) * 32 / (8 * 32 + 4));
+    const bool range_known = ctx.key_min <= ctx.key_max;
+    const uint64_t range   = range_known ? ctx.key_max - ctx.key_min + 1 : ~0ull;
+    if (e.integer_keys && range_known && range <= direct_rows_max && pl.num_rows >= 65536 && ctx.opt.force_path != 2) {
+      const uint64_t pad  = std::min<uint64_t>({(uint64_t)64, (direct_rows_max - range) / 2, ctx.key_min});
+      const uint64_t base = ctx.key_min - pad;
+      const uint32_t rows = (uint32_t)std::min<uint64_t>(direct_rows_max, range + 2 * pad + 64);
+      int rc = run_smem_path(ctx, e, 0, rows, true, base);
+      if (rc) return rc;
+      done = true; path = "smem-direct";
+      return BGB_OK;
+    }
+    // (b) hashed: split the shared memory between dense group rows (key + 8 B of accumulators) and the 2-byte index
+    //     slots: rows for the estimated groups plus slack for insert races, then as many index slots as fit (load
+    //     factor <= 0.5 whenever the memory allows it)
     const int row_bytes   = e.smem_key_bytes + 8;
     const double g        = std::max(64.0, ctx.g_raw);
     const uint32_t d_max  = (uint32_t)std::min<size_t>(65000, (bytes - 2 * 1024) / row_bytes);
@@ -124,7 +147,7 @@ int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path)
         slots = (uint32_t)((bytes - (size_t)dense * row_bytes) / 2);
       }
       slots &= ~1u;
-      int rc = run_smem_path(ctx, e, slots, dense);
+      int rc = run_smem_path(ctx, e, slots, dense, false, 0);
       if (rc) return rc;
       done = true; path = "smem";
       return BGB_OK;

@@ -14,6 +14,7 @@ struct BuildContext {
   bgb_options opt;
   double g_raw;             // sampled cardinality estimate (no safety factor)
   uint64_t max_abs_value;   // largest |v| among the sampled rows of the SUM column (0 when not sampled)
+  uint64_t key_min, key_max;  // sampled range of the order-preserving key image (min > max: not sampled)
   cudaStream_t stream;
   Profiler* prof;
   int num_sms;
@@ -24,6 +25,8 @@ struct SmemEligibility {
   bool ok = false;
   int value_col = -1, sum_acc = -1, cntv_acc = -1, cnta_acc = -1;
   int key_mode = 0, smem_key_bytes = 8, value_width = 0;
+  bool integer_keys = false;   // every key column is an integer type: the packed key has a meaningful numeric range
+  uint64_t key_flip = 0;       // sign bit of a single signed key column (makes the image order-preserving)
 };
 SmemEligibility smem_eligibility(const Plan& plan);
 

@@ -124,7 +124,7 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     if (rc_ != BGB_OK) { h->free_all(); delete h; return rc_; } \
   } while (0)
 
-  uint32_t* status = (uint32_t*)h->dalloc(8 * sizeof(uint32_t));
+  uint32_t* status = (uint32_t*)h->dalloc(16 * sizeof(uint32_t));
   if (!status) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "status alloc"));
   h->table.status    = status;
   h->table.key_words = pl.key_words;
@@ -133,7 +133,7 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
   const uint64_t cap_max = next_pow2((uint64_t)(2 * N < 1024 ? 1024 : 2 * N));
   uint64_t capacity      = 0;
   double g_est           = (double)N, g_raw = (double)N;
-  uint64_t max_abs       = ~0ull;
+  uint64_t max_abs       = ~0ull, key_min = 1, key_max = 0;  // key_min > key_max: range not sampled
   int num_sms            = 148;
   { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev); }
   if (opt.capacity_log2 > 0) capacity = 1ull << opt.capacity_log2;
@@ -152,15 +152,17 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
       ep.acc[0].data = (const uint8_t*)v.v.data; ep.acc[0].mask = v.v.null_mask; ep.acc[0].offset = v.v.offset; ep.acc[0].src = v.src;
     }
     h->prof.begin("estimate_cardinality");
-    FAIL_RC(check_cuda(launch_estimate_cardinality(ep, sample, set, setcap, status + 4, s), "estimate"));
+    FAIL_RC(check_cuda(launch_estimate_cardinality(ep, sample, set, setcap, status + 8, se.key_flip, s), "estimate"));
     h->prof.end();
-    uint32_t est[4] = {0, 0, 0, 0};
-    FAIL_RC(check_cuda(cudaMemcpyAsync(est, status + 4, sizeof est, cudaMemcpyDeviceToHost, s), "estimate copy"));
+    uint32_t est[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    FAIL_RC(check_cuda(cudaMemcpyAsync(est, status + 8, sizeof est, cudaMemcpyDeviceToHost, s), "estimate copy"));
     FAIL_RC(check_cuda(cudaStreamSynchronize(s), "estimate sync"));
     h->prof.resolve();
     h->dfree(set);
     const double d = est[0], m = est[1];
     max_abs = (uint64_t)est[2] | ((uint64_t)est[3] << 32);
+    key_min = (uint64_t)est[4] | ((uint64_t)est[5] << 32);
+    key_max = (uint64_t)est[6] | ((uint64_t)est[7] << 32);
     if (m == 0) g_raw = 1;
     else if (d > 0.9 * m) g_raw = (double)N;  // nearly all sampled keys distinct: cardinality unknown, assume the worst
     else g_raw = std::min((double)N, solve_cardinality(d, m));
@@ -181,7 +183,7 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     // init + aggregate, kMaxAccs accumulators per launch (the first launch also initialises the keys)
     std::string path;
     bool done = false;
-    BuildContext ctx{&pl, h->table, opt, g_raw, max_abs, s, &h->prof, num_sms};
+    BuildContext ctx{&pl, h->table, opt, g_raw, max_abs, key_min, key_max, s, &h->prof, num_sms};
     FAIL_RC(try_fast_paths(ctx, done, path));
     if (!done) {
       size_t na = pl.accs.size();
@@ -226,6 +228,7 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     capacity = cap_max;
     g_est    = (double)N;
     g_raw    = (double)N;
+    key_min = 1; key_max = 0;
   }
 #undef FAIL_RC
   *num_groups = h->num_groups;

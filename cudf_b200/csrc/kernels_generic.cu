@@ -121,54 +121,77 @@ cudaError_t launch_aggregate_global(const AggParams& p, cudaStream_t s)
 // ------------------------------------------------------------------ cardinality estimator
 // Inserts the packed keys of `sample_rows` evenly spaced rows into a scratch set; out[0] = distinct, out[1] = sampled
 // rows that were not skipped. Only a regime hint: correctness never depends on it (overflow -> host retries bigger).
-__global__ void __launch_bounds__(256) estimate_kernel(const __grid_constant__ AggParams p, int64_t sample_rows, int64_t step,
-                                                       uint64_t* set, uint64_t set_capacity, uint32_t* out)
+__device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v)
 {
-  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= sample_rows) return;
-  int64_t row = t * step;
-  if (row >= p.num_rows) return;
-  uint64_t k0, k1;
-  if (!pack_key(p, row, k0, k1)) return;
-  atomicAdd(out + 1, 1u);
-  if (p.num_accs == 1 && p.acc[0].data != nullptr) {  // magnitude of the sampled integer SUM inputs (sizes the smem count field)
-    const AccDesc& a = p.acc[0];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { unsigned long long w = __shfl_xor_sync(0xffffffffu, v, o); v = w > v ? w : v; }
+  return v;
+}
+
+__global__ void __launch_bounds__(256) estimate_kernel(const __grid_constant__ AggParams p, int64_t sample_rows, int64_t step,
+                                                       uint64_t* set, uint64_t set_capacity, uint32_t* out, uint64_t key_flip)
+{
+  const int64_t t   = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t row = t * step;
+  uint64_t k0 = 0, k1 = 0;
+  const bool live = t < sample_rows && row < p.num_rows && pack_key(p, row, k0, k1);
+  // per-warp reductions first: one atomic per warp instead of one per sampled row
+  unsigned long long kimg = live && p.table.key_words == 1 ? (unsigned long long)(k0 ^ key_flip) : 0ull;
+  unsigned long long mag  = 0;
+  if (live && p.num_accs == 1 && p.acc[0].data != nullptr) {  // magnitude of the sampled integer SUM inputs (sizes the smem count field)
+    const AccDesc& a  = p.acc[0];
     const int64_t idx = (int64_t)a.offset + row;
     if (a.mask == nullptr || bit_is_set(a.mask, idx)) {
       const int64_t v = raw_to_i64(load_raw(a.data, src_width(a.src), idx), a.src);
-      const unsigned long long mag = v < 0 ? ~(unsigned long long)v : (unsigned long long)v;
-      if (mag) atomicMax(reinterpret_cast<unsigned long long*>(out + 2), mag);
+      mag             = v < 0 ? ~(unsigned long long)v : (unsigned long long)v;
     }
   }
+  const unsigned long long wmax = warp_max_u64(kimg);
+  const unsigned long long wmin = ~warp_max_u64(live && p.table.key_words == 1 ? ~kimg : 0ull);
+  const unsigned long long wmag = warp_max_u64(mag);
+  const uint32_t nlive          = __popc(__ballot_sync(0xffffffffu, live));
+  if ((threadIdx.x & 31) == 0 && nlive) {
+    atomicAdd(out + 1, nlive);
+    if (p.table.key_words == 1) {  // range of the order-preserving key image (direct-address eligibility)
+      atomicMin(reinterpret_cast<unsigned long long*>(out + 4), wmin);
+      atomicMax(reinterpret_cast<unsigned long long*>(out + 6), wmax);
+    }
+    if (wmag) atomicMax(reinterpret_cast<unsigned long long*>(out + 2), wmag);
+  }
+  if (!live) return;
   uint64_t f = hash_key(k0, k1, p.table.key_words);
   if (f == kEmpty) f = 0;
   uint64_t slot = mix64(f) & (set_capacity - 1);
   unsigned long long* s = reinterpret_cast<unsigned long long*>(set);
+  uint32_t fresh = 0;
   for (uint64_t probes = 0; probes < set_capacity; ++probes) {
     unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(s + slot);
-    if (cur == f) return;
+    if (cur == f) break;
     if (cur == kEmpty) {
       unsigned long long old = atomicCAS(s + slot, (unsigned long long)kEmpty, (unsigned long long)f);
-      if (old == kEmpty) { atomicAdd(out, 1u); return; }
-      if (old == f) return;
+      if (old == kEmpty) { fresh = 1; break; }
+      if (old == f) break;
     }
     slot = (slot + 1) & (set_capacity - 1);
   }
+  if (fresh) atomicAdd(out, 1u);  // (ptxas aggregates this per warp)
 }
 
 cudaError_t launch_estimate_cardinality(const AggParams& p, int64_t sample_rows, uint64_t* scratch_set, uint64_t set_capacity,
-                                        uint32_t* out_distinct, cudaStream_t s)
+                                        uint32_t* out_distinct, uint64_t key_flip, cudaStream_t s)
 {
   cudaError_t e = cudaMemsetAsync(scratch_set, 0xff, set_capacity * sizeof(uint64_t), s);
   if (e != cudaSuccess) return e;
-  e = cudaMemsetAsync(out_distinct, 0, 4 * sizeof(uint32_t), s);
+  e = cudaMemsetAsync(out_distinct, 0, 8 * sizeof(uint32_t), s);
+  if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(out_distinct + 4, 0xff, 2 * sizeof(uint32_t), s);  // running minimum starts at all ones
   if (e != cudaSuccess) return e;
   if (sample_rows > p.num_rows) sample_rows = p.num_rows;
   if (sample_rows <= 0) return cudaSuccess;
   int64_t step = p.num_rows / sample_rows;
   if (step < 1) step = 1;
   int blocks = (int)((sample_rows + 255) / 256);
-  estimate_kernel<<<blocks, 256, 0, s>>>(p, sample_rows, step, scratch_set, set_capacity, out_distinct);
+  estimate_kernel<<<blocks, 256, 0, s>>>(p, sample_rows, step, scratch_set, set_capacity, out_distinct, key_flip);
   return note_launch();
 }
 

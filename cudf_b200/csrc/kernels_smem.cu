@@ -21,6 +21,8 @@
 // Replaces the reference's shared-memory path: compute_mapping_indices + single_pass_shmem_aggs_kernel
 // (/root/reference/cpp/src/groupby/hash/compute_mapping_indices.cuh:23-151,
 //  /root/reference/cpp/src/groupby/hash/compute_shared_memory_aggs.cu:121-353), which caps out at 128 groups per block.
+#include <type_traits>
+
 #include "device_utils.cuh"
 #include "kernels_smem.h"
 
@@ -28,15 +30,16 @@ namespace bgb {
 
 namespace {
 
-constexpr int kThreads      = 1024;
+constexpr int kThreads      = 1024;  // 32 warps: the per-row dependency chain (LDS -> LDS -> ATOMS) is hidden by warps, not ILP
 constexpr int kRowsPerThread = 4;
 constexpr int kChunk        = kThreads * kRowsPerThread;
 
+// 32-bit mix whose HIGH bits select the slot (slot = umulhi(h, S)): two multiplies and one xor-shift
 __device__ __forceinline__ uint32_t hash32(uint64_t k)
 {
-  uint32_t h = (uint32_t)k ^ ((uint32_t)(k >> 32) * 0x85EBCA6Bu);
-  h ^= h >> 16; h *= 0x7FEB352Du; h ^= h >> 15; h *= 0x846CA68Bu; h ^= h >> 16;
-  return h;
+  uint32_t h = ((uint32_t)k ^ ((uint32_t)(k >> 32) * 0x85EBCA6Bu)) * 0x9E3779B1u;
+  h ^= h >> 15;
+  return h * 0x2C1B3C6Du;
 }
 
 template <int W>
@@ -147,22 +150,24 @@ __device__ __noinline__ uint32_t smem_insert_key(const SmemParams& p, uint64_t k
 
 }  // namespace
 
-template <int SK, int KEYMODE, int VW>
+template <int SK, int KEYMODE, int VW, bool DIRECT>
 __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_constant__ SmemParams p)
 {
   using skey_t = typename SKey<SK>::type;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const uint32_t S = p.slots;   // index slots (even)
   const uint32_t D = p.dense;   // dense group rows
+  // hashed mode: skd[D] | slo[D] | shc[D] | sidx[S];  direct mode (dense id = key - key_base): slo[D] | shc[D] | seen[D/32]
   skey_t* skd        = reinterpret_cast<skey_t*>(smem_raw);
-  uint32_t* slo      = reinterpret_cast<uint32_t*>(skd + D);
+  uint32_t* slo      = DIRECT ? reinterpret_cast<uint32_t*>(smem_raw) : reinterpret_cast<uint32_t*>(skd + D);
   uint32_t* shc      = slo + D;
-  uint32_t* sidx32   = shc + D;  // S/2 words, two 16-bit entries each
+  uint32_t* sidx32   = shc + D;  // hashed: S/2 words, two 16-bit entries each; direct: "group seen" bitmap
   __shared__ uint32_t s_count;  // dense rows handed out (may exceed D: those inserts bypass)
   __shared__ int s_abort;
 
   for (uint32_t i = threadIdx.x; i < D; i += kThreads) { slo[i] = 0; shc[i] = 0; }
-  for (uint32_t i = threadIdx.x; i < S / 2; i += kThreads) sidx32[i] = 0xFFFFFFFFu;
+  if (DIRECT) { for (uint32_t i = threadIdx.x; i < (D + 31) / 32; i += kThreads) sidx32[i] = 0; }
+  else { for (uint32_t i = threadIdx.x; i < S / 2; i += kThreads) sidx32[i] = 0xFFFFFFFFu; }
   if (threadIdx.x == 0) { s_count = 0; s_abort = 0; }
   __syncthreads();
 
@@ -174,26 +179,25 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
   const int m_bits     = p.val_bits;
   const KeyColDesc kc0 = a.kc[0];
 
-  // ---- chunk loader: thread t owns rows {2t, 2t+1} of each half-chunk, so every load is a 16-byte (or 8-byte) vector
-  auto load_chunk = [&](int64_t c, RowBuf& rb) {
+  // ---- chunk loader: thread t owns rows {2t, 2t+1} of each 2*kThreads-row slice, so every load is a 16-byte (or
+  // 8-byte) vector. `full` (block-uniform) = the chunk lies entirely inside the column: no bounds logic on that path.
+  auto load_chunk_impl = [&](int64_t c, RowBuf& rb, auto full_tag) {
+    constexpr bool FULL = decltype(full_tag)::value;
     rb.flags = 0;
 #pragma unroll
-    for (int half = 0; half < kRowsPerThread / 2; ++half) {
-      const int64_t r = c * kChunk + (int64_t)half * (kChunk / 2) + (int64_t)threadIdx.x * 2;
-      const int i0 = half * 2;
+    for (int pr = 0; pr < kRowsPerThread / 2; ++pr) {
+      const int64_t r = c * kChunk + (int64_t)pr * (kThreads * 2) + (int64_t)threadIdx.x * 2;
+      const int i0 = pr * 2;
       rb.k[i0] = rb.k[i0 + 1] = 0; rb.v[i0] = rb.v[i0 + 1] = 0;
-      if (r >= n) continue;
-      const bool two = r + 1 < n;
+      if (!FULL && r >= n) continue;
+      const bool two = FULL || r + 1 < n;
       uint32_t present = two ? 3u : 1u;
       if (KEYMODE == 1) {
+        // raw loads only: anything that consumes the data (canonicalisation, sign extension, null masks) waits until
+        // decode_chunk() at processing time, so these loads really stay in flight while the previous chunk is processed
         const int64_t idx = (int64_t)kc0.offset + r;
         if (two) load_pair<SK>(kc0.data, idx, rb.k[i0], rb.k[i0 + 1]);
         else rb.k[i0] = load_one<SK>(kc0.data, idx);
-        if (kc0.fclass) { rb.k[i0] = canon_key_bits(rb.k[i0], kc0.fclass); rb.k[i0 + 1] = canon_key_bits(rb.k[i0 + 1], kc0.fclass); }
-        if (kc0.mask != nullptr) {  // EXCLUDE policy: rows with a null key are dropped (direct mode never sees INCLUDE + mask)
-          if (!bit_is_set(kc0.mask, idx)) present &= ~1u;
-          if (two && !bit_is_set(kc0.mask, idx + 1)) present &= ~2u;
-        }
       } else {
         // packed key of rows r, r+1 (no early exit: both rows walk the key columns together)
         uint64_t ka = 0, kb = 0;
@@ -220,15 +224,47 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
         const int64_t vidx = (int64_t)p.v_offset + r;
         if (two) load_pair<VW>(p.v_data, vidx, rb.v[i0], rb.v[i0 + 1]);
         else rb.v[i0] = load_one<VW>(p.v_data, vidx);
-        if (VW == 4 && p.v_signed) { rb.v[i0] = (uint64_t)(int64_t)(int32_t)rb.v[i0]; rb.v[i0 + 1] = (uint64_t)(int64_t)(int32_t)rb.v[i0 + 1]; }
       }
-      if (p.v_mask != nullptr) {  // COUNT_VALID without a SUM still honours the value column's mask
-        const int64_t vidx = (int64_t)p.v_offset + r;
-        if (!bit_is_set(p.v_mask, vidx)) vvalid &= ~1u;
-        if (two && !bit_is_set(p.v_mask, vidx + 1)) vvalid &= ~2u;
+      if (KEYMODE == 0) {
+        if (VW == 4 && p.v_signed) { rb.v[i0] = (uint64_t)(int64_t)(int32_t)rb.v[i0]; rb.v[i0 + 1] = (uint64_t)(int64_t)(int32_t)rb.v[i0 + 1]; }
+        if (p.v_mask != nullptr) {  // COUNT_VALID without a SUM still honours the value column's mask
+          const int64_t vidx = (int64_t)p.v_offset + r;
+          if (!bit_is_set(p.v_mask, vidx)) vvalid &= ~1u;
+          if (two && !bit_is_set(p.v_mask, vidx + 1)) vvalid &= ~2u;
+        }
       }
       rb.flags |= (present << i0) | (vvalid << (8 + i0));
     }
+  };
+  // KEYMODE 1: the consuming half of the loader, run when the chunk is processed (one chunk after its loads were issued)
+  auto decode_chunk = [&](int64_t c, RowBuf& rb) {
+    if (KEYMODE != 1) return;
+    const bool plain = kc0.fclass == 0 && kc0.mask == nullptr && p.v_mask == nullptr && !(VW == 4 && p.v_signed);
+    if (plain) return;
+#pragma unroll
+    for (int pr = 0; pr < kRowsPerThread / 2; ++pr) {
+      const int64_t r = c * kChunk + (int64_t)pr * (kThreads * 2) + (int64_t)threadIdx.x * 2;
+      const int i0 = pr * 2;
+      uint32_t present = (rb.flags >> i0) & 3u, vvalid = (rb.flags >> (8 + i0)) & 3u;
+      if (kc0.fclass) { rb.k[i0] = canon_key_bits(rb.k[i0], kc0.fclass); rb.k[i0 + 1] = canon_key_bits(rb.k[i0 + 1], kc0.fclass); }
+      if (VW == 4 && p.v_signed) { rb.v[i0] = (uint64_t)(int64_t)(int32_t)rb.v[i0]; rb.v[i0 + 1] = (uint64_t)(int64_t)(int32_t)rb.v[i0 + 1]; }
+      if (kc0.mask != nullptr && present) {  // EXCLUDE policy: rows with a null key are dropped (direct mode never sees INCLUDE + mask)
+        const int64_t idx = (int64_t)kc0.offset + r;
+        if ((present & 1u) && !bit_is_set(kc0.mask, idx)) present &= ~1u;
+        if ((present & 2u) && !bit_is_set(kc0.mask, idx + 1)) present &= ~2u;
+      }
+      vvalid &= present;
+      if (p.v_mask != nullptr && vvalid) {  // COUNT_VALID without a SUM still honours the value column's mask
+        const int64_t vidx = (int64_t)p.v_offset + r;
+        if ((vvalid & 1u) && !bit_is_set(p.v_mask, vidx)) vvalid &= ~1u;
+        if ((vvalid & 2u) && !bit_is_set(p.v_mask, vidx + 1)) vvalid &= ~2u;
+      }
+      rb.flags = (rb.flags & ~((3u << i0) | (3u << (8 + i0)))) | (present << i0) | (vvalid << (8 + i0));
+    }
+  };
+  auto load_chunk = [&](int64_t c, RowBuf& rb) {
+    if ((c + 1) * kChunk <= n) load_chunk_impl(c, rb, std::true_type{});
+    else load_chunk_impl(c, rb, std::false_type{});
   };
 
   uint32_t kd_a = smem_addr(skd), lo_a = smem_addr(slo), hc_a = smem_addr(shc), idx_a = smem_addr(sidx32);
@@ -248,7 +284,12 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
       id[i] = kIdSkip;
       if (present) {
         const bool in_range = VW == 0 || ((v + m_bias) >> (m_bits + 1)) == 0;
-        if (!in_range) { smem_global_row(p, k, v, vvalid, VW != 0, &s_abort); }
+        const uint64_t didx = (k ^ p.key_flip) - p.key_base;  // direct mode: order-preserving image minus the base
+        if (!in_range || (DIRECT && didx >= D)) { smem_global_row(p, k, v, vvalid, VW != 0, &s_abort); }
+        else if (DIRECT) {
+          if (vvalid) id[i] = (uint32_t)didx;
+          else atomicOr(sidx32 + (didx >> 5), 1u << (didx & 31));  // all-null group: remember that it exists
+        }
         else {
           uint32_t sa = idx_a + 2 * __umulhi(hash32(k), S);
           uint32_t e;
@@ -267,8 +308,9 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
           else if (vvalid) id[i] = e;  // null value: the group exists, nothing to add (device_aggregators.cuh:434-436)
         }
       }
+      if (!DIRECT) __syncwarp();  // lanes leave the probe loop at different steps: re-join before the next row
     }
-    __syncwarp();
+    if (DIRECT) __syncwarp();
 #pragma unroll
     for (int i = 0; i < kRowsPerThread; ++i) {
       if (id[i] < kIdEmpty) {
@@ -287,15 +329,19 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
   auto flush = [&]() {
     __syncthreads();
     if (p.debug && threadIdx.x == 0) atomicAdd(a.table.status + 5, 1u);
-    const uint32_t used = min(*reinterpret_cast<volatile uint32_t*>(&s_count), D);
+    const uint32_t used = DIRECT ? D : min(*reinterpret_cast<volatile uint32_t*>(&s_count), D);
     const uint32_t rot  = used ? (uint32_t)(((uint64_t)blockIdx.x * used) / gridDim.x) : 0;
     for (uint32_t i = threadIdx.x; i < used; i += kThreads) {
       uint32_t s = i + rot; if (s >= used) s -= used;
       const uint32_t hc = shc[s], lo = slo[s];
-      if (hc == 0) continue;  // no valid row since the last flush (the count field is never 0 once a row was added)
+      bool seen = false;
+      if (DIRECT && hc == 0) seen = (sidx32[s >> 5] >> (s & 31)) & 1u;
+      if (hc == 0 && !seen) continue;  // no row since the last flush (the count field is never 0 once a valid row was added)
       shc[s] = 0; slo[s] = 0;
-      const uint64_t g = find_or_insert(a.table, (uint64_t)skd[s], 0);
+      const uint64_t key = DIRECT ? ((p.key_base + s) ^ p.key_flip) : (uint64_t)skd[s];
+      const uint64_t g = find_or_insert(a.table, key, 0);
       if (g == kNoSlot) { s_abort = 1; continue; }
+      if (hc == 0) continue;
       const uint32_t cnt = hc & c_mask;
       if (VW != 0 && p.sum_cells) {
         const int64_t hi = (int64_t)((int32_t)hc >> c_bits);
@@ -305,6 +351,10 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
       if (p.cnta_cells) atomicAdd(p.cnta_cells + g, (int)cnt);
     }
     __syncthreads();
+    if (DIRECT) {
+      for (uint32_t i = threadIdx.x; i < (D + 31) / 32; i += kThreads) sidx32[i] = 0;
+      __syncthreads();
+    }
   };
 
   RowBuf cur, nxt;
@@ -315,6 +365,7 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
     __syncwarp();  // the trip count is block-uniform: re-join lanes that drifted apart in the previous iteration
     const int64_t cn = c + gridDim.x;
     if (cn < nchunk) load_chunk(cn, nxt); else nxt.flags = 0;
+    decode_chunk(c, cur);
     process(cur);
     cur = nxt;
     rows_since_flush += kChunk;
@@ -329,8 +380,9 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
 }
 
 // ------------------------------------------------------------------ host side
-size_t smem_table_bytes(uint32_t slots, uint32_t dense, int smem_key_bytes)
+size_t smem_table_bytes(uint32_t slots, uint32_t dense, int smem_key_bytes, bool direct)
 {
+  if (direct) return (size_t)dense * 8 + (((size_t)dense + 31) / 32) * 4;
   return (size_t)dense * (smem_key_bytes + 8) + (size_t)slots * 2;
 }
 
@@ -340,10 +392,10 @@ size_t smem_table_max_bytes()
   return 232448 - 64;
 }
 
-template <int SK, int KEYMODE, int VW>
+template <int SK, int KEYMODE, int VW, bool DIRECT>
 static cudaError_t launch_one(const SmemParams& p, int grid, size_t smem, cudaStream_t s)
 {
-  auto kern = agg_smem_kernel<SK, KEYMODE, VW>;
+  auto kern = agg_smem_kernel<SK, KEYMODE, VW, DIRECT>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   kern<<<grid, kThreads, smem, s>>>(p);
@@ -353,11 +405,13 @@ static cudaError_t launch_one(const SmemParams& p, int grid, size_t smem, cudaSt
 cudaError_t launch_aggregate_smem(const SmemParams& p, int smem_key_bytes, int key_mode, int value_width, int num_sms, cudaStream_t s)
 {
   if (p.a.num_rows == 0) return cudaSuccess;
-  const size_t smem = smem_table_bytes(p.slots, p.dense, smem_key_bytes);
+  const bool direct = p.direct != 0;
+  const size_t smem = smem_table_bytes(p.slots, p.dense, smem_key_bytes, direct);
   const int64_t nchunk = (p.a.num_rows + kChunk - 1) / kChunk;
   const int grid = (int)(nchunk < num_sms ? nchunk : num_sms);
 #define BGB_SMEM_CASE(SK, KM, VW) \
-  if (smem_key_bytes == SK && key_mode == KM && value_width == VW) return launch_one<SK, KM, VW>(p, grid, smem, s);
+  if (smem_key_bytes == SK && key_mode == KM && value_width == VW)       \
+    return direct ? launch_one<SK, KM, VW, true>(p, grid, smem, s) : launch_one<SK, KM, VW, false>(p, grid, smem, s);
   BGB_SMEM_CASE(8, 1, 8) BGB_SMEM_CASE(8, 1, 4) BGB_SMEM_CASE(8, 1, 0)
   BGB_SMEM_CASE(4, 1, 8) BGB_SMEM_CASE(4, 1, 4) BGB_SMEM_CASE(4, 1, 0)
   BGB_SMEM_CASE(8, 0, 8) BGB_SMEM_CASE(8, 0, 4) BGB_SMEM_CASE(8, 0, 0)

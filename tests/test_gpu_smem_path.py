@@ -139,3 +139,59 @@ def test_sliced_unaligned_columns_take_generic_key_mode_or_generic_path():
     np.testing.assert_array_equal(kk[o], ko[0][0])
     np.testing.assert_array_equal(res[0].columns()[0].to_numpy()[0][o], ao[0][0])
     np.testing.assert_array_equal(res[0].columns()[1].to_numpy()[0][o], ao[1][0])
+
+
+# ------------------------------------------------------------------ direct-address variant (dense integer key domains)
+def _check_direct(keys, vals, aggs, include=False, name=""):
+    G, path = gpu_util.compare_with_oracle(keys, vals, aggs, include_null_keys=include, options={"force_path": 4}, name=name)
+    assert path == "smem-direct", f"{name}: expected the direct-address kernel, got {path}"
+    return G
+
+
+@pytest.mark.parametrize("ktype", ["int64", "int32", "uint32", "int16", "uint8"])
+def test_direct_address_dense_integer_keys(ktype):
+    rng = np.random.default_rng(11)
+    n = 500_000
+    lo, hi = (-3000, 3000) if ktype in ("int64", "int32", "int16") else (0, 200 if ktype == "uint8" else 6000)
+    keys = [H(rng.integers(lo, hi, n).astype(ktype), rng.random(n) > 0.03)]
+    vals = [H(rng.integers(-1000, 1001, n).astype(np.int64), rng.random(n) > 0.1)]
+    _check_direct(keys, vals, SUMCOUNT + [(0, "mean", 1)], name=f"direct/{ktype}")
+    # INCLUDE adds a null flag above the value bits: signed keys then span the whole unsigned image (not a dense domain)
+    gpu_util.compare_with_oracle(keys, vals, SUMCOUNT, include_null_keys=True, options={"force_path": 4}, name=f"direct/{ktype}/include")
+
+
+def test_direct_address_outliers_outside_the_sampled_range_bypass():
+    rng = np.random.default_rng(12)
+    n = 1_000_000
+    k = rng.integers(100, 5100, n).astype(np.int64)
+    out = rng.choice(n, 40, replace=False)  # 40 rows far outside: the 65536-row sample almost surely misses them
+    k[out[:10]] = 10**12 + np.arange(10)
+    k[out[10:20]] = -7
+    k[out[20:30]] = np.iinfo(np.int64).min
+    k[out[30:]] = 99  # just below the sampled minimum (inside the padding)
+    v = rng.integers(-1000, 1001, n).astype(np.int64)
+    _check_direct([H(k)], [H(v)], SUMCOUNT, name="direct/outliers")
+
+
+def test_direct_address_all_null_group_and_count_only():
+    k = np.repeat(np.arange(300, dtype=np.int32), 400)
+    v = np.ones(len(k), dtype=np.int64)
+    valid = k != 17
+    G = _check_direct([H(k)], [H(v, valid)], SUMCOUNT, name="direct/all-null group")
+    assert G == 300
+    _check_direct([H(k)], [H(v, valid)], [(0, "count_valid", 1)], name="direct/count only")
+
+
+def test_direct_address_packed_two_small_keys_and_config_a():
+    rng = np.random.default_rng(13)
+    n = 400_000
+    a = H(rng.integers(0, 3, n).astype(np.int8))
+    b = H(rng.integers(0, 2, n).astype(np.int8), rng.random(n) > 0.05)
+    v = H(rng.integers(-50, 50, n).astype(np.int32))
+    _check_direct([a, b], [v], SUMCOUNT, name="direct/2xint8")
+    # INCLUDE puts b's null flag at bit 16: the packed image spans 65K values, more than the direct table holds -> hashed
+    gpu_util.compare_with_oracle([a, b], [v], SUMCOUNT, include_null_keys=True, options={"force_path": 4}, name="direct/2xint8/include")
+    rows = np.arange(2_000_000, dtype=np.uint64)
+    k = (orc.splitmix64(42, rows) % np.uint64(10_000)).astype(np.int64)
+    vv = (orc.splitmix64(43, rows) % np.uint64(2001)).astype(np.int64) - 1000
+    assert _check_direct([H(k)], [H(vv)], SUMCOUNT, name="direct/configA") == 10_000

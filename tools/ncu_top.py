@@ -16,7 +16,7 @@ for row in r[2:]:
             print(f"  {k:70s} {row[h.index(k)]:>16s} {u[h.index(k)]}")
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
-hdr = rows[1]; data = rows[2:]
+hdr = rows[1]; data = [x for x in rows[2:] if len(x) == len(hdr) and x[0] != 'Address']
 ia, isrc, ie, it, iss = hdr.index("Address"), hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("Avg. Threads Executed"), hdr.index("Warp Stall Sampling (All Samples)")
 tot_s = sum(int(x[iss] or 0) for x in data); tot_i = sum(int(x[ie] or 0) for x in data)
 print(f"total stall samples {tot_s}, warp instructions {tot_i}")
