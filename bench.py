@@ -220,50 +220,62 @@ def run_reference_arm(args):
 
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
-    """One long-running `nvidia-smi -lms` child started BEFORE the timed region (spawning a process inside it would
-    steal host time from the steps); its output is parsed after the region ends."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock + throttle reasons DURING the timed region, through NVML (pynvml): one sample from the main thread in the
+    middle of the region plus a 20 ms background thread (clock and reason queries cost microseconds and do not disturb the
+    steps: tools/nvml_cost.py; the max-clock query costs milliseconds and is made once before the region). (An `nvidia-smi -lms` child polling every
+    50 ms stretched 3 ms steps to 14 ms on this box -- the driver serialises its queries with kernel launches -- so the
+    sampler is kept this light; the samples are still taken while the steps run.)"""
 
     def __init__(self, index: int):
         self.index = index
-        self.proc = None
-        self.t_start = None
+        self.samples = []
+        self._stop = threading.Event()
+        self._t = None
+        self.h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)  # slow query (ms): once, up front
+        except Exception:
+            self.nv = None
+            self.h = None
+
+    def sample(self):
+        if self.h is None:
+            return
+        try:
+            nv = self.nv
+            sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)  # microseconds: cached by the driver
+            mx = self.max_mhz
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            self.samples.append((sm, mx, int(r)))
+        except Exception:
+            pass
+
+    def _run(self):
+        while not self._stop.wait(0.02):
+            self.sample()
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            time.sleep(0.3)  # let it print its first sample before the timed region starts
-        except Exception:
-            self.proc = None
-
-    def mark(self):
-        self.t_start = time.time()
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
 
     def stop(self):
-        out = ""
-        if self.proc is not None:
-            time.sleep(0.12)
-            self.proc.terminate()
-            try:
-                out, _ = self.proc.communicate(timeout=5)
-            except Exception:
-                self.proc.kill()
-        sm, mx, reasons = [], 0.0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.splitlines():
-            smp = [x.strip() for x in line.split(",")]
-            try:
-                sm.append(float(smp[0])); mx = max(mx, float(smp[1]))
-                for nm, val in zip(names, smp[3:7]):
-                    if val.lower().startswith("active"):
-                        reasons.add(nm)
-            except Exception:
-                continue
-        # the samples span a little more than the timed region (start-up + tail): the maximum-load ones are what matter
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=2)
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        reasons = set()
+        for _, _, r in self.samples:
+            for bit, nm in names.items():
+                if r & bit:
+                    reasons.add(nm)
+        sm = [x[0] for x in self.samples]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max((x[1] for x in self.samples), default=None),
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self.h is not None else "unavailable"}
 
 
 # ------------------------------------------------------------------------------------------------ our arm
@@ -341,8 +353,10 @@ def main():
     prof_acc = {}
     barrier()
     e0.record()
-    for _ in range(args.steps):
+    for it in range(args.steps):
         step()
+        if rank == 0 and it == args.steps // 2:
+            clocks.sample()  # mid-region sample from the main thread (the GPU is between two back-to-back steps)
         src = dgb.last_profile if dgb is not None else gb.last_profile
         for name, ms in src:
             prof_acc.setdefault(name, []).append(ms)

@@ -61,7 +61,8 @@ struct AccDesc {
   int32_t offset;
   uint8_t src;            // Src
   uint8_t op;             // AccOp
-  uint8_t pad[2];
+  uint8_t byte_mask;      // mask points at one validity BYTE per row (partitioned copies) instead of a bitmask
+  uint8_t pad;
   void* cells;            // capacity+1 cells
 };
 
@@ -82,6 +83,7 @@ struct AggParams {
   int32_t num_accs;
   int32_t skip_null_keys;  // null_policy::EXCLUDE and some key column has a mask
   int32_t init_keys;       // init kernel: also reset keys + status (first accumulator chunk)
+  const uint32_t* num_rows_dev;  // when set, the row count lives on the device (partitioned copy: rows kept by the scatter)
 };
 
 // final (output) operations of the emit kernel

@@ -3,51 +3,21 @@
 // host buffers. Device work is identical to the device-pointer entry points; nothing is computed on the CPU.
 #include <cstdlib>
 #include <cstring>
-#include <mutex>
 #include <vector>
 
 #include "errors.h"
 #include "plan.h"
+#include "pool.h"
 
 using namespace bgb;
 
 namespace {
 
-// private stream-ordered pool that keeps its pages across calls (the default pool hands them back to the driver at
-// every synchronise, which costs more than the PCIe copy for GB-sized columns)
-cudaMemPool_t staging_pool()
-{
-  static std::mutex mu;
-  static cudaMemPool_t pools[64] = {};
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-  std::lock_guard<std::mutex> lock(mu);
-  if (!pools[dev]) {
-    cudaMemPoolProps props{};
-    props.allocType = cudaMemAllocationTypePinned;
-    props.location.type = cudaMemLocationTypeDevice;
-    props.location.id = dev;
-    if (cudaMemPoolCreate(&pools[dev], &props) != cudaSuccess) { cudaGetLastError(); pools[dev] = nullptr; return nullptr; }
-    uint64_t keep = ~0ull;
-    cudaMemPoolSetAttribute(pools[dev], cudaMemPoolAttrReleaseThreshold, &keep);
-  }
-  return pools[dev];
-}
-
-void* pool_alloc(void* ctx, size_t bytes, cudaStream_t s)
-{
-  void* p = nullptr;
-  cudaMemPool_t pool = (cudaMemPool_t)ctx;
-  cudaError_t e = pool ? cudaMallocFromPoolAsync(&p, bytes ? bytes : 16, pool, s) : cudaMallocAsync(&p, bytes ? bytes : 16, s);
-  if (e != cudaSuccess) { cudaGetLastError(); return nullptr; }
-  return p;
-}
-void* alloc_cb(size_t bytes, void* stream, void* ctx) { return pool_alloc(ctx, bytes, (cudaStream_t)stream); }
-void free_cb(void* ptr, size_t, void* stream, void*) { cudaFreeAsync(ptr, (cudaStream_t)stream); }
+void* alloc_cb(size_t bytes, void* stream, void*) { return pool_alloc_async(bytes, (cudaStream_t)stream); }
+void free_cb(void* ptr, size_t, void* stream, void*) { pool_free_async(ptr, (cudaStream_t)stream); }
 
 struct DeviceStage {
   cudaStream_t s = nullptr;
-  cudaMemPool_t pool = nullptr;
   std::vector<void*> bufs;
   ~DeviceStage()
   {
@@ -56,7 +26,7 @@ struct DeviceStage {
   }
   void* alloc(size_t bytes)
   {
-    void* p = pool_alloc(pool, bytes, s);
+    void* p = pool_alloc_async(bytes, s);
     if (p) bufs.push_back(p);
     return p;
   }
@@ -115,8 +85,7 @@ extern "C" int bgb_groupby_host(const bgb_column_view* host_keys, int32_t num_ke
   DeviceStage st;
   int rc = check_cuda(cudaStreamCreateWithFlags(&st.s, cudaStreamNonBlocking), "stream");
   if (rc) return rc;
-  st.pool = staging_pool();
-  bgb_allocator pool_allocator{alloc_cb, free_cb, (void*)st.pool};
+  bgb_allocator pool_allocator{alloc_cb, free_cb, nullptr};
   std::vector<bgb_column_view> dkeys(num_keys);
   for (int i = 0; i < num_keys; ++i) if ((rc = stage_column(st, host_keys[i], dkeys[i]))) return rc;
   std::vector<bgb_request> dreqs(num_requests > 0 ? num_requests : 0);

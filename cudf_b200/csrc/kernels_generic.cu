@@ -72,7 +72,10 @@ __device__ __forceinline__ void apply_acc(const AccDesc& a, int64_t row, uint64_
 {
   const int64_t idx = (int64_t)a.offset + row;
   if (a.op == ACC_COUNT_ALL) { atomicAdd(reinterpret_cast<int*>(a.cells) + slot, 1); return; }
-  if (a.mask != nullptr && !bit_is_set(a.mask, idx)) return;  // null source skipped (device_aggregators.cuh:434-436)
+  if (a.mask != nullptr) {  // null source skipped (device_aggregators.cuh:434-436)
+    const bool valid = a.byte_mask ? __ldg(reinterpret_cast<const uint8_t*>(a.mask) + idx) != 0 : bit_is_set(a.mask, idx);
+    if (!valid) return;
+  }
   if (a.op == ACC_COUNT_VALID) { atomicAdd(reinterpret_cast<int*>(a.cells) + slot, 1); return; }
   const uint64_t raw = load_raw(a.data, src_width(a.src), idx);
   unsigned long long* c64 = reinterpret_cast<unsigned long long*>(a.cells) + slot;
@@ -99,7 +102,8 @@ __device__ __forceinline__ void apply_acc(const AccDesc& a, int64_t row, uint64_
 __global__ void __launch_bounds__(256) aggregate_global_kernel(const __grid_constant__ AggParams p)
 {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < p.num_rows; row += stride) {
+  const int64_t nrows  = p.num_rows_dev ? (int64_t)*p.num_rows_dev : p.num_rows;
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < nrows; row += stride) {
     uint64_t k0, k1;
     if (!pack_key(p, row, k0, k1)) continue;
     const uint64_t slot = find_or_insert(p.table, k0, k1);

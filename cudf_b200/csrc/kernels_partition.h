@@ -1,0 +1,36 @@
+// Parameters of the radix-partitioning kernels (kernels_partition.cu).
+#pragma once
+#include "bgb_internal.cuh"
+
+namespace bgb {
+
+constexpr int kMaxPartValues = 16;
+
+struct PartValue {
+  const uint8_t* data;      // source value column
+  const uint32_t* mask;     // source bitmask or nullptr
+  int32_t offset;
+  int32_t width;            // element bytes 1/2/4/8
+  uint8_t* out_data;        // partition-ordered copy (null elements written as 0)
+  uint8_t* out_valid;       // one byte per row, only when mask != nullptr
+};
+
+struct PartParams {
+  AggParams a;              // key columns, num_rows, table (capacity + key_words decide the partition of a key)
+  int32_t log2_parts;       // P = 1 << log2_parts, P <= 4096
+  int32_t slot_shift;       // partition = slot >> slot_shift  (slot_shift = log2(capacity) - log2_parts)
+  uint32_t* counts;         // [P]   rows per partition (zeroed by the caller)
+  uint32_t* offsets;        // [P+1] exclusive scan; offsets[P] = rows kept (rows with a null key under EXCLUDE are dropped)
+  uint32_t* cursors;        // [P]   running write positions
+  uint64_t* out_k0;         // packed key, low word (8-byte elements, or 4-byte when key_out_width == 4)
+  uint64_t* out_k1;         // high word when key_words == 2
+  int32_t key_out_width;
+  int32_t num_vals;
+  PartValue v[kMaxPartValues];
+};
+
+cudaError_t launch_partition_hist(const PartParams& p, int num_sms, cudaStream_t s);
+cudaError_t launch_partition_scan(const PartParams& p, cudaStream_t s);
+cudaError_t launch_partition_scatter(const PartParams& p, int num_sms, cudaStream_t s);
+
+}  // namespace bgb

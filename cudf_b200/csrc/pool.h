@@ -1,0 +1,11 @@
+// Library-private stream-ordered memory pool used when the caller passes no bgb_allocator.
+// It keeps its pages across calls: the CUDA default pool returns them to the driver at every stream synchronise, which
+// costs hundreds of milliseconds for the tens-of-GB group tables of the high-cardinality configs.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+
+namespace bgb {
+void* pool_alloc_async(size_t bytes, cudaStream_t s);   // nullptr on failure (error state cleared)
+void pool_free_async(void* p, cudaStream_t s);
+}  // namespace bgb
