@@ -8,6 +8,7 @@
 
 #include "errors.h"
 #include "kernels_smem.h"
+#include "kernels_tiny.h"
 
 namespace bgb {
 
@@ -110,11 +111,91 @@ static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint
   return rc;
 }
 
+// ---- tiny-cardinality path (kernels_tiny.cu): per-thread private accumulators, no atomics on the row path
+static bool tiny_plan(const Plan& pl, TinyParams& tp)
+{
+  memset(&tp, 0, sizeof tp);
+  if (pl.key_words != 1 || pl.accs.empty() || pl.accs.size() > (size_t)kMaxAccs) return false;
+  auto column_of = [&](int value_col) -> int {  // COUNT_ALL (value_col -1) rides on a data-less, mask-less pseudo column
+    for (int j = 0; j < tp.num_cols; ++j) {
+      const TinyCol& c = tp.cols[j];
+      if (value_col < 0 ? (c.data == nullptr && c.width == 0)
+                        : (c.width != 0 && c.data == (const uint8_t*)pl.values[value_col].v.data && c.mask == pl.values[value_col].v.null_mask &&
+                           c.offset == pl.values[value_col].v.offset && c.src == pl.values[value_col].src))
+        return j;
+    }
+    if (tp.num_cols == kTinyMaxCols) return -1;
+    TinyCol& c = tp.cols[tp.num_cols];
+    c.acc_sum = c.acc_sumsq = c.acc_min = c.acc_max = c.acc_count = -1;
+    c.sum_op = ACC_SUM_I64;
+    if (value_col >= 0) {
+      const ValuePlan& v = pl.values[value_col];
+      c.data = (const uint8_t*)v.v.data; c.mask = v.v.null_mask; c.offset = v.v.offset; c.src = v.src; c.width = (uint8_t)type_width(v.v.type_id);
+      c.sum_op = v.src == S_F64 ? ACC_SUM_F64 : v.src == S_F32 ? ACC_SUM_F32 : ACC_SUM_I64;
+    } else { c.data = nullptr; c.mask = nullptr; c.offset = 0; c.src = S_I32; c.width = 0; }
+    return tp.num_cols++;
+  };
+  for (size_t i = 0; i < pl.accs.size(); ++i) {
+    const AccPlan& a = pl.accs[i];
+    const int j = column_of(a.value_col);
+    if (j < 0) return false;
+    TinyCol& c = tp.cols[j];
+    int* where = nullptr;
+    switch (a.op) {
+      case ACC_SUM_I64: case ACC_SUM_F64: case ACC_SUM_F32: where = &c.acc_sum; break;
+      case ACC_SUMSQ_I64: case ACC_SUMSQ_F64: case ACC_SUMSQ_F32: where = &c.acc_sumsq; c.need_sq = 1; break;
+      case ACC_MIN: where = &c.acc_min; c.need_minmax = 1; break;
+      case ACC_MAX: where = &c.acc_max; c.need_minmax = 1; break;
+      case ACC_COUNT_VALID: case ACC_COUNT_ALL: where = &c.acc_count; break;
+      default: return false;  // PRODUCT, ARGMIN/ARGMAX: general path
+    }
+    if (*where >= 0) return false;  // (the planner already merges identical accumulators)
+    *where = (int)i;
+  }
+  int cells = 0;
+  for (int j = 0; j < tp.num_cols; ++j) { tp.cols[j].cell_base = cells; cells += 2 + (tp.cols[j].need_sq ? 1 : 0) + (tp.cols[j].need_minmax ? 2 : 0); }
+  tp.cells = cells;
+  return true;
+}
+
+static int run_tiny_path(const BuildContext& ctx, TinyParams& tp)
+{
+  const Plan& pl = *ctx.plan;
+  tp.a.num_rows = pl.num_rows; tp.a.num_key_cols = (int)pl.keys.size(); tp.a.skip_null_keys = pl.skip_null_keys;
+  for (size_t c = 0; c < pl.keys.size(); ++c) {
+    const KeyPlan& k = pl.keys[c];
+    tp.a.kc[c] = KeyColDesc{(const uint8_t*)k.v.data, k.v.null_mask, k.v.offset, k.width, k.fclass, k.shift, k.null_bit};
+  }
+  tp.a.table = ctx.table; tp.a.init_keys = 1; tp.a.num_accs = (int)pl.accs.size();
+  for (size_t i = 0; i < pl.accs.size(); ++i) { tp.a.acc[i].op = pl.accs[i].op; tp.a.acc[i].cells = pl.accs[i].cells; }
+  ctx.prof->begin("init_table");
+  int rc = check_cuda(launch_init_table(tp.a, ctx.stream), "init_table");
+  ctx.prof->end();
+  if (rc) return rc;
+  ctx.prof->begin("aggregate_tiny");
+  rc = check_cuda(launch_aggregate_tiny(tp, ctx.num_sms, ctx.stream), "aggregate_tiny");
+  ctx.prof->end();
+  return rc;
+}
+
 int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path)
 {
   done = false;
   const Plan& pl = *ctx.plan;
   if (ctx.opt.force_path == 1) return BGB_OK;  // generic kernel only
+  if ((ctx.opt.force_path == 0 && !ctx.skip_tiny && ctx.g_raw <= 24 && pl.num_rows >= 65536) || ctx.opt.force_path == 5) {
+    TinyParams tp;
+    if (tiny_plan(pl, tp)) {
+      const int cap = (int)std::min<size_t>(60, (200 * 1024) / ((size_t)tp.cells * kTinyThreads * 8));
+      if (cap >= 2 && (ctx.opt.force_path == 5 || cap >= ctx.g_raw + 1)) {
+        tp.group_cap = cap;
+        int rc = run_tiny_path(ctx, tp);
+        if (rc) return rc;
+        done = true; path = "tiny";
+        return BGB_OK;
+      }
+    }
+  }
   const SmemEligibility e = smem_eligibility(pl);
   if (e.ok && (ctx.opt.force_path == 0 || ctx.opt.force_path == 2 || ctx.opt.force_path == 4)) {
     const size_t bytes = smem_table_max_bytes();

@@ -18,6 +18,7 @@ struct BuildContext {
   cudaStream_t stream;
   Profiler* prof;
   int num_sms;
+  bool skip_tiny;           // the tiny-cardinality kernel met more groups than it holds: take another path
 };
 
 // which accumulator set the shared-memory kernel can serve; value_col = -1 when there is no SUM/COUNT_VALID column

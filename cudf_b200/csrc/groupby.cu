@@ -285,6 +285,7 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     if (capacity > cap_max) capacity = cap_max;
   }
 
+  bool skip_tiny = false;
   for (int attempt = 0;; ++attempt) {
     h->table.capacity = capacity;
     const uint64_t slots = capacity + 1;
@@ -297,7 +298,7 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     // init + aggregate, kMaxAccs accumulators per launch (the first launch also initialises the keys)
     std::string path;
     bool done = false;
-    BuildContext ctx{&pl, h->table, opt, g_raw, max_abs, key_min, key_max, s, &h->prof, num_sms};
+    BuildContext ctx{&pl, h->table, opt, g_raw, max_abs, key_min, key_max, s, &h->prof, num_sms, skip_tiny};
     FAIL_RC(try_fast_paths(ctx, done, path));
     if (!done && opt.force_path != 1 && opt.force_path != 2 && opt.force_path != 4) {
       size_t slot_bytes = 8 * (size_t)pl.key_words;
@@ -342,7 +343,17 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
     h->prof.resolve();
     h->dfree(scan_state);
     if (getenv("BGB_DEBUG")) fprintf(stderr, "[bgb] path=%s groups=%u overflow=%u bypass_rows=%u flushes=%u\n", path.c_str(), st[1], st[0], st[4], st[5]);
-    if (st[0] == 0) { h->num_groups = (int32_t)st[1]; break; }
+    if (st[0] == 0 && st[3] == 0) { h->num_groups = (int32_t)st[1]; break; }
+    if (st[0] == 0 && st[3] != 0 && !skip_tiny) {
+      // the tiny-cardinality kernel met more distinct keys than it has rows for: same table, general path
+      if (opt.force_path == 5) opt.force_path = 0;
+      skip_tiny = true;
+      h->dfree(h->group_slots); h->group_slots = nullptr;
+      h->dfree(h->table.keys); h->table.keys = nullptr;
+      for (AccPlan& a : pl.accs) { h->dfree(a.cells); a.cells = nullptr; }
+      --attempt;
+      continue;
+    }
     // table overloaded: free it and retry at the size that fits every row as its own group
     if (capacity >= cap_max || attempt >= 2) FAIL_RC(set_error(BGB_CUDA_ERROR, "group table overflow at maximum capacity"));
     h->dfree(h->group_slots); h->group_slots = nullptr;

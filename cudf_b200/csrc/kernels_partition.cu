@@ -6,7 +6,7 @@
 //   pass 1  partition_hist_kernel     keys only  -> rows per partition (shared-memory histogram, one RED per bin per CTA)
 //   pass 2  partition_scan_kernel     exclusive scan of the P counters (one CTA)
 //   pass 3  partition_scatter_kernel  keys + values -> packed key column, value columns, validity bytes in partition order.
-//           Each CTA ranks a 4096-row tile by partition in shared memory (ATOMS rank + block scan), reserves one contiguous
+//           Each CTA ranks a 2048-row tile by partition in shared memory (ATOMS rank + block scan), reserves one contiguous
 //           run per partition with a single RED per (tile, partition), and writes the tile out in runs (coalesced).
 //   pass 4  aggregate_global_kernel   (kernels_generic.cu) over the partitioned copy: consecutive rows hit one
 //           table region of capacity/P slots, which stays in L2.
@@ -21,9 +21,11 @@
 namespace bgb {
 
 namespace {
-constexpr int kPThreads = 1024;
+constexpr int kPThreads = 512;   // two CTAs per SM (64 registers each): one loads/ranks while the other writes out
 constexpr int kPRows    = 4;
 constexpr int kPTile    = kPThreads * kPRows;
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 __device__ __forceinline__ uint32_t partition_of(const PartParams& p, uint64_t k0, uint64_t k1)
 {
@@ -38,10 +40,15 @@ __global__ void __launch_bounds__(kPThreads) partition_hist_kernel(const __grid_
   for (uint32_t i = threadIdx.x; i < P; i += kPThreads) s_hist[i] = 0;
   __syncthreads();
   const int64_t stride = (int64_t)gridDim.x * kPThreads;
-  for (int64_t row = (int64_t)blockIdx.x * kPThreads + threadIdx.x; row < p.a.num_rows; row += stride) {
-    uint64_t k0, k1;
-    if (!pack_key(p.a, row, k0, k1)) continue;
-    atomicAdd(&s_hist[partition_of(p, k0, k1)], 1u);
+  const int64_t n      = p.a.num_rows;
+  for (int64_t base = (int64_t)blockIdx.x * kPThreads + threadIdx.x; base < n; base += 4 * stride) {
+    // four independent rows per thread: their key loads are all in flight before the first hash
+    uint64_t k0[4], k1[4];
+    bool keep[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { const int64_t row = base + j * stride; keep[j] = row < n && pack_key(p.a, row, k0[j], k1[j]); }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) if (keep[j]) atomicAdd(&s_hist[partition_of(p, k0[j], k1[j])], 1u);
   }
   __syncthreads();
   for (uint32_t i = threadIdx.x; i < P; i += kPThreads)
@@ -74,7 +81,7 @@ __global__ void __launch_bounds__(1024) partition_scan_kernel(const uint32_t* co
   if (threadIdx.x == 0) offsets[P] = s_carry;
 }
 
-__global__ void __launch_bounds__(kPThreads) partition_scatter_kernel(const __grid_constant__ PartParams p)
+__global__ void __launch_bounds__(kPThreads, 2) partition_scatter_kernel(const __grid_constant__ PartParams p)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const uint32_t P = 1u << p.log2_parts;
@@ -91,6 +98,14 @@ __global__ void __launch_bounds__(kPThreads) partition_scatter_kernel(const __gr
   const int64_t ntiles = (n + kPTile - 1) / kPTile;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     for (uint32_t i = threadIdx.x; i < P; i += kPThreads) s_cnt[i] = 0;
+    // pull this tile's value columns (consumed a few phases from now) and the next tile's key columns towards L2
+#pragma unroll
+    for (int j = 0; j < kPRows; ++j) {
+      const int64_t row = tile * kPTile + (int64_t)j * kPThreads + threadIdx.x;
+      if (row < n) for (int c = 0; c < p.num_vals; ++c) prefetch_l2(p.v[c].data + ((int64_t)p.v[c].offset + row) * p.v[c].width);
+      const int64_t nrow = row + (int64_t)gridDim.x * kPTile;
+      if (nrow < n) for (int c = 0; c < p.a.num_key_cols; ++c) prefetch_l2(p.a.kc[c].data + ((int64_t)p.a.kc[c].offset + nrow) * p.a.kc[c].width);
+    }
     __syncthreads();
     // ---- rank every row inside its partition (ATOMS.ADD with return)
     uint64_t k0[kPRows], k1[kPRows];
@@ -116,7 +131,7 @@ __global__ void __launch_bounds__(kPThreads) partition_scatter_kernel(const __gr
         if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = incl;
         __syncthreads();
         uint32_t woff = 0, total = 0;
-        for (int w = 0; w < 32; ++w) { uint32_t t = s_warp[w]; if (w < (int)(threadIdx.x >> 5)) woff += t; total += t; }
+        for (int w = 0; w < kPThreads / 32; ++w) { uint32_t t = s_warp[w]; if (w < (int)(threadIdx.x >> 5)) woff += t; total += t; }
         if (i < P) {
           s_off[i] = carry + woff + incl - v;
           if (v) s_gbas[i] = atomicAdd(p.cursors + i, v);
@@ -185,7 +200,7 @@ cudaError_t launch_partition_hist(const PartParams& p, int num_sms, cudaStream_t
 {
   if (p.a.num_rows == 0) return cudaSuccess;
   const int64_t want = (p.a.num_rows + kPThreads - 1) / kPThreads;
-  const int grid     = (int)(want < 2 * num_sms ? want : 2 * num_sms);
+  const int grid     = (int)(want < 4 * num_sms ? want : 4 * num_sms);
   partition_hist_kernel<<<grid, kPThreads, sizeof(uint32_t) << p.log2_parts, s>>>(p);
   return note_launch();
 }
@@ -203,7 +218,7 @@ cudaError_t launch_partition_scatter(const PartParams& p, int num_sms, cudaStrea
   cudaError_t e = cudaFuncSetAttribute(partition_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int64_t ntiles = (p.a.num_rows + kPTile - 1) / kPTile;
-  const int per_sm     = smem <= 100 * 1024 ? 2 : 1;
+  const int per_sm     = 2;
   const int grid       = (int)(ntiles < (int64_t)per_sm * num_sms ? ntiles : (int64_t)per_sm * num_sms);
   partition_scatter_kernel<<<grid, kPThreads, smem, s>>>(p);
   return note_launch();

@@ -1,0 +1,37 @@
+// Parameters of the tiny-cardinality kernel (kernels_tiny.cu): a handful of groups, any mix of SUM / SUM_OF_SQUARES /
+// COUNT / MIN / MAX accumulators, accumulated in per-thread private shared-memory cells (no atomics on the row path).
+#pragma once
+#include "bgb_internal.cuh"
+
+namespace bgb {
+
+constexpr int kTinyMaxCols = 4;   // distinct value columns (+ the pseudo column that carries COUNT_ALL)
+constexpr int kTinyThreads = 512;
+
+// one value column and everything accumulated from it. Cells (8 bytes each) of a group row, in this order:
+//   [count of valid rows] [sum] [sum of squares, if need_sq] [min, max, if need_minmax]
+struct TinyCol {
+  const uint8_t* data;   // nullptr for the pseudo column that counts all rows
+  const uint32_t* mask;
+  int32_t offset;
+  uint8_t src;           // Src
+  uint8_t width;
+  uint8_t need_sq;
+  uint8_t need_minmax;
+  int32_t cell_base;     // first cell of this column inside a group row
+  int32_t acc_sum, acc_sumsq, acc_min, acc_max, acc_count;  // AggParams::acc[] entries fed at the end (-1: not requested)
+  int32_t sum_op;        // AccOp of the sum / sum-of-squares pair (decides integer, float64 or float32 arithmetic)
+};
+
+struct TinyParams {
+  AggParams a;           // key columns, HBM table, acc[] (global cells)
+  TinyCol cols[kTinyMaxCols];
+  int32_t num_cols;
+  int32_t cells;         // 8-byte cells per group row
+  int32_t group_cap;     // groups a CTA can hold; more distinct keys -> status[3] = 1 and the host takes another path
+};
+
+size_t tiny_smem_bytes(int cells, int group_cap);
+cudaError_t launch_aggregate_tiny(const TinyParams& p, int num_sms, cudaStream_t s);
+
+}  // namespace bgb
