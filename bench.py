@@ -376,7 +376,8 @@ def main():
     # ---- roofline of the dominant kernel (CUDA events on the call's stream, recorded inside the timed steps)
     peak, peak_src = peaks()
     kern_ms = {k: sum(v) / len(v) for k, v in prof_acc.items()}
-    dom = max(kern_ms, key=kern_ms.get) if kern_ms else None
+    local_ms = {k: v for k, v in kern_ms.items() if not k.startswith("dist_")}  # dist_* are whole phases, not kernels
+    dom = max(local_ms, key=local_ms.get) if local_ms else None
     alg = algorithmic_bytes(wl, n, g)
     roof = None
     if dom:

@@ -8,6 +8,7 @@ class Kind:
     """cudf::aggregation::Kind (/root/reference/cpp/include/cudf/aggregation.hpp:78-121)."""
     SUM, SUM_OVERFLOW, PRODUCT, MIN, MAX, COUNT_VALID, COUNT_ALL, ANY, ALL, SUM_OF_SQUARES = range(10)
     MEAN, M2, VARIANCE, STD, MEDIAN, QUANTILE, ARGMAX, ARGMIN, NUNIQUE, NTH_ELEMENT = range(10, 20)
+    MERGE_COUNT = 100  # library extension: sum of INT32 partial counts -> INT32 (include/bgb.h)
 
 
 class NullPolicy:
@@ -46,3 +47,8 @@ def variance(ddof: int = 1):
 
 def std(ddof: int = 1):
     return Aggregation(Kind.STD, ddof)
+
+
+def merge_count():
+    """Sum of partial COUNT columns, returned as size_type (the reduce step of a distributed / streaming groupby)."""
+    return Aggregation(Kind.MERGE_COUNT)

@@ -29,7 +29,10 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 
 __device__ __forceinline__ uint32_t partition_of(const PartParams& p, uint64_t k0, uint64_t k1)
 {
-  return (uint32_t)((hash_key(k0, k1, p.a.table.key_words) & (p.a.table.capacity - 1)) >> p.slot_shift);
+  const uint64_t h = hash_key(k0, k1, p.a.table.key_words);
+  // owner-rank partitioning uses a second mix so that it is independent of the table slot (hash2(key) % P)
+  if (p.mod_parts > 0) return (uint32_t)(mix64(h ^ 0xA0761D6478BD642Full) % (uint32_t)p.mod_parts);
+  return (uint32_t)((h & (p.a.table.capacity - 1)) >> p.slot_shift);
 }
 }  // namespace
 
@@ -151,9 +154,10 @@ __global__ void __launch_bounds__(kPThreads, 2) partition_scatter_kernel(const _
       if (keep[j]) { pos[j] = s_off[pid[j]] + rank[j]; dst[pos[j]] = s_gbas[pid[j]] + rank[j]; stage[pos[j]] = k0[j]; }
     }
     __syncthreads();
-    if (p.key_out_width == 8) { for (uint32_t i = threadIdx.x; i < total; i += kPThreads) p.out_k0[dst[i]] = stage[i]; }
+    if (p.out_k0 == nullptr) { /* owner-rank partitioning permutes the caller's columns only */ }
+    else if (p.key_out_width == 8) { for (uint32_t i = threadIdx.x; i < total; i += kPThreads) p.out_k0[dst[i]] = stage[i]; }
     else { for (uint32_t i = threadIdx.x; i < total; i += kPThreads) reinterpret_cast<uint32_t*>(p.out_k0)[dst[i]] = (uint32_t)stage[i]; }
-    if (p.a.table.key_words == 2) {
+    if (p.a.table.key_words == 2 && p.out_k1 != nullptr) {
       __syncthreads();
 #pragma unroll
       for (int j = 0; j < kPRows; ++j) if (keep[j]) stage[pos[j]] = k1[j];

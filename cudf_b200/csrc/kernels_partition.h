@@ -19,10 +19,11 @@ struct PartParams {
   AggParams a;              // key columns, num_rows, table (capacity + key_words decide the partition of a key)
   int32_t log2_parts;       // P = 1 << log2_parts, P <= 4096
   int32_t slot_shift;       // partition = slot >> slot_shift  (slot_shift = log2(capacity) - log2_parts)
+  int32_t mod_parts;        // > 0: partition = hash2(key) % mod_parts instead (multi-GPU exchange: owner rank of a key)
   uint32_t* counts;         // [P]   rows per partition (zeroed by the caller)
   uint32_t* offsets;        // [P+1] exclusive scan; offsets[P] = rows kept (rows with a null key under EXCLUDE are dropped)
   uint32_t* cursors;        // [P]   running write positions
-  uint64_t* out_k0;         // packed key, low word (8-byte elements, or 4-byte when key_out_width == 4)
+  uint64_t* out_k0;         // packed key, low word (8-byte elements, or 4-byte when key_out_width == 4); nullptr: not written
   uint64_t* out_k1;         // high word when key_words == 2
   int32_t key_out_width;
   int32_t num_vals;

@@ -54,6 +54,7 @@ int32_t target_type(int32_t t, int32_t k)
   switch (k) {
     case BGB_MIN: case BGB_MAX: return t;
     case BGB_COUNT_VALID: case BGB_COUNT_ALL: case BGB_ARGMIN: case BGB_ARGMAX: return BGB_INT32;
+    case BGB_MERGE_COUNT: return t == BGB_INT32 ? BGB_INT32 : -1;
     case BGB_SUM:
       if (is_integral(t)) return BGB_INT64;
       if (is_floating(t) || is_duration(t) || is_decimal(t)) return t;
@@ -83,7 +84,7 @@ static bool kind_is_hash_capable(int32_t k)
   // is_hash_aggregation (/root/reference/cpp/src/groupby/common/utils.hpp:66-86) minus SUM_OVERFLOW (not built yet)
   switch (k) {
     case BGB_SUM: case BGB_PRODUCT: case BGB_MIN: case BGB_MAX: case BGB_COUNT_VALID: case BGB_COUNT_ALL: case BGB_SUM_OF_SQUARES:
-    case BGB_MEAN: case BGB_M2: case BGB_VARIANCE: case BGB_STD: case BGB_ARGMIN: case BGB_ARGMAX: return true;
+    case BGB_MEAN: case BGB_M2: case BGB_VARIANCE: case BGB_STD: case BGB_ARGMIN: case BGB_ARGMAX: case BGB_MERGE_COUNT: return true;
     default: return false;
   }
 }
@@ -203,6 +204,8 @@ int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_nul
           o.op = o.acc_op == ACC_PROD_F64 ? OUT_COPY_F64 : o.acc_op == ACC_PROD_F32 ? OUT_COPY_F32 : OUT_COPY_I64; break;
         case BGB_MIN: o.acc_op = ACC_MIN; o.acc_a = get_acc(plan, vc, ACC_MIN); o.op = OUT_MINMAX; break;
         case BGB_MAX: o.acc_op = ACC_MAX; o.acc_a = get_acc(plan, vc, ACC_MAX); o.op = OUT_MINMAX; break;
+        case BGB_MERGE_COUNT:  // sum of partial counts, narrowed back to size_type (a merged group has < 2^31 rows)
+          o.acc_op = ACC_SUM_I64; o.acc_a = get_acc(plan, vc, ACC_SUM_I64); o.op = OUT_COPY_I64; o.nullable = false; break;
         case BGB_COUNT_VALID: o.acc_op = ACC_COUNT_VALID; o.acc_a = need_cnt(); o.op = OUT_COUNT; o.nullable = false; break;
         case BGB_COUNT_ALL: o.acc_op = ACC_COUNT_ALL; o.acc_a = get_acc(plan, -1, ACC_COUNT_ALL); o.op = OUT_COUNT; o.nullable = false; break;
         case BGB_ARGMIN: case BGB_ARGMAX:

@@ -57,7 +57,10 @@ typedef enum bgb_type_id {
 typedef enum bgb_agg_kind {
   BGB_SUM = 0, BGB_SUM_OVERFLOW = 1, BGB_PRODUCT = 2, BGB_MIN = 3, BGB_MAX = 4, BGB_COUNT_VALID = 5, BGB_COUNT_ALL = 6,
   BGB_ANY = 7, BGB_ALL = 8, BGB_SUM_OF_SQUARES = 9, BGB_MEAN = 10, BGB_M2 = 11, BGB_VARIANCE = 12, BGB_STD = 13,
-  BGB_MEDIAN = 14, BGB_QUANTILE = 15, BGB_ARGMAX = 16, BGB_ARGMIN = 17, BGB_NUNIQUE = 18, BGB_NTH_ELEMENT = 19
+  BGB_MEDIAN = 14, BGB_QUANTILE = 15, BGB_ARGMAX = 16, BGB_ARGMIN = 17, BGB_NUNIQUE = 18, BGB_NTH_ELEMENT = 19,
+  /* library extension used when MERGING partial results (streaming_groupby::merge / distributed reduce step): the sum
+   * of INT32 partial counts, returned as INT32 like a COUNT (cpp/src/groupby/streaming_groupby/merge.cu:30-144) */
+  BGB_MERGE_COUNT = 100
 } bgb_agg_kind;
 
 /* POD mirror of cudf::column_view's fields (/root/reference/cpp/include/cudf/column/column_view.hpp:236-243):
@@ -180,6 +183,30 @@ int bgb_groupby_host(const bgb_column_view* host_keys, int32_t num_keys, int32_t
                      int32_t* num_groups, bgb_host_column** out_keys, bgb_host_column** out_results,
                      int32_t* num_results);
 void bgb_free_host_result(bgb_host_column* cols, int32_t n);
+
+/* ---- multi-GPU building blocks (one process per GPU; the exchange itself is an NCCL all-to-all run by the host layer,
+ *      cudf_b200/distributed.py) --------------------------------------------------------------------- */
+
+/* Permute `cols` (all with as many rows as the keys) into num_parts contiguous runs, run r holding the rows whose key has
+ * hash2(key) % num_parts == r (null keys hash like any other packed image). out_cols[i].data receives the permuted
+ * elements; for a column with a null mask, out_cols[i].null_mask must point at ONE BYTE PER ROW (uint8_t*, 1 = valid):
+ * validity travels through the exchange as bytes and is packed again with bgb_bytes_to_bitmask on the receiving side.
+ * part_offsets_host[num_parts + 1] (host) receives the run boundaries; the call synchronises `stream` once.
+ * Role of cudf::hash_partition in the reference's distributed callers (cpp/include/cudf/partitioning.hpp:103-145). */
+int bgb_partition_by_key_hash(const bgb_column_view* keys, int32_t num_keys, const bgb_column_view* cols, int32_t num_cols,
+                              int32_t num_parts, bgb_mutable_column* out_cols, int32_t* part_offsets_host, void* stream);
+
+/* validity bytes (1 = valid) -> cudf bitmask words ((n + 31) / 32 of them); *null_count_host = number of zero bytes */
+int bgb_bytes_to_bitmask(const uint8_t* valid_bytes, int64_t n, uint32_t* mask_words, int32_t* null_count_host, void* stream);
+
+/* MEAN / M2 / VARIANCE / STD from MERGED partial columns: sum (and sumsq, unused for MEAN) are the merged SUM /
+ * SUM_OF_SQUARES columns (INT64, UINT64, FLOAT32, FLOAT64, or a duration type for MEAN), count the merged INT32 count.
+ * out->data receives n FLOAT64 values (the duration type for a duration MEAN); out->null_mask, when not NULL, receives
+ * the validity words (MEAN: count > 0; VARIANCE/STD: count - ddof > 0) and out->null_count the number of nulls.
+ * Same arithmetic as the single-GPU finalisers (cpp/src/groupby/hash/hash_compound_agg_finalizer.cu:94-133,
+ * cpp/src/groupby/common/m2_var_std.cu:49-59,138-187). */
+int bgb_finalize_moments(int32_t kind, int32_t ddof, const bgb_column_view* sum, const bgb_column_view* sumsq,
+                         const bgb_column_view* count, bgb_mutable_column* out, void* stream);
 
 /* ---- synthetic inputs (SURVEY.md 8d generators; bench + tests only) --------------------------------------------- */
 
