@@ -1,0 +1,291 @@
+// Header-only C++ host layer over the C ABI (include/bgb.h) with the shape of the reference's public groupby API:
+//   cudf::groupby::groupby(table_view keys, null_policy).aggregate(span<aggregation_request>, stream)
+//   (/root/reference/cpp/include/cudf/groupby.hpp:54-184), aggregation factories
+//   (/root/reference/cpp/include/cudf/aggregation.hpp:293-420), error classes (cudf/utilities/error.hpp:35-97).
+// Device memory comes from cudaMallocAsync on the call's stream (the role of the rmm resource). No compute here:
+// every call forwards to libbgb.so; a missing GPU or library is an exception, never a fallback.
+#pragma once
+
+#include <cuda_runtime_api.h>
+
+#include <cstdint>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../bgb.h"
+
+namespace cudf_b200 {
+
+using size_type = int32_t;  // cudf::size_type (cudf/types.hpp:76)
+
+enum class type_id : int32_t {  // cudf::type_id (cudf/types.hpp:185-217)
+  EMPTY = 0, INT8, INT16, INT32, INT64, UINT8, UINT16, UINT32, UINT64, FLOAT32, FLOAT64, BOOL8,
+  TIMESTAMP_DAYS, TIMESTAMP_SECONDS, TIMESTAMP_MILLISECONDS, TIMESTAMP_MICROSECONDS, TIMESTAMP_NANOSECONDS,
+  DURATION_DAYS, DURATION_SECONDS, DURATION_MILLISECONDS, DURATION_MICROSECONDS, DURATION_NANOSECONDS,
+  DICTIONARY32, STRING, LIST, DECIMAL32, DECIMAL64, DECIMAL128, STRUCT
+};
+enum class null_policy : bool { EXCLUDE = false, INCLUDE = true };
+
+struct logic_error : std::logic_error { using std::logic_error::logic_error; };     // cudf::logic_error
+struct cuda_error : std::runtime_error { using std::runtime_error::runtime_error; };  // cudf::cuda_error
+struct unsupported_error : std::runtime_error { using std::runtime_error::runtime_error; };  // "take the sort path"
+
+namespace detail {
+inline void throw_on(int status)
+{
+  if (status == BGB_OK) return;
+  std::string msg = bgb_last_error();
+  if (status == BGB_INVALID_ARGUMENT) throw logic_error(msg);
+  if (status == BGB_UNSUPPORTED) throw unsupported_error(msg);
+  if (status == BGB_OUT_OF_MEMORY) throw std::bad_alloc();
+  throw cuda_error(msg);
+}
+inline void cuda_try(cudaError_t e)
+{
+  if (e != cudaSuccess) throw cuda_error(std::string(cudaGetErrorName(e)) + ": " + cudaGetErrorString(e));
+}
+inline size_type width_of(type_id t)
+{
+  switch (t) {
+    case type_id::INT8: case type_id::UINT8: case type_id::BOOL8: return 1;
+    case type_id::INT16: case type_id::UINT16: return 2;
+    case type_id::INT32: case type_id::UINT32: case type_id::FLOAT32: case type_id::TIMESTAMP_DAYS: case type_id::DURATION_DAYS:
+    case type_id::DECIMAL32: return 4;
+    case type_id::EMPTY: case type_id::DICTIONARY32: case type_id::STRING: case type_id::LIST: case type_id::DECIMAL128:
+    case type_id::STRUCT: return 0;
+    default: return 8;
+  }
+}
+}  // namespace detail
+
+struct data_type {
+  type_id id_{type_id::EMPTY};
+  int32_t scale_{0};
+  data_type() = default;
+  explicit data_type(type_id id, int32_t scale = 0) : id_(id), scale_(scale) {}
+  type_id id() const { return id_; }
+  int32_t scale() const { return scale_; }
+};
+
+// non-owning view with cudf::column_view's fields (cudf/column/column_view.hpp:236-243)
+class column_view {
+ public:
+  column_view() = default;
+  column_view(data_type type, size_type size, void const* data, uint32_t const* null_mask = nullptr, size_type null_count = 0,
+              size_type offset = 0)
+    : _type(type), _size(size), _data(data), _null_mask(null_mask), _null_count(null_mask ? null_count : 0), _offset(offset) {}
+  data_type type() const { return _type; }
+  size_type size() const { return _size; }
+  size_type null_count() const { return _null_count; }
+  bool has_nulls() const { return _null_count > 0; }
+  bool nullable() const { return _null_mask != nullptr; }
+  size_type offset() const { return _offset; }
+  void const* head() const { return _data; }
+  uint32_t const* null_mask() const { return _null_mask; }
+  bgb_column_view abi() const
+  {
+    return {static_cast<int32_t>(_type.id()), _type.scale(), _size, _null_count, _offset, 0, _data, _null_mask};
+  }
+
+ private:
+  data_type _type;
+  size_type _size{0};
+  void const* _data{nullptr};
+  uint32_t const* _null_mask{nullptr};
+  size_type _null_count{0};
+  size_type _offset{0};
+};
+
+// owning device column (stream-ordered allocation)
+class column {
+ public:
+  column(data_type type, size_type size, bool with_mask, cudaStream_t stream) : _type(type), _size(size), _stream(stream)
+  {
+    size_t bytes = static_cast<size_t>(size) * detail::width_of(type.id());
+    if (bytes) detail::cuda_try(cudaMallocAsync(&_data, bytes, stream));
+    if (with_mask && size) detail::cuda_try(cudaMallocAsync(reinterpret_cast<void**>(&_mask), sizeof(uint32_t) * ((size + 31) / 32), stream));
+  }
+  column(column const&)            = delete;
+  column& operator=(column const&) = delete;
+  ~column()
+  {
+    if (_data) cudaFreeAsync(_data, _stream);
+    if (_mask) cudaFreeAsync(_mask, _stream);
+  }
+  // host -> device convenience for tests and examples (cudf::test::fixed_width_column_wrapper's role)
+  template <typename T>
+  static std::unique_ptr<column> from_host(type_id id, std::vector<T> const& values, std::vector<bool> const& valid = {},
+                                           cudaStream_t stream = nullptr)
+  {
+    auto const n = static_cast<size_type>(values.size());
+    auto c       = std::make_unique<column>(data_type{id}, n, !valid.empty(), stream);
+    if (n) detail::cuda_try(cudaMemcpyAsync(c->_data, values.data(), sizeof(T) * n, cudaMemcpyHostToDevice, stream));
+    if (!valid.empty() && n) {
+      std::vector<uint32_t> words((n + 31) / 32, 0u);
+      for (size_type i = 0; i < n; ++i) {
+        if (valid[i]) words[i / 32] |= 1u << (i % 32);
+        else ++c->_null_count;
+      }
+      detail::cuda_try(cudaMemcpyAsync(c->_mask, words.data(), sizeof(uint32_t) * words.size(), cudaMemcpyHostToDevice, stream));
+    }
+    detail::cuda_try(cudaStreamSynchronize(stream));
+    return c;
+  }
+  template <typename T>
+  std::pair<std::vector<T>, std::vector<bool>> to_host() const
+  {
+    std::vector<T> v(_size);
+    std::vector<bool> ok(_size, true);
+    if (_size) detail::cuda_try(cudaMemcpyAsync(v.data(), _data, sizeof(T) * _size, cudaMemcpyDeviceToHost, _stream));
+    std::vector<uint32_t> words((_size + 31) / 32);
+    if (_mask && _size) detail::cuda_try(cudaMemcpyAsync(words.data(), _mask, sizeof(uint32_t) * words.size(), cudaMemcpyDeviceToHost, _stream));
+    detail::cuda_try(cudaStreamSynchronize(_stream));
+    if (_mask)
+      for (size_type i = 0; i < _size; ++i) ok[i] = (words[i / 32] >> (i % 32)) & 1u;
+    return {std::move(v), std::move(ok)};
+  }
+  column_view view() const { return column_view(_type, _size, _data, _mask, _null_count, 0); }
+  data_type type() const { return _type; }
+  size_type size() const { return _size; }
+  size_type null_count() const { return _null_count; }
+  bool nullable() const { return _mask != nullptr; }
+  void set_null_count(size_type n) { _null_count = n; }
+  bgb_mutable_column abi_mutable() { return {static_cast<int32_t>(_type.id()), _size, _data, _mask, 0, 0}; }
+
+ private:
+  data_type _type;
+  size_type _size;
+  void* _data{nullptr};
+  uint32_t* _mask{nullptr};
+  size_type _null_count{0};
+  cudaStream_t _stream;
+};
+
+class table_view {
+ public:
+  table_view() = default;
+  table_view(std::vector<column_view> cols) : _cols(std::move(cols)) {}
+  size_type num_columns() const { return static_cast<size_type>(_cols.size()); }
+  size_type num_rows() const { return _cols.empty() ? 0 : _cols[0].size(); }
+  column_view const& column(size_type i) const { return _cols.at(i); }
+  auto begin() const { return _cols.begin(); }
+  auto end() const { return _cols.end(); }
+
+ private:
+  std::vector<column_view> _cols;
+};
+
+class table {
+ public:
+  explicit table(std::vector<std::unique_ptr<column>> cols) : _cols(std::move(cols)) {}
+  size_type num_columns() const { return static_cast<size_type>(_cols.size()); }
+  size_type num_rows() const { return _cols.empty() ? 0 : _cols[0]->size(); }
+  column const& get_column(size_type i) const { return *_cols.at(i); }
+
+ private:
+  std::vector<std::unique_ptr<column>> _cols;
+};
+
+// cudf::groupby_aggregation and its factories (cudf/aggregation.hpp:293-420)
+struct groupby_aggregation {
+  int32_t kind;
+  int32_t ddof{1};
+};
+inline std::unique_ptr<groupby_aggregation> make_agg(int32_t kind, int32_t ddof = 1) { return std::unique_ptr<groupby_aggregation>(new groupby_aggregation{kind, ddof}); }
+inline auto make_sum_aggregation() { return make_agg(BGB_SUM); }
+inline auto make_product_aggregation() { return make_agg(BGB_PRODUCT); }
+inline auto make_min_aggregation() { return make_agg(BGB_MIN); }
+inline auto make_max_aggregation() { return make_agg(BGB_MAX); }
+inline auto make_count_aggregation(null_policy null_handling = null_policy::EXCLUDE)
+{
+  return make_agg(null_handling == null_policy::EXCLUDE ? BGB_COUNT_VALID : BGB_COUNT_ALL);
+}
+inline auto make_sum_of_squares_aggregation() { return make_agg(BGB_SUM_OF_SQUARES); }
+inline auto make_mean_aggregation() { return make_agg(BGB_MEAN); }
+inline auto make_m2_aggregation() { return make_agg(BGB_M2); }
+inline auto make_variance_aggregation(size_type ddof = 1) { return make_agg(BGB_VARIANCE, ddof); }
+inline auto make_std_aggregation(size_type ddof = 1) { return make_agg(BGB_STD, ddof); }
+inline auto make_argmax_aggregation() { return make_agg(BGB_ARGMAX); }
+inline auto make_argmin_aggregation() { return make_agg(BGB_ARGMIN); }
+inline auto make_median_aggregation() { return make_agg(BGB_MEDIAN); }
+
+namespace groupby {
+
+struct aggregation_request {  // cudf/groupby.hpp:54-57
+  column_view values;
+  std::vector<std::unique_ptr<groupby_aggregation>> aggregations;
+};
+struct aggregation_result {  // cudf/groupby.hpp:67-70
+  std::vector<std::unique_ptr<column>> results;
+};
+
+class groupby {
+ public:
+  explicit groupby(table_view const& keys, null_policy null_handling = null_policy::EXCLUDE) : _keys(keys), _null_handling(null_handling) {}
+
+  // detail::hash::can_use_hash_groupby (hash/groupby.cu:115-131) for this library
+  bool can_use_hash_groupby(std::vector<aggregation_request> const& requests) const
+  {
+    marshalled m(_keys, requests);
+    int32_t ok = 0;
+    detail::throw_on(bgb_can_use_hash_groupby(m.keys.data(), (int32_t)m.keys.size(), m.reqs.data(), (int32_t)m.reqs.size(), &ok));
+    return ok != 0;
+  }
+
+  // groupby::aggregate (cudf/groupby.hpp:148-184): unique keys (arbitrary order) + one aggregation_result per request
+  std::pair<std::unique_ptr<table>, std::vector<aggregation_result>> aggregate(std::vector<aggregation_request> const& requests,
+                                                                               cudaStream_t stream = nullptr) const
+  {
+    marshalled m(_keys, requests);
+    bgb_groupby* h = nullptr;
+    int32_t n      = 0;
+    detail::throw_on(bgb_groupby_build(m.keys.data(), (int32_t)m.keys.size(), _null_handling == null_policy::INCLUDE, m.reqs.data(),
+                                       (int32_t)m.reqs.size(), stream, nullptr, nullptr, &h, &n));
+    struct guard { bgb_groupby* h; ~guard() { bgb_groupby_destroy(h); } } g{h};
+    std::vector<std::unique_ptr<column>> kcols;
+    std::vector<bgb_mutable_column> km, rm;
+    for (int32_t i = 0; i < (int32_t)m.keys.size(); ++i) {
+      int32_t t, s, nl;
+      detail::throw_on(bgb_groupby_key_info(h, i, &t, &s, &nl));
+      kcols.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream));
+      km.push_back(kcols.back()->abi_mutable());
+    }
+    std::vector<aggregation_result> results(requests.size());
+    for (size_t i = 0; i < requests.size(); ++i)
+      for (size_t j = 0; j < requests[i].aggregations.size(); ++j) {
+        int32_t t, s, nl;
+        detail::throw_on(bgb_groupby_result_info(h, (int32_t)i, (int32_t)j, &t, &s, &nl));
+        results[i].results.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream));
+        rm.push_back(results[i].results.back()->abi_mutable());
+      }
+    detail::throw_on(bgb_groupby_emit(h, km.data(), rm.data(), stream));
+    for (size_t i = 0; i < kcols.size(); ++i) kcols[i]->set_null_count(km[i].null_count);
+    size_t q = 0;
+    for (auto& r : results)
+      for (auto& c : r.results) c->set_null_count(rm[q++].null_count);
+    return {std::make_unique<table>(std::move(kcols)), std::move(results)};
+  }
+
+ private:
+  struct marshalled {
+    std::vector<bgb_column_view> keys;
+    std::vector<std::vector<bgb_aggregation>> aggs;
+    std::vector<bgb_request> reqs;
+    marshalled(table_view const& k, std::vector<aggregation_request> const& requests) : aggs(requests.size())
+    {
+      for (auto const& c : k) keys.push_back(c.abi());
+      for (size_t i = 0; i < requests.size(); ++i) {
+        for (auto const& a : requests[i].aggregations) aggs[i].push_back({a->kind, a->ddof});
+        reqs.push_back({requests[i].values.abi(), aggs[i].data(), (int32_t)aggs[i].size(), 0});
+      }
+    }
+  };
+  table_view _keys;
+  null_policy _null_handling;
+};
+
+}  // namespace groupby
+}  // namespace cudf_b200
