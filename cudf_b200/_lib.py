@@ -31,6 +31,10 @@ class CudaError(BgbError):       # cudf::cuda_error
     pass
 
 
+class PeerOverflow(BgbError):    # BGB_PEER_OVERFLOW: every rank of the exchange reports it in the same step
+    pass
+
+
 class ColumnView(C.Structure):
     _fields_ = [("type_id", C.c_int32), ("scale", C.c_int32), ("size", C.c_int32), ("null_count", C.c_int32),
                 ("offset", C.c_int32), ("reserved", C.c_int32), ("data", C.c_void_p), ("null_mask", C.c_void_p)]
@@ -102,6 +106,15 @@ def lib():
     L.bgb_bytes_to_bitmask.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_int32), C.c_void_p]
     L.bgb_finalize_moments.argtypes = [C.c_int32, C.c_int32, C.POINTER(ColumnView), C.POINTER(ColumnView), C.POINTER(ColumnView),
                                        C.POINTER(MutableColumn), C.c_void_p]
+    L.bgb_peer_create.argtypes = [C.c_int32, C.c_int32, C.c_int64, C.POINTER(C.c_void_p)]
+    L.bgb_peer_export.argtypes = [C.c_void_p, C.c_void_p]
+    L.bgb_peer_attach.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+    L.bgb_peer_attach_local.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
+    L.bgb_peer_segment_capacity.argtypes = [C.c_void_p, C.c_int32]
+    L.bgb_peer_segment_capacity.restype = C.c_int64
+    L.bgb_peer_destroy.argtypes = [C.c_void_p]
+    L.bgb_peer_destroy.restype = None
+    L.bgb_groupby_build_peer.argtypes = [C.c_void_p] + list(L.bgb_groupby_build.argtypes)
     _lib = L
     return L
 
@@ -114,4 +127,6 @@ def check(status: int):
         raise LogicError(status, msg)
     if status == 2:
         raise UnsupportedError(status, msg)
+    if status == 6:
+        raise PeerOverflow(status, msg)
     raise CudaError(status, msg)

@@ -162,4 +162,24 @@ __device__ __forceinline__ int64_t raw_to_i64(uint64_t raw, int src)
   }
 }
 
+// CAS-loop products (no hardware atomic multiply; update_target_element<Source, PRODUCT>)
+__device__ __forceinline__ void atomic_mul_i64(unsigned long long* addr, int64_t v)
+{
+  unsigned long long old = *addr, assumed;
+  do { assumed = old; old = atomicCAS(addr, assumed, (unsigned long long)((int64_t)assumed * v)); } while (old != assumed);
+}
+__device__ __forceinline__ void atomic_mul_f64(unsigned long long* addr, double v)
+{
+  unsigned long long old = *addr, assumed;
+  do {
+    assumed = old;
+    old     = atomicCAS(addr, assumed, (unsigned long long)__double_as_longlong(__longlong_as_double((long long)assumed) * v));
+  } while (old != assumed);
+}
+__device__ __forceinline__ void atomic_mul_f32(unsigned int* addr, float v)
+{
+  unsigned int old = *addr, assumed;
+  do { assumed = old; old = atomicCAS(addr, assumed, __float_as_uint(__uint_as_float(assumed) * v)); } while (old != assumed);
+}
+
 }  // namespace bgb

@@ -1,14 +1,17 @@
 // C ABI: bgb_groupby_build / _emit / _result_info / _destroy.  See include/bgb.h for the contract.
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "errors.h"
 #include "fastpaths.h"
 #include "kernels_partition.h"
+#include "kernels_peer.h"
 #include "plan.h"
 #include "pool.h"
 #include "profiler.h"
@@ -189,15 +192,15 @@ int run_partitioned(bgb_groupby* h, int num_sms, bool& done)
 
 }  // namespace
 
-extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
-                                 const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
-                                 const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups)
+static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
+                       const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
+                       const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups, bool rank_independent = false)
 {
   if (!out_handle || !num_groups) return set_error(BGB_INVALID_ARGUMENT, "null output pointer");
   *out_handle = nullptr;
   *num_groups = 0;
   bgb_groupby* h = new bgb_groupby();
-  int rc = make_plan(keys, num_keys, include_null_keys, requests, num_requests, h->plan);
+  int rc = make_plan(keys, num_keys, include_null_keys, requests, num_requests, h->plan, rank_independent);
   if (rc != BGB_OK) { delete h; return rc; }
   h->stream = (cudaStream_t)stream;
   if (alloc && alloc->allocate && alloc->deallocate) { h->alloc = *alloc; h->has_alloc = true; }
@@ -370,6 +373,13 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
   return BGB_OK;
 }
 
+extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
+                                 const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
+                                 const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups)
+{
+  return build_local(keys, num_keys, include_null_keys, requests, num_requests, stream, alloc, options, out_handle, num_groups);
+}
+
 extern "C" int bgb_groupby_result_info(const bgb_groupby* h, int32_t request, int32_t aggregation, int32_t* type_id,
                                        int32_t* scale, int32_t* nullable)
 {
@@ -488,4 +498,267 @@ extern "C" void bgb_groupby_destroy(bgb_groupby* h)
   if (!h) return;
   h->free_all();
   delete h;
+}
+
+// =====================================================================================================================
+// Peer-memory multi-GPU build: local aggregation -> records scattered into the owners' regions over NVLink -> merge.
+// =====================================================================================================================
+
+struct bgb_peer {
+  int rank = 0, world = 1, device = 0;
+  uint8_t* buffer = nullptr;          // header page + two regions (double-buffered by step parity)
+  size_t region_bytes = 0;
+  uint8_t* peer_buffer[kMaxPeers] = {};  // every rank's buffer as mapped into this process (own buffer at [rank])
+  bool opened[kMaxPeers] = {};           // mapped through cudaIpcOpenMemHandle (must be closed)
+  bool same_process = false;             // some peer was attached with bgb_peer_attach_local
+  uint32_t epoch = 0;
+  uint64_t timeout_ns = 20ull * 1000 * 1000 * 1000;
+};
+
+extern "C" int bgb_peer_create(int32_t rank, int32_t world, int64_t region_bytes, bgb_peer** out)
+{
+  if (!out) return set_error(BGB_INVALID_ARGUMENT, "null output pointer");
+  *out = nullptr;
+  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return set_error(BGB_INVALID_ARGUMENT, "rank %d / world %d (at most %d ranks)", rank, world, kMaxPeers);
+  if (region_bytes < 4096) return set_error(BGB_INVALID_ARGUMENT, "region_bytes must be at least 4096");
+  bgb_peer* p = new bgb_peer();
+  p->rank = rank; p->world = world;
+  p->region_bytes = ((size_t)region_bytes + 255) & ~(size_t)255;
+  cudaGetDevice(&p->device);
+  // plain cudaMalloc: the legacy IPC handle needs a cudaMalloc'ed base (pool memory cannot be exported this way)
+  int rc = check_cuda(cudaMalloc((void**)&p->buffer, kPeerHeaderBytes + 2 * p->region_bytes), "peer buffer");
+  if (!rc) rc = check_cuda(cudaMemset(p->buffer, 0, kPeerHeaderBytes), "peer header");
+  if (!rc) rc = check_cuda(cudaDeviceSynchronize(), "peer header");
+  if (rc) { if (p->buffer) cudaFree(p->buffer); delete p; return rc; }
+  p->peer_buffer[rank] = p->buffer;
+  if (const char* t = getenv("BGB_PEER_TIMEOUT_MS")) p->timeout_ns = (uint64_t)atoll(t) * 1000000ull;
+  *out = p;
+  return BGB_OK;
+}
+
+extern "C" int bgb_peer_export(const bgb_peer* p, void* handle_out)
+{
+  if (!p || !handle_out) return set_error(BGB_INVALID_ARGUMENT, "null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == BGB_PEER_HANDLE_BYTES, "handle size");
+  cudaIpcMemHandle_t h;
+  int rc = check_cuda(cudaIpcGetMemHandle(&h, p->buffer), "cudaIpcGetMemHandle");
+  if (!rc) memcpy(handle_out, &h, sizeof h);
+  return rc;
+}
+
+extern "C" int bgb_peer_attach(bgb_peer* p, int32_t peer_rank, const void* handle)
+{
+  if (!p || !handle || peer_rank < 0 || peer_rank >= p->world) return set_error(BGB_INVALID_ARGUMENT, "bad peer rank %d", peer_rank);
+  if (peer_rank == p->rank) return BGB_OK;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof h);
+  void* ptr = nullptr;
+  int rc = check_cuda(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess), "cudaIpcOpenMemHandle");
+  if (rc) return rc;
+  p->peer_buffer[peer_rank] = (uint8_t*)ptr;
+  p->opened[peer_rank] = true;
+  return BGB_OK;
+}
+
+extern "C" int bgb_peer_attach_local(bgb_peer* p, int32_t peer_rank, const bgb_peer* other)
+{
+  if (!p || !other || peer_rank < 0 || peer_rank >= p->world) return set_error(BGB_INVALID_ARGUMENT, "bad peer rank %d", peer_rank);
+  if (other->region_bytes != p->region_bytes || other->world != p->world) return set_error(BGB_INVALID_ARGUMENT, "peer contexts differ in shape");
+  if (other->device != p->device) {
+    int can = 0;
+    cudaDeviceCanAccessPeer(&can, p->device, other->device);
+    if (!can) return set_error(BGB_UNSUPPORTED, "device %d cannot access device %d", p->device, other->device);
+    cudaError_t e = cudaDeviceEnablePeerAccess(other->device, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return check_cuda(e, "cudaDeviceEnablePeerAccess");
+    cudaGetLastError();
+  }
+  p->peer_buffer[peer_rank] = other->buffer;
+  p->same_process = true;
+  return BGB_OK;
+}
+
+extern "C" void bgb_peer_destroy(bgb_peer* p)
+{
+  if (!p) return;
+  for (int r = 0; r < p->world; ++r)
+    if (p->opened[r]) cudaIpcCloseMemHandle(p->peer_buffer[r]);
+  if (p->buffer) cudaFree(p->buffer);
+  delete p;
+}
+
+extern "C" int64_t bgb_peer_segment_capacity(const bgb_peer* p, int32_t record_bytes)
+{
+  if (!p || record_bytes <= 0) return 0;
+  return (int64_t)((p->region_bytes / ((size_t)p->world * (size_t)record_bytes)) & ~(size_t)31);
+}
+
+extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
+                                      const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
+                                      const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups)
+{
+  if (!peer) return set_error(BGB_INVALID_ARGUMENT, "null peer context");
+  for (int r = 0; r < peer->world; ++r)
+    if (!peer->peer_buffer[r]) return set_error(BGB_INVALID_ARGUMENT, "rank %d is not attached", r);
+  bgb_groupby* h = nullptr;
+  int32_t g_local = 0;
+  // ---- (1) this rank's rows through the single-GPU path
+  int rc = build_local(keys, num_keys, include_null_keys, requests, num_requests, stream, alloc, options, &h, &g_local, /*rank_independent=*/true);
+  if (rc) return rc;  // NOTE: an error here leaves the other ranks waiting until their timeout
+  *out_handle = nullptr;
+  *num_groups = 0;
+  Plan& pl       = h->plan;
+  cudaStream_t s = h->stream;
+#define FAIL_RC(expr)            \
+  do {                           \
+    int rc_ = (expr);            \
+    if (rc_ != BGB_OK) { h->free_all(); delete h; return rc_; } \
+  } while (0)
+  for (const AccPlan& a : pl.accs)
+    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX) FAIL_RC(set_error(BGB_UNSUPPORTED, "ARGMIN/ARGMAX have no cross-rank merge (row numbers are rank-local)"));
+  if (pl.accs.size() > (size_t)kMaxAccs) FAIL_RC(set_error(BGB_UNSUPPORTED, "more than %d accumulators in one peer exchange", kMaxAccs));
+
+  const int world = peer->world, me = peer->rank;
+  const uint32_t epoch = ++peer->epoch;
+  const int parity     = (int)(epoch & 1u);
+  // ---- record layout inside a region: key word arrays, then one array per accumulator, each world * cap entries
+  size_t record_bytes = 8 * (size_t)pl.key_words;
+  for (const AccPlan& a : pl.accs) record_bytes += acc_cell_bytes(a.op);
+  const uint64_t cap = (uint64_t)bgb_peer_segment_capacity(peer, (int32_t)record_bytes);
+  if (cap == 0) FAIL_RC(set_error(BGB_INVALID_ARGUMENT, "peer region too small for %d ranks of %zu-byte records", world, record_bytes));
+  const uint64_t entries = (uint64_t)world * cap;
+  uint64_t off           = 8 * entries;
+  const uint64_t key1_off = off;
+  if (pl.key_words == 2) off += 8 * entries;
+  std::vector<uint64_t> acc_off(pl.accs.size());
+  for (size_t a = 0; a < pl.accs.size(); ++a) { acc_off[a] = off; off += (uint64_t)acc_cell_bytes(pl.accs[a].op) * entries; }
+
+  uint32_t* scratch = (uint32_t*)h->dalloc(sizeof(uint32_t) * (3 * kMaxPeers + 4));  // cursors | wait output
+  if (!scratch) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "peer scratch"));
+  uint32_t* cursors  = scratch;
+  uint32_t* wait_out = scratch + kMaxPeers;
+  FAIL_RC(check_cuda(cudaMemsetAsync(cursors, 0, sizeof(uint32_t) * kMaxPeers, s), "peer cursors"));
+
+  // ---- (2) scatter the local groups into their owners' regions, then publish counts + epoch
+  h->prof.begin("peer_scatter");
+  if (g_local > 0) {
+    PeerScatterParams sp;
+    memset(&sp, 0, sizeof sp);
+    sp.keys = h->table.keys; sp.group_slots = h->group_slots; sp.num_groups = g_local;
+    sp.key_words = pl.key_words; sp.num_accs = (int)pl.accs.size(); sp.world = world; sp.me = me;
+    sp.cap = cap; sp.key1_off = key1_off; sp.cursors = cursors;
+    for (int r = 0; r < world; ++r) sp.region[r] = peer->peer_buffer[r] + kPeerHeaderBytes + (size_t)parity * peer->region_bytes;
+    for (size_t a = 0; a < pl.accs.size(); ++a) {
+      sp.acc[a].cells = pl.accs[a].cells; sp.acc[a].region_off = acc_off[a]; sp.acc[a].op = pl.accs[a].op;
+      sp.acc[a].cell_bytes = (uint8_t)acc_cell_bytes(pl.accs[a].op);
+    }
+    FAIL_RC(check_cuda(launch_peer_scatter(sp, s), "peer_scatter"));
+  }
+  {
+    PeerSignalParams gp;
+    memset(&gp, 0, sizeof gp);
+    for (int r = 0; r < world; ++r) gp.header[r] = (PeerHeader*)peer->peer_buffer[r];
+    gp.cursors = cursors; gp.cap = cap; gp.world = world; gp.me = me; gp.parity = parity; gp.epoch = epoch;
+    FAIL_RC(check_cuda(launch_peer_signal(gp, s), "peer_signal"));
+  }
+  h->prof.end();
+
+  // ---- (3) wait for every source, learn how many records arrived
+  h->prof.begin("peer_wait");
+  std::vector<uint32_t> got(2 * world + 1, 0);
+  if (!peer->same_process) {
+    // one process per GPU: a one-block kernel spins (bounded) on the flags, then hands counts to the host
+    FAIL_RC(check_cuda(launch_peer_wait((const PeerHeader*)peer->buffer, parity, epoch, world, peer->timeout_ns, wait_out, s), "peer_wait"));
+    h->prof.end();
+    FAIL_RC(check_cuda(cudaMemcpyAsync(got.data(), wait_out, sizeof(uint32_t) * got.size(), cudaMemcpyDeviceToHost, s), "peer counts"));
+    FAIL_RC(check_cuda(cudaStreamSynchronize(s), "peer wait sync"));
+  } else {
+    // ranks sharing a process (and possibly one GPU): a spinning kernel could sit in front of another rank's scatter in
+    // the same hardware queue, so the HOST polls the flags instead; counts are read only after the flags were seen
+    const PeerHeader* mine = (const PeerHeader*)peer->buffer;
+    std::vector<uint32_t> flags(world, 0);
+    const auto t0 = std::chrono::steady_clock::now();
+    for (;;) {
+      FAIL_RC(check_cuda(cudaMemcpyAsync(flags.data(), &mine->flag[parity][0], sizeof(uint32_t) * world, cudaMemcpyDeviceToHost, s), "peer flags"));
+      FAIL_RC(check_cuda(cudaStreamSynchronize(s), "peer flag sync"));
+      bool ready = true;
+      for (int r = 0; r < world; ++r) ready &= (int32_t)(flags[r] - epoch) >= 0;
+      if (ready) break;
+      if ((uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count() > peer->timeout_ns) { got[2 * world] = 1; break; }
+      std::this_thread::yield();
+    }
+    h->prof.end();
+    if (!got[2 * world]) {
+      FAIL_RC(check_cuda(cudaMemcpyAsync(got.data(), &mine->count[parity][0], sizeof(uint32_t) * world, cudaMemcpyDeviceToHost, s), "peer counts"));
+      FAIL_RC(check_cuda(cudaMemcpyAsync(got.data() + world, &mine->overflow[parity][0], sizeof(uint32_t) * world, cudaMemcpyDeviceToHost, s), "peer overflow"));
+      FAIL_RC(check_cuda(cudaStreamSynchronize(s), "peer wait sync"));
+    }
+  }
+  h->prof.resolve();
+  if (got[2 * world]) FAIL_RC(set_error(BGB_CUDA_ERROR, "peer exchange timed out waiting for another rank (epoch %u)", epoch));
+  uint64_t total = 0;
+  bool overflow  = false;
+  for (int r = 0; r < world; ++r) { total += got[r]; overflow |= got[world + r] != 0; }
+  // the local partial table is no longer needed (its records are in the owners' regions)
+  if (h->group_slots) { h->dfree(h->group_slots); h->group_slots = nullptr; }
+  if (h->table.keys) { h->dfree(h->table.keys); h->table.keys = nullptr; }
+  for (AccPlan& a : pl.accs) if (a.cells) { h->dfree(a.cells); a.cells = nullptr; }
+  if (overflow) FAIL_RC(set_error(BGB_PEER_OVERFLOW, "a peer segment (%llu records) is too small for this exchange", (unsigned long long)cap));
+  if (total > 0x7fffffffull) FAIL_RC(set_error(BGB_INVALID_ARGUMENT, "a rank would own more than 2^31-1 partial groups (cudf::size_type)"));
+
+  // ---- (4) final table sized for what arrived; merge; compact
+  uint32_t* status = (uint32_t*)h->dalloc(16 * sizeof(uint32_t));
+  if (!status) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "status alloc"));
+  h->table.status    = status;
+  h->table.key_words = pl.key_words;
+  const uint64_t capacity = next_pow2(std::max<uint64_t>(1024, 2 * total));
+  h->table.capacity       = capacity;
+  const uint64_t slots    = capacity + 1;
+  h->table.keys = (uint64_t*)h->dalloc(slots * 8 * pl.key_words);
+  if (!h->table.keys) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "final table keys"));
+  for (AccPlan& a : pl.accs) {
+    a.cells = h->dalloc(slots * acc_cell_bytes(a.op));
+    if (!a.cells) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "final table accumulators"));
+  }
+  h->prof.begin("peer_merge");
+  {
+    size_t na = pl.accs.size();
+    for (size_t b = 0; b == 0 || b < na; b += kMaxAccs) {
+      AggParams p;
+      fill_agg_params(*h, p, b, std::min(na, b + kMaxAccs));
+      p.init_keys = (b == 0);
+      FAIL_RC(check_cuda(launch_init_table(p, s), "init_table"));
+    }
+    PeerMergeParams mp;
+    memset(&mp, 0, sizeof mp);
+    mp.region = peer->buffer + kPeerHeaderBytes + (size_t)parity * peer->region_bytes;
+    mp.cap = cap; mp.key1_off = key1_off; mp.key_words = pl.key_words; mp.num_accs = (int)na; mp.world = world;
+    for (int r = 0; r < world; ++r) mp.prefix[r + 1] = mp.prefix[r] + got[r];
+    mp.table = h->table;
+    for (size_t a = 0; a < na; ++a) {
+      mp.acc[a].cells = pl.accs[a].cells; mp.acc[a].region_off = acc_off[a]; mp.acc[a].op = pl.accs[a].op;
+      mp.acc[a].cell_bytes = (uint8_t)acc_cell_bytes(pl.accs[a].op);
+    }
+    FAIL_RC(check_cuda(launch_peer_merge(mp, s), "peer_merge"));
+  }
+  h->prof.end();
+  const uint64_t max_groups = std::max<uint64_t>(1, std::min<uint64_t>(slots, total));
+  h->group_slots            = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
+  uint32_t* scan_state      = (uint32_t*)h->dalloc(compact_scan_state_bytes(capacity));
+  if (!h->group_slots || !scan_state) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "compaction scratch"));
+  h->prof.begin("compact_final");
+  FAIL_RC(check_cuda(launch_compact(h->table, h->group_slots, scan_state, s), "compact"));
+  h->prof.end();
+  uint32_t st[4] = {0, 0, 0, 0};
+  FAIL_RC(check_cuda(cudaMemcpyAsync(st, status, sizeof st, cudaMemcpyDeviceToHost, s), "status copy"));
+  FAIL_RC(check_cuda(cudaStreamSynchronize(s), "peer build sync"));
+  h->prof.resolve();
+  h->dfree(scan_state);
+  h->dfree(scratch);
+  if (st[0]) FAIL_RC(set_error(BGB_CUDA_ERROR, "final table overflow during the merge"));
+#undef FAIL_RC
+  h->num_groups = (int32_t)st[1];
+  h->path += "+peer";
+  *num_groups = h->num_groups;
+  *out_handle = h;
+  return BGB_OK;
 }

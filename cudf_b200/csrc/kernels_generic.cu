@@ -49,25 +49,6 @@ cudaError_t launch_init_table(const AggParams& p, cudaStream_t s)
 }
 
 // ------------------------------------------------------------------ one row into one accumulator
-__device__ __forceinline__ void atomic_mul_i64(unsigned long long* addr, int64_t v)
-{
-  unsigned long long old = *addr, assumed;
-  do { assumed = old; old = atomicCAS(addr, assumed, (unsigned long long)((int64_t)assumed * v)); } while (old != assumed);
-}
-__device__ __forceinline__ void atomic_mul_f64(unsigned long long* addr, double v)
-{
-  unsigned long long old = *addr, assumed;
-  do {
-    assumed = old;
-    old     = atomicCAS(addr, assumed, (unsigned long long)__double_as_longlong(__longlong_as_double((long long)assumed) * v));
-  } while (old != assumed);
-}
-__device__ __forceinline__ void atomic_mul_f32(unsigned int* addr, float v)
-{
-  unsigned int old = *addr, assumed;
-  do { assumed = old; old = atomicCAS(addr, assumed, __float_as_uint(__uint_as_float(assumed) * v)); } while (old != assumed);
-}
-
 __device__ __forceinline__ void apply_acc(const AccDesc& a, int64_t row, uint64_t slot)
 {
   const int64_t idx = (int64_t)a.offset + row;

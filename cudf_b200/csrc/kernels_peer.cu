@@ -1,0 +1,179 @@
+// Kernels of the peer-memory exchange (see kernels_peer.h). HBM / NVLink-bound byte movement; no tensor-core work.
+#include "device_utils.cuh"
+#include "kernels_peer.h"
+
+namespace bgb {
+namespace {
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p)
+{
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t global_timer_ns()
+{
+  uint64_t t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+}  // namespace
+
+// One record per local group: key words + every accumulator cell, written into the OWNER's region at
+// [me * cap + position]. Positions come from one global atomic per (block, destination): the block counts its records
+// per destination in shared memory first.
+__global__ void __launch_bounds__(kThreads) peer_scatter_kernel(const __grid_constant__ PeerScatterParams p)
+{
+  __shared__ uint32_t s_cnt[kMaxPeers];
+  __shared__ uint32_t s_base[kMaxPeers];
+  const int64_t G = p.num_groups;
+  for (int64_t tile = (int64_t)blockIdx.x * kThreads; tile < G; tile += (int64_t)gridDim.x * kThreads) {
+    if (threadIdx.x < p.world) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t j   = tile + threadIdx.x;
+    const bool active = j < G;
+    uint64_t slot = 0, k0 = 0, k1 = 0;
+    uint32_t owner = 0, rank = 0;
+    if (active) {
+      slot = p.group_slots[j];
+      if (p.key_words == 1) k0 = p.keys[slot];
+      else { k0 = p.keys[2 * slot]; k1 = p.keys[2 * slot + 1]; }
+      owner = owner_mix(hash_key(k0, k1, p.key_words), (uint32_t)p.world);
+      rank  = atomicAdd(&s_cnt[owner], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < p.world && s_cnt[threadIdx.x]) s_base[threadIdx.x] = atomicAdd(p.cursors + threadIdx.x, s_cnt[threadIdx.x]);
+    __syncthreads();
+    if (active) {
+      const uint64_t pos = (uint64_t)s_base[owner] + rank;
+      if (pos < p.cap) {  // else: counted, not written; the signal kernel reports the overflow to the owner
+        uint8_t* r         = p.region[owner];
+        const uint64_t idx = (uint64_t)p.me * p.cap + pos;
+        reinterpret_cast<uint64_t*>(r)[idx] = k0;
+        if (p.key_words == 2) reinterpret_cast<uint64_t*>(r + p.key1_off)[idx] = k1;
+#pragma unroll 1
+        for (int a = 0; a < p.num_accs; ++a) {
+          const PeerAcc& pa = p.acc[a];
+          if (pa.cell_bytes == 8) reinterpret_cast<uint64_t*>(r + pa.region_off)[idx] = reinterpret_cast<const uint64_t*>(pa.cells)[slot];
+          else reinterpret_cast<uint32_t*>(r + pa.region_off)[idx] = reinterpret_cast<const uint32_t*>(pa.cells)[slot];
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+cudaError_t launch_peer_scatter(const PeerScatterParams& p, cudaStream_t s)
+{
+  if (p.num_groups <= 0) return cudaSuccess;
+  int64_t blocks = ((int64_t)p.num_groups + kThreads - 1) / kThreads;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  peer_scatter_kernel<<<(int)blocks, kThreads, 0, s>>>(p);
+  return note_launch();
+}
+
+// Runs after the scatter kernel in stream order: thread d tells rank d how many records this rank left in its segment,
+// then publishes the step's epoch with a system-scope release (cumulative over the scatter kernel's stores).
+__global__ void peer_signal_kernel(const __grid_constant__ PeerSignalParams p)
+{
+  const int d = threadIdx.x;
+  if (d >= p.world) return;
+  const uint32_t produced = p.cursors[d];
+  PeerHeader* h           = p.header[d];
+  // an overflow towards ANY destination is reported to EVERY rank, so that all ranks fail the step together
+  uint32_t overflow = 0;
+  for (int r = 0; r < p.world; ++r) overflow |= p.cursors[r] > p.cap ? 1u : 0u;
+  h->count[p.parity][p.me]    = produced < p.cap ? produced : (uint32_t)p.cap;
+  h->overflow[p.parity][p.me] = overflow;
+  __threadfence_system();
+  st_release_sys(&h->flag[p.parity][p.me], p.epoch);
+}
+
+cudaError_t launch_peer_signal(const PeerSignalParams& p, cudaStream_t s)
+{
+  peer_signal_kernel<<<1, kMaxPeers, 0, s>>>(p);
+  return note_launch();
+}
+
+// One block, one thread per source: spins (bounded) on that source's flag. A single small block so that ranks sharing
+// one GPU (the simulated-rank tests) cannot starve each other of SMs.
+__global__ void peer_wait_kernel(const PeerHeader* mine, int parity, uint32_t epoch, int world, uint64_t timeout_ns, uint32_t* out)
+{
+  const int s = threadIdx.x;
+  if (s == 0) out[2 * world] = 0;
+  __syncthreads();
+  if (s >= world) return;
+  const uint64_t t0 = global_timer_ns();
+  bool ok           = true;
+  // flags only grow; (int32) difference tolerates wrap-around of the epoch counter
+  while ((int32_t)(ld_acquire_sys(&mine->flag[parity][s]) - epoch) < 0) {
+    if (global_timer_ns() - t0 > timeout_ns) { ok = false; break; }
+    __nanosleep(200);
+  }
+  if (!ok) { out[2 * world] = 1; out[s] = 0; out[world + s] = 0; return; }
+  out[s]         = *reinterpret_cast<const volatile uint32_t*>(&mine->count[parity][s]);
+  out[world + s] = *reinterpret_cast<const volatile uint32_t*>(&mine->overflow[parity][s]);
+}
+
+cudaError_t launch_peer_wait(const PeerHeader* mine, int parity, uint32_t epoch, int world, uint64_t timeout_ns, uint32_t* out, cudaStream_t s)
+{
+  peer_wait_kernel<<<1, kMaxPeers, 0, s>>>(mine, parity, epoch, world, timeout_ns, out);
+  return note_launch();
+}
+
+// merge one received record into the final table: the associative merges of streaming_groupby::merge
+// (/root/reference/cpp/src/groupby/streaming_groupby/merge.cu:30-144) applied to accumulator cells
+__device__ __forceinline__ void merge_cell(uint8_t op, void* cells, uint64_t slot, uint64_t v)
+{
+  unsigned long long* c64 = reinterpret_cast<unsigned long long*>(cells) + slot;
+  unsigned int* c32       = reinterpret_cast<unsigned int*>(cells) + slot;
+  switch (op) {
+    case ACC_SUM_I64: case ACC_SUMSQ_I64: atomicAdd(c64, (unsigned long long)v); break;
+    case ACC_SUM_F64: case ACC_SUMSQ_F64: atomicAdd(reinterpret_cast<double*>(c64), __longlong_as_double((long long)v)); break;
+    case ACC_SUM_F32: case ACC_SUMSQ_F32: atomicAdd(reinterpret_cast<float*>(c32), __uint_as_float((uint32_t)v)); break;
+    case ACC_PROD_I64: atomic_mul_i64(c64, (int64_t)v); break;
+    case ACC_PROD_F64: atomic_mul_f64(c64, __longlong_as_double((long long)v)); break;
+    case ACC_PROD_F32: atomic_mul_f32(c32, __uint_as_float((uint32_t)v)); break;
+    case ACC_MIN: atomicMin(c64, (unsigned long long)v); break;
+    case ACC_MAX: atomicMax(c64, (unsigned long long)v); break;
+    case ACC_COUNT_VALID: case ACC_COUNT_ALL: atomicAdd(c32, (unsigned int)v); break;
+    default: break;  // ARGMIN / ARGMAX hold rank-local row numbers: rejected before the exchange
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) peer_merge_kernel(const __grid_constant__ PeerMergeParams p)
+{
+  const uint32_t total  = p.prefix[p.world];
+  const uint32_t stride = gridDim.x * kThreads;
+  for (uint32_t i = blockIdx.x * kThreads + threadIdx.x; i < total; i += stride) {
+    int src = 0;
+    while (i >= p.prefix[src + 1]) ++src;
+    const uint64_t idx = (uint64_t)src * p.cap + (i - p.prefix[src]);
+    // .cg loads: the records were written by another GPU, never through this SM's L1
+    const uint64_t k0 = __ldcg(reinterpret_cast<const unsigned long long*>(p.region) + idx);
+    const uint64_t k1 = p.key_words == 2 ? __ldcg(reinterpret_cast<const unsigned long long*>(p.region + p.key1_off) + idx) : 0;
+    const uint64_t slot = find_or_insert(p.table, k0, k1);
+    if (slot == kNoSlot) continue;
+#pragma unroll 1
+    for (int a = 0; a < p.num_accs; ++a) {
+      const PeerAcc& pa = p.acc[a];
+      const uint64_t v  = pa.cell_bytes == 8 ? __ldcg(reinterpret_cast<const unsigned long long*>(p.region + pa.region_off) + idx)
+                                             : __ldcg(reinterpret_cast<const unsigned int*>(p.region + pa.region_off) + idx);
+      merge_cell(pa.op, pa.cells, slot, v);
+    }
+  }
+}
+
+cudaError_t launch_peer_merge(const PeerMergeParams& p, cudaStream_t s)
+{
+  const uint32_t total = p.prefix[p.world];
+  if (total == 0) return cudaSuccess;
+  uint32_t blocks = (total + kThreads - 1) / kThreads;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  peer_merge_kernel<<<blocks, kThreads, 0, s>>>(p);
+  return note_launch();
+}
+
+}  // namespace bgb

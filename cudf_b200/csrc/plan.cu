@@ -110,7 +110,7 @@ static bool same_column(const bgb_column_view& a, const bgb_column_view& b)
 }
 
 int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys, const bgb_request* requests,
-              int32_t num_requests, Plan& plan)
+              int32_t num_requests, Plan& plan, bool rank_independent)
 {
   if (num_keys <= 0 || keys == nullptr) return set_error(BGB_INVALID_ARGUMENT, "groupby needs at least one key column");
   if (num_requests < 0 || (num_requests > 0 && requests == nullptr)) return set_error(BGB_INVALID_ARGUMENT, "bad requests");
@@ -136,7 +136,8 @@ int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_nul
     int w = type_width(keys[c].type_id);
     if (w == 0) return set_error(BGB_UNSUPPORTED, "key column %d: type %d is not a fixed-width type of <= 8 bytes", c, keys[c].type_id);
     total_bits += 8 * w;
-    if (keys[c].null_mask != nullptr) { any_key_mask = true; if (plan.include_null_keys) ++null_bits; }
+    if (keys[c].null_mask != nullptr) any_key_mask = true;
+    if (plan.include_null_keys && (keys[c].null_mask != nullptr || rank_independent)) ++null_bits;
   }
   if (total_bits + null_bits > 128) return set_error(BGB_UNSUPPORTED, "packed key wider than 128 bits (%d)", total_bits + null_bits);
   plan.key_words      = (total_bits + null_bits > 64) ? 2 : 1;
@@ -155,7 +156,7 @@ int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_nul
     k.fclass   = keys[c].type_id == BGB_FLOAT32 ? 1 : keys[c].type_id == BGB_FLOAT64 ? 2 : 0;
     k.shift    = (uint8_t)bit;
     k.null_bit = -1;
-    k.nullable_out = plan.include_null_keys && keys[c].null_mask != nullptr;
+    k.nullable_out = plan.include_null_keys && (keys[c].null_mask != nullptr || rank_independent);
     bit += 8 * k.width;
   }
   for (int c = 0; c < num_keys; ++c)
@@ -176,7 +177,8 @@ int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_nul
       ValuePlan vp;
       vp.v         = rq.values;
       vp.src       = src;
-      vp.has_nulls = rq.values.null_count > 0 && rq.values.null_mask != nullptr;
+      // rank_independent: another rank's shard of this column may hold nulls, and every rank must lay out the same cells
+      vp.has_nulls = rank_independent || (rq.values.null_count > 0 && rq.values.null_mask != nullptr);
       vp.has_mask  = rq.values.null_mask != nullptr;
       plan.values.push_back(vp);
       vc = (int)plan.values.size() - 1;

@@ -62,7 +62,10 @@ uint8_t type_src(int32_t type_id);               // Src or S_BAD
 int32_t target_type(int32_t type_id, int32_t kind);  // -1 invalid
 
 // status: BGB_OK / BGB_INVALID_ARGUMENT / BGB_UNSUPPORTED (message via set_error)
+// rank_independent: the key image layout and the accumulator set must not depend on which columns happen to carry a null
+// mask on THIS rank (multi-GPU exchange: every rank packs keys and lays out records identically); every value column is
+// then treated as nullable and, under INCLUDE, every key column gets a null flag bit.
 int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys, const bgb_request* requests,
-              int32_t num_requests, Plan& plan);
+              int32_t num_requests, Plan& plan, bool rank_independent = false);
 
 }  // namespace bgb

@@ -129,6 +129,12 @@ class TorchComm:
     def all_to_all(self, buffers, send_counts, recv_counts):
         return exchange_columns(buffers, send_counts, recv_counts, self.group)
 
+    def peer_connect(self, region_bytes, device):
+        import torch.distributed as dist
+        if device.type != "cuda" or dist.get_backend(self.group) != "nccl":
+            return None
+        return _connect_over_torch(self.group, region_bytes, device)
+
 
 class SingleComm:
     """world == 1: nothing to exchange (the partition / merge steps still run, which is what the 1-GPU tests exercise)."""
@@ -139,6 +145,73 @@ class SingleComm:
 
     def all_to_all(self, buffers, send_counts, recv_counts):
         return list(buffers)
+
+    def peer_connect(self, region_bytes, device):
+        return PeerContext(0, 1, region_bytes, device)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# 2b. peer-memory exchange context (bgb_peer_*): every rank's receive buffer mapped into every other rank
+
+
+class PeerContext:
+    """One rank's exchange buffer plus the mappings of its peers' buffers (include/bgb.h, bgb_peer_create ...)."""
+
+    def __init__(self, rank: int, world: int, region_bytes: int, device):
+        self.rank, self.world, self.region_bytes, self.device = rank, world, int(region_bytes), device
+        self.handle = C.c_void_p()
+        with torch.cuda.device(device):
+            _lib.check(_lib.lib().bgb_peer_create(rank, world, self.region_bytes, C.byref(self.handle)))
+
+    def export(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bgb_peer_export(self.handle, buf))
+        return buf.raw
+
+    def attach(self, peer_rank: int, handle: bytes):
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bgb_peer_attach(self.handle, peer_rank, C.c_char_p(handle)))
+
+    def attach_local(self, peer_rank: int, other: "PeerContext"):
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().bgb_peer_attach_local(self.handle, peer_rank, other.handle))
+
+    def close(self):
+        if self.handle:
+            with torch.cuda.device(self.device):
+                torch.cuda.synchronize()
+                _lib.lib().bgb_peer_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+
+def _connect_over_torch(group, region_bytes: int, device):
+    """Collective: create this rank's context, swap the IPC handles, map every peer. None when any rank cannot."""
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    ctx, handle = None, None
+    try:
+        ctx = PeerContext(rank, world, region_bytes, device)
+        handle = ctx.export()
+    except _lib.BgbError:
+        handle = None
+    handles = [None] * world
+    dist.all_gather_object(handles, handle, group=group)
+    ok = all(h is not None for h in handles)
+    if ok:
+        try:
+            for r, h in enumerate(handles):
+                if r != rank:
+                    ctx.attach(r, h)
+        except _lib.BgbError:
+            ok = False
+    oks = [None] * world
+    dist.all_gather_object(oks, ok, group=group)  # also the barrier that makes every buffer ready before its first use
+    if all(oks):
+        return ctx
+    if ctx is not None and ctx.handle:
+        ctx.close()
+    return None
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -219,7 +292,10 @@ class DistributedGroupBy:
     Same call shape as GroupBy (pylibcudf groupby.pyx:33-214): DistributedGroupBy(keys, null_handling).aggregate(requests)
     -> (keys Table, [Table per request]) holding the groups THIS rank owns. `keys` / request values are this rank's rows."""
 
-    def __init__(self, keys: Table, null_handling: int = NullPolicy.EXCLUDE, *, options: dict | None = None, group=None, comm=None):
+    def __init__(self, keys: Table, null_handling: int = NullPolicy.EXCLUDE, *, options: dict | None = None, group=None, comm=None,
+                 exchange: str = "auto", peer_region_bytes: int = 64 << 20):
+        """exchange: "peer" = fused peer-memory path (P2P stores over NVLink, bgb_groupby_build_peer), "nccl" = partition +
+        all-to-all-v + merge through torch.distributed, "auto" = peer when every rank can map every other rank's buffer."""
         self._keys = keys
         self._null_handling = null_handling
         self._options = dict(options or {})
@@ -227,6 +303,11 @@ class DistributedGroupBy:
             import torch.distributed as dist
             comm = TorchComm(group) if dist.is_available() and dist.is_initialized() else SingleComm()
         self._comm = comm
+        if exchange not in ("auto", "peer", "nccl"):
+            raise ValueError("exchange must be 'auto', 'peer' or 'nccl'")
+        self._exchange = exchange
+        self._peer_region_bytes = int(peer_region_bytes)
+        self.last_exchange = None
         self.last_path = None
         self._local_profile = []
         self._phase_events = []
@@ -254,12 +335,60 @@ class DistributedGroupBy:
         e1.record(torch.cuda.current_stream(device))
         self._phase_events.append((tok[0], tok[1], e1))
 
+    # -- peer contexts are expensive (cudaMalloc + IPC mapping): one per communicator, kept until it has to grow
+    def _peer_context(self, device, grow=False):
+        comm = self._comm
+        ctx = getattr(comm, "_bgb_peer_ctx", None)
+        if ctx is not None and not grow and ctx.region_bytes >= self._peer_region_bytes:
+            return ctx
+        want = self._peer_region_bytes
+        if ctx is not None:
+            want = max(want, ctx.region_bytes * (4 if grow else 1))
+            ctx.close()
+            comm._bgb_peer_ctx = None
+        if getattr(comm, "_bgb_peer_failed", False):
+            return None
+        ctx = comm.peer_connect(want, device)
+        if ctx is None:
+            comm._bgb_peer_failed = True  # every rank got the same answer (collective): do not try again
+        comm._bgb_peer_ctx = ctx
+        return ctx
+
+    def _aggregate_peer(self, requests, device):
+        from .groupby import GroupBy
+        for r in requests:
+            decompose(r._aggregations)  # raises UnsupportedError for kinds without a cross-rank merge, before any exchange
+        grow = False
+        for _ in range(6):
+            ctx = self._peer_context(device, grow)
+            if ctx is None:
+                return None
+            gb = GroupBy(self._keys, self._null_handling, options=self._options)
+            gb._peer = ctx
+            try:
+                out = gb.aggregate(requests)
+            except _lib.PeerOverflow:
+                grow = True  # reported by EVERY rank in the same step, so all ranks take this branch together
+                continue
+            self._local_profile = list(gb.last_profile)
+            self.last_path = gb.last_path
+            self.last_exchange = "peer"
+            return out
+        raise _lib.CudaError(3, "peer exchange region could not be grown enough")
+
     def aggregate(self, requests):
         from .groupby import GroupBy, GroupByRequest
         comm = self._comm
         world = comm.world
         device = self._keys.columns()[0].data.device
         self._phase_events = []
+        if self._exchange in ("auto", "peer"):
+            out = self._aggregate_peer(requests, device)
+            if out is not None:
+                return out
+            if self._exchange == "peer":
+                raise _lib.UnsupportedError(2, "peer-memory exchange is not available between these ranks")
+        self.last_exchange = "nccl"
 
         # (1) local pre-aggregation of this rank's rows: one partial column per (request, partial kind)
         plans = [decompose(r._aggregations) for r in requests]

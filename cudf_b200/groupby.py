@@ -29,6 +29,7 @@ class GroupBy:
         self._options = options or {}
         self.last_path = None
         self.last_profile = []  # [(kernel name, device ms)] when options["profile"] is set
+        self._peer = None       # distributed.PeerContext: build through bgb_groupby_build_peer (collective)
 
     def _c_requests(self, requests):
         n = len(requests)
@@ -62,8 +63,12 @@ class GroupBy:
         handle = C.c_void_p()
         ngroups = C.c_int32(0)
         with torch.cuda.device(device):
-            _lib.check(L.bgb_groupby_build(ckeys, nk, int(self._null_handling), creq, len(requests), sptr, None, C.byref(opt),
-                                           C.byref(handle), C.byref(ngroups)))
+            if self._peer is not None:
+                _lib.check(L.bgb_groupby_build_peer(self._peer.handle, ckeys, nk, int(self._null_handling), creq, len(requests), sptr,
+                                                    None, C.byref(opt), C.byref(handle), C.byref(ngroups)))
+            else:
+                _lib.check(L.bgb_groupby_build(ckeys, nk, int(self._null_handling), creq, len(requests), sptr, None, C.byref(opt),
+                                               C.byref(handle), C.byref(ngroups)))
             try:
                 G = ngroups.value
                 self.last_path = L.bgb_groupby_path(handle).decode()

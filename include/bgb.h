@@ -40,7 +40,9 @@ typedef enum bgb_status {
   BGB_UNSUPPORTED = 2,      /* can_use_hash_groupby() == false: caller takes its sort fallback */
   BGB_CUDA_ERROR = 3,       /* cudf::cuda_error */
   BGB_NCCL_ERROR = 4,
-  BGB_OUT_OF_MEMORY = 5
+  BGB_OUT_OF_MEMORY = 5,
+  BGB_PEER_OVERFLOW = 6     /* bgb_groupby_build_peer: a receive segment was too small; every rank reports it, the caller
+                               re-creates the peer context with a larger region (or uses the NCCL exchange) */
 } bgb_status;
 
 /* cudf::type_id, same numeric values (/root/reference/cpp/include/cudf/types.hpp:185-217) */
@@ -207,6 +209,34 @@ int bgb_bytes_to_bitmask(const uint8_t* valid_bytes, int64_t n, uint32_t* mask_w
  * cpp/src/groupby/common/m2_var_std.cu:49-59,138-187). */
 int bgb_finalize_moments(int32_t kind, int32_t ddof, const bgb_column_view* sum, const bgb_column_view* sumsq,
                          const bgb_column_view* count, bgb_mutable_column* out, void* stream);
+
+/* ---- multi-GPU, peer-memory exchange: ONE fused path, no collective on the data path -------------------------------
+ * Every rank owns an exchange buffer (bgb_peer_create) that its peers map through CUDA IPC (bgb_peer_export /
+ * bgb_peer_attach; the 64-byte handles travel through whatever bootstrap channel the host layer has - torch.distributed
+ * all_gather_object in cudf_b200/distributed.py). bgb_groupby_build_peer then (1) aggregates this rank's rows with the
+ * single-GPU path, (2) writes one record per local group straight into the OWNER rank's buffer over NVLink (P2P stores;
+ * owner = hash2(key) % world, as bgb_partition_by_key_hash), (3) publishes the per-destination counts and the step's
+ * epoch with system-scope release stores, (4) waits for every source's epoch, and (5) merges the received records into
+ * the final table (SUM of sums, SUM of counts, MIN of mins, MAX of maxes, PRODUCT of products - the merges of
+ * cpp/src/groupby/streaming_groupby/merge.cu:30-144) before compaction. The handle it returns is used exactly like
+ * bgb_groupby_build's (result_info / emit / destroy) and holds the groups THIS rank owns; MEAN/M2/VARIANCE/STD are
+ * finalised by emit from merged SUM/SUMSQ/COUNT cells, so integer inputs give bit-identical results on any world size.
+ * The call is COLLECTIVE: every rank of the context must make it, with the same key/request shapes. Regions are
+ * double-buffered by call parity, so no barrier is needed between consecutive calls. */
+typedef struct bgb_peer bgb_peer;
+#define BGB_PEER_HANDLE_BYTES 64
+/* region_bytes: size of ONE receive region (two are allocated); a (source, destination) segment holds
+ * region_bytes / (world * record_bytes) records, record_bytes = 8 * key words + accumulator cells (20 B for int64 SUM+COUNT) */
+int bgb_peer_create(int32_t rank, int32_t world, int64_t region_bytes, bgb_peer** out);
+int bgb_peer_export(const bgb_peer* peer, void* handle_out /* BGB_PEER_HANDLE_BYTES */);
+int bgb_peer_attach(bgb_peer* peer, int32_t peer_rank, const void* handle /* from that rank's bgb_peer_export */);
+/* same-process ranks (one process driving several GPUs, or several simulated ranks on one GPU in the tests) */
+int bgb_peer_attach_local(bgb_peer* peer, int32_t peer_rank, const bgb_peer* other);
+int64_t bgb_peer_segment_capacity(const bgb_peer* peer, int32_t record_bytes);
+void bgb_peer_destroy(bgb_peer* peer);
+int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
+                           const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
+                           const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups);
 
 /* ---- synthetic inputs (SURVEY.md 8d generators; bench + tests only) --------------------------------------------- */
 

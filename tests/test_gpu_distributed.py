@@ -138,6 +138,7 @@ class _Shared:
         self.barrier = threading.Barrier(world)
         self.vecs = [None] * world
         self.bufs = [None] * world
+        self.ctxs = [None] * world
 
 
 class ThreadComm:
@@ -152,6 +153,17 @@ class ThreadComm:
         m = torch.tensor(self.s.vecs, dtype=torch.int64)
         self.s.barrier.wait()
         return m
+
+    def peer_connect(self, region_bytes, device):
+        """Same-process ranks: map each other's exchange buffers directly (bgb_peer_attach_local)."""
+        ctx = D.PeerContext(self.rank, self.world, region_bytes, device)
+        self.s.ctxs[self.rank] = ctx
+        self.s.barrier.wait()
+        for r in range(self.world):
+            if r != self.rank:
+                ctx.attach_local(r, self.s.ctxs[r])
+        self.s.barrier.wait()
+        return ctx
 
     def all_to_all(self, buffers, send_counts, recv_counts):
         torch.cuda.synchronize()
@@ -175,14 +187,29 @@ class ThreadComm:
         return out
 
 
-def run_simulated(world, shards, aggs, include_null_keys=False, options=None):
+EXCHANGES = ["nccl", "peer"]
+LAST = {}
+
+
+def run_simulated(world, shards, aggs, include_null_keys=False, options=None, exchange="nccl", peer_region_bytes=8 << 20):
     """shards: per rank (keys [HostColumn], values [HostColumn]). aggs: [(value_index, kind, ddof)].
-    Returns key-sorted (G, keys, results) over all ranks plus per-rank key sets."""
+    Returns key-sorted (G, keys, results) over all ranks plus per-rank key sets.
+    Every simulated rank runs on its own CUDA stream: the peer path's wait kernel spins until the OTHER ranks' scatter
+    kernels have run, which on one GPU needs them to be able to run concurrently."""
     shared = _Shared(world)
     results, errors = [None] * world, []
+    comms = [ThreadComm(shared, r) for r in range(world)]
 
     def work(rank):
         try:
+            with torch.cuda.stream(torch.cuda.Stream()):
+                work_on_stream(rank)
+        except BaseException as e:  # noqa: BLE001
+            errors.append(e)
+            shared.barrier.abort()
+
+    def work_on_stream(rank):
+        if True:
             keys, values = shards[rank]
             dk = [to_device(k) for k in keys]
             dv = [to_device(v) for v in values]
@@ -195,23 +222,29 @@ def run_simulated(world, shards, aggs, include_null_keys=False, options=None):
                 for j, (pos, _, _) in enumerate(lst):
                     where[pos] = (len(reqs) - 1, j)
             dgb = D.DistributedGroupBy(cb.Table(dk), cb.NullPolicy.INCLUDE if include_null_keys else cb.NullPolicy.EXCLUDE,
-                                       options=options, comm=ThreadComm(shared, rank))
+                                       options=options, comm=comms[rank], exchange=exchange, peer_region_bytes=peer_region_bytes)
             kt, rts = dgb.aggregate(reqs)
+            torch.cuda.current_stream().synchronize()
             kout = [c.to_numpy() for c in kt.columns()]
             aout = []
             for pos in range(len(aggs)):
                 r, j = where[pos]
                 aout.append(rts[r].columns()[j].to_numpy())
             results[rank] = (kout, aout)
-        except BaseException as e:  # noqa: BLE001
-            errors.append(e)
-            shared.barrier.abort()
+            LAST[rank] = (dgb.last_exchange, dgb.last_path)
 
     threads = [threading.Thread(target=work, args=(r,)) for r in range(world)]
     for t in threads:
         t.start()
     for t in threads:
         t.join()
+    for c in shared.ctxs:
+        if c is not None:
+            c.close()
+    for c in comms:
+        ctx = getattr(c, "_bgb_peer_ctx", None)
+        if ctx is not None and ctx not in shared.ctxs:
+            ctx.close()
     if errors:
         raise errors[0]
     nk = len(results[0][0])
@@ -236,10 +269,11 @@ def concat_shards(shards):
     return [cat([s[0][i] for s in shards]) for i in range(nk)], [cat([s[1][i] for s in shards]) for i in range(nv)]
 
 
-def check_against_oracle(world, shards, aggs, include_null_keys=False, options=None, rtol=1e-9):
+def check_against_oracle(world, shards, aggs, include_null_keys=False, options=None, rtol=1e-9, exchange="nccl", **kw):
     keys, values = concat_shards(shards)
     Go, ko, ao = orc.groupby(keys, values, aggs, include_null_keys=include_null_keys, threads=4)
-    G, kg, ag, sizes = run_simulated(world, shards, aggs, include_null_keys, options)
+    G, kg, ag, sizes = run_simulated(world, shards, aggs, include_null_keys, options, exchange=exchange, **kw)
+    assert all(LAST[r][0] == exchange for r in range(world)), LAST
     assert G == Go, f"{G} groups over {world} ranks, oracle has {Go}"
     for c in range(len(keys)):
         np.testing.assert_array_equal(kg[c][1], ko[c][1])
@@ -266,36 +300,41 @@ def int_shards(world, n, groups, null_frac=0.0, seed=0, key_dtype=np.int64):
 
 
 @pytest.mark.parametrize("world", [1, 2, 3, 4])
-def test_sum_count_int64(world):
+@pytest.mark.parametrize("exchange", EXCHANGES)
+def test_sum_count_int64(exchange, world):
     shards = int_shards(world, 100_000, 1000)
-    sizes = check_against_oracle(world, shards, [(0, "sum", 0), (0, "count_valid", 0), (0, "count_all", 0)])
+    sizes = check_against_oracle(world, shards, [(0, "sum", 0), (0, "count_valid", 0), (0, "count_all", 0)], exchange=exchange)
     assert sum(sizes) == 1000 and (world == 1 or min(sizes) > 0)
 
 
 @pytest.mark.parametrize("world", [2, 3])
-def test_all_kinds_with_nulls(world):
+@pytest.mark.parametrize("exchange", EXCHANGES)
+def test_all_kinds_with_nulls(exchange, world):
     shards = int_shards(world, 50_000, 500, null_frac=0.3, seed=5)
     check_against_oracle(world, shards, [(0, "sum", 0), (0, "min", 0), (0, "max", 0), (0, "count_valid", 0), (0, "mean", 0),
-                                         (0, "variance", 1), (0, "std", 0), (0, "m2", 0), (0, "sum_of_squares", 0), (0, "count_all", 0)])
+                                         (0, "variance", 1), (0, "std", 0), (0, "m2", 0), (0, "sum_of_squares", 0), (0, "count_all", 0)], exchange=exchange)
 
 
-def test_only_one_rank_has_a_null_mask():
+@pytest.mark.parametrize("exchange", EXCHANGES)
+def test_only_one_rank_has_a_null_mask(exchange):
     shards = int_shards(2, 20_000, 300, null_frac=0.0, seed=9)
     k, v = shards[0]
     valid = np.random.default_rng(1).random(20_000) > 0.5
     shards[0] = (k, [orc.HostColumn(v[0].data, valid)])
-    check_against_oracle(2, shards, [(0, "sum", 0), (0, "max", 0), (0, "mean", 0)])
+    check_against_oracle(2, shards, [(0, "sum", 0), (0, "max", 0), (0, "mean", 0)], exchange=exchange)
 
 
-def test_group_null_on_every_rank_stays_null():
+@pytest.mark.parametrize("exchange", EXCHANGES)
+def test_group_null_on_every_rank_stays_null(exchange):
     shards = int_shards(2, 5000, 50, null_frac=0.2, seed=2)
     for k, v in shards:
         v[0].valid[k[0].data == 7] = False
-    check_against_oracle(2, shards, [(0, "sum", 0), (0, "min", 0), (0, "mean", 0), (0, "variance", 1), (0, "count_valid", 0)])
+    check_against_oracle(2, shards, [(0, "sum", 0), (0, "min", 0), (0, "mean", 0), (0, "variance", 1), (0, "count_valid", 0)], exchange=exchange)
 
 
 @pytest.mark.parametrize("include", [False, True])
-def test_null_keys_two_key_columns(include):
+@pytest.mark.parametrize("exchange", EXCHANGES)
+def test_null_keys_two_key_columns(exchange, include):
     shards = []
     for r in range(3):
         rng = np.random.default_rng(40 + r)
@@ -307,10 +346,11 @@ def test_null_keys_two_key_columns(include):
         vv = rng.random(n) > 0.1
         shards.append(([orc.HostColumn(k0, k0v), orc.HostColumn(k1)], [orc.HostColumn(v, vv)]))
     check_against_oracle(3, shards, [(0, "sum", 0), (0, "min", 0), (0, "max", 0), (0, "mean", 0), (0, "std", 1), (0, "count_valid", 0)],
-                         include_null_keys=include)
+                         include_null_keys=include, exchange=exchange)
 
 
-def test_float_values_two_requests():
+@pytest.mark.parametrize("exchange", EXCHANGES)
+def test_float_values_two_requests(exchange):
     shards = []
     for r in range(2):
         rng = np.random.default_rng(60 + r)
@@ -319,21 +359,75 @@ def test_float_values_two_requests():
         a = rng.standard_normal(n)
         b = rng.integers(0, 1000, n).astype(np.int32)
         shards.append(([orc.HostColumn(k)], [orc.HostColumn(a), orc.HostColumn(b)]))
-    check_against_oracle(2, shards, [(0, "sum", 0), (1, "sum", 0), (0, "mean", 0), (1, "max", 0), (1, "variance", 1), (0, "min", 0)])
+    check_against_oracle(2, shards, [(0, "sum", 0), (1, "sum", 0), (0, "mean", 0), (1, "max", 0), (1, "variance", 1), (0, "min", 0)], exchange=exchange)
 
 
-def test_keys_only_and_empty_rank():
+@pytest.mark.parametrize("exchange", EXCHANGES)
+def test_keys_only_and_empty_rank(exchange):
     shards = int_shards(2, 10_000, 100, seed=3)
     # rank 1 holds no rows at all
     shards[1] = ([orc.HostColumn(np.empty(0, np.int64))], [orc.HostColumn(np.empty(0, np.int64))])
-    check_against_oracle(2, shards, [(0, "sum", 0), (0, "count_valid", 0)])
-    check_against_oracle(2, int_shards(2, 10_000, 100, seed=3), [])
+    check_against_oracle(2, shards, [(0, "sum", 0), (0, "count_valid", 0)], exchange=exchange)
+    check_against_oracle(2, int_shards(2, 10_000, 100, seed=3), [], exchange=exchange)
 
 
-def test_high_cardinality_goes_through_the_partitioned_merge():
+@pytest.mark.parametrize("exchange", EXCHANGES)
+def test_high_cardinality_goes_through_the_partitioned_merge(exchange):
     shards = int_shards(2, 400_000, 300_000, seed=8)
-    sizes = check_against_oracle(2, shards, [(0, "sum", 0), (0, "count_valid", 0)])
+    sizes = check_against_oracle(2, shards, [(0, "sum", 0), (0, "count_valid", 0)], exchange=exchange)
     assert abs(sizes[0] - sizes[1]) < 0.05 * sum(sizes)
+
+
+def test_peer_region_grows_after_overflow():
+    """A 4 KB region holds 64 records per (source, destination) segment; 1000 groups overflow it on every rank, every rank
+    reports BGB_PEER_OVERFLOW in the same step and the communicator re-creates a larger region until the exchange fits."""
+    shards = int_shards(2, 50_000, 1000, seed=12)
+    check_against_oracle(2, shards, [(0, "sum", 0), (0, "count_valid", 0)], exchange="peer", peer_region_bytes=4096)
+
+
+def test_peer_two_steps_reuse_the_context():
+    """Consecutive calls alternate between the two regions (parity of the epoch) without any barrier in between."""
+    world = 2
+    shared = _Shared(world)
+    comms = [ThreadComm(shared, r) for r in range(world)]
+    out, errors = {}, []
+
+    def work(rank):
+        try:
+            with torch.cuda.stream(torch.cuda.Stream()):
+                for step in range(5):
+                    rng = np.random.default_rng(1000 * step + rank)
+                    k = rng.integers(0, 200 + 50 * step, 20_000).astype(np.int64)
+                    v = rng.integers(-5, 5, 20_000).astype(np.int64)
+                    dgb = D.DistributedGroupBy(cb.Table([cb.Column.from_numpy(k)]), comm=comms[rank], exchange="peer", peer_region_bytes=1 << 20)
+                    kt, rts = dgb.aggregate([cb.GroupByRequest(cb.Column.from_numpy(v), [agg.sum(), agg.count()])])
+                    torch.cuda.current_stream().synchronize()
+                    out[(step, rank)] = (k, v, kt.columns()[0].to_numpy()[0], rts[0].columns()[0].to_numpy()[0], rts[0].columns()[1].to_numpy()[0])
+        except BaseException as e:  # noqa: BLE001
+            errors.append(e)
+            shared.barrier.abort()
+
+    threads = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for c in shared.ctxs:
+        if c is not None:
+            c.close()
+    if errors:
+        raise errors[0]
+    for step in range(5):
+        k = np.concatenate([out[(step, r)][0] for r in range(world)])
+        v = np.concatenate([out[(step, r)][1] for r in range(world)])
+        gk = np.concatenate([out[(step, r)][2] for r in range(world)])
+        gs = np.concatenate([out[(step, r)][3] for r in range(world)])
+        gc = np.concatenate([out[(step, r)][4] for r in range(world)])
+        order = np.argsort(gk)
+        uk, inv = np.unique(k, return_inverse=True)
+        np.testing.assert_array_equal(gk[order], uk)
+        np.testing.assert_array_equal(gs[order], np.bincount(inv, weights=v).astype(np.int64))
+        np.testing.assert_array_equal(gc[order], np.bincount(inv))
 
 
 def test_unsupported_kind_raises():
@@ -358,10 +452,13 @@ def _nccl_worker(rank, world, port, outdir):
         keys, values = int_shards(world, 200_000, 20_000, null_frac=0.1, seed=77)[rank]
         dk = [cb.Column.from_numpy(k.data, k.valid, device=f"cuda:{rank}") for k in keys]
         dv = [cb.Column.from_numpy(v.data, v.valid, device=f"cuda:{rank}") for v in values]
-        dgb = D.DistributedGroupBy(cb.Table(dk))
-        kt, rts = dgb.aggregate([cb.GroupByRequest(dv[0], [agg.sum(), agg.count(), agg.min(), agg.mean()])])
-        cols = [kt.columns()[0].to_numpy()] + [c.to_numpy() for c in rts[0].columns()]
-        np.savez(os.path.join(outdir, f"r{rank}.npz"), **{f"d{i}": c[0] for i, c in enumerate(cols)}, **{f"v{i}": c[1] for i, c in enumerate(cols)})
+        for exchange in ("nccl", "peer"):
+            dgb = D.DistributedGroupBy(cb.Table(dk), exchange=exchange)
+            kt, rts = dgb.aggregate([cb.GroupByRequest(dv[0], [agg.sum(), agg.count(), agg.min(), agg.mean()])])
+            assert dgb.last_exchange == exchange
+            cols = [kt.columns()[0].to_numpy()] + [c.to_numpy() for c in rts[0].columns()]
+            np.savez(os.path.join(outdir, f"{exchange}_r{rank}.npz"), **{f"d{i}": c[0] for i, c in enumerate(cols)},
+                     **{f"v{i}": c[1] for i, c in enumerate(cols)})
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -380,16 +477,17 @@ def test_nccl_two_gpus(tmp_path):
     shards = int_shards(world, 200_000, 20_000, null_frac=0.1, seed=77)
     keys, values = concat_shards(shards)
     Go, ko, ao = orc.groupby(keys, values, [(0, "sum", 0), (0, "count_valid", 0), (0, "min", 0), (0, "mean", 0)], threads=4)
-    parts = [np.load(tmp_path / f"r{r}.npz") for r in range(world)]
-    k = np.concatenate([p["d0"] for p in parts])
-    order = np.argsort(k, kind="stable")
-    assert len(k) == Go
-    np.testing.assert_array_equal(k[order], ko[0][0])
-    for i in range(4):
-        d = np.concatenate([p[f"d{i + 1}"] for p in parts])[order]
-        v = np.concatenate([p[f"v{i + 1}"] for p in parts])[order]
-        np.testing.assert_array_equal(v, ao[i][1])
-        if d.dtype.kind == "f":
-            np.testing.assert_allclose(d[v], ao[i][0][ao[i][1]], rtol=1e-9, atol=0)
-        else:
-            np.testing.assert_array_equal(d[v], ao[i][0][ao[i][1]])
+    for exchange in ("nccl", "peer"):
+        parts = [np.load(tmp_path / f"{exchange}_r{r}.npz") for r in range(world)]
+        k = np.concatenate([p["d0"] for p in parts])
+        order = np.argsort(k, kind="stable")
+        assert len(k) == Go
+        np.testing.assert_array_equal(k[order], ko[0][0])
+        for i in range(4):
+            d = np.concatenate([p[f"d{i + 1}"] for p in parts])[order]
+            v = np.concatenate([p[f"v{i + 1}"] for p in parts])[order]
+            np.testing.assert_array_equal(v, ao[i][1])
+            if d.dtype.kind == "f":
+                np.testing.assert_allclose(d[v], ao[i][0][ao[i][1]], rtol=1e-9, atol=0)
+            else:
+                np.testing.assert_array_equal(d[v], ao[i][0][ao[i][1]])
