@@ -215,14 +215,14 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit_line(line)
 
 
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
-    """SM clock + throttle reasons DURING the timed region, through NVML (pynvml): one sample from the main thread in the
-    middle of the region plus a 20 ms background thread (clock and reason queries cost microseconds and do not disturb the
-    steps: tools/nvml_cost.py; the max-clock query costs milliseconds and is made once before the region). (An `nvidia-smi -lms` child polling every
+    """SM clock + throttle reasons DURING the timed region, through NVML (pynvml): a 20 ms background thread (its queries
+    run with the GIL released; tools/nvml_cost.py), plus one sample right after the last step is enqueued when the region
+    was shorter than the period; the max-clock query costs milliseconds and is made once before the region. (An `nvidia-smi -lms` child polling every
     50 ms stretched 3 ms steps to 14 ms on this box -- the driver serialises its queries with kernel launches -- so the
     sampler is kept this light; the samples are still taken while the steps run.)"""
 
@@ -279,7 +279,30 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ our arm
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """Libraries (NCCL's version banner, torchrun) may write to fd 1; the contract is ONE JSON line on stdout. Everything
+    else goes to stderr: fd 1 is pointed at fd 2 for the run and the JSON line is written to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        os.write(1, data)
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    _quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -353,14 +376,19 @@ def main():
     prof_acc = {}
     barrier()
     e0.record()
+    host_ms = []
     for it in range(args.steps):
+        th = time.perf_counter()
         step()
-        if rank == 0 and it == args.steps // 2:
-            clocks.sample()  # mid-region sample from the main thread (the GPU is between two back-to-back steps)
+        host_ms.append((time.perf_counter() - th) * 1e3)
         src = dgb.last_profile if dgb is not None else gb.last_profile
         for name, ms in src:
             prof_acc.setdefault(name, []).append(ms)
     e1.record()
+    if rank == 0 and not clocks.samples:
+        # region shorter than the sampler's 20 ms period: one sample while the GPU is still finishing the last step. Taken
+        # after e1 is recorded because an NVML query from the launching thread costs ~2 ms (it would be billed to the steps).
+        clocks.sample()
     barrier()
     total_ms = e0.elapsed_time(e1)
     launches = L.bgb_kernel_launches() - launches0
@@ -417,10 +445,12 @@ def main():
                        "l2": "inputs (%.1f GB per step) are larger than the 126 MB L2; no flush needed" % (alg / 1e9),
                        "parallelism": f"shard{world}" if world > 1 else "single"},
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
+            # host wall-clock of each call (every call ends in a stream sync, so this tracks device time): spread of the steps
+            "step_ms": {"median": statistics.median(host_ms), "min": min(host_ms), "max": max(host_ms)},
         }
         if pandas_b:
             line["pandas_baseline"] = pandas_b
-        print(json.dumps(line), flush=True)
+        emit_line(line)
     if dist is not None:
         dist.destroy_process_group()
 

@@ -59,6 +59,23 @@ struct bgb_groupby {
 
 namespace {
 
+// BGB_TRACE=1: host wall-clock of each phase of a call, printed to stderr (diagnostics only)
+struct HostTrace {
+  bool on = getenv("BGB_TRACE") != nullptr;
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  std::string line;
+  void mark(const char* what)
+  {
+    if (!on) return;
+    auto t = std::chrono::steady_clock::now();
+    char buf[64];
+    snprintf(buf, sizeof buf, " %s=%.1fus", what, std::chrono::duration<double, std::micro>(t - t0).count());
+    line += buf;
+    t0 = t;
+  }
+  void flush(const char* tag) { if (on) fprintf(stderr, "[bgb trace] %s:%s\n", tag, line.c_str()); }
+};
+
 uint64_t next_pow2(uint64_t x) { uint64_t p = 1; while (p < x) p <<= 1; return p; }
 
 void fill_agg_params(const bgb_groupby& h, AggParams& p, size_t acc_begin, size_t acc_end)
@@ -210,7 +227,9 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
   h->prof.stream = (cudaStream_t)stream;
   Plan& pl = h->plan;
   const int64_t N = pl.num_rows;
-  if (N == 0) { *out_handle = h; return BGB_OK; }  // groupby.cu:233: empty input -> empty outputs
+  if (N == 0) { *out_handle = h; return BGB_OK; }
+  HostTrace tr;
+  tr.mark("plan");  // groupby.cu:233: empty input -> empty outputs
   cudaStream_t s = h->stream;
 
 #define FAIL_RC(expr)            \
@@ -252,6 +271,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     uint32_t est[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     FAIL_RC(check_cuda(cudaMemcpyAsync(est, status + 8, sizeof est, cudaMemcpyDeviceToHost, s), "estimate copy"));
     FAIL_RC(check_cuda(cudaStreamSynchronize(s), "estimate sync"));
+    tr.mark("estimate+sync");
     h->prof.resolve();
     h->dfree(set);
     double d = est[0], m = est[1];
@@ -342,7 +362,9 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     h->prof.end();
     uint32_t st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     FAIL_RC(check_cuda(cudaMemcpyAsync(st, status, sizeof st, cudaMemcpyDeviceToHost, s), "status copy"));
+    tr.mark("launches");
     FAIL_RC(check_cuda(cudaStreamSynchronize(s), "build sync"));
+    tr.mark("build sync");
     h->prof.resolve();
     h->dfree(scan_state);
     if (getenv("BGB_DEBUG")) fprintf(stderr, "[bgb] path=%s groups=%u overflow=%u bypass_rows=%u flushes=%u\n", path.c_str(), st[1], st[0], st[4], st[5]);
@@ -368,6 +390,8 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     key_min = 1; key_max = 0;
   }
 #undef FAIL_RC
+  tr.mark("tail");
+  tr.flush("build_local");
   *num_groups = h->num_groups;
   *out_handle = h;
   return BGB_OK;
@@ -604,6 +628,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
   // ---- (1) this rank's rows through the single-GPU path
   int rc = build_local(keys, num_keys, include_null_keys, requests, num_requests, stream, alloc, options, &h, &g_local, /*rank_independent=*/true);
   if (rc) return rc;  // NOTE: an error here leaves the other ranks waiting until their timeout
+  HostTrace tr;
   *out_handle = nullptr;
   *num_groups = 0;
   Plan& pl       = h->plan;
@@ -662,6 +687,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
   }
   h->prof.end();
 
+  tr.mark("scatter+signal launches");
   // ---- (3) wait for every source, learn how many records arrived
   h->prof.begin("peer_wait");
   std::vector<uint32_t> got(2 * world + 1, 0);
@@ -693,6 +719,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
       FAIL_RC(check_cuda(cudaStreamSynchronize(s), "peer wait sync"));
     }
   }
+  tr.mark("wait+sync");
   h->prof.resolve();
   if (got[2 * world]) FAIL_RC(set_error(BGB_CUDA_ERROR, "peer exchange timed out waiting for another rank (epoch %u)", epoch));
   uint64_t total = 0;
@@ -750,12 +777,15 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
   h->prof.end();
   uint32_t st[4] = {0, 0, 0, 0};
   FAIL_RC(check_cuda(cudaMemcpyAsync(st, status, sizeof st, cudaMemcpyDeviceToHost, s), "status copy"));
+  tr.mark("merge launches");
   FAIL_RC(check_cuda(cudaStreamSynchronize(s), "peer build sync"));
+  tr.mark("final sync");
   h->prof.resolve();
   h->dfree(scan_state);
   h->dfree(scratch);
   if (st[0]) FAIL_RC(set_error(BGB_CUDA_ERROR, "final table overflow during the merge"));
 #undef FAIL_RC
+  tr.flush("build_peer");
   h->num_groups = (int32_t)st[1];
   h->path += "+peer";
   *num_groups = h->num_groups;
