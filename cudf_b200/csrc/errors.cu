@@ -31,3 +31,5 @@ extern "C" const char* bgb_last_error(void) { return bgb::last_error(); }
 namespace bgb { long long launches(); }
 extern "C" int64_t bgb_kernel_launches(void) { return bgb::launches(); }
 extern "C" int bgb_version(void) { return BGB_VERSION; }
+namespace bgb { void pool_trim(); }
+extern "C" void bgb_release_cached_memory(void) { bgb::pool_trim(); }

@@ -1,4 +1,6 @@
 // C ABI: bgb_groupby_build / _emit / _result_info / _destroy.  See include/bgb.h for the contract.
+#include <unistd.h>
+
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -73,8 +75,10 @@ struct HostTrace {
     line += buf;
     t0 = t;
   }
-  void flush(const char* tag) { if (on) fprintf(stderr, "[bgb trace] %s:%s\n", tag, line.c_str()); }
+  void flush(const char* tag) { if (on) fprintf(stderr, "[bgb trace %d] %s:%s\n", (int)getpid(), tag, line.c_str()); }
 };
+thread_local HostTrace* g_tr = nullptr;
+inline void TR(const char* what) { if (g_tr) g_tr->mark(what); }
 
 uint64_t next_pow2(uint64_t x) { uint64_t p = 1; while (p < x) p <<= 1; return p; }
 
@@ -162,6 +166,7 @@ int run_partitioned(bgb_groupby* h, int num_sms, bool& done)
     ok = o.out_data && (!v.has_mask || o.out_valid);
   }
   if (!ok) { release(); return set_error(BGB_OUT_OF_MEMORY, "partition buffers (%lld rows)", (long long)N); }
+  TR("part alloc");
   int rc = check_cuda(cudaMemsetAsync(counters, 0, sizeof(uint32_t) * P, s), "partition counters");
   if (rc) { release(); return rc; }
   h->prof.begin("partition_hist");
@@ -201,7 +206,9 @@ int run_partitioned(bgb_groupby* h, int num_sms, bool& done)
     rc = check_cuda(launch_aggregate_global(p, s), "aggregate_partitioned");
   }
   h->prof.end();
+  TR("part launches");
   release();  // stream-ordered: freed after the kernels above
+  TR("part release");
   if (rc) return rc;
   done = true;
   return BGB_OK;
@@ -229,6 +236,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
   const int64_t N = pl.num_rows;
   if (N == 0) { *out_handle = h; return BGB_OK; }
   HostTrace tr;
+  g_tr = &tr;
   tr.mark("plan");  // groupby.cu:233: empty input -> empty outputs
   cudaStream_t s = h->stream;
 
@@ -319,6 +327,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
       if (!a.cells) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "group table accumulators"));
     }
     // init + aggregate, kMaxAccs accumulators per launch (the first launch also initialises the keys)
+    TR("table alloc");
     std::string path;
     bool done = false;
     BuildContext ctx{&pl, h->table, opt, g_raw, max_abs, key_min, key_max, s, &h->prof, num_sms, skip_tiny};
@@ -357,9 +366,11 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     h->group_slots            = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
     uint32_t* scan_state      = (uint32_t*)h->dalloc(compact_scan_state_bytes(capacity));
     if (!h->group_slots || !scan_state) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "compaction scratch"));
+    TR("compact alloc");
     h->prof.begin("compact");
     FAIL_RC(check_cuda(launch_compact(h->table, h->group_slots, scan_state, s), "compact"));
     h->prof.end();
+    TR("compact launch");
     uint32_t st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     FAIL_RC(check_cuda(cudaMemcpyAsync(st, status, sizeof st, cudaMemcpyDeviceToHost, s), "status copy"));
     tr.mark("launches");
@@ -392,6 +403,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
 #undef FAIL_RC
   tr.mark("tail");
   tr.flush("build_local");
+  g_tr = nullptr;
   *num_groups = h->num_groups;
   *out_handle = h;
   return BGB_OK;

@@ -8,4 +8,5 @@
 namespace bgb {
 void* pool_alloc_async(size_t bytes, cudaStream_t s);   // nullptr on failure (error state cleared)
 void pool_free_async(void* p, cudaStream_t s);
+void pool_trim();  // hand every cached block of the current device back to the driver
 }  // namespace bgb

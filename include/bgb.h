@@ -255,6 +255,10 @@ int bgb_gen_categorical_i8(int8_t* out, int64_t n, uint64_t seed, uint64_t first
 
 const char* bgb_last_error(void);
 int bgb_version(void);
+/* The library keeps freed scratch blocks (group tables, partition copies) cached per device and stream so that a repeated
+ * query does not re-enter the driver allocator (at most 40 % of the device, BGB_CACHE_LIMIT_MB overrides). This hands
+ * every cached block of the current device back (the role of rmm's pool release / torch.cuda.empty_cache). */
+void bgb_release_cached_memory(void);
 
 #ifdef __cplusplus
 }
