@@ -158,8 +158,10 @@ static bool tiny_plan(const Plan& pl, TinyParams& tp)
   return true;
 }
 
-static int run_tiny_path(const BuildContext& ctx, TinyParams& tp)
+static int run_tiny_path(const BuildContext& ctx, TinyParams& tp, bool allow_smem_variant, bool& used_reg, bool& done)
 {
+  used_reg = false;
+  done     = false;
   const Plan& pl = *ctx.plan;
   tp.a.num_rows = pl.num_rows; tp.a.num_key_cols = (int)pl.keys.size(); tp.a.skip_null_keys = pl.skip_null_keys;
   for (size_t c = 0; c < pl.keys.size(); ++c) {
@@ -168,10 +170,23 @@ static int run_tiny_path(const BuildContext& ctx, TinyParams& tp)
   }
   tp.a.table = ctx.table; tp.a.init_keys = 1; tp.a.num_accs = (int)pl.accs.size();
   for (size_t i = 0; i < pl.accs.size(); ++i) { tp.a.acc[i].op = pl.accs[i].op; tp.a.acc[i].cells = pl.accs[i].cells; }
+  const bool use_reg = ctx.opt.force_path != 5 && tiny_reg_eligible(tp) && (ctx.opt.force_path == 6 || ctx.g_raw <= 8.5);
+  if (!use_reg && ctx.opt.force_path == 6) return set_error(BGB_UNSUPPORTED, "force_path 6: this shape is not served by the register-resident tiny kernel");
+  if (!use_reg && !allow_smem_variant) return BGB_OK;
+  done = true;
   ctx.prof->begin("init_table");
   int rc = check_cuda(launch_init_table(tp.a, ctx.stream), "init_table");
   ctx.prof->end();
   if (rc) return rc;
+  // at most 8 groups and a shape the register kernel serves: accumulators live in registers (force_path 6 insists on it,
+  // 5 on the shared-memory variant)
+  if (ctx.opt.force_path != 5 && tiny_reg_eligible(tp) && (ctx.opt.force_path == 6 || ctx.g_raw <= 8.5)) {
+    used_reg = true;
+    ctx.prof->begin("aggregate_tiny_reg");
+    rc = check_cuda(launch_aggregate_tiny_reg(tp, ctx.g_raw <= 4.5 && ctx.opt.force_path != 6 ? 4 : 8, ctx.num_sms, ctx.stream), "aggregate_tiny_reg");
+    ctx.prof->end();
+    return rc;
+  }
   ctx.prof->begin("aggregate_tiny");
   rc = check_cuda(launch_aggregate_tiny(tp, ctx.num_sms, ctx.stream), "aggregate_tiny");
   ctx.prof->end();
@@ -183,18 +198,21 @@ int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path)
   done = false;
   const Plan& pl = *ctx.plan;
   if (ctx.opt.force_path == 1) return BGB_OK;  // generic kernel only
-  if ((ctx.opt.force_path == 0 && !ctx.skip_tiny && ctx.g_raw <= 24 && pl.num_rows >= 65536) || ctx.opt.force_path == 5) {
+  const bool force_tiny = ctx.opt.force_path == 5 || ctx.opt.force_path == 6;
+  if ((ctx.opt.force_path == 0 && !ctx.skip_tiny && ctx.g_raw <= 24 && pl.num_rows >= 65536) || force_tiny) {
     TinyParams tp;
     if (tiny_plan(pl, tp)) {
       const int cap = (int)std::min<size_t>(60, (200 * 1024) / ((size_t)tp.cells * kTinyThreads * 8));
-      if (cap >= 2 && (ctx.opt.force_path == 5 || cap >= ctx.g_raw + 1)) {
+      // (the register variant holds 8 groups whatever the cell count; run_tiny_path picks it when the shape allows)
+      const bool smem_ok = cap >= 2 && (force_tiny || cap >= ctx.g_raw + 1);
+      if (smem_ok || (ctx.g_raw <= 8.5 && ctx.opt.force_path != 5)) {
         tp.group_cap = cap;
-        int rc = run_tiny_path(ctx, tp);
+        bool used_reg = false;
+        int rc = run_tiny_path(ctx, tp, smem_ok, used_reg, done);
         if (rc) return rc;
-        done = true; path = "tiny";
-        return BGB_OK;
+        if (done) { path = used_reg ? "tiny-reg" : "tiny"; return BGB_OK; }
       }
-    }
+    } else if (ctx.opt.force_path == 6) return set_error(BGB_UNSUPPORTED, "force_path 6: this plan has no tiny-cardinality form");
   }
   const SmemEligibility e = smem_eligibility(pl);
   if (e.ok && (ctx.opt.force_path == 0 || ctx.opt.force_path == 2 || ctx.opt.force_path == 4)) {

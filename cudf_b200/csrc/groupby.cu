@@ -382,7 +382,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     if (st[0] == 0 && st[3] == 0) { h->num_groups = (int32_t)st[1]; break; }
     if (st[0] == 0 && st[3] != 0 && !skip_tiny) {
       // the tiny-cardinality kernel met more distinct keys than it has rows for: same table, general path
-      if (opt.force_path == 5) opt.force_path = 0;
+      if (opt.force_path == 5 || opt.force_path == 6) opt.force_path = 0;
       skip_tiny = true;
       h->dfree(h->group_slots); h->group_slots = nullptr;
       h->dfree(h->table.keys); h->table.keys = nullptr;

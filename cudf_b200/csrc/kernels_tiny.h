@@ -34,4 +34,8 @@ struct TinyParams {
 size_t tiny_smem_bytes(int cells, int group_cap);
 cudaError_t launch_aggregate_tiny(const TinyParams& p, int num_sms, cudaStream_t s);
 
+// register-resident variant (kernels_tiny_reg.cu): at most 8 groups, one or two 8-byte value columns, SUM/SUMSQ/COUNT
+bool tiny_reg_eligible(const TinyParams& p);  // p.a (keys, table) must be filled
+cudaError_t launch_aggregate_tiny_reg(const TinyParams& p, int group_cap /* 4 or 8 */, int num_sms, cudaStream_t s);
+
 }  // namespace bgb

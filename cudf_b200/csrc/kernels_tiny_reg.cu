@@ -1,0 +1,348 @@
+// Register-resident variant of the tiny-cardinality kernel (BASELINE config Q1: 4 groups, 6e8 rows, two int8 keys,
+// MEAN + VAR + COUNT of two float64 columns = 18 B/row, 1.7 ms at the HBM roofline).
+//
+// With at most 8 groups every accumulator of every group fits in REGISTERS: a row is "compare its packed key with the
+// G cached group keys, then G predicated adds per accumulator" -- no shared memory, no atomics, no indexed access on the
+// row path. A warp reads 256 consecutive rows per iteration as fully coalesced vectors: lane l owns rows
+// {64 j + 2 l, 64 j + 2 l + 1}, j = 0..3, so a float64 column is four LDG.128 per lane and an int8 key column four
+// LDG.U16. Group keys are learnt through the same CAS dictionary as kernels_tiny.cu and then cached in registers;
+// a CTA that meets more than G keys raises status[3] and the host takes another path.
+// Reference counterpart: the replicated shared-memory accumulators for low cardinalities,
+// /root/reference/cpp/src/groupby/hash/compute_shared_memory_aggs.cu:260-353.
+#include "device_utils.cuh"
+#include "kernels_tiny.h"
+
+namespace bgb {
+namespace {
+
+constexpr int kRT        = 128;  // threads per CTA (111-183 registers per thread: 2-4 CTAs per SM)
+constexpr int kPairs     = 4;    // row pairs per lane per iteration (warp tile = 32 lanes * 2 rows * 4 = 256 rows)
+constexpr int kWarpTile  = 64 * kPairs;
+constexpr int kDictSlots = 64;
+
+struct RegParams {
+  AggParams a;
+  const uint8_t* vdata[2];
+  const uint32_t* vmask[2];
+  int32_t voffset[2];
+  int32_t acc_sum[2], acc_sumsq[2], acc_count[2];
+  int32_t acc_count_all;
+};
+
+// two consecutive elements of width w starting at element index idx (idx even, base suitably aligned)
+__device__ __forceinline__ void load_pair(const uint8_t* data, int w, int64_t idx, uint64_t& e0, uint64_t& e1)
+{
+  switch (w) {
+    case 1: { const uint32_t v = __ldg(reinterpret_cast<const uint16_t*>(data + idx)); e0 = v & 0xffu; e1 = v >> 8; break; }
+    case 2: { const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(data + 2 * idx)); e0 = v & 0xffffu; e1 = v >> 16; break; }
+    case 4: { const uint2 v = __ldg(reinterpret_cast<const uint2*>(data + 4 * idx)); e0 = v.x; e1 = v.y; break; }
+    default: {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(data + 8 * idx));
+      e0 = (uint64_t)v.x | ((uint64_t)v.y << 32);
+      e1 = (uint64_t)v.z | ((uint64_t)v.w << 32);
+    }
+  }
+}
+
+__device__ __noinline__ int reg_insert_key(uint64_t k, unsigned long long* dict_key, int* dict_gid, unsigned long long* group_key, int* groups, int cap)
+{
+  uint32_t slot = (uint32_t)(mix64(k) >> 58);
+  for (int moved = 0; moved < kDictSlots;) {
+    const unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&dict_key[slot]);
+    if (cur == k) {
+      const int g = *reinterpret_cast<volatile int*>(&dict_gid[slot]);
+      if (g == -1) continue;  // the owner publishes right after its CAS
+      return g;
+    }
+    if (cur == kEmpty) {
+      const unsigned long long old = atomicCAS(&dict_key[slot], (unsigned long long)kEmpty, (unsigned long long)k);
+      if (old == kEmpty) {
+        const int g = atomicAdd(groups, 1);
+        if (g < cap) *reinterpret_cast<volatile unsigned long long*>(&group_key[g]) = k;
+        __threadfence_block();
+        *reinterpret_cast<volatile int*>(&dict_gid[slot]) = g < cap ? g : -2;
+        return g < cap ? g : -2;
+      }
+      if (old == k) continue;
+    }
+    slot = (slot + 1) & (kDictSlots - 1);
+    ++moved;
+  }
+  return -2;
+}
+
+template <bool F64> struct Arith;
+template <> struct Arith<true> {
+  using T = double;
+  static __device__ __forceinline__ T from_bits(uint64_t b) { return __longlong_as_double((long long)b); }
+  static __device__ __forceinline__ uint64_t to_bits(T v) { return (uint64_t)__double_as_longlong(v); }
+};
+template <> struct Arith<false> {
+  using T = unsigned long long;  // wraps like the reference's int64 atomic add
+  static __device__ __forceinline__ T from_bits(uint64_t b) { return b; }
+  static __device__ __forceinline__ uint64_t to_bits(T v) { return v; }
+};
+
+// one (group, column) update under the predicate gc == g
+template <bool SQ>
+__device__ __forceinline__ void pred_update(double& sum, double& sq, int& cnt, double v, int gc, int g)
+{
+  if (SQ)
+    asm volatile("{ .reg .pred p; setp.eq.s32 p, %4, %5; @p add.f64 %0, %0, %3; @p fma.rn.f64 %1, %3, %3, %1; @p add.s32 %2, %2, 1; }"
+                 : "+d"(sum), "+d"(sq), "+r"(cnt) : "d"(v), "r"(gc), "r"(g));
+  else
+    asm volatile("{ .reg .pred p; setp.eq.s32 p, %3, %4; @p add.f64 %0, %0, %2; @p add.s32 %1, %1, 1; }"
+                 : "+d"(sum), "+r"(cnt) : "d"(v), "r"(gc), "r"(g));
+}
+template <bool SQ>
+__device__ __forceinline__ void pred_update(unsigned long long& sum, unsigned long long& sq, int& cnt, unsigned long long v, int gc, int g)
+{
+  if (SQ)
+    asm volatile("{ .reg .pred p; setp.eq.s32 p, %4, %5; @p add.u64 %0, %0, %3; @p mad.lo.u64 %1, %3, %3, %1; @p add.s32 %2, %2, 1; }"
+                 : "+l"(sum), "+l"(sq), "+r"(cnt) : "l"(v), "r"(gc), "r"(g));
+  else
+    asm volatile("{ .reg .pred p; setp.eq.s32 p, %3, %4; @p add.u64 %0, %0, %2; @p add.s32 %1, %1, 1; }"
+                 : "+l"(sum), "+r"(cnt) : "l"(v), "r"(gc), "r"(g));
+}
+
+template <int G, int NC, bool SQ, bool F64>
+__global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant__ RegParams p)
+{
+  using A = Arith<F64>;
+  using T = typename A::T;
+  __shared__ unsigned long long s_dict_key[kDictSlots];
+  __shared__ int s_dict_gid[kDictSlots];
+  __shared__ unsigned long long s_group_key[G];
+  __shared__ int s_groups, s_abort;
+  __shared__ unsigned long long s_acc[G][NC][2];  // block totals: [sum, sumsq] bit patterns (added with a CAS loop)
+  __shared__ int s_cnt[G][NC + 1];                // valid counts per column, [NC] = all rows
+
+  for (int i = threadIdx.x; i < kDictSlots; i += kRT) { s_dict_key[i] = kEmpty; s_dict_gid[i] = -1; }
+  if (threadIdx.x < G) s_group_key[threadIdx.x] = kEmpty;
+  for (int i = threadIdx.x; i < G * NC * 2; i += kRT) (&s_acc[0][0][0])[i] = A::to_bits((T)0);
+  for (int i = threadIdx.x; i < G * (NC + 1); i += kRT) (&s_cnt[0][0])[i] = 0;
+  if (threadIdx.x == 0) { s_groups = 0; s_abort = 0; }
+  __syncthreads();
+
+  T sum[G][NC], sq[G][NC];
+  int cnt[G][NC], cnt_all[G];
+  unsigned long long gk[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    gk[g] = kEmpty; cnt_all[g] = 0;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) { sum[g][c] = (T)0; sq[g][c] = (T)0; cnt[g][c] = 0; }
+  }
+  bool abort_seen = false;
+
+  const int64_t n      = p.a.num_rows;
+  const int lane       = threadIdx.x & 31;
+  const int64_t warp0  = (int64_t)blockIdx.x * (kRT / 32) + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)gridDim.x * (kRT / 32);
+  for (int64_t wb = warp0 * kWarpTile; wb < n; wb += nwarps * kWarpTile) {
+    // ---- all loads of the tile first: 4 row pairs per lane
+    uint64_t img[kPairs][2], val[NC][kPairs][2];
+    uint32_t ok[kPairs];  // bit 0/1: row usable (in range, key not dropped); bits 2c+2 / 2c+3: value column c valid
+#pragma unroll
+    for (int j = 0; j < kPairs; ++j) {
+      const int64_t row = wb + 64 * j + 2 * lane;
+      ok[j]     = 0;
+      img[j][0] = img[j][1] = 0;
+      const bool in0 = row < n, in1 = row + 1 < n;
+      if (in0) ok[j] = in1 ? 3u : 1u;
+#pragma unroll 1
+      for (int c = 0; c < p.a.num_key_cols; ++c) {
+        const KeyColDesc& kc = p.a.kc[c];
+        uint64_t e0 = 0, e1 = 0;
+        const int64_t idx = (int64_t)kc.offset + row;
+        if (in1) load_pair(kc.data, kc.width, idx, e0, e1);
+        else if (in0) e0 = load_raw(kc.data, kc.width, idx);
+        uint32_t kv = 3u;
+        if (kc.mask != nullptr && in0) kv = (__ldg(kc.mask + (idx >> 5)) >> (idx & 31)) & 3u;  // idx is even: both bits in one word
+        if (kv != 3u) {
+          if (p.a.skip_null_keys) ok[j] &= kv;  // EXCLUDE: the row is dropped
+          else {                                 // INCLUDE: the null flag is part of the key, value bits stay zero
+            if (!(kv & 1u)) { e0 = 0; img[j][0] |= 1ull << kc.null_bit; }
+            if (!(kv & 2u)) { e1 = 0; img[j][1] |= 1ull << kc.null_bit; }
+          }
+        }
+        img[j][0] |= e0 << kc.shift;
+        img[j][1] |= e1 << kc.shift;
+      }
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        val[c][j][0] = val[c][j][1] = 0;
+        const int64_t idx = (int64_t)p.voffset[c] + row;
+        if (in1) load_pair(p.vdata[c], 8, idx, val[c][j][0], val[c][j][1]);
+        else if (in0) val[c][j][0] = load_raw(p.vdata[c], 8, idx);
+        uint32_t vv = 3u;
+        if (p.vmask[c] != nullptr && in0) vv = (__ldg(p.vmask[c] + (idx >> 5)) >> (idx & 31)) & 3u;
+        ok[j] |= vv << (2 * c + 2);
+      }
+    }
+    // ---- rows into the register accumulators
+#pragma unroll
+    for (int j = 0; j < kPairs; ++j) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const bool usable = (ok[j] >> h) & 1u;
+        const unsigned long long k = img[j][h];
+        int gid = -1;
+#pragma unroll
+        for (int g = 0; g < G; ++g) gid = (gk[g] == k) ? g : gid;
+        if (usable && gid < 0) {  // first rows only: learn the key, then refresh the cached group keys
+          gid = (k == kEmpty) ? -2 : reg_insert_key(k, s_dict_key, s_dict_gid, s_group_key, &s_groups, G);
+          if (gid < 0) abort_seen = true;
+#pragma unroll
+          for (int g = 0; g < G; ++g) gk[g] = *reinterpret_cast<volatile unsigned long long*>(&s_group_key[g]);
+        }
+        if (!usable) gid = -1;
+        // G x NC predicated updates. Written as predicated PTX on purpose: as C++ `if`s the compiler emitted a divergent
+        // branch per (group, column) (582 M branches, IPC 0.67 in ncu); selects would double the instruction count.
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          asm volatile("{ .reg .pred p; setp.eq.s32 p, %1, %2; @p add.s32 %0, %0, 1; }" : "+r"(cnt_all[g]) : "r"(gid), "r"(g));
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          // null source skipped (device_aggregators.cuh:434-436): the column sees group -1 for this row
+          const int gc = ((ok[j] >> (2 * c + 2 + h)) & 1u) ? gid : -1;
+          const T v    = A::from_bits(val[c][j][h]);
+#pragma unroll
+          for (int g = 0; g < G; ++g) pred_update<SQ>(sum[g][c], sq[g][c], cnt[g][c], v, gc, g);
+        }
+      }
+    }
+    __syncwarp();
+  }
+  if (abort_seen) s_abort = 1;
+  __syncthreads();
+  if (s_abort) { if (threadIdx.x == 0) p.a.table.status[3] = 1; return; }
+
+  // ---- group ids are CTA-wide (every thread cached the same s_group_key order): fold lanes, then warps, then one global
+  //      atomic per (CTA, group, accumulator)
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    int ca = cnt_all[g];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) ca += __shfl_xor_sync(0xffffffffu, ca, d);
+    if (lane == 0 && ca) atomicAdd(&s_cnt[g][NC], ca);
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      T s = sum[g][c], q = sq[g][c];
+      int m = cnt[g][c];
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+        s += A::from_bits(__shfl_xor_sync(0xffffffffu, (unsigned long long)A::to_bits(s), d));
+        if (SQ) q += A::from_bits(__shfl_xor_sync(0xffffffffu, (unsigned long long)A::to_bits(q), d));
+        m += __shfl_xor_sync(0xffffffffu, m, d);
+      }
+      if (lane == 0 && m) {
+        atomicAdd(&s_cnt[g][c], m);
+        if (F64) {
+          atomicAdd(reinterpret_cast<double*>(&s_acc[g][c][0]), __longlong_as_double((long long)A::to_bits(s)));
+          if (SQ) atomicAdd(reinterpret_cast<double*>(&s_acc[g][c][1]), __longlong_as_double((long long)A::to_bits(q)));
+        } else {
+          atomicAdd(&s_acc[g][c][0], (unsigned long long)A::to_bits(s));
+          if (SQ) atomicAdd(&s_acc[g][c][1], (unsigned long long)A::to_bits(q));
+        }
+      }
+    }
+  }
+  __syncthreads();
+  const int groups = s_groups < G ? s_groups : G;
+  if (threadIdx.x < groups) {
+    const int g = threadIdx.x;
+    if (s_cnt[g][NC] > 0) {  // a group learnt by this CTA always has at least one row here
+      const uint64_t slot = find_or_insert(p.a.table, s_group_key[g], 0);
+      if (slot == kNoSlot) { p.a.table.status[0] = 1; return; }
+      if (p.acc_count_all >= 0) atomicAdd(reinterpret_cast<int*>(p.a.acc[p.acc_count_all].cells) + slot, s_cnt[g][NC]);
+      for (int c = 0; c < NC; ++c) {
+        if (s_cnt[g][c] == 0) continue;
+        if (p.acc_count[c] >= 0) atomicAdd(reinterpret_cast<int*>(p.a.acc[p.acc_count[c]].cells) + slot, s_cnt[g][c]);
+        if (p.acc_sum[c] >= 0) {
+          if (F64) atomicAdd(reinterpret_cast<double*>(p.a.acc[p.acc_sum[c]].cells) + slot, __longlong_as_double((long long)s_acc[g][c][0]));
+          else atomicAdd(reinterpret_cast<unsigned long long*>(p.a.acc[p.acc_sum[c]].cells) + slot, s_acc[g][c][0]);
+        }
+        if (SQ && p.acc_sumsq[c] >= 0) {
+          if (F64) atomicAdd(reinterpret_cast<double*>(p.a.acc[p.acc_sumsq[c]].cells) + slot, __longlong_as_double((long long)s_acc[g][c][1]));
+          else atomicAdd(reinterpret_cast<unsigned long long*>(p.a.acc[p.acc_sumsq[c]].cells) + slot, s_acc[g][c][1]);
+        }
+      }
+    }
+  }
+}
+
+template <int G, int NC, bool SQ, bool F64>
+cudaError_t launch_one(const RegParams& rp, int num_sms, cudaStream_t s)
+{
+  int per_sm = 1;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, agg_tiny_reg_kernel<G, NC, SQ, F64>, kRT, 0);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 1) per_sm = 1;
+  const int64_t tiles = (rp.a.num_rows + (int64_t)kWarpTile * (kRT / 32) - 1) / ((int64_t)kWarpTile * (kRT / 32));
+  const int64_t grid  = tiles < (int64_t)num_sms * per_sm ? tiles : (int64_t)num_sms * per_sm;
+  agg_tiny_reg_kernel<G, NC, SQ, F64><<<(int)grid, kRT, 0, s>>>(rp);
+  return note_launch();
+}
+
+template <int G, int NC>
+cudaError_t launch_gn(const RegParams& rp, bool sq, bool f64, int num_sms, cudaStream_t s)
+{
+  if (sq) return f64 ? launch_one<G, NC, true, true>(rp, num_sms, s) : launch_one<G, NC, true, false>(rp, num_sms, s);
+  return f64 ? launch_one<G, NC, false, true>(rp, num_sms, s) : launch_one<G, NC, false, false>(rp, num_sms, s);
+}
+
+bool aligned(const void* base, int64_t elem_offset, int width, int bytes)
+{
+  return ((uintptr_t)base + (uintptr_t)(elem_offset * width)) % (uintptr_t)bytes == 0;
+}
+
+}  // namespace
+
+// which shapes the register kernel serves: 64-bit key image of integer-like columns, one or two 8-byte value columns of
+// one arithmetic class (float64, or int64/uint64), SUM / SUM_OF_SQUARES / COUNT only, pair-aligned column starts
+bool tiny_reg_eligible(const TinyParams& tp)
+{
+  if (tp.a.table.key_words != 1) return false;
+  for (int c = 0; c < tp.a.num_key_cols; ++c) {
+    const KeyColDesc& k = tp.a.kc[c];
+    if (k.fclass != 0 || (k.offset & 1) || !aligned(k.data, k.offset, k.width, 2 * k.width)) return false;
+  }
+  int real = 0, cls = -1;
+  for (int j = 0; j < tp.num_cols; ++j) {
+    const TinyCol& col = tp.cols[j];
+    if (col.need_minmax) return false;
+    if (col.data == nullptr) continue;  // COUNT_ALL pseudo column
+    if (++real > 2) return false;
+    if (col.width != 8 || (col.offset & 1) || !aligned(col.data, col.offset, 8, 16)) return false;
+    const int c = col.sum_op == ACC_SUM_F64 ? 1 : (col.src == S_I64 || col.src == S_U64) ? 0 : -2;
+    if (c == -2 || (cls >= 0 && cls != c)) return false;
+    cls = c;
+  }
+  return real >= 1;
+}
+
+cudaError_t launch_aggregate_tiny_reg(const TinyParams& tp, int group_cap, int num_sms, cudaStream_t s)
+{
+  if (tp.a.num_rows == 0) return cudaSuccess;
+  RegParams rp;
+  memset(&rp, 0, sizeof rp);
+  rp.a = tp.a;
+  rp.acc_count_all = -1;
+  int nc = 0;
+  bool sq = false, f64 = false;
+  for (int j = 0; j < tp.num_cols; ++j) {
+    const TinyCol& col = tp.cols[j];
+    if (col.data == nullptr) { rp.acc_count_all = col.acc_count; continue; }
+    rp.vdata[nc] = col.data; rp.vmask[nc] = col.mask; rp.voffset[nc] = col.offset;
+    rp.acc_sum[nc] = col.acc_sum; rp.acc_sumsq[nc] = col.acc_sumsq; rp.acc_count[nc] = col.acc_count;
+    sq |= col.need_sq != 0;
+    f64 = col.sum_op == ACC_SUM_F64;
+    ++nc;
+  }
+  if (group_cap <= 4) return nc == 1 ? launch_gn<4, 1>(rp, sq, f64, num_sms, s) : launch_gn<4, 2>(rp, sq, f64, num_sms, s);
+  return nc == 1 ? launch_gn<8, 1>(rp, sq, f64, num_sms, s) : launch_gn<8, 2>(rp, sq, f64, num_sms, s);
+}
+
+}  // namespace bgb

@@ -116,7 +116,8 @@ typedef struct bgb_allocator {
  * (/root/reference/cpp/src/groupby/hash/helpers.cuh:19-40) but selectable for tests. */
 typedef struct bgb_options {
   int32_t force_path;        /* 0 auto, 1 global-table kernel only, 2 shared-memory hashed pre-aggregation, 3 partitioned,
-                                4 shared-memory (direct-address variant allowed), 5 tiny-cardinality kernel */
+                                4 shared-memory (direct-address variant allowed), 5 tiny-cardinality kernel (shared-memory
+                                accumulators), 6 tiny-cardinality kernel with register accumulators (<= 8 groups) */
   int32_t capacity_log2;     /* 0 auto; else global table has 2^capacity_log2 slots */
   int32_t sample_rows;       /* 0 auto (65536) rows sampled by the cardinality estimator */
   int32_t profile;           /* != 0: bracket every kernel with CUDA events on the call's stream (bgb_groupby_profile) */

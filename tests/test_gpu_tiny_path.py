@@ -35,7 +35,57 @@ def test_config_q1_shape_reduced_forced_and_auto():
     G, path = gpu_util.compare_with_oracle(keys, vals, Q1_AGGS, options={"force_path": 5}, name="Q1/forced")
     assert path == "tiny" and G == 4
     G, path = gpu_util.compare_with_oracle(keys, vals, Q1_AGGS, name="Q1/auto")
-    assert path == "tiny" and G == 4
+    assert path == "tiny-reg" and G == 4  # 4 groups, two float64 columns: accumulators live in registers
+    G, path = gpu_util.compare_with_oracle(keys, vals, Q1_AGGS, options={"force_path": 6}, name="Q1/forced-reg8")
+    assert path == "tiny-reg" and G == 4
+
+
+@pytest.mark.parametrize("vtype", ["int64", "uint64", "float64"])
+@pytest.mark.parametrize("ncols", [1, 2])
+def test_register_variant_with_nulls(vtype, ncols):
+    rng = np.random.default_rng(41 + ncols)
+    n = 500_001  # odd: the last pair of the last tile is half outside the column
+    keys = [H(rng.integers(0, 7, n).astype(np.int16), rng.random(n) > 0.05), H(rng.integers(0, 1, n).astype(np.int8))]
+    vals = [H(rng.integers(0, 1000, n).astype(vtype), rng.random(n) > 0.2) for _ in range(ncols)]
+    aggs = []
+    for c in range(ncols):
+        aggs += [(c, "sum", 1), (c, "count_valid", 1), (c, "mean", 1), (c, "variance", 1), (c, "sum_of_squares", 1)]
+    aggs.append((0, "count_all", 1))
+    for include in (False, True):
+        G, path = gpu_util.compare_with_oracle(keys, vals, aggs, include_null_keys=include, options={"force_path": 6},
+                                               name=f"tiny-reg/{vtype}/{ncols}/{include}")
+        assert path == "tiny-reg" and G == (8 if include else 7)
+    G, path = gpu_util.compare_with_oracle(keys, vals, aggs, name=f"tiny-reg/{vtype}/{ncols}/auto")
+    assert path == "tiny-reg"
+
+
+def test_register_variant_more_than_8_groups_falls_back():
+    rng = np.random.default_rng(43)
+    n = 300_000
+    k = rng.integers(0, 12, n).astype(np.int64)
+    keys, vals = [H(k)], [H(rng.standard_normal(n))]
+    aggs = [(0, "sum", 1), (0, "variance", 1), (0, "count_valid", 1)]
+    G, path = gpu_util.compare_with_oracle(keys, vals, aggs, options={"force_path": 6}, name="tiny-reg/overflow")
+    assert path != "tiny-reg" and G == 12
+    # negative zero and NaN values go through the same adds as the reference's
+    v = rng.standard_normal(n)
+    v[::7] = -0.0
+    k2 = rng.integers(0, 3, n).astype(np.int64)
+    gpu_util.compare_with_oracle([H(k2)], [H(v)], [(0, "sum", 1), (0, "mean", 1)], options={"force_path": 6}, name="tiny-reg/negzero")
+
+
+def test_register_variant_declines_min_max_and_narrow_values():
+    import cudf_b200 as cb
+    rng = np.random.default_rng(44)
+    n = 100_000
+    keys = [H(rng.integers(0, 3, n).astype(np.int32))]
+    with pytest.raises(cb.UnsupportedError):
+        gpu_util.run_gpu(keys, [H(rng.standard_normal(n))], [(0, "min", 1)], options={"force_path": 6})
+    with pytest.raises(cb.UnsupportedError):
+        gpu_util.run_gpu(keys, [H(rng.integers(0, 9, n).astype(np.int32))], [(0, "sum", 1)], options={"force_path": 6})
+    # without forcing, the same calls are served by the shared-memory variant
+    G, path = gpu_util.compare_with_oracle(keys, [H(rng.standard_normal(n))], [(0, "min", 1), (0, "sum", 1)], name="tiny/minmax-auto")
+    assert path == "tiny"
 
 
 @pytest.mark.parametrize("vtype", ["int8", "int32", "int64", "uint16", "float32", "float64"])
