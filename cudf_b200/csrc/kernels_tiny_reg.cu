@@ -29,21 +29,6 @@ struct RegParams {
   int32_t acc_count_all;
 };
 
-// two consecutive elements of width w starting at element index idx (idx even, base suitably aligned)
-__device__ __forceinline__ void load_pair(const uint8_t* data, int w, int64_t idx, uint64_t& e0, uint64_t& e1)
-{
-  switch (w) {
-    case 1: { const uint32_t v = __ldg(reinterpret_cast<const uint16_t*>(data + idx)); e0 = v & 0xffu; e1 = v >> 8; break; }
-    case 2: { const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(data + 2 * idx)); e0 = v & 0xffffu; e1 = v >> 16; break; }
-    case 4: { const uint2 v = __ldg(reinterpret_cast<const uint2*>(data + 4 * idx)); e0 = v.x; e1 = v.y; break; }
-    default: {
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(data + 8 * idx));
-      e0 = (uint64_t)v.x | ((uint64_t)v.y << 32);
-      e1 = (uint64_t)v.z | ((uint64_t)v.w << 32);
-    }
-  }
-}
-
 __device__ __noinline__ int reg_insert_key(uint64_t k, unsigned long long* dict_key, int* dict_gid, unsigned long long* group_key, int* groups, int cap)
 {
   uint32_t slot = (uint32_t)(mix64(k) >> 58);
@@ -83,31 +68,67 @@ template <> struct Arith<false> {
   static __device__ __forceinline__ uint64_t to_bits(T v) { return v; }
 };
 
-// one (group, column) update under the predicate gc == g
-template <bool SQ>
-__device__ __forceinline__ void pred_update(double& sum, double& sq, int& cnt, double v, int gc, int g)
+// raw pair of W-byte elements as loaded (decoded later by split_pair): one 2W-byte vector, or element-wise at the tail
+template <int W, bool FULL>
+__device__ __forceinline__ void load_pair_raw(const uint8_t* data, int64_t idx, int64_t row, int64_t n, uint64_t (&r)[2])
 {
-  if (SQ)
-    asm volatile("{ .reg .pred p; setp.eq.s32 p, %4, %5; @p add.f64 %0, %0, %3; @p fma.rn.f64 %1, %3, %3, %1; @p add.s32 %2, %2, 1; }"
-                 : "+d"(sum), "+d"(sq), "+r"(cnt) : "d"(v), "r"(gc), "r"(g));
-  else
-    asm volatile("{ .reg .pred p; setp.eq.s32 p, %3, %4; @p add.f64 %0, %0, %2; @p add.s32 %1, %1, 1; }"
-                 : "+d"(sum), "+r"(cnt) : "d"(v), "r"(gc), "r"(g));
+  r[0] = r[1] = 0;
+  if (FULL) {
+    if (W == 1) r[0] = __ldg(reinterpret_cast<const uint16_t*>(data + idx));
+    else if (W == 2) r[0] = __ldg(reinterpret_cast<const uint32_t*>(data + 2 * idx));
+    else if (W == 4) { const uint2 v = __ldg(reinterpret_cast<const uint2*>(data + 4 * idx)); r[0] = (uint64_t)v.x | ((uint64_t)v.y << 32); }
+    else {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(data + 8 * idx));
+      r[0] = (uint64_t)v.x | ((uint64_t)v.y << 32);
+      r[1] = (uint64_t)v.z | ((uint64_t)v.w << 32);
+    }
+  } else {
+    uint64_t e0 = 0, e1 = 0;
+    if (row < n) e0 = load_raw(data, W, idx);
+    if (row + 1 < n) e1 = load_raw(data, W, idx + 1);
+    if (W == 8) { r[0] = e0; r[1] = e1; }
+    else r[0] = e0 | (e1 << (8 * (W & 7)));
+  }
 }
-template <bool SQ>
-__device__ __forceinline__ void pred_update(unsigned long long& sum, unsigned long long& sq, int& cnt, unsigned long long v, int gc, int g)
+template <int W>
+__device__ __forceinline__ void split_pair(const uint64_t (&r)[2], uint64_t& e0, uint64_t& e1)
 {
-  if (SQ)
-    asm volatile("{ .reg .pred p; setp.eq.s32 p, %4, %5; @p add.u64 %0, %0, %3; @p mad.lo.u64 %1, %3, %3, %1; @p add.s32 %2, %2, 1; }"
-                 : "+l"(sum), "+l"(sq), "+r"(cnt) : "l"(v), "r"(gc), "r"(g));
-  else
-    asm volatile("{ .reg .pred p; setp.eq.s32 p, %3, %4; @p add.u64 %0, %0, %2; @p add.s32 %1, %1, 1; }"
-                 : "+l"(sum), "+r"(cnt) : "l"(v), "r"(gc), "r"(g));
+  if (W == 8) { e0 = r[0]; e1 = r[1]; }
+  else { e0 = r[0] & ((1ull << (8 * (W & 7))) - 1); e1 = r[0] >> (8 * (W & 7)); }
 }
 
-template <int G, int NC, bool SQ, bool F64>
+template <int NC, int W, int KCMAX, bool FULL, bool MASKS>
+__device__ __forceinline__ void tile_loads(const RegParams& p, int64_t wb, int lane, int64_t n, uint64_t (&kr)[kPairs][KCMAX][2],
+                                           uint32_t (&km)[kPairs][KCMAX], uint64_t (&val)[NC][kPairs][2], uint32_t (&vm)[NC][kPairs])
+{
+#pragma unroll
+  for (int j = 0; j < kPairs; ++j) {
+    const int64_t row = wb + 64 * j + 2 * lane;
+#pragma unroll
+    for (int c = 0; c < KCMAX; ++c) {
+      kr[j][c][0] = kr[j][c][1] = 0;
+      km[j][c]    = 0xffffffffu;
+      if (c < p.a.num_key_cols) {
+        const KeyColDesc& kc = p.a.kc[c];
+        const int64_t idx    = (int64_t)kc.offset + row;
+        load_pair_raw<W, FULL>(kc.data, idx, row, n, kr[j][c]);
+        if (MASKS && kc.mask != nullptr && (FULL || row < n)) km[j][c] = __ldg(kc.mask + (idx >> 5)) >> (idx & 31);  // idx even: both bits in one word
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      vm[c][j]          = 0xffffffffu;
+      const int64_t idx = (int64_t)p.voffset[c] + row;
+      load_pair_raw<8, FULL>(p.vdata[c], idx, row, n, val[c][j]);
+      if (MASKS && p.vmask[c] != nullptr && (FULL || row < n)) vm[c][j] = __ldg(p.vmask[c] + (idx >> 5)) >> (idx & 31);
+    }
+  }
+}
+
+template <int G, int NC, bool SQ, bool F64, int W>
 __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant__ RegParams p)
 {
+  constexpr int KCMAX = W == 8 ? 1 : W == 4 ? 2 : 4;  // the packed key image is at most 64 bits
   using A = Arith<F64>;
   using T = typename A::T;
   __shared__ unsigned long long s_dict_key[kDictSlots];
@@ -125,60 +146,66 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
   __syncthreads();
 
   T sum[G][NC], sq[G][NC];
-  int cnt[G][NC], cnt_all[G];
+  int nulls[G][NC], cnt_all[G];  // valid count of a column = rows of the group - its nulls
   unsigned long long gk[G];
 #pragma unroll
   for (int g = 0; g < G; ++g) {
     gk[g] = kEmpty; cnt_all[g] = 0;
 #pragma unroll
-    for (int c = 0; c < NC; ++c) { sum[g][c] = (T)0; sq[g][c] = (T)0; cnt[g][c] = 0; }
+    for (int c = 0; c < NC; ++c) { sum[g][c] = (T)0; sq[g][c] = (T)0; nulls[g][c] = 0; }
   }
   bool abort_seen = false;
+  bool any_vmask  = false;
+#pragma unroll
+  for (int c = 0; c < NC; ++c) any_vmask |= p.vmask[c] != nullptr;
+  bool any_mask = any_vmask;
+  for (int c = 0; c < p.a.num_key_cols; ++c) any_mask |= p.a.kc[c].mask != nullptr;
 
   const int64_t n      = p.a.num_rows;
   const int lane       = threadIdx.x & 31;
   const int64_t warp0  = (int64_t)blockIdx.x * (kRT / 32) + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * (kRT / 32);
   for (int64_t wb = warp0 * kWarpTile; wb < n; wb += nwarps * kWarpTile) {
-    // ---- all loads of the tile first: 4 row pairs per lane
-    uint64_t img[kPairs][2], val[NC][kPairs][2];
+    // ---- phase 1: every load of the tile is issued before anything is decoded, in ONE basic block (tile_loads): the
+    //      earlier forms decoded each key right after its load, or kept each load behind its own uniform branch, and
+    //      ncu showed eight serialised long-scoreboard stalls per tile (12-15 ms on Q1). Lane l owns the row pairs
+    //      {wb + 64 j + 2 l, +1}; a pair of W-byte keys is one 2W-byte load, a pair of 8-byte values one LDG.128.
+    uint64_t kr[kPairs][KCMAX][2], val[NC][kPairs][2];
+    uint32_t km[kPairs][KCMAX], vm[NC][kPairs];
+    if (wb + kWarpTile <= n) {  // warp-uniform; only the last tile takes the guarded element loads
+      if (any_mask) tile_loads<NC, W, KCMAX, true, true>(p, wb, lane, n, kr, km, val, vm);
+      else tile_loads<NC, W, KCMAX, true, false>(p, wb, lane, n, kr, km, val, vm);
+    } else {
+      tile_loads<NC, W, KCMAX, false, true>(p, wb, lane, n, kr, km, val, vm);
+    }
+    // ---- phase 2: packed key images and validity bits
+    uint64_t img[kPairs][2];
     uint32_t ok[kPairs];  // bit 0/1: row usable (in range, key not dropped); bits 2c+2 / 2c+3: value column c valid
 #pragma unroll
     for (int j = 0; j < kPairs; ++j) {
       const int64_t row = wb + 64 * j + 2 * lane;
-      ok[j]     = 0;
+      ok[j]     = row + 1 < n ? 3u : row < n ? 1u : 0u;
       img[j][0] = img[j][1] = 0;
-      const bool in0 = row < n, in1 = row + 1 < n;
-      if (in0) ok[j] = in1 ? 3u : 1u;
-#pragma unroll 1
-      for (int c = 0; c < p.a.num_key_cols; ++c) {
-        const KeyColDesc& kc = p.a.kc[c];
-        uint64_t e0 = 0, e1 = 0;
-        const int64_t idx = (int64_t)kc.offset + row;
-        if (in1) load_pair(kc.data, kc.width, idx, e0, e1);
-        else if (in0) e0 = load_raw(kc.data, kc.width, idx);
-        uint32_t kv = 3u;
-        if (kc.mask != nullptr && in0) kv = (__ldg(kc.mask + (idx >> 5)) >> (idx & 31)) & 3u;  // idx is even: both bits in one word
-        if (kv != 3u) {
-          if (p.a.skip_null_keys) ok[j] &= kv;  // EXCLUDE: the row is dropped
-          else {                                 // INCLUDE: the null flag is part of the key, value bits stay zero
-            if (!(kv & 1u)) { e0 = 0; img[j][0] |= 1ull << kc.null_bit; }
-            if (!(kv & 2u)) { e1 = 0; img[j][1] |= 1ull << kc.null_bit; }
+#pragma unroll
+      for (int c = 0; c < KCMAX; ++c) {
+        if (c < p.a.num_key_cols) {
+          const KeyColDesc& kc = p.a.kc[c];
+          uint64_t e0, e1;
+          split_pair<W>(kr[j][c], e0, e1);
+          const uint32_t kv = km[j][c] & 3u;
+          if (kv != 3u) {
+            if (p.a.skip_null_keys) ok[j] &= kv;  // EXCLUDE: the row is dropped
+            else {                                 // INCLUDE: the null flag is part of the key, value bits stay zero
+              if (!(kv & 1u)) { e0 = 0; img[j][0] |= 1ull << kc.null_bit; }
+              if (!(kv & 2u)) { e1 = 0; img[j][1] |= 1ull << kc.null_bit; }
+            }
           }
+          img[j][0] |= e0 << kc.shift;
+          img[j][1] |= e1 << kc.shift;
         }
-        img[j][0] |= e0 << kc.shift;
-        img[j][1] |= e1 << kc.shift;
       }
 #pragma unroll
-      for (int c = 0; c < NC; ++c) {
-        val[c][j][0] = val[c][j][1] = 0;
-        const int64_t idx = (int64_t)p.voffset[c] + row;
-        if (in1) load_pair(p.vdata[c], 8, idx, val[c][j][0], val[c][j][1]);
-        else if (in0) val[c][j][0] = load_raw(p.vdata[c], 8, idx);
-        uint32_t vv = 3u;
-        if (p.vmask[c] != nullptr && in0) vv = (__ldg(p.vmask[c] + (idx >> 5)) >> (idx & 31)) & 3u;
-        ok[j] |= vv << (2 * c + 2);
-      }
+      for (int c = 0; c < NC; ++c) ok[j] |= (vm[c][j] & 3u) << (2 * c + 2);
     }
     // ---- rows into the register accumulators
 #pragma unroll
@@ -197,19 +224,34 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
           for (int g = 0; g < G; ++g) gk[g] = *reinterpret_cast<volatile unsigned long long*>(&s_group_key[g]);
         }
         if (!usable) gid = -1;
-        // G x NC predicated updates. Written as predicated PTX on purpose: as C++ `if`s the compiler emitted a divergent
-        // branch per (group, column) (582 M branches, IPC 0.67 in ncu); selects would double the instruction count.
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-          asm volatile("{ .reg .pred p; setp.eq.s32 p, %1, %2; @p add.s32 %0, %0, 1; }" : "+r"(cnt_all[g]) : "r"(gid), "r"(g));
-        }
+        // G x NC updates with the select on the INPUT: vg = (gid == g) ? v : 0, then unconditional adds. Adding +0.0 is
+        // exact here (a running sum that starts at +0.0 is never -0.0, and x + 0.0 == x for every other x incl. NaN/inf).
+        // Earlier forms, for the record (ncu, Q1): `if`s became 582 M divergent branches (21 ms); predicated PTX adds were
+        // lowered by ptxas to add + 2 FSEL on every RESULT word, 189 instructions per row (12.4 ms).
+        T vz[NC];
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
-          // null source skipped (device_aggregators.cuh:434-436): the column sees group -1 for this row
-          const int gc = ((ok[j] >> (2 * c + 2 + h)) & 1u) ? gid : -1;
-          const T v    = A::from_bits(val[c][j][h]);
+          vz[c] = A::from_bits(val[c][j][h]);
+          if (any_vmask && !((ok[j] >> (2 * c + 2 + h)) & 1u)) vz[c] = (T)0;  // null source skipped (device_aggregators.cuh:434-436)
+        }
 #pragma unroll
-          for (int g = 0; g < G; ++g) pred_update<SQ>(sum[g][c], sq[g][c], cnt[g][c], v, gc, g);
+        for (int g = 0; g < G; ++g) {
+          const bool hit = gid == g;
+          cnt_all[g] += hit ? 1 : 0;
+#pragma unroll
+          for (int c = 0; c < NC; ++c) {
+            const T vg = hit ? vz[c] : (T)0;
+            sum[g][c] += vg;
+            if (SQ) sq[g][c] += vg * vg;
+          }
+        }
+        if (any_vmask) {  // warp-uniform: columns without a mask never pay for null counting
+#pragma unroll
+          for (int c = 0; c < NC; ++c) {
+            const bool is_null = !((ok[j] >> (2 * c + 2 + h)) & 1u);
+#pragma unroll
+            for (int g = 0; g < G; ++g) nulls[g][c] += (is_null && gid == g) ? 1 : 0;
+          }
         }
       }
     }
@@ -230,7 +272,7 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
 #pragma unroll
     for (int c = 0; c < NC; ++c) {
       T s = sum[g][c], q = sq[g][c];
-      int m = cnt[g][c];
+      int m = cnt_all[g] - nulls[g][c];
 #pragma unroll
       for (int d = 16; d > 0; d >>= 1) {
         s += A::from_bits(__shfl_xor_sync(0xffffffffu, (unsigned long long)A::to_bits(s), d));
@@ -273,17 +315,28 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
   }
 }
 
-template <int G, int NC, bool SQ, bool F64>
-cudaError_t launch_one(const RegParams& rp, int num_sms, cudaStream_t s)
+template <int G, int NC, bool SQ, bool F64, int W>
+cudaError_t launch_w(const RegParams& rp, int num_sms, cudaStream_t s)
 {
   int per_sm = 1;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, agg_tiny_reg_kernel<G, NC, SQ, F64>, kRT, 0);
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, agg_tiny_reg_kernel<G, NC, SQ, F64, W>, kRT, 0);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   const int64_t tiles = (rp.a.num_rows + (int64_t)kWarpTile * (kRT / 32) - 1) / ((int64_t)kWarpTile * (kRT / 32));
   const int64_t grid  = tiles < (int64_t)num_sms * per_sm ? tiles : (int64_t)num_sms * per_sm;
-  agg_tiny_reg_kernel<G, NC, SQ, F64><<<(int)grid, kRT, 0, s>>>(rp);
+  agg_tiny_reg_kernel<G, NC, SQ, F64, W><<<(int)grid, kRT, 0, s>>>(rp);
   return note_launch();
+}
+
+template <int G, int NC, bool SQ, bool F64>
+cudaError_t launch_one(const RegParams& rp, int num_sms, cudaStream_t s)
+{
+  switch (rp.a.kc[0].width) {  // tiny_reg_eligible: every key column has this width
+    case 1: return launch_w<G, NC, SQ, F64, 1>(rp, num_sms, s);
+    case 2: return launch_w<G, NC, SQ, F64, 2>(rp, num_sms, s);
+    case 4: return launch_w<G, NC, SQ, F64, 4>(rp, num_sms, s);
+    default: return launch_w<G, NC, SQ, F64, 8>(rp, num_sms, s);
+  }
 }
 
 template <int G, int NC>
@@ -300,13 +353,16 @@ bool aligned(const void* base, int64_t elem_offset, int width, int bytes)
 
 }  // namespace
 
-// which shapes the register kernel serves: 64-bit key image of integer-like columns, one or two 8-byte value columns of
+// which shapes the register kernel serves: 64-bit key image of integer-like columns of one width, one or two 8-byte value columns of
 // one arithmetic class (float64, or int64/uint64), SUM / SUM_OF_SQUARES / COUNT only, pair-aligned column starts
 bool tiny_reg_eligible(const TinyParams& tp)
 {
   if (tp.a.table.key_words != 1) return false;
+  const int w0 = tp.a.kc[0].width;
+  if (tp.a.num_key_cols > (w0 == 8 ? 1 : w0 == 4 ? 2 : 4)) return false;
   for (int c = 0; c < tp.a.num_key_cols; ++c) {
     const KeyColDesc& k = tp.a.kc[c];
+    if (k.width != w0) return false;  // the kernel is specialised on ONE key width (loads are issued without decoding)
     if (k.fclass != 0 || (k.offset & 1) || !aligned(k.data, k.offset, k.width, 2 * k.width)) return false;
   }
   int real = 0, cls = -1;

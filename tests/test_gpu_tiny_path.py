@@ -45,7 +45,7 @@ def test_config_q1_shape_reduced_forced_and_auto():
 def test_register_variant_with_nulls(vtype, ncols):
     rng = np.random.default_rng(41 + ncols)
     n = 500_001  # odd: the last pair of the last tile is half outside the column
-    keys = [H(rng.integers(0, 7, n).astype(np.int16), rng.random(n) > 0.05), H(rng.integers(0, 1, n).astype(np.int8))]
+    keys = [H(rng.integers(0, 7, n).astype(np.int16), rng.random(n) > 0.05), H(rng.integers(0, 1, n).astype(np.int16))]
     vals = [H(rng.integers(0, 1000, n).astype(vtype), rng.random(n) > 0.2) for _ in range(ncols)]
     aggs = []
     for c in range(ncols):
@@ -74,11 +74,24 @@ def test_register_variant_more_than_8_groups_falls_back():
     gpu_util.compare_with_oracle([H(k2)], [H(v)], [(0, "sum", 1), (0, "mean", 1)], options={"force_path": 6}, name="tiny-reg/negzero")
 
 
+@pytest.mark.parametrize("ktype", ["int8", "int16", "int32", "int64", "uint32"])
+def test_register_variant_key_widths(ktype):
+    rng = np.random.default_rng(45)
+    n = 200_003
+    keys = [H(rng.integers(0, 5, n).astype(ktype))]
+    vals = [H(rng.standard_normal(n), rng.random(n) > 0.1)]
+    G, path = gpu_util.compare_with_oracle(keys, vals, [(0, "sum", 1), (0, "std", 1), (0, "count_valid", 1), (0, "count_all", 1)],
+                                           options={"force_path": 6}, name=f"tiny-reg/key {ktype}")
+    assert path == "tiny-reg" and G == 5
+
+
 def test_register_variant_declines_min_max_and_narrow_values():
     import cudf_b200 as cb
     rng = np.random.default_rng(44)
     n = 100_000
     keys = [H(rng.integers(0, 3, n).astype(np.int32))]
+    with pytest.raises(cb.UnsupportedError):  # key columns of different widths
+        gpu_util.run_gpu([keys[0], H(rng.integers(0, 2, n).astype(np.int8))], [H(rng.standard_normal(n))], [(0, "sum", 1)], options={"force_path": 6})
     with pytest.raises(cb.UnsupportedError):
         gpu_util.run_gpu(keys, [H(rng.standard_normal(n))], [(0, "min", 1)], options={"force_path": 6})
     with pytest.raises(cb.UnsupportedError):
