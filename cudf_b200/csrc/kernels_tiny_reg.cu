@@ -3,8 +3,8 @@
 //
 // With at most 8 groups every accumulator of every group fits in REGISTERS: a row is "compare its packed key with the
 // G cached group keys, then G predicated adds per accumulator" -- no shared memory, no atomics, no indexed access on the
-// row path. A warp reads 256 consecutive rows per iteration as fully coalesced vectors: lane l owns rows
-// {64 j + 2 l, 64 j + 2 l + 1}, j = 0..3, so a float64 column is four LDG.128 per lane and an int8 key column four
+// row path. A warp reads 64 * kPairs consecutive rows per iteration as fully coalesced vectors: lane l owns rows
+// {64 j + 2 l, 64 j + 2 l + 1}, j < kPairs, so a float64 column is kPairs LDG.128 per lane and an int8 key column kPairs
 // LDG.U16. Group keys are learnt through the same CAS dictionary as kernels_tiny.cu and then cached in registers;
 // a CTA that meets more than G keys raises status[3] and the host takes another path.
 // Reference counterpart: the replicated shared-memory accumulators for low cardinalities,
@@ -16,7 +16,7 @@ namespace bgb {
 namespace {
 
 constexpr int kRT        = 128;  // threads per CTA (111-183 registers per thread: 2-4 CTAs per SM)
-constexpr int kPairs     = 4;    // row pairs per lane per iteration (warp tile = 32 lanes * 2 rows * 4 = 256 rows)
+constexpr int kPairs     = 2;    // row pairs per lane per iteration (warp tile = 128 rows). Measured on Q1: 4 pairs 6.7 ms (186 registers, 8 warps/SM), 2 pairs 4.6 ms, 1 pair 5.6 ms
 constexpr int kWarpTile  = 64 * kPairs;
 constexpr int kDictSlots = 64;
 
