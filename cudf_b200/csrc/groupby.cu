@@ -136,7 +136,8 @@ int run_partitioned(bgb_groupby* h, int num_sms, bool& done)
   for (const AccPlan& a : pl.accs) slot_bytes += acc_cell_bytes(a.op);
   const double table_bytes = (double)h->table.capacity * slot_bytes;
   int log2cap = 0; while ((1ull << log2cap) < h->table.capacity) ++log2cap;
-  int log2p = 4; while (log2p < 12 && table_bytes / (double)(1u << log2p) > 16e6) ++log2p;
+  static const double region_bytes = getenv("BGB_PART_REGION_MB") ? atof(getenv("BGB_PART_REGION_MB")) * 1e6 : 16e6;
+  int log2p = 4; while (log2p < 12 && table_bytes / (double)(1u << log2p) > region_bytes) ++log2p;
   if (log2p > log2cap) log2p = log2cap;
   const uint32_t P = 1u << log2p;
 
