@@ -217,6 +217,7 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
         int gid = -1;
 #pragma unroll
         for (int g = 0; g < G; ++g) gid = (gk[g] == k) ? g : gid;
+        if (k == kEmpty) gid = -1;  // the all-ones image equals the 'unused' marker of gk[]: never a cached group (-> abort below)
         if (usable && gid < 0) {  // first rows only: learn the key, then refresh the cached group keys
           gid = (k == kEmpty) ? -2 : reg_insert_key(k, s_dict_key, s_dict_gid, s_group_key, &s_groups, G);
           if (gid < 0) abort_seen = true;

@@ -127,6 +127,16 @@ def test_more_groups_than_rows_falls_back_to_the_general_path():
     gpu_util.compare_with_oracle(keys, vals, aggs, name="tiny/overflow/auto")
 
 
+def test_register_variant_all_ones_key_image():
+    rng = np.random.default_rng(46)
+    n = 200_000
+    k = rng.integers(-2, 2, n).astype(np.int64)  # -1 packs to the all-ones image, which the kernels reserve: general path
+    v = rng.integers(-1000, 1001, n).astype(np.int64)
+    for fp in (0, 6):
+        G, path = gpu_util.compare_with_oracle([H(k)], [H(v)], [(0, "sum", 1), (0, "count_valid", 1)], options={"force_path": fp}, name=f"tiny-reg/all-ones/{fp}")
+        assert G == 4 and path != "tiny-reg"
+
+
 def test_all_ones_key_and_single_group():
     k = np.full(100_000, -1, dtype=np.int64)  # packed image == EMPTY: must still be aggregated (general path)
     v = np.arange(100_000, dtype=np.int64)
