@@ -54,6 +54,10 @@ class MutableColumn(C.Structure):
                 ("null_count", C.c_int32), ("reserved", C.c_int32)]
 
 
+class StreamRequest(C.Structure):
+    _fields_ = [("column_index", C.c_int32), ("kind", C.c_int32), ("ddof", C.c_int32), ("reserved", C.c_int32)]
+
+
 class Options(C.Structure):
     _fields_ = [("force_path", C.c_int32), ("capacity_log2", C.c_int32), ("sample_rows", C.c_int32), ("profile", C.c_int32),
                 ("reserved", C.c_int32 * 4)]
@@ -106,6 +110,15 @@ def lib():
     L.bgb_bytes_to_bitmask.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_int32), C.c_void_p]
     L.bgb_finalize_moments.argtypes = [C.c_int32, C.c_int32, C.POINTER(ColumnView), C.POINTER(ColumnView), C.POINTER(ColumnView),
                                        C.POINTER(MutableColumn), C.c_void_p]
+    L.bgb_is_streaming_groupby_supported.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_int32)]
+    L.bgb_stream_create.argtypes = [C.POINTER(C.c_int32), C.c_int32, C.POINTER(StreamRequest), C.c_int32, C.c_int32, C.c_int32,
+                                    C.POINTER(C.c_void_p)]
+    L.bgb_stream_aggregate.argtypes = [C.c_void_p, C.POINTER(ColumnView), C.c_int32, C.c_void_p, C.POINTER(Options)]
+    L.bgb_stream_merge.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.bgb_stream_distinct_keys.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+    L.bgb_stream_finalize.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int32)]
+    L.bgb_stream_destroy.argtypes = [C.c_void_p]
+    L.bgb_stream_destroy.restype = None
     L.bgb_peer_create.argtypes = [C.c_int32, C.c_int32, C.c_int64, C.POINTER(C.c_void_p)]
     L.bgb_peer_export.argtypes = [C.c_void_p, C.c_void_p]
     L.bgb_peer_attach.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]

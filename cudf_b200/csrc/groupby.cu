@@ -805,3 +805,228 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
   *out_handle = h;
   return BGB_OK;
 }
+
+// =====================================================================================================================
+// streaming_groupby (cpp/include/cudf/groupby.hpp:428-598): a persistent table fed batch by batch. Every batch runs
+// through the stateless path above (so it takes whichever kernel fits: tiny, shared-memory, partitioned, generic) into
+// a batch-local partial table, which is then folded into the persistent table with the cell-level merges of
+// streaming_groupby/merge.cu:30-144. merge() folds another object's table the same way; finalize() compacts the
+// persistent table and returns an ordinary handle for bgb_groupby_emit without touching the state.
+// =====================================================================================================================
+
+struct bgb_stream {
+  std::vector<int32_t> key_indices;
+  std::vector<bgb_stream_request> requests;
+  int32_t max_keys = 0;
+  int32_t include_null_keys = 0;
+  bool initialized = false;
+  Plan master;                    // layout of the persistent table (rank/batch independent: every value nullable)
+  TableDesc table{};
+  std::vector<void*> cells;       // one array per accumulator of `master`
+  uint32_t* new_keys = nullptr;   // device counter of distinct keys
+  int32_t distinct = 0;
+  cudaStream_t last_stream = nullptr;
+};
+
+static bool stream_kind_supported(int32_t kind)
+{
+  switch (kind) {  // impl.cu:40-60: the hash kinds minus ARGMIN/ARGMAX (row indices are batch-local)
+    case BGB_SUM: case BGB_PRODUCT: case BGB_MIN: case BGB_MAX: case BGB_COUNT_VALID: case BGB_COUNT_ALL: case BGB_SUM_OF_SQUARES:
+    case BGB_MEAN: case BGB_M2: case BGB_VARIANCE: case BGB_STD: return true;
+    default: return false;
+  }
+}
+
+extern "C" int bgb_is_streaming_groupby_supported(int32_t values_type_id, int32_t kind, int32_t* out)
+{
+  if (!out) return set_error(BGB_INVALID_ARGUMENT, "null output pointer");
+  *out = stream_kind_supported(kind) && type_width(values_type_id) > 0 && type_src(values_type_id) != S_BAD &&
+         target_type(values_type_id, kind) >= 0;
+  return BGB_OK;
+}
+
+extern "C" int bgb_stream_create(const int32_t* key_indices, int32_t num_keys, const bgb_stream_request* requests, int32_t num_requests,
+                                 int32_t max_distinct_keys, int32_t include_null_keys, bgb_stream** out)
+{
+  if (!out) return set_error(BGB_INVALID_ARGUMENT, "null output pointer");
+  *out = nullptr;
+  if (max_distinct_keys <= 0) return set_error(BGB_INVALID_ARGUMENT, "max_distinct_keys must be positive");
+  if (num_keys <= 0 || !key_indices) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby needs at least one key column");
+  if (num_requests < 0 || (num_requests > 0 && !requests)) return set_error(BGB_INVALID_ARGUMENT, "bad requests");
+  for (int i = 0; i < num_requests; ++i)
+    if (!stream_kind_supported(requests[i].kind))
+      return set_error(BGB_INVALID_ARGUMENT, "Unsupported aggregation kind for streaming groupby. ARGMIN/ARGMAX are not supported because row indices are batch-local.");
+  bgb_stream* s = new bgb_stream();
+  s->key_indices.assign(key_indices, key_indices + num_keys);
+  s->requests.assign(requests, requests + num_requests);
+  s->max_keys = max_distinct_keys;
+  s->include_null_keys = include_null_keys != 0;
+  *out = s;
+  return BGB_OK;
+}
+
+extern "C" void bgb_stream_destroy(bgb_stream* s)
+{
+  if (!s) return;
+  if (s->table.keys) pool_free_async(s->table.keys, s->last_stream);
+  if (s->table.status) pool_free_async(s->table.status, s->last_stream);
+  for (void* c : s->cells) if (c) pool_free_async(c, s->last_stream);
+  delete s;
+}
+
+static bool plans_compatible(const Plan& a, const Plan& b)
+{
+  if (a.key_words != b.key_words || a.keys.size() != b.keys.size() || a.accs.size() != b.accs.size()) return false;
+  for (size_t i = 0; i < a.keys.size(); ++i)
+    if (a.keys[i].v.type_id != b.keys[i].v.type_id || a.keys[i].shift != b.keys[i].shift || a.keys[i].null_bit != b.keys[i].null_bit) return false;
+  for (size_t i = 0; i < a.accs.size(); ++i)
+    if (a.accs[i].op != b.accs[i].op) return false;
+  if (a.outs.size() != b.outs.size()) return false;
+  for (size_t i = 0; i < a.outs.size(); ++i)
+    if (a.outs[i].type_id != b.outs[i].type_id || a.outs[i].op != b.outs[i].op) return false;
+  return true;
+}
+
+// folds the groups of (src table, src_slots[0..n)) into the persistent table; reads back the distinct-key counter
+static int stream_fold(bgb_stream* st, const TableDesc& src, const uint32_t* src_slots, int32_t n, const std::vector<void*>& src_cells, cudaStream_t s)
+{
+  TableMergeParams mp;
+  memset(&mp, 0, sizeof mp);
+  mp.src_keys = src.keys; mp.src_group_slots = src_slots; mp.num_groups = n;
+  mp.key_words = st->master.key_words; mp.num_accs = (int)st->master.accs.size();
+  mp.dst = st->table; mp.new_keys = st->new_keys;
+  for (size_t a = 0; a < st->master.accs.size(); ++a) {
+    mp.src_acc[a].cells = src_cells[a]; mp.src_acc[a].op = st->master.accs[a].op; mp.src_acc[a].cell_bytes = (uint8_t)acc_cell_bytes(st->master.accs[a].op);
+    mp.dst_cells[a] = st->cells[a];
+  }
+  int rc = check_cuda(launch_table_merge(mp, s), "table_merge");
+  uint32_t host[2] = {0, 0};
+  if (!rc) rc = check_cuda(cudaMemcpyAsync(&host[0], st->new_keys, sizeof(uint32_t), cudaMemcpyDeviceToHost, s), "distinct copy");
+  if (!rc) rc = check_cuda(cudaMemcpyAsync(&host[1], st->table.status, sizeof(uint32_t), cudaMemcpyDeviceToHost, s), "status copy");
+  if (!rc) rc = check_cuda(cudaStreamSynchronize(s), "stream fold sync");
+  if (rc) return rc;
+  st->distinct = (int32_t)host[0];
+  if (host[1] != 0 || host[0] > (uint32_t)st->max_keys)
+    return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: cumulative distinct keys (%u) exceed max_distinct_keys (%d)", host[0], st->max_keys);
+  return BGB_OK;
+}
+
+extern "C" int bgb_stream_aggregate(bgb_stream* st, const bgb_column_view* columns, int32_t num_columns, void* stream, const bgb_options* options)
+{
+  if (!st || (num_columns > 0 && !columns)) return set_error(BGB_INVALID_ARGUMENT, "null argument");
+  std::vector<bgb_column_view> keys;
+  for (int32_t k : st->key_indices) {
+    if (k < 0 || k >= num_columns) return set_error(BGB_INVALID_ARGUMENT, "key index %d out of range (%d columns)", k, num_columns);
+    keys.push_back(columns[k]);
+  }
+  std::vector<bgb_aggregation> aggs(st->requests.size());
+  std::vector<bgb_request> reqs(st->requests.size());
+  for (size_t i = 0; i < st->requests.size(); ++i) {
+    const bgb_stream_request& r = st->requests[i];
+    if (r.column_index < 0 || r.column_index >= num_columns) return set_error(BGB_INVALID_ARGUMENT, "value column index %d out of range", r.column_index);
+    aggs[i] = bgb_aggregation{r.kind, r.ddof};
+    reqs[i] = bgb_request{columns[r.column_index], &aggs[i], 1, 0};
+  }
+  const int64_t rows = keys[0].size;
+  if (rows > st->max_keys) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: a batch of %lld rows exceeds max_distinct_keys (%d)", (long long)rows, st->max_keys);
+  if (rows == 0) return BGB_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  bgb_groupby* hb = nullptr;
+  int32_t gb = 0;
+  int rc = build_local(keys.data(), (int32_t)keys.size(), st->include_null_keys, reqs.data(), (int32_t)reqs.size(), stream, nullptr, options, &hb, &gb,
+                       /*rank_independent=*/true);
+  if (rc) return rc;
+  struct Guard { bgb_groupby* h; ~Guard() { if (h) { h->free_all(); delete h; } } } guard{hb};
+  if (!st->initialized) {
+    st->master = hb->plan;
+    const uint64_t capacity = next_pow2(std::max<uint64_t>(1024, 2 * (uint64_t)st->max_keys));
+    const uint64_t slots    = capacity + 1;
+    st->table.capacity  = capacity;
+    st->table.key_words = st->master.key_words;
+    st->table.keys   = (uint64_t*)pool_alloc_async(slots * 8 * st->master.key_words, s);
+    st->table.status = (uint32_t*)pool_alloc_async(17 * sizeof(uint32_t), s);
+    bool ok = st->table.keys && st->table.status;
+    st->cells.assign(st->master.accs.size(), nullptr);
+    for (size_t a = 0; a < st->master.accs.size() && ok; ++a) {
+      st->cells[a] = pool_alloc_async(slots * acc_cell_bytes(st->master.accs[a].op), s);
+      ok = st->cells[a] != nullptr;
+    }
+    st->last_stream = s;
+    if (!ok) return set_error(BGB_OUT_OF_MEMORY, "persistent table for %d distinct keys", st->max_keys);
+    st->new_keys = st->table.status + 16;
+    rc = check_cuda(cudaMemsetAsync(st->table.status, 0, 17 * sizeof(uint32_t), s), "stream status");
+    const size_t na = st->master.accs.size();
+    for (size_t b = 0; (b == 0 || b < na) && !rc; b += kMaxAccs) {
+      AggParams p;
+      memset(&p, 0, sizeof p);
+      p.table = st->table; p.init_keys = (b == 0);
+      p.num_accs = (int)(std::min(na, b + kMaxAccs) - b);
+      for (int a = 0; a < p.num_accs; ++a) { p.acc[a].op = st->master.accs[b + a].op; p.acc[a].cells = st->cells[b + a]; }
+      rc = check_cuda(launch_init_table(p, s), "init_table");
+    }
+    if (rc) return rc;
+    st->initialized = true;
+  } else if (!plans_compatible(st->master, hb->plan)) {
+    return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: this batch's column types differ from the first batch's");
+  }
+  st->last_stream = s;
+  if (st->master.accs.size() > (size_t)kMaxAccs) return set_error(BGB_UNSUPPORTED, "more than %d accumulators in a streaming groupby", kMaxAccs);
+  std::vector<void*> src_cells;
+  for (const AccPlan& a : hb->plan.accs) src_cells.push_back(a.cells);
+  return stream_fold(st, hb->table, hb->group_slots, gb, src_cells, s);
+}
+
+extern "C" int bgb_stream_merge(bgb_stream* st, const bgb_stream* other, void* stream)
+{
+  if (!st || !other) return set_error(BGB_INVALID_ARGUMENT, "null argument");
+  if (!st->initialized) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: merge() needs an object that has seen at least one aggregate()");
+  if (!other->initialized || other->distinct == 0) return BGB_OK;
+  if (!plans_compatible(st->master, other->master)) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: the two objects have different aggregation requests or column types");
+  if (other->distinct > st->max_keys) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: the other object holds %d distinct keys, more than max_distinct_keys (%d)", other->distinct, st->max_keys);
+  cudaStream_t s = (cudaStream_t)stream;
+  uint32_t* slots = (uint32_t*)pool_alloc_async(sizeof(uint32_t) * (size_t)(other->distinct + 1), s);
+  uint32_t* scan  = (uint32_t*)pool_alloc_async(compact_scan_state_bytes(other->table.capacity), s);
+  if (!slots || !scan) { if (slots) pool_free_async(slots, s); if (scan) pool_free_async(scan, s); return set_error(BGB_OUT_OF_MEMORY, "merge scratch"); }
+  int rc = check_cuda(launch_compact(other->table, slots, scan, s), "compact");
+  if (!rc) rc = stream_fold(st, other->table, slots, other->distinct, other->cells, s);
+  pool_free_async(slots, s);
+  pool_free_async(scan, s);
+  st->last_stream = s;
+  return rc;
+}
+
+extern "C" int bgb_stream_distinct_keys(const bgb_stream* st, int32_t* out)
+{
+  if (!st || !out) return set_error(BGB_INVALID_ARGUMENT, "null argument");
+  *out = st->distinct;
+  return BGB_OK;
+}
+
+extern "C" int bgb_stream_finalize(const bgb_stream* st, void* stream, bgb_groupby** out_handle, int32_t* num_groups)
+{
+  if (!st || !out_handle || !num_groups) return set_error(BGB_INVALID_ARGUMENT, "null argument");
+  *out_handle = nullptr;
+  *num_groups = 0;
+  if (!st->initialized) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: no data has been accumulated");
+  bgb_groupby* h = new bgb_groupby();
+  h->plan   = st->master;
+  h->stream = (cudaStream_t)stream;
+  h->table  = st->table;  // borrowed: the handle owns only its compaction list, the persistent state is not modified
+  for (size_t a = 0; a < h->plan.accs.size(); ++a) h->plan.accs[a].cells = st->cells[a];
+  cudaStream_t s = h->stream;
+  const uint64_t max_groups = (uint64_t)st->distinct + 1;
+  h->group_slots       = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
+  uint32_t* scan_state = (uint32_t*)h->dalloc(compact_scan_state_bytes(st->table.capacity));
+  int rc = (!h->group_slots || !scan_state) ? set_error(BGB_OUT_OF_MEMORY, "compaction scratch") : BGB_OK;
+  if (!rc) rc = check_cuda(launch_compact(h->table, h->group_slots, scan_state, s), "compact");
+  uint32_t count = 0;
+  if (!rc) rc = check_cuda(cudaMemcpyAsync(&count, st->table.status + 1, sizeof count, cudaMemcpyDeviceToHost, s), "group count");
+  if (!rc) rc = check_cuda(cudaStreamSynchronize(s), "finalize sync");
+  if (rc) { h->free_all(); delete h; return rc; }
+  h->dfree(scan_state);
+  h->num_groups = (int32_t)count;
+  h->path       = "stream";
+  *num_groups   = h->num_groups;
+  *out_handle   = h;
+  return BGB_OK;
+}

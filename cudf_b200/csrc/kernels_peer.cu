@@ -166,6 +166,66 @@ __global__ void __launch_bounds__(kThreads) peer_merge_kernel(const __grid_const
   }
 }
 
+// find_or_insert that also reports whether the key was new (the streaming object tracks its distinct-key count)
+__device__ __forceinline__ uint64_t find_or_insert_counting(const TableDesc& t, uint64_t k0, uint64_t k1, uint32_t* new_keys)
+{
+  const uint64_t cap = t.capacity;
+  if (t.key_words == 1) {
+    if (k0 == kEmpty) { if (atomicExch(&t.status[2], 1u) == 0u) atomicAdd(new_keys, 1u); return cap; }
+    uint64_t slot = hash_key(k0, 0, 1) & (cap - 1);
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(t.keys);
+    for (uint32_t probes = 0; probes < kMaxProbes; ++probes) {
+      unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(keys + slot);
+      if (cur == k0) return slot;
+      if (cur == kEmpty) {
+        unsigned long long old = atomicCAS(keys + slot, (unsigned long long)kEmpty, (unsigned long long)k0);
+        if (old == kEmpty) { atomicAdd(new_keys, 1u); return slot; }
+        if (old == k0) return slot;
+      }
+      slot = (slot + 1) & (cap - 1);
+    }
+  } else {
+    if (k0 == kEmpty && k1 == kEmpty) { if (atomicExch(&t.status[2], 1u) == 0u) atomicAdd(new_keys, 1u); return cap; }
+    uint64_t slot = hash_key(k0, k1, 2) & (cap - 1);
+    for (uint32_t probes = 0; probes < kMaxProbes; ++probes) {
+      uint64_t o0, o1;
+      cas128(t.keys + 2 * slot, kEmpty, kEmpty, k0, k1, o0, o1);  // merges are rare relative to rows: always take the CAS
+      if (o0 == kEmpty && o1 == kEmpty) { atomicAdd(new_keys, 1u); return slot; }
+      if (o0 == k0 && o1 == k1) return slot;
+      slot = (slot + 1) & (cap - 1);
+    }
+  }
+  t.status[0] = 1;
+  return kNoSlot;
+}
+
+__global__ void __launch_bounds__(kThreads) table_merge_kernel(const __grid_constant__ TableMergeParams p)
+{
+  const uint32_t stride = gridDim.x * kThreads;
+  for (uint32_t j = blockIdx.x * kThreads + threadIdx.x; j < (uint32_t)p.num_groups; j += stride) {
+    const uint64_t src = p.src_group_slots[j];
+    const uint64_t k0  = p.key_words == 1 ? p.src_keys[src] : p.src_keys[2 * src];
+    const uint64_t k1  = p.key_words == 1 ? 0 : p.src_keys[2 * src + 1];
+    const uint64_t dst = find_or_insert_counting(p.dst, k0, k1, p.new_keys);
+    if (dst == kNoSlot) continue;
+#pragma unroll 1
+    for (int a = 0; a < p.num_accs; ++a) {
+      const PeerAcc& pa = p.src_acc[a];
+      const uint64_t v  = pa.cell_bytes == 8 ? reinterpret_cast<const uint64_t*>(pa.cells)[src] : reinterpret_cast<const uint32_t*>(pa.cells)[src];
+      merge_cell(pa.op, p.dst_cells[a], dst, v);
+    }
+  }
+}
+
+cudaError_t launch_table_merge(const TableMergeParams& p, cudaStream_t s)
+{
+  if (p.num_groups <= 0) return cudaSuccess;
+  int64_t blocks = ((int64_t)p.num_groups + kThreads - 1) / kThreads;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  table_merge_kernel<<<(int)blocks, kThreads, 0, s>>>(p);
+  return note_launch();
+}
+
 cudaError_t launch_peer_merge(const PeerMergeParams& p, cudaStream_t s)
 {
   const uint32_t total = p.prefix[p.world];

@@ -54,6 +54,20 @@ struct PeerMergeParams {
   PeerAcc acc[kMaxAccs];
 };
 
+// table -> table merge (streaming_groupby: a batch's partial table, or another object's state, folded into the persistent
+// table; streaming_groupby/merge.cu:30-144): every group of `src` is found-or-inserted in `dst` and its cells merged
+struct TableMergeParams {
+  const uint64_t* src_keys;
+  const uint32_t* src_group_slots;  // dense list of occupied source slots
+  int32_t num_groups;
+  int32_t key_words, num_accs;
+  TableDesc dst;
+  uint32_t* new_keys;               // device counter: groups that did not exist in dst before
+  PeerAcc src_acc[kMaxAccs];        // .cells = source cells (region_off unused)
+  void* dst_cells[kMaxAccs];
+};
+cudaError_t launch_table_merge(const TableMergeParams& p, cudaStream_t s);
+
 cudaError_t launch_peer_scatter(const PeerScatterParams& p, cudaStream_t s);
 cudaError_t launch_peer_signal(const PeerSignalParams& p, cudaStream_t s);
 // waits until every source's flag reaches `epoch` (or timeout_ns passes: out[2 * world] = 1), then copies

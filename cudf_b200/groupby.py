@@ -70,50 +70,56 @@ class GroupBy:
                 _lib.check(L.bgb_groupby_build(ckeys, nk, int(self._null_handling), creq, len(requests), sptr, None, C.byref(opt),
                                                C.byref(handle), C.byref(ngroups)))
             try:
-                G = ngroups.value
                 self.last_path = L.bgb_groupby_path(handle).decode()
-                with torch.cuda.stream(stream):
-                    # caller-allocated outputs (the role of the caller's rmm memory resource)
-                    okeys = (_lib.MutableColumn * max(nk, 1))()
-                    key_cols = []
-                    for i in range(nk):
-                        t, sc, nl = C.c_int32(), C.c_int32(), C.c_int32()
-                        _lib.check(L.bgb_groupby_key_info(handle, i, C.byref(t), C.byref(sc), C.byref(nl)))
-                        data = torch.empty(G, dtype=torch_dtype(t.value), device=device)
-                        mask = torch.zeros((G + 31) // 32, dtype=torch.int32, device=device) if nl.value else None
-                        key_cols.append(Column(data, mask, 0, t.value, scale=sc.value))
-                        okeys[i] = _lib.MutableColumn(t.value, G, data.data_ptr() if G else None,
-                                                      mask.data_ptr() if mask is not None and G else None, 0, 0)
-                    nres = sum(len(r._aggregations) for r in requests)
-                    ores = (_lib.MutableColumn * max(nres, 1))()
-                    res_cols = []
-                    k = 0
-                    for ri, r in enumerate(requests):
-                        cols = []
-                        for ai in range(len(r._aggregations)):
-                            t, sc, nl = C.c_int32(), C.c_int32(), C.c_int32()
-                            _lib.check(L.bgb_groupby_result_info(handle, ri, ai, C.byref(t), C.byref(sc), C.byref(nl)))
-                            data = torch.empty(G, dtype=torch_dtype(t.value), device=device)
-                            mask = torch.zeros((G + 31) // 32, dtype=torch.int32, device=device) if nl.value else None
-                            cols.append(Column(data, mask, 0, t.value, scale=sc.value))
-                            ores[k] = _lib.MutableColumn(t.value, G, data.data_ptr() if G else None,
-                                                         mask.data_ptr() if mask is not None and G else None, 0, 0)
-                            k += 1
-                        res_cols.append(cols)
-                _lib.check(L.bgb_groupby_emit(handle, okeys, ores, sptr))
+                key_cols, res_cols = emit_handle(L, handle, ngroups.value, nk, [len(r._aggregations) for r in requests], device, stream)
                 if opt.profile:
                     self.last_profile = _read_profile(L, handle)
-                for i, c in enumerate(key_cols):
-                    c.null_count = okeys[i].null_count
-                k = 0
-                for cols in res_cols:
-                    for c in cols:
-                        c.null_count = ores[k].null_count
-                        k += 1
             finally:
                 L.bgb_groupby_destroy(handle)
         del keep
         return Table(key_cols), [Table(cols) for cols in res_cols]
+
+
+def emit_handle(L, handle, G, nk, aggs_per_request, device, stream):
+    """Caller-allocated outputs (the role of the caller's rmm memory resource) + bgb_groupby_emit for a built handle.
+    Returns ([key Column], [[result Column] per request])."""
+    sptr = C.c_void_p(stream.cuda_stream)
+    with torch.cuda.stream(stream):
+        okeys = (_lib.MutableColumn * max(nk, 1))()
+        key_cols = []
+        for i in range(nk):
+            t, sc, nl = C.c_int32(), C.c_int32(), C.c_int32()
+            _lib.check(L.bgb_groupby_key_info(handle, i, C.byref(t), C.byref(sc), C.byref(nl)))
+            data = torch.empty(G, dtype=torch_dtype(t.value), device=device)
+            mask = torch.zeros((G + 31) // 32, dtype=torch.int32, device=device) if nl.value else None
+            key_cols.append(Column(data, mask, 0, t.value, scale=sc.value))
+            okeys[i] = _lib.MutableColumn(t.value, G, data.data_ptr() if G else None,
+                                          mask.data_ptr() if mask is not None and G else None, 0, 0)
+        nres = sum(aggs_per_request)
+        ores = (_lib.MutableColumn * max(nres, 1))()
+        res_cols = []
+        k = 0
+        for ri, na in enumerate(aggs_per_request):
+            cols = []
+            for ai in range(na):
+                t, sc, nl = C.c_int32(), C.c_int32(), C.c_int32()
+                _lib.check(L.bgb_groupby_result_info(handle, ri, ai, C.byref(t), C.byref(sc), C.byref(nl)))
+                data = torch.empty(G, dtype=torch_dtype(t.value), device=device)
+                mask = torch.zeros((G + 31) // 32, dtype=torch.int32, device=device) if nl.value else None
+                cols.append(Column(data, mask, 0, t.value, scale=sc.value))
+                ores[k] = _lib.MutableColumn(t.value, G, data.data_ptr() if G else None,
+                                             mask.data_ptr() if mask is not None and G else None, 0, 0)
+                k += 1
+            res_cols.append(cols)
+    _lib.check(L.bgb_groupby_emit(handle, okeys, ores, sptr))
+    for i, c in enumerate(key_cols):
+        c.null_count = okeys[i].null_count
+    k = 0
+    for cols in res_cols:
+        for c in cols:
+            c.null_count = ores[k].null_count
+            k += 1
+    return key_cols, res_cols
 
 
 def _read_profile(L, handle):

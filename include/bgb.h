@@ -187,6 +187,34 @@ int bgb_groupby_host(const bgb_column_view* host_keys, int32_t num_keys, int32_t
                      int32_t* num_results);
 void bgb_free_host_result(bgb_host_column* cols, int32_t n);
 
+/* ---- streaming groupby: a persistent group table fed batch by batch -------------------------------------------------
+ * cudf::groupby::streaming_groupby (cpp/include/cudf/groupby.hpp:428-598; src/groupby/streaming_groupby/). Key and value
+ * columns are named by their index in the table passed to every aggregate() call, one aggregation per request
+ * (streaming_aggregation_request, groupby.hpp:419-422). Supported kinds: SUM, SUM_OF_SQUARES, PRODUCT, MIN, MAX,
+ * COUNT_VALID, COUNT_ALL, MEAN, M2, VARIANCE, STD (ARGMIN/ARGMAX are rejected: row indices are batch-local).
+ * Cumulative rows are unbounded; cumulative distinct keys are bounded by max_distinct_keys, and so is a single batch
+ * (the reference's limit, kept so callers see the same errors). */
+typedef struct bgb_stream bgb_stream;
+typedef struct bgb_stream_request {
+  int32_t column_index;
+  int32_t kind; /* bgb_agg_kind */
+  int32_t ddof;
+  int32_t reserved;
+} bgb_stream_request;
+int bgb_is_streaming_groupby_supported(int32_t values_type_id, int32_t kind, int32_t* out);
+int bgb_stream_create(const int32_t* key_indices, int32_t num_keys, const bgb_stream_request* requests, int32_t num_requests,
+                      int32_t max_distinct_keys, int32_t include_null_keys, bgb_stream** out);
+/* one batch: columns[] is the data table (keys and values by index). The batch is aggregated with the stateless path into
+ * a partial table and folded into the persistent one; returns after the stream is synchronised (distinct-key check). */
+int bgb_stream_aggregate(bgb_stream* s, const bgb_column_view* columns, int32_t num_columns, void* stream, const bgb_options* options);
+/* fold another object's accumulated state into this one (the other object is not modified) */
+int bgb_stream_merge(bgb_stream* s, const bgb_stream* other, void* stream);
+int bgb_stream_distinct_keys(const bgb_stream* s, int32_t* out);
+/* compact the persistent table into a handle for bgb_groupby_key_info / _result_info / _emit / _destroy; the state is not
+ * modified and aggregate() may be called again afterwards. The handle must be destroyed before the stream object. */
+int bgb_stream_finalize(const bgb_stream* s, void* stream, bgb_groupby** out_handle, int32_t* num_groups);
+void bgb_stream_destroy(bgb_stream* s);
+
 /* ---- multi-GPU building blocks (one process per GPU; the exchange itself is an NCCL all-to-all run by the host layer,
  *      cudf_b200/distributed.py) --------------------------------------------------------------------- */
 
