@@ -287,5 +287,81 @@ class groupby {
   null_policy _null_handling;
 };
 
+// cudf::groupby::streaming_aggregation_request / streaming_groupby (cudf/groupby.hpp:419-598)
+struct streaming_aggregation_request {
+  size_type column_index;
+  std::unique_ptr<groupby_aggregation> aggregation;
+};
+
+inline bool is_streaming_groupby_supported(data_type values_type, int32_t kind)
+{
+  int32_t ok = 0;
+  detail::throw_on(bgb_is_streaming_groupby_supported(static_cast<int32_t>(values_type.id()), kind, &ok));
+  return ok != 0;
+}
+
+class streaming_groupby {
+ public:
+  streaming_groupby()                                    = delete;
+  streaming_groupby(streaming_groupby const&)            = delete;
+  streaming_groupby& operator=(streaming_groupby const&) = delete;
+  streaming_groupby(streaming_groupby&& o) noexcept : _h(o._h), _nk(o._nk), _nreq(o._nreq) { o._h = nullptr; }
+  ~streaming_groupby() { bgb_stream_destroy(_h); }
+
+  streaming_groupby(std::vector<size_type> const& key_indices, std::vector<streaming_aggregation_request> const& requests,
+                    size_type max_distinct_keys, null_policy null_handling = null_policy::EXCLUDE)
+    : _nk(static_cast<int32_t>(key_indices.size())), _nreq(static_cast<int32_t>(requests.size()))
+  {
+    std::vector<bgb_stream_request> r;
+    for (auto const& q : requests) r.push_back({q.column_index, q.aggregation->kind, q.aggregation->ddof, 0});
+    detail::throw_on(bgb_stream_create(key_indices.data(), _nk, r.data(), _nreq, max_distinct_keys, null_handling == null_policy::INCLUDE, &_h));
+  }
+
+  void aggregate(table_view const& data, cudaStream_t stream = nullptr)
+  {
+    std::vector<bgb_column_view> cols;
+    for (auto const& c : data) cols.push_back(c.abi());
+    detail::throw_on(bgb_stream_aggregate(_h, cols.data(), (int32_t)cols.size(), stream, nullptr));
+  }
+  void merge(streaming_groupby const& other, cudaStream_t stream = nullptr) { detail::throw_on(bgb_stream_merge(_h, other._h, stream)); }
+  size_type distinct_keys() const
+  {
+    int32_t n = 0;
+    detail::throw_on(bgb_stream_distinct_keys(_h, &n));
+    return n;
+  }
+  // does not modify the state; aggregate() may be called again afterwards
+  std::pair<std::unique_ptr<table>, std::vector<aggregation_result>> finalize(cudaStream_t stream = nullptr) const
+  {
+    bgb_groupby* h = nullptr;
+    int32_t n      = 0;
+    detail::throw_on(bgb_stream_finalize(_h, stream, &h, &n));
+    struct guard { bgb_groupby* h; ~guard() { bgb_groupby_destroy(h); } } g{h};
+    std::vector<std::unique_ptr<column>> kcols;
+    std::vector<bgb_mutable_column> km, rm;
+    for (int32_t i = 0; i < _nk; ++i) {
+      int32_t t, s, nl;
+      detail::throw_on(bgb_groupby_key_info(h, i, &t, &s, &nl));
+      kcols.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream));
+      km.push_back(kcols.back()->abi_mutable());
+    }
+    std::vector<aggregation_result> results(_nreq);
+    for (int32_t i = 0; i < _nreq; ++i) {
+      int32_t t, s, nl;
+      detail::throw_on(bgb_groupby_result_info(h, i, 0, &t, &s, &nl));
+      results[i].results.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream));
+      rm.push_back(results[i].results.back()->abi_mutable());
+    }
+    detail::throw_on(bgb_groupby_emit(h, km.data(), rm.data(), stream));
+    for (size_t i = 0; i < kcols.size(); ++i) kcols[i]->set_null_count(km[i].null_count);
+    for (int32_t i = 0; i < _nreq; ++i) results[i].results[0]->set_null_count(rm[i].null_count);
+    return {std::make_unique<table>(std::move(kcols)), std::move(results)};
+  }
+
+ private:
+  bgb_stream* _h{nullptr};
+  int32_t _nk, _nreq;
+};
+
 }  // namespace groupby
 }  // namespace cudf_b200

@@ -145,6 +145,46 @@ int main()
     auto [tbl, res] = gb.aggregate(reqs);
     CHECK(tbl->num_rows() == 0 && res[0].results.size() == 2 && res[0].results[1]->type().id() == type_id::FLOAT32);
   }
+  {  // streaming_groupby_test.cpp MergeTwoObjects: worker1 {1,2,1}/{10,20,30} + worker2 {2,3}/{40,50} -> {1,2,3} / {40,60,50}
+    auto mk = [] {
+      std::vector<groupby::streaming_aggregation_request> r;
+      r.push_back({1, make_sum_aggregation()});
+      return r;
+    };
+    groupby::streaming_groupby w1({0}, mk(), 1024), w2({0}, mk(), 1024);
+    auto k1 = column::from_host<K>(type_id::INT32, {1, 2, 1});
+    auto v1 = column::from_host<int32_t>(type_id::INT32, {10, 20, 30});
+    auto k2 = column::from_host<K>(type_id::INT32, {2, 3});
+    auto v2 = column::from_host<int32_t>(type_id::INT32, {40, 50});
+    w1.aggregate(table_view({k1->view(), v1->view()}));
+    w2.aggregate(table_view({k2->view(), v2->view()}));
+    w1.merge(w2);
+    auto [tbl, res] = w1.finalize();
+    auto [k, kv]    = tbl->get_column(0).to_host<K>();
+    auto [v, vv]    = res[0].results[0]->to_host<int64_t>();
+    std::vector<std::pair<K, int64_t>> got;
+    for (size_t i = 0; i < k.size(); ++i) got.push_back({k[i], v[i]});
+    std::sort(got.begin(), got.end());
+    CHECK((got == std::vector<std::pair<K, int64_t>>{{1, 40}, {2, 60}, {3, 50}}));
+    CHECK(w1.distinct_keys() == 3 && w2.distinct_keys() == 2);
+    // ExceedsDistinctKeyCapacityThrows / UnsupportedAggThrows / FinalizeBeforeAggregateThrows
+    groupby::streaming_groupby small({0}, mk(), 2);
+    bool threw = false;
+    try { small.finalize(); } catch (logic_error const&) { threw = true; }
+    CHECK(threw);
+    small.aggregate(table_view({k2->view(), v2->view()}));
+    threw = false;
+    try { small.aggregate(table_view({k1->view(), v1->view()})); } catch (logic_error const&) { threw = true; }  // 3 rows > 2
+    CHECK(threw);
+    threw = false;
+    try {
+      std::vector<groupby::streaming_aggregation_request> bad;
+      bad.push_back({1, make_argmax_aggregation()});
+      groupby::streaming_groupby x({0}, bad, 16);
+    } catch (logic_error const&) { threw = true; }
+    CHECK(threw);
+    CHECK(groupby::is_streaming_groupby_supported(data_type{type_id::FLOAT64}, BGB_STD));
+  }
   std::printf(g_fail ? "%d check(s) FAILED\n" : "all C++ host-layer checks passed\n", g_fail);
   return g_fail ? 1 : 0;
 }
