@@ -8,4 +8,5 @@ from ._lib import BgbError, CudaError, LogicError, UnsupportedError  # noqa: F40
 from .aggregation import NullPolicy  # noqa: F401
 from .column import Column, Table, TypeId  # noqa: F401
 from .groupby import GroupBy, GroupByRequest, HostColumnView, can_use_hash_groupby, groupby_host  # noqa: F401
+from . import partitioning  # noqa: F401
 from .streaming import StreamingAggregationRequest, StreamingGroupBy, is_streaming_groupby_supported  # noqa: F401

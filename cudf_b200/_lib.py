@@ -107,6 +107,8 @@ def lib():
     L.bgb_kernel_launches.restype = C.c_int64
     L.bgb_partition_by_key_hash.argtypes = [C.POINTER(ColumnView), C.c_int32, C.POINTER(ColumnView), C.c_int32, C.c_int32,
                                             C.POINTER(MutableColumn), C.POINTER(C.c_int32), C.c_void_p]
+    L.bgb_hash_partition.argtypes = [C.POINTER(ColumnView), C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32, C.c_uint32,
+                                     C.POINTER(MutableColumn), C.POINTER(C.c_int32), C.c_void_p]
     L.bgb_bytes_to_bitmask.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_int32), C.c_void_p]
     L.bgb_finalize_moments.argtypes = [C.c_int32, C.c_int32, C.POINTER(ColumnView), C.POINTER(ColumnView), C.POINTER(ColumnView),
                                        C.POINTER(MutableColumn), C.c_void_p]

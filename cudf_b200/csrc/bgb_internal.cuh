@@ -50,7 +50,7 @@ struct KeyColDesc {
   const uint32_t* mask;   // nullptr = no nulls
   int32_t offset;
   uint8_t width;          // bytes: 1,2,4,8
-  uint8_t fclass;         // 0 integer-like, 1 float32, 2 float64 (normalise -0 / NaN)
+  uint8_t fclass;         // 0 integer-like, 1 float32, 2 float64 (normalise -0 / NaN), 3 bool (non-zero -> 1)
   uint8_t shift;          // bit position of the value field in the packed key (0..127)
   int8_t null_bit;        // bit position of the "is null" flag (INCLUDE policy), -1 if none
 };

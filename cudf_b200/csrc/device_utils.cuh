@@ -35,7 +35,55 @@ __device__ __forceinline__ uint64_t canon_key_bits(uint64_t raw, int fclass)
     if ((raw & 0x7fffffffffffffffull) == 0) return 0;
     if ((raw & 0x7fffffffffffffffull) > 0x7ff0000000000000ull) return 0x7ff8000000000000ull;
   }
+  if (fclass == 3) return raw != 0;  // BOOL8: element<bool>() reads any non-zero byte as true
   return raw;
+}
+
+// ---- the reference's row hash for hash_partition: MurmurHash3_x86_32 of every element's bytes (seeded), nulls hash to
+// UINT32_MAX, columns folded with boost's hash_combine (cudf/hashing/detail/murmurhash3_x86_32.cuh:26-60,
+// cudf/detail/row_operator/hashing.cuh:40-134, cudf/hashing/detail/hashing.hpp:83-86). The element is hashed in its native
+// width after the same canonicalisation as the key image (-0 -> +0, one NaN, bool -> 0/1).
+__device__ __forceinline__ uint32_t rotl32(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
+__device__ __forceinline__ uint32_t murmur3_fixed(uint64_t bits, int width, uint32_t seed)
+{
+  constexpr uint32_t c1 = 0xcc9e2d51u, c2 = 0x1b873593u;
+  uint32_t h = seed;
+  auto block = [&](uint32_t k) { k *= c1; k = rotl32(k, 15); k *= c2; h ^= k; h = rotl32(h, 13); h = h * 5u + 0xe6546b64u; };
+  if (width >= 4) block((uint32_t)bits);
+  if (width == 8) block((uint32_t)(bits >> 32));
+  if (width < 4) {  // 1- and 2-byte elements are all tail
+    uint32_t k = (uint32_t)bits & (width == 1 ? 0xffu : 0xffffu);
+    k *= c1; k = rotl32(k, 15); k *= c2; h ^= k;
+  }
+  h ^= (uint32_t)width;
+  h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+  return h;
+}
+__device__ __forceinline__ uint32_t hash_combine32(uint32_t lhs, uint32_t rhs) { return lhs ^ (rhs + 0x9e3779b9u + (lhs << 6) + (lhs >> 2)); }
+
+// mode 1 = MurmurHash3_x86_32, mode 2 = the reference's IdentityHash (static_cast<uint32_t>(element): sign-extended
+// integers truncated to 32 bits, floats converted with the saturating cvt.rzi.u32; partitioning.cu:855-874)
+__device__ __forceinline__ uint32_t cudf_row_hash(const AggParams& p, int64_t row, uint32_t seed, int mode, uint32_t signed_cols)
+{
+  uint32_t h = seed;
+#pragma unroll 1
+  for (int c = 0; c < p.num_key_cols; ++c) {
+    const KeyColDesc& kc = p.kc[c];
+    const int64_t idx    = (int64_t)kc.offset + row;
+    uint32_t e           = 0xffffffffu;  // null element
+    if (kc.mask == nullptr || bit_is_set(kc.mask, idx)) {
+      const uint64_t raw = load_raw(kc.data, kc.width, idx);
+      if (mode == 1) e = murmur3_fixed(canon_key_bits(raw, kc.fclass), kc.width, seed);
+      else if (kc.fclass == 1) e = __float2uint_rz(__uint_as_float((uint32_t)raw));
+      else if (kc.fclass == 2) e = __double2uint_rz(__longlong_as_double((long long)raw));
+      else if (kc.fclass == 3) e = raw != 0;
+      else if (kc.width == 1 && ((signed_cols >> c) & 1)) e = (uint32_t)(int32_t)(int8_t)raw;
+      else if (kc.width == 2 && ((signed_cols >> c) & 1)) e = (uint32_t)(int32_t)(int16_t)raw;
+      else e = (uint32_t)raw;
+    }
+    h = c == 0 ? e : hash_combine32(h, e);
+  }
+  return h;
 }
 
 // packs the key columns of `row` into (k0,k1); returns false when the row must be skipped (EXCLUDE + null key)

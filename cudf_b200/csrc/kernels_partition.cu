@@ -34,6 +34,14 @@ __device__ __forceinline__ uint32_t partition_of(const PartParams& p, uint64_t k
   if (p.mod_parts > 0) return (uint32_t)(mix64(h ^ 0xA0761D6478BD642Full) % (uint32_t)p.mod_parts);
   return (uint32_t)((h & (p.a.table.capacity - 1)) >> p.slot_shift);
 }
+// keep + partition of one row (the general kernels); murmur mode never packs the key
+__device__ __forceinline__ bool row_partition(const PartParams& p, int64_t row, uint64_t& k0, uint64_t& k1, uint32_t& pid)
+{
+  if (p.cudf_hash) { k0 = k1 = 0; pid = cudf_row_hash(p.a, row, p.hash_seed, p.cudf_hash, p.signed_cols) % (uint32_t)p.mod_parts; return true; }
+  if (!pack_key(p.a, row, k0, k1)) return false;
+  pid = partition_of(p, k0, k1);
+  return true;
+}
 }  // namespace
 
 __global__ void __launch_bounds__(kPThreads) partition_hist_kernel(const __grid_constant__ PartParams p)
@@ -47,11 +55,12 @@ __global__ void __launch_bounds__(kPThreads) partition_hist_kernel(const __grid_
   for (int64_t base = (int64_t)blockIdx.x * kPThreads + threadIdx.x; base < n; base += 4 * stride) {
     // four independent rows per thread: their key loads are all in flight before the first hash
     uint64_t k0[4], k1[4];
+    uint32_t pid[4];
     bool keep[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { const int64_t row = base + j * stride; keep[j] = row < n && pack_key(p.a, row, k0[j], k1[j]); }
+    for (int j = 0; j < 4; ++j) { const int64_t row = base + j * stride; keep[j] = row < n && row_partition(p, row, k0[j], k1[j], pid[j]); }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) if (keep[j]) atomicAdd(&s_hist[partition_of(p, k0[j], k1[j])], 1u);
+    for (int j = 0; j < 4; ++j) if (keep[j]) atomicAdd(&s_hist[pid[j]], 1u);
   }
   __syncthreads();
   for (uint32_t i = threadIdx.x; i < P; i += kPThreads)
@@ -119,9 +128,9 @@ __global__ void __launch_bounds__(kPThreads, (kPRows <= 8 ? 2 : 1)) partition_sc
 #pragma unroll
     for (int j = 0; j < kPRows; ++j) {
       const int64_t row = tile * kPTile + (int64_t)j * kPThreads + threadIdx.x;
-      keep[j] = row < n && pack_key(p.a, row, k0[j], k1[j]);
       pid[j] = 0; rank[j] = 0;
-      if (keep[j]) { pid[j] = partition_of(p, k0[j], k1[j]); rank[j] = atomicAdd(&s_cnt[pid[j]], 1u); }
+      keep[j] = row < n && row_partition(p, row, k0[j], k1[j], pid[j]);
+      if (keep[j]) rank[j] = atomicAdd(&s_cnt[pid[j]], 1u);
     }
     __syncthreads();
     // ---- exclusive scan of the P counters (P <= 4096: up to 4 bins per thread) + one global reservation per partition
@@ -165,6 +174,13 @@ __global__ void __launch_bounds__(kPThreads, (kPRows <= 8 ? 2 : 1)) partition_sc
       for (int j = 0; j < kPRows; ++j) if (keep[j]) stage[pos[j]] = k1[j];
       __syncthreads();
       for (uint32_t i = threadIdx.x; i < total; i += kPThreads) p.out_k1[dst[i]] = stage[i];
+    }
+    if (p.out_row != nullptr) {
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < kPRows; ++j) if (keep[j]) stage[pos[j]] = (uint64_t)(tile * kPTile + (int64_t)j * kPThreads + threadIdx.x);
+      __syncthreads();
+      for (uint32_t i = threadIdx.x; i < total; i += kPThreads) p.out_row[dst[i]] = (uint32_t)stage[i];
     }
     for (int c = 0; c < p.num_vals; ++c) {
       const PartValue& v = p.v[c];
@@ -340,6 +356,7 @@ __global__ void __launch_bounds__(kPThreads, 2) partition_scatter_fast_kernel(co
 
 static bool scatter_fast_eligible(const PartParams& p)
 {
+  if (p.cudf_hash || p.out_row) return false;
   if (p.a.num_key_cols != 1 || p.a.table.key_words != 1 || p.a.kc[0].mask != nullptr || p.a.kc[0].fclass != 0) return false;
   if (p.a.kc[0].width != 4 && p.a.kc[0].width != 8) return false;
   if (p.num_vals < 1 || p.num_vals > 2) return false;

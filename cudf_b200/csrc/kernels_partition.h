@@ -20,6 +20,12 @@ struct PartParams {
   int32_t log2_parts;       // P = 1 << log2_parts, P <= 4096
   int32_t slot_shift;       // partition = slot >> slot_shift  (slot_shift = log2(capacity) - log2_parts)
   int32_t mod_parts;        // > 0: partition = hash2(key) % mod_parts instead (multi-GPU exchange: owner rank of a key)
+  int32_t cudf_hash;        // != 0 (with mod_parts > 0): partition = cudf row hash % mod_parts (1 MurmurHash3_x86_32, 2 identity;
+                            // columns folded with hash_combine, nulls hash to UINT32_MAX, every row kept): the assignment of
+                            // cudf::hash_partition, bit for bit. The key columns are read in a.kc[] order and never packed.
+  uint32_t hash_seed;
+  uint32_t signed_cols;     // identity hash: bit c set = key column c is a signed integer (sign-extend before truncation)
+  uint32_t* out_row;        // != nullptr: source row of every output row (gather map for tables wider than kMaxPartValues)
   uint32_t* counts;         // [P]   rows per partition (zeroed by the caller)
   uint32_t* offsets;        // [P+1] exclusive scan; offsets[P] = rows kept (rows with a null key under EXCLUDE are dropped)
   uint32_t* cursors;        // [P]   running write positions

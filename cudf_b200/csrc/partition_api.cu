@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "errors.h"
+#include "device_utils.cuh"
 #include "kernels_partition.h"
 #include "plan.h"
 #include "pool.h"
@@ -204,5 +205,154 @@ extern "C" int bgb_partition_by_key_hash(const bgb_column_view* keys, int32_t nu
   if (rc) return rc;
   for (int i = 0; i <= num_parts; ++i) part_offsets_host[i] = (int32_t)off[i < (int)P ? i : P];
   part_offsets_host[num_parts] = (int32_t)off[P];
+  return BGB_OK;
+}
+
+// ---- cudf::hash_partition drop-in ---------------------------------------------------------------------------------------
+namespace bgb {
+struct GatherParams {
+  const uint32_t* map; int64_t n; int32_t num_cols;
+  PartValue v[kMaxPartValues];
+};
+// out[i] = in[map[i]] for up to kMaxPartValues columns (tables wider than one scatter launch can carry)
+__global__ void __launch_bounds__(256) gather_rows_kernel(const __grid_constant__ GatherParams g)
+{
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < g.n; i += stride) {
+    const int64_t src = g.map[i];
+    for (int c = 0; c < g.num_cols; ++c) {
+      const PartValue& v = g.v[c];
+      const int64_t idx  = (int64_t)v.offset + src;
+      const bool valid   = v.mask == nullptr || bit_is_set(v.mask, idx);
+      const uint64_t x   = valid ? load_raw(v.data, v.width, idx) : 0ull;
+      switch (v.width) {
+        case 1: v.out_data[i] = (uint8_t)x; break;
+        case 2: reinterpret_cast<uint16_t*>(v.out_data)[i] = (uint16_t)x; break;
+        case 4: reinterpret_cast<uint32_t*>(v.out_data)[i] = (uint32_t)x; break;
+        default: reinterpret_cast<uint64_t*>(v.out_data)[i] = x; break;
+      }
+      if (v.out_valid) v.out_valid[i] = valid;
+    }
+  }
+}
+static bool type_is_signed_int(int32_t t)
+{
+  return t == BGB_INT8 || t == BGB_INT16 || t == BGB_INT32 || t == BGB_INT64;
+}
+static bool type_is_numeric(int32_t t)  // cudf::is_numeric: integers, floats, bool
+{
+  return (t >= BGB_INT8 && t <= BGB_FLOAT64) || t == BGB_BOOL8;
+}
+}  // namespace bgb
+
+extern "C" int bgb_hash_partition(const bgb_column_view* input, int32_t num_cols, const int32_t* columns_to_hash, int32_t num_hash_cols,
+                                  int32_t num_partitions, int32_t hash_function, uint32_t seed, bgb_mutable_column* out_cols,
+                                  int32_t* offsets_host, void* stream)
+{
+  if (hash_function != BGB_HASH_IDENTITY && hash_function != BGB_HASH_MURMUR3)
+    return set_error(BGB_INVALID_ARGUMENT, "Unsupported hash function in hash_partition");
+  if (num_cols < 0 || num_hash_cols < 0 || (num_cols > 0 && !input) || (num_hash_cols > 0 && !columns_to_hash))
+    return set_error(BGB_INVALID_ARGUMENT, "bgb_hash_partition: null argument");
+  if (num_partitions > 0 && !offsets_host) return set_error(BGB_INVALID_ARGUMENT, "bgb_hash_partition: null offsets_host");
+  for (int i = 0; i <= (num_partitions > 0 ? num_partitions : -1); ++i) offsets_host[i] = 0;
+  for (int c = 0; c < num_cols; ++c)
+    if (out_cols) out_cols[c].null_count = 0;
+  const int64_t N = num_cols > 0 ? input[0].size : 0;
+  for (int c = 1; c < num_cols; ++c)
+    if (input[c].size != N) return set_error(BGB_INVALID_ARGUMENT, "Column size mismatch: column %d has %d rows, column 0 has %lld", c, input[c].size, (long long)N);
+  for (int h = 0; h < num_hash_cols; ++h)
+    if (columns_to_hash[h] < 0 || columns_to_hash[h] >= num_cols) return set_error(BGB_INVALID_ARGUMENT, "columns_to_hash[%d] = %d is out of range", h, columns_to_hash[h]);
+  // empty result: no partitions, no rows, or nothing to hash (partitioning.cu:885-888)
+  if (num_partitions <= 0 || N == 0 || num_hash_cols == 0) return BGB_OK;
+  if (num_partitions > 4096) return set_error(BGB_UNSUPPORTED, "bgb_hash_partition: more than 4096 partitions");
+  if (num_hash_cols > kMaxKeyCols) return set_error(BGB_UNSUPPORTED, "bgb_hash_partition: more than %d columns to hash", kMaxKeyCols);
+  if (!out_cols) return set_error(BGB_INVALID_ARGUMENT, "bgb_hash_partition: null out_cols");
+
+  PartParams pp;
+  memset(&pp, 0, sizeof pp);
+  pp.a.num_rows = N; pp.a.num_key_cols = num_hash_cols;
+  for (int h = 0; h < num_hash_cols; ++h) {
+    const bgb_column_view& k = input[columns_to_hash[h]];
+    const int w = type_width(k.type_id);
+    if (w == 0) return set_error(BGB_UNSUPPORTED, "bgb_hash_partition: column %d (type %d) is not a fixed-width type of at most 8 bytes", columns_to_hash[h], k.type_id);
+    if (hash_function == BGB_HASH_IDENTITY && !type_is_numeric(k.type_id)) return set_error(BGB_INVALID_ARGUMENT, "IdentityHash does not support this data type");
+    const uint8_t fclass = k.type_id == BGB_FLOAT32 ? 1 : k.type_id == BGB_FLOAT64 ? 2 : k.type_id == BGB_BOOL8 ? 3 : 0;
+    // a mask without nulls hashes like no mask; cudf checks nulls only when the hashed table has any (partitioning.cu:895-901)
+    pp.a.kc[h] = KeyColDesc{(const uint8_t*)k.data, k.null_count != 0 ? k.null_mask : nullptr, k.offset, (uint8_t)w, fclass, 0, 0};
+    if (type_is_signed_int(k.type_id)) pp.signed_cols |= 1u << h;
+  }
+  for (int c = 0; c < num_cols; ++c) {
+    if (type_width(input[c].type_id) == 0) return set_error(BGB_UNSUPPORTED, "bgb_hash_partition: column %d (type %d) is not a fixed-width type of at most 8 bytes", c, input[c].type_id);
+    if (!out_cols[c].data || out_cols[c].size < N) return set_error(BGB_INVALID_ARGUMENT, "out_cols[%d] holds fewer rows than the input", c);
+    if (input[c].null_mask && input[c].null_count != 0 && !out_cols[c].null_mask) return set_error(BGB_INVALID_ARGUMENT, "out_cols[%d] needs a null mask", c);
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  int num_sms = 148;
+  { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev); }
+  pp.a.table.key_words = 1; pp.a.table.capacity = 1;
+  pp.mod_parts = num_partitions;
+  pp.cudf_hash = hash_function == BGB_HASH_MURMUR3 ? 1 : 2;
+  pp.hash_seed = seed;
+  int log2p = 0; while ((1 << log2p) < num_partitions) ++log2p;
+  pp.log2_parts = log2p;
+  pp.key_out_width = 8;
+  const uint32_t P = 1u << log2p;
+
+  // scratch: counters | gather map (wide tables only) | one validity byte per row for every column that carries nulls
+  std::vector<int> nullable;
+  for (int c = 0; c < num_cols; ++c) if (input[c].null_mask && input[c].null_count != 0) nullable.push_back(c);
+  const bool wide          = num_cols > kMaxPartValues;
+  const size_t cnt_bytes   = ((sizeof(uint32_t) * (3 * (size_t)P + 1 + nullable.size()) + 255) / 256) * 256;
+  const size_t map_bytes   = wide ? (((size_t)N * 4 + 255) / 256) * 256 : 0;
+  const size_t bytes_each  = (((size_t)N + 255) / 256) * 256;
+  uint8_t* scratch = (uint8_t*)pool_alloc_async(cnt_bytes + map_bytes + bytes_each * nullable.size(), s);
+  if (!scratch) return set_error(BGB_OUT_OF_MEMORY, "hash_partition scratch");
+  uint32_t* counters = (uint32_t*)scratch;
+  pp.counts = counters; pp.cursors = counters + P; pp.offsets = counters + 2 * (size_t)P;
+  int* d_nulls = (int*)(counters + 3 * (size_t)P + 1);
+  uint32_t* map = wide ? (uint32_t*)(scratch + cnt_bytes) : nullptr;
+  uint8_t* vbytes = scratch + cnt_bytes + map_bytes;
+  std::vector<uint8_t*> col_bytes(num_cols, nullptr);
+  for (size_t i = 0; i < nullable.size(); ++i) col_bytes[nullable[i]] = vbytes + i * bytes_each;
+  auto describe = [&](int c, PartValue& o) {
+    o.data = (const uint8_t*)input[c].data; o.mask = col_bytes[c] ? input[c].null_mask : nullptr; o.offset = input[c].offset;
+    o.width = type_width(input[c].type_id); o.out_data = (uint8_t*)out_cols[c].data; o.out_valid = col_bytes[c];
+  };
+  int rc = check_cuda(cudaMemsetAsync(counters, 0, cnt_bytes, s), "partition counters");
+  if (!rc) rc = check_cuda(launch_partition_hist(pp, num_sms, s), "partition_hist");
+  if (!rc) rc = check_cuda(launch_partition_scan(pp, s), "partition_scan");
+  if (!wide) {
+    pp.num_vals = num_cols;
+    for (int c = 0; c < num_cols; ++c) describe(c, pp.v[c]);
+    if (!rc) rc = check_cuda(launch_partition_scatter(pp, num_sms, s), "partition_scatter");
+  } else {
+    pp.num_vals = 0; pp.out_row = map;
+    if (!rc) rc = check_cuda(launch_partition_scatter(pp, num_sms, s), "partition_scatter");
+    for (int c0 = 0; c0 < num_cols && !rc; c0 += kMaxPartValues) {
+      GatherParams g;
+      memset(&g, 0, sizeof g);
+      g.map = map; g.n = N; g.num_cols = num_cols - c0 < kMaxPartValues ? num_cols - c0 : kMaxPartValues;
+      for (int c = 0; c < g.num_cols; ++c) describe(c0 + c, g.v[c]);
+      const int64_t want = (N + 255) / 256;
+      gather_rows_kernel<<<(int)(want < (int64_t)num_sms * 16 ? want : (int64_t)num_sms * 16), 256, 0, s>>>(g);
+      rc = check_cuda(note_launch(), "gather_rows");
+    }
+  }
+  for (size_t i = 0; i < nullable.size() && !rc; ++i) {
+    const int64_t want = (N + 255) / 256;
+    bytes_to_bitmask_kernel<<<(int)(want < (int64_t)num_sms * 8 ? want : (int64_t)num_sms * 8), 256, 0, s>>>(col_bytes[nullable[i]], N, (uint32_t*)out_cols[nullable[i]].null_mask, d_nulls + i);
+    rc = check_cuda(note_launch(), "bytes_to_bitmask");
+  }
+  // a mask supplied for a column without nulls is returned all-valid
+  for (int c = 0; c < num_cols && !rc; ++c)
+    if (!col_bytes[c] && out_cols[c].null_mask) rc = check_cuda(cudaMemsetAsync(out_cols[c].null_mask, 0xff, sizeof(uint32_t) * (size_t)((N + 31) / 32), s), "mask fill");
+  std::vector<uint32_t> host(P + 1 + nullable.size(), 0);
+  if (!rc) rc = check_cuda(cudaMemcpyAsync(host.data(), pp.offsets, sizeof(uint32_t) * (P + 1 + nullable.size()), cudaMemcpyDeviceToHost, s), "offsets copy");
+  pool_free_async(scratch, s);
+  if (!rc) rc = check_cuda(cudaStreamSynchronize(s), "hash_partition sync");
+  if (rc) return rc;
+  for (int i = 0; i < num_partitions; ++i) offsets_host[i] = (int32_t)host[i];
+  offsets_host[num_partitions] = (int32_t)host[P];
+  for (size_t i = 0; i < nullable.size(); ++i) out_cols[nullable[i]].null_count = (int32_t)host[P + 1 + i];
   return BGB_OK;
 }

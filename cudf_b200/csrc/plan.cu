@@ -153,7 +153,7 @@ int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_nul
     KeyPlan& k = plan.keys[c];
     k.v        = keys[c];
     k.width    = (uint8_t)type_width(keys[c].type_id);
-    k.fclass   = keys[c].type_id == BGB_FLOAT32 ? 1 : keys[c].type_id == BGB_FLOAT64 ? 2 : 0;
+    k.fclass   = keys[c].type_id == BGB_FLOAT32 ? 1 : keys[c].type_id == BGB_FLOAT64 ? 2 : keys[c].type_id == BGB_BOOL8 ? 3 : 0;
     k.shift    = (uint8_t)bit;
     k.null_bit = -1;
     k.nullable_out = plan.include_null_keys && (keys[c].null_mask != nullptr || rank_independent);

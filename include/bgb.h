@@ -227,6 +227,28 @@ void bgb_stream_destroy(bgb_stream* s);
 int bgb_partition_by_key_hash(const bgb_column_view* keys, int32_t num_keys, const bgb_column_view* cols, int32_t num_cols,
                               int32_t num_parts, bgb_mutable_column* out_cols, int32_t* part_offsets_host, void* stream);
 
+/* ---- cudf::hash_partition drop-in -------------------------------------------------------------
+ * Reorders the rows of `input` (num_cols fixed-width columns of equal size) so that rows with the same partition are
+ * contiguous; partition = row_hash(columns_to_hash) % num_partitions, where row_hash is the REFERENCE's row hash, bit for
+ * bit: MurmurHash3_x86_32 (seeded) of every hashed element's native bytes after normalising -0.0 / NaN and bool -> 0/1,
+ * a null element hashing to UINT32_MAX, columns folded left to right with hash_combine
+ * (cpp/include/cudf/hashing/detail/murmurhash3_x86_32.cuh:20-70, cpp/include/cudf/detail/row_operator/hashing.cuh:40-140,
+ * cpp/include/cudf/hashing/detail/hashing.hpp:83-86, partitioners cpp/src/partitioning/partitioning.cu:41-77), or the
+ * reference's IdentityHash (static_cast<uint32_t>(element), numeric columns only, partitioning.cu:855-874).
+ * out_cols[i] (caller-allocated, >= rows of input) receives column i in partition order; when input[i] has nulls,
+ * out_cols[i].null_mask (bitmask words) receives its validity and out_cols[i].null_count the count. offsets_host receives
+ * num_partitions + 1 row offsets, partition p = rows [offsets[p], offsets[p + 1]). The order of rows INSIDE a partition
+ * is unspecified, as in the reference (its block-level scatter ranks rows with shared-memory atomics).
+ * num_partitions <= 0, zero rows or zero columns_to_hash give the reference's empty result: all offsets 0, nothing
+ * written (partitioning.cu:885-888). Replaces cudf::hash_partition (cpp/include/cudf/partitioning.hpp:103-145,
+ * cpp/src/partitioning/partitioning.cu:567-760,876-950). Synchronises `stream` once. Limits: <= 4096 partitions, <= 8
+ * hashed columns, elements of at most 8 bytes (else BGB_UNSUPPORTED: the caller keeps the reference's own path). */
+typedef enum bgb_hash_id { BGB_HASH_IDENTITY = 0, BGB_HASH_MURMUR3 = 1 } bgb_hash_id; /* cudf::hash_id, partitioning.hpp:28-31 */
+#define BGB_DEFAULT_HASH_SEED 0u /* cudf::DEFAULT_HASH_SEED, cpp/include/cudf/hashing.hpp:29 */
+int bgb_hash_partition(const bgb_column_view* input, int32_t num_cols, const int32_t* columns_to_hash, int32_t num_hash_cols,
+                       int32_t num_partitions, int32_t hash_function, uint32_t seed, bgb_mutable_column* out_cols,
+                       int32_t* offsets_host, void* stream);
+
 /* validity bytes (1 = valid) -> cudf bitmask words ((n + 31) / 32 of them); *null_count_host = number of zero bytes */
 int bgb_bytes_to_bitmask(const uint8_t* valid_bytes, int64_t n, uint32_t* mask_words, int32_t* null_count_host, void* stream);
 
