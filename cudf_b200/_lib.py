@@ -60,7 +60,7 @@ class StreamRequest(C.Structure):
 
 class Options(C.Structure):
     _fields_ = [("force_path", C.c_int32), ("capacity_log2", C.c_int32), ("sample_rows", C.c_int32), ("profile", C.c_int32),
-                ("reserved", C.c_int32 * 4)]
+                ("bucket_slice_log2", C.c_int32), ("reserved", C.c_int32 * 3)]
 
 
 class HostColumn(C.Structure):

@@ -236,4 +236,42 @@ __device__ __forceinline__ void atomic_mul_f32(unsigned int* addr, float v)
   do { assumed = old; old = atomicCAS(addr, assumed, __float_as_uint(__uint_as_float(assumed) * v)); } while (old != assumed);
 }
 
+// one valid source element into one accumulator cell (update_target_element<Source, K>,
+// /root/reference/cpp/include/cudf/detail/aggregation/device_aggregators.cuh:24-160). `cells` may point at the HBM table or
+// at a shared-memory slice of it (kernels_bucket.cu): the atomics are the generic-address forms.
+__device__ __forceinline__ void apply_value(uint8_t op, uint8_t src, void* cells, uint64_t slot, uint64_t raw, int64_t row)
+{
+  unsigned long long* c64 = reinterpret_cast<unsigned long long*>(cells) + slot;
+  unsigned int* c32       = reinterpret_cast<unsigned int*>(cells) + slot;
+  switch (op) {
+    case ACC_COUNT_VALID: case ACC_COUNT_ALL: atomicAdd(c32, 1u); break;
+    case ACC_SUM_I64: atomicAdd(c64, (unsigned long long)raw_to_i64(raw, src)); break;
+    case ACC_SUM_F64: atomicAdd(reinterpret_cast<double*>(c64), __longlong_as_double((long long)raw)); break;
+    case ACC_SUM_F32: atomicAdd(reinterpret_cast<float*>(c32), __uint_as_float((uint32_t)raw)); break;
+    case ACC_SUMSQ_I64: { uint64_t v = (uint64_t)raw_to_i64(raw, src); atomicAdd(c64, (unsigned long long)(v * v)); break; }
+    case ACC_SUMSQ_F64: { double v = __longlong_as_double((long long)raw); atomicAdd(reinterpret_cast<double*>(c64), v * v); break; }
+    case ACC_SUMSQ_F32: { float v = __uint_as_float((uint32_t)raw); atomicAdd(reinterpret_cast<float*>(c32), v * v); break; }
+    case ACC_PROD_I64: atomic_mul_i64(c64, raw_to_i64(raw, src)); break;
+    case ACC_PROD_F64: atomic_mul_f64(c64, __longlong_as_double((long long)raw)); break;
+    case ACC_PROD_F32: atomic_mul_f32(c32, __uint_as_float((uint32_t)raw)); break;
+    case ACC_MIN: { unsigned long long v = ordered_image(raw, src); if (v < *reinterpret_cast<volatile unsigned long long*>(c64)) atomicMin(c64, v); break; }
+    case ACC_MAX: { unsigned long long v = ordered_image(raw, src); if (v > *reinterpret_cast<volatile unsigned long long*>(c64)) atomicMax(c64, v); break; }
+    case ACC_ARGMIN: atomicMin(c64, (unsigned long long)((ordered_image(raw, src) << 32) | (uint32_t)row)); break;
+    case ACC_ARGMAX: atomicMax(c64, (unsigned long long)((ordered_image(raw, src) << 32) | (0xFFFFFFFFu - (uint32_t)row))); break;
+    default: break;
+  }
+}
+
+// aggregation identities of the accumulator cells (cudf::detail::identity_initializer, aggregation.cu:39-97)
+__device__ __forceinline__ uint64_t acc_identity64(uint8_t op)
+{
+  switch (op) {
+    case ACC_PROD_I64: return 1ull;
+    case ACC_PROD_F64: return 0x3ff0000000000000ull;  // 1.0
+    case ACC_MIN: case ACC_ARGMIN: return ~0ull;
+    default: return 0ull;  // sums, MAX (smallest ordered image), ARGMAX
+  }
+}
+__device__ __forceinline__ uint32_t acc_identity32(uint8_t op) { return op == ACC_PROD_F32 ? 0x3f800000u : 0u; }
+
 }  // namespace bgb

@@ -12,6 +12,7 @@
 
 #include "errors.h"
 #include "fastpaths.h"
+#include "kernels_bucket.h"
 #include "kernels_partition.h"
 #include "kernels_peer.h"
 #include "plan.h"
@@ -215,6 +216,184 @@ int run_partitioned(bgb_groupby* h, int num_sms, bool& done)
   return BGB_OK;
 }
 
+// Bucketed high-cardinality path (kernels_bucket.cu): one or two scatter levels into fixed-capacity buckets, one per
+// shared-memory-sized table slice, then a slice kernel that never touches the HBM table with atomics. `h->table` and the
+// accumulator cells are allocated (NOT initialised: every slice is stored whole). done=false when the plan does not fit.
+int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool& done)
+{
+  done = false;
+  Plan& pl = h->plan;
+  const int64_t N = pl.num_rows;
+  if (pl.key_words != 1 || pl.values.size() > (size_t)kMaxBucketValues || pl.accs.size() > (size_t)kMaxAccs || N >= (1ll << 31)) return BGB_OK;
+  // shared-memory bytes per slot: key + the accumulators that live in shared memory (kernels_bucket.h: BucketAccMode)
+  auto acc_mode = [](uint8_t op) -> uint8_t {
+    switch (op) {
+      case ACC_COUNT_VALID: case ACC_COUNT_ALL: return BM_COUNT;
+      case ACC_SUM_I64: case ACC_SUMSQ_I64: return BM_LIMBS;
+      case ACC_MIN: case ACC_MAX: return BM_MINMAX;
+      default: return BM_GLOBAL;
+    }
+  };
+  auto mode_bytes = [](uint8_t m) -> size_t { return m == BM_COUNT ? 4 : m == BM_LIMBS ? 12 : m == BM_MINMAX ? 8 : 0; };
+  size_t slot_bytes = 8;
+  for (const AccPlan& a : pl.accs) {
+    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX) return BGB_OK;  // row numbers are lost by the scatter
+    slot_bytes += mode_bytes(acc_mode(a.op));
+  }
+  int log2cap = 0; while ((1ull << log2cap) < h->table.capacity) ++log2cap;
+  // validity word: one bit per masked value column
+  int nvb = 0;
+  std::vector<int> vbit(pl.values.size(), -1);
+  for (size_t c = 0; c < pl.values.size(); ++c) if (pl.values[c].v.null_mask != nullptr) vbit[c] = nvb++;
+  int key_bits = 0;
+  for (const KeyPlan& k : pl.keys) key_bits = std::max(key_bits, std::max((int)k.shift + 8 * k.width, (int)k.null_bit + 1));
+  const bool in_low32 = nvb > 0 && key_bits <= 32;
+  const int vbw   = (nvb == 0 || in_low32) ? 0 : (nvb <= 8 ? 1 : 4);  // separate validity column between the levels
+  const int vbw_s = nvb == 0 ? 0 : (nvb <= 8 ? 1 : 4);                // validity word per row in shared memory
+  auto round16 = [](uint64_t x) { return (x + 15) & ~15ull; };
+  // rows a bucket of the LAST level can hold: expected rows + 12.5 % (one level) or + 27 % (two levels) + slack
+  auto last_capacity = [&](int bits) { return round16(bits <= 8 ? (uint64_t)((double)N / (double)(1u << bits) * 1.125) + 1024 : (uint64_t)((double)N / (double)(1u << bits) * 1.27) + 256); };
+  // shared memory of one bucket CTA: the slice + a 16-bit slot and the validity word of every row. Two CTAs per SM
+  // (<= 108 KB each) unless opt.bucket_slice_log2 fixes the slice (tests force several levels on small inputs); a bucket
+  // stays below 65536 rows (16-bit digits in 32-bit counters) and a slice below 65535 slots (16-bit slot numbers).
+  auto cta_bytes = [&](int ls_) { const uint64_t C = last_capacity(log2cap - ls_); return ((uint64_t)slot_bytes << ls_) + round16(C * 2) + round16(C * vbw_s); };
+  int ls = -1;
+  if (opt.bucket_slice_log2 > 0) {
+    ls = std::min(opt.bucket_slice_log2, log2cap - 1);
+    if (ls < 4 || ls > 15 || log2cap - ls > 18 || cta_bytes(ls) > 200 * 1024 || last_capacity(log2cap - ls) > 65535) return BGB_OK;
+  } else {
+    for (int c = std::min(15, log2cap - 1); c >= 4 && log2cap - c <= 18; --c)
+      if (cta_bytes(c) <= 108 * 1024 && last_capacity(log2cap - c) <= 65535) { ls = c; break; }
+    if (ls < 0) return BGB_OK;
+  }
+  const int b  = log2cap - ls;
+  const int b1 = b <= 8 ? b : (b + 1) / 2, b2 = b - b1;
+  const uint32_t P1 = 1u << b1, NB = 1u << b;
+  cudaStream_t s = h->stream;
+
+  const uint64_t C1  = b2 ? round16((uint64_t)((double)N / P1 * 1.125) + 1024) : last_capacity(b);
+  const uint64_t C2  = last_capacity(b);
+  const uint64_t OV  = round16((uint64_t)N / 16 + 4096);
+  const uint64_t rows1 = (uint64_t)P1 * C1 + OV + 1;
+  const uint64_t rows2 = b2 ? (uint64_t)NB * C2 + OV + 1 : 0;
+  if (rows1 >= (1ull << 32) || rows2 >= (1ull << 32)) return BGB_OK;
+
+  std::vector<void*> scratch;
+  auto grab = [&](size_t bytes) { void* p = h->dalloc(bytes); if (p) scratch.push_back(p); return p; };
+  auto release = [&]() { for (void* p : scratch) h->dfree(p); scratch.clear(); };
+  struct Level { uint64_t* key = nullptr; uint8_t* vbits = nullptr; std::vector<uint8_t*> val; };
+  auto alloc_level = [&](Level& L, uint64_t rows) {
+    L.key = (uint64_t*)grab(rows * 8);
+    bool ok = L.key != nullptr;
+    if (vbw) { L.vbits = (uint8_t*)grab(rows * vbw); ok = ok && L.vbits; }
+    for (size_t c = 0; c < pl.values.size() && ok; ++c) {
+      L.val.push_back((uint8_t*)grab(rows * type_width(pl.values[c].v.type_id)));
+      ok = L.val.back() != nullptr;
+    }
+    return ok;
+  };
+  Level L1, L2;
+  const size_t ncount = (size_t)P1 + (b2 ? NB : 0) + 2;
+  uint32_t* counters = (uint32_t*)grab(sizeof(uint32_t) * ncount);
+  bool ok = counters && alloc_level(L1, rows1) && (!b2 || alloc_level(L2, rows2));
+  if (!ok) { release(); return set_error(BGB_OUT_OF_MEMORY, "bucket buffers (%lld rows)", (long long)N); }
+  uint32_t* cursor1 = counters;
+  uint32_t* cursor2 = counters + P1;
+  uint32_t* ov1     = counters + ncount - 2;
+  uint32_t* ov2     = counters + ncount - 1;
+  TR("bucket alloc");
+  int rc = check_cuda(cudaMemsetAsync(counters, 0, sizeof(uint32_t) * ncount, s), "bucket counters");
+  if (rc) { release(); return rc; }
+
+  // ---- aggregation parameters (also used by the reserved-slot initialiser)
+  BucketAggParams ap;
+  memset(&ap, 0, sizeof ap);
+  ap.table = h->table;
+  ap.key_in_low32 = in_low32; ap.vbits_width = vbw;
+  ap.log2_slice = ls; ap.num_buckets = NB;
+  ap.num_accs = (int)pl.accs.size();
+  const Level& LF = b2 ? L2 : L1;
+  uint32_t off = (uint32_t)(8u << ls);
+  for (int pass = 0; pass < 2; ++pass)  // 8-byte cells first, then the 4-byte ones: every slice stays 16-byte aligned
+    for (size_t a = 0; a < pl.accs.size(); ++a) {
+      const AccPlan& acc = pl.accs[a];
+      const uint8_t mode = acc_mode(acc.op);
+      if ((pass == 0) != (mode == BM_MINMAX)) continue;
+      BucketAcc& d = ap.acc[a];
+      d.cells = acc.cells; d.op = acc.op; d.mode = mode; d.smem_off = off;
+      off += (uint32_t)(mode_bytes(mode) << ls);
+      if (acc.value_col >= 0) { d.data = LF.val[acc.value_col]; d.src = pl.values[acc.value_col].src; d.vbit = (int16_t)vbit[acc.value_col]; }
+      else { d.data = nullptr; d.src = S_I32; d.vbit = -1; }
+    }
+  const uint64_t CL = b2 ? C2 : C1;
+  ap.loc_off = off; off += (uint32_t)round16(CL * 2);
+  ap.vb_off = off; ap.vb_width = vbw_s; off += (uint32_t)round16(CL * vbw_s);
+  const size_t slice_smem = off;
+  rc = check_cuda(launch_bucket_init_reserved(ap, s), "bucket_init_reserved");
+
+  // ---- level 1
+  BucketScatterParams sp;
+  memset(&sp, 0, sizeof sp);
+  fill_agg_params(*h, sp.a, 0, 0);
+  sp.level = 1;
+  sp.key_mode = 0;
+  if (pl.keys.size() == 1 && pl.keys[0].v.null_mask == nullptr && pl.keys[0].fclass == 0 && (pl.keys[0].width == 4 || pl.keys[0].width == 8)) sp.key_mode = pl.keys[0].width;
+  sp.log2_parts = b1; sp.slot_shift = log2cap - b1;
+  sp.key_in_low32 = in_low32; sp.vbits_width = vbw;
+  sp.cursor = cursor1; sp.bucket_capacity = (uint32_t)C1;
+  sp.ov_cursor = ov1; sp.ov_capacity = (uint32_t)OV; sp.ov_base = (uint32_t)((uint64_t)P1 * C1);
+  sp.status = h->table.status;
+  sp.out_key = L1.key; sp.out_vbits = L1.vbits;
+  sp.num_vals = (int)pl.values.size();
+  for (size_t c = 0; c < pl.values.size(); ++c) {
+    const ValuePlan& v = pl.values[c];
+    sp.v[c] = BucketValue{(const uint8_t*)v.v.data, v.v.null_mask, v.v.offset, type_width(v.v.type_id), vbit[c], L1.val[c]};
+  }
+  h->prof.begin("bucket_scatter1");
+  if (!rc) rc = check_cuda(launch_bucket_scatter(sp, num_sms, s), "bucket_scatter1");
+  h->prof.end();
+
+  // ---- level 2: every level-1 bucket is a segment
+  if (b2 && !rc) {
+    BucketScatterParams s2 = sp;
+    s2.level = 2;
+    s2.in_key = L1.key; s2.in_vbits = L1.vbits;
+    s2.seg_cursor = cursor1; s2.seg_capacity = (uint32_t)C1; s2.num_segs = P1;
+    s2.log2_parts = b2; s2.slot_shift = log2cap - b;
+    s2.cursor = cursor2; s2.bucket_capacity = (uint32_t)C2;
+    s2.ov_cursor = ov2; s2.ov_base = (uint32_t)((uint64_t)NB * C2);
+    s2.out_key = L2.key; s2.out_vbits = L2.vbits;
+    for (size_t c = 0; c < pl.values.size(); ++c) { s2.v[c].in = L1.val[c]; s2.v[c].in_mask = nullptr; s2.v[c].in_offset = 0; s2.v[c].out = L2.val[c]; }
+    h->prof.begin("bucket_scatter2");
+    rc = check_cuda(launch_bucket_scatter(s2, num_sms, s), "bucket_scatter2");
+    h->prof.end();
+  }
+
+  // ---- slices, then the overflow rows of the last level (and of level 1 when there were two)
+  ap.key = LF.key; ap.vbits = LF.vbits;
+  ap.cursor = b2 ? cursor2 : cursor1;
+  ap.bucket_capacity = (uint32_t)(b2 ? C2 : C1);
+  h->prof.begin("bucket_aggregate");
+  if (!rc) rc = check_cuda(launch_bucket_aggregate(ap, slice_smem, s), "bucket_aggregate");
+  h->prof.end();
+  h->prof.begin("bucket_overflow");
+  ap.ov_cursor = b2 ? ov2 : ov1; ap.ov_capacity = (uint32_t)OV; ap.ov_base = (uint32_t)((uint64_t)NB * (b2 ? C2 : C1));
+  if (!rc) rc = check_cuda(launch_bucket_overflow(ap, s), "bucket_overflow");
+  if (b2 && !rc) {
+    BucketAggParams a1 = ap;
+    a1.key = L1.key; a1.vbits = L1.vbits;
+    for (size_t a = 0; a < pl.accs.size(); ++a) if (pl.accs[a].value_col >= 0) a1.acc[a].data = L1.val[pl.accs[a].value_col];
+    a1.ov_cursor = ov1; a1.ov_base = (uint32_t)((uint64_t)P1 * C1);
+    rc = check_cuda(launch_bucket_overflow(a1, s), "bucket_overflow");
+  }
+  h->prof.end();
+  TR("bucket launches");
+  release();  // stream-ordered
+  if (rc) return rc;
+  done = true;
+  return BGB_OK;
+}
+
 }  // namespace
 
 static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
@@ -317,7 +496,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     if (capacity > cap_max) capacity = cap_max;
   }
 
-  bool skip_tiny = false;
+  bool skip_tiny = false, no_bucket = false;
   for (int attempt = 0;; ++attempt) {
     h->table.capacity = capacity;
     const uint64_t slots = capacity + 1;
@@ -337,7 +516,12 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
       size_t slot_bytes = 8 * (size_t)pl.key_words;
       for (const AccPlan& a : pl.accs) slot_bytes += acc_cell_bytes(a.op);
       // the table will not stay in L2: partition first (measured 3-5x faster than random HBM atomics at 1e8 groups)
-      if (opt.force_path == 3 || ((double)capacity * slot_bytes > 96e6 && N >= (1 << 22))) {
+      const bool big = (double)capacity * slot_bytes > 96e6 && N >= (1 << 22);
+      if ((opt.force_path == 7 || (opt.force_path == 0 && big)) && !no_bucket) {
+        FAIL_RC(run_bucketed(h, num_sms, opt, done));
+        if (done) path = "bucketed";
+      }
+      if (!done && (opt.force_path == 3 || opt.force_path == 7 || big)) {
         FAIL_RC(run_partitioned(h, num_sms, done));
         if (done) path = "partitioned";
       }
@@ -380,6 +564,15 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     h->prof.resolve();
     h->dfree(scan_state);
     if (getenv("BGB_DEBUG")) fprintf(stderr, "[bgb] path=%s groups=%u overflow=%u bypass_rows=%u flushes=%u\n", path.c_str(), st[1], st[0], st[4], st[5]);
+    if (st[6] != 0 && path == "bucketed") {
+      // skewed keys filled the buckets' overflow region: same table size, exact-offset partitioned path
+      no_bucket = true;
+      h->dfree(h->group_slots); h->group_slots = nullptr;
+      h->dfree(h->table.keys); h->table.keys = nullptr;
+      for (AccPlan& a : pl.accs) { h->dfree(a.cells); a.cells = nullptr; }
+      --attempt;
+      continue;
+    }
     if (st[0] == 0 && st[3] == 0) { h->num_groups = (int32_t)st[1]; break; }
     if (st[0] == 0 && st[3] != 0 && !skip_tiny) {
       // the tiny-cardinality kernel met more distinct keys than it has rows for: same table, general path

@@ -12,18 +12,6 @@
 
 namespace bgb {
 
-// ------------------------------------------------------------------ identities
-__device__ __forceinline__ uint64_t acc_identity64(uint8_t op)
-{
-  switch (op) {
-    case ACC_PROD_I64: return 1ull;
-    case ACC_PROD_F64: return 0x3ff0000000000000ull;  // 1.0
-    case ACC_MIN: case ACC_ARGMIN: return ~0ull;
-    default: return 0ull;  // sums, MAX (smallest ordered image), ARGMAX
-  }
-}
-__device__ __forceinline__ uint32_t acc_identity32(uint8_t op) { return op == ACC_PROD_F32 ? 0x3f800000u : 0u; }
-
 __global__ void __launch_bounds__(256) init_table_kernel(const __grid_constant__ AggParams p)
 {
   const uint64_t n      = p.table.capacity + 1;
@@ -60,25 +48,7 @@ __device__ __forceinline__ void apply_acc(const AccDesc& a, int64_t row, uint64_
     if (!valid) return;
   }
   if (a.op == ACC_COUNT_VALID) { atomicAdd(reinterpret_cast<int*>(a.cells) + slot, 1); return; }
-  const uint64_t raw = load_raw(a.data, src_width(a.src), idx);
-  unsigned long long* c64 = reinterpret_cast<unsigned long long*>(a.cells) + slot;
-  unsigned int* c32       = reinterpret_cast<unsigned int*>(a.cells) + slot;
-  switch (a.op) {
-    case ACC_SUM_I64: atomicAdd(c64, (unsigned long long)raw_to_i64(raw, a.src)); break;
-    case ACC_SUM_F64: atomicAdd(reinterpret_cast<double*>(c64), __longlong_as_double((long long)raw)); break;
-    case ACC_SUM_F32: atomicAdd(reinterpret_cast<float*>(c32), __uint_as_float((uint32_t)raw)); break;
-    case ACC_SUMSQ_I64: { uint64_t v = (uint64_t)raw_to_i64(raw, a.src); atomicAdd(c64, (unsigned long long)(v * v)); break; }
-    case ACC_SUMSQ_F64: { double v = __longlong_as_double((long long)raw); atomicAdd(reinterpret_cast<double*>(c64), v * v); break; }
-    case ACC_SUMSQ_F32: { float v = __uint_as_float((uint32_t)raw); atomicAdd(reinterpret_cast<float*>(c32), v * v); break; }
-    case ACC_PROD_I64: atomic_mul_i64(c64, raw_to_i64(raw, a.src)); break;
-    case ACC_PROD_F64: atomic_mul_f64(c64, __longlong_as_double((long long)raw)); break;
-    case ACC_PROD_F32: atomic_mul_f32(c32, __uint_as_float((uint32_t)raw)); break;
-    case ACC_MIN: { unsigned long long v = ordered_image(raw, a.src); if (v < *reinterpret_cast<volatile unsigned long long*>(c64)) atomicMin(c64, v); break; }
-    case ACC_MAX: { unsigned long long v = ordered_image(raw, a.src); if (v > *reinterpret_cast<volatile unsigned long long*>(c64)) atomicMax(c64, v); break; }
-    case ACC_ARGMIN: atomicMin(c64, (unsigned long long)((ordered_image(raw, a.src) << 32) | (uint32_t)row)); break;
-    case ACC_ARGMAX: atomicMax(c64, (unsigned long long)((ordered_image(raw, a.src) << 32) | (0xFFFFFFFFu - (uint32_t)row))); break;
-    default: break;
-  }
+  apply_value(a.op, a.src, a.cells, slot, load_raw(a.data, src_width(a.src), idx), row);
 }
 
 // ------------------------------------------------------------------ fused hash + probe + aggregate (HBM table)

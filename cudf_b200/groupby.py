@@ -60,6 +60,7 @@ class GroupBy:
         opt.capacity_log2 = int(self._options.get("capacity_log2", 0))
         opt.sample_rows = int(self._options.get("sample_rows", 0))
         opt.profile = int(self._options.get("profile", 0))
+        opt.bucket_slice_log2 = int(self._options.get("bucket_slice_log2", 0))
         handle = C.c_void_p()
         ngroups = C.c_int32(0)
         with torch.cuda.device(device):
@@ -172,6 +173,7 @@ def groupby_host(keys, requests, null_handling: int = NullPolicy.EXCLUDE, option
     opt = _lib.Options()
     opt.force_path = int(options.get("force_path", 0))
     opt.capacity_log2 = int(options.get("capacity_log2", 0))
+    opt.bucket_slice_log2 = int(options.get("bucket_slice_log2", 0))
     ng, nres = C.c_int32(0), C.c_int32(0)
     hk, hr = C.POINTER(_lib.HostColumn)(), C.POINTER(_lib.HostColumn)()
     _lib.check(L.bgb_groupby_host(ckeys, nk, int(null_handling), creq, len(requests), C.byref(opt), C.byref(ng), C.byref(hk),
