@@ -253,8 +253,8 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool& done
   auto round16 = [](uint64_t x) { return (x + 15) & ~15ull; };
   // rows a bucket of the LAST level can hold: expected rows + 12.5 % (one level) or + 27 % (two levels) + slack
   auto last_capacity = [&](int bits) { return round16(bits <= 8 ? (uint64_t)((double)N / (double)(1u << bits) * 1.125) + 1024 : (uint64_t)((double)N / (double)(1u << bits) * 1.27) + 256); };
-  // shared memory of one bucket CTA: the slice + a 16-bit slot and the validity word of every row. Two CTAs per SM
-  // (<= 108 KB each) unless opt.bucket_slice_log2 fixes the slice (tests force several levels on small inputs); a bucket
+  // shared memory of one bucket CTA: the slice + a 16-bit slot and the validity word of every row. Three CTAs per SM
+  // (<= 72 KB each) unless opt.bucket_slice_log2 fixes the slice (tests force several levels on small inputs); a bucket
   // stays below 65536 rows (16-bit digits in 32-bit counters) and a slice below 65535 slots (16-bit slot numbers).
   auto cta_bytes = [&](int ls_) { const uint64_t C = last_capacity(log2cap - ls_); return ((uint64_t)slot_bytes << ls_) + round16(C * 2) + round16(C * vbw_s); };
   int ls = -1;
@@ -263,7 +263,7 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool& done
     if (ls < 4 || ls > 15 || log2cap - ls > 18 || cta_bytes(ls) > 200 * 1024 || last_capacity(log2cap - ls) > 65535) return BGB_OK;
   } else {
     for (int c = std::min(15, log2cap - 1); c >= 4 && log2cap - c <= 18; --c)
-      if (cta_bytes(c) <= 108 * 1024 && last_capacity(log2cap - c) <= 65535) { ls = c; break; }
+      if (cta_bytes(c) <= 72 * 1024 && last_capacity(log2cap - c) <= 65535) { ls = c; break; }
     if (ls < 0) return BGB_OK;
   }
   const int b  = log2cap - ls;

@@ -23,8 +23,23 @@
 
 namespace bgb {
 
+// Slot hash of this path. The table a bucketed call builds is read back only by compaction/emit (slot order is not
+// observable) and by this file's own overflow kernel, so the path is free to use a cheaper hash than hash_key(): the
+// SplitMix64 finaliser costs ~35 SASS instructions (two 64-bit multiplies) and was a quarter of the scatter kernel. Here:
+// Fibonacci product folded to 32 bits, then the murmur3 32-bit finaliser (11 instructions). 32 bits index any table this
+// path can build (capacity <= 2^32 slots).
+__device__ __forceinline__ uint32_t bucket_hash(uint64_t k)
+{
+  const uint64_t h = k * 0x9E3779B97F4A7C15ull;
+  uint32_t x = (uint32_t)(h >> 32) ^ (uint32_t)h;
+  x *= 0x85EBCA6Bu; x ^= x >> 13;
+  x *= 0xC2B2AE35u; x ^= x >> 16;
+  return x;
+}
+
 namespace {
 constexpr int kBThreads = 512;
+constexpr int kBCtasPerSm = 2;
 constexpr int kBRows    = kBucketTile / kBThreads;  // 8
 constexpr uint32_t kOvFail = 0xFFFFFFFFu;
 }  // namespace
@@ -32,7 +47,7 @@ constexpr uint32_t kOvFail = 0xFFFFFFFFu;
 // MODE: 0 level 1 with the general key packer, 4 / 8 level 1 with one unmasked integer-like key column of that width,
 //       2 level 2 (packed input)
 template <int MODE>
-__global__ void __launch_bounds__(kBThreads, 2) bucket_scatter_kernel(const __grid_constant__ BucketScatterParams p)
+__global__ void __launch_bounds__(kBThreads, kBCtasPerSm) bucket_scatter_kernel(const __grid_constant__ BucketScatterParams p)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const uint32_t P = 1u << p.log2_parts;
@@ -45,10 +60,10 @@ __global__ void __launch_bounds__(kBThreads, 2) bucket_scatter_kernel(const __gr
   uint32_t* s_room = s_gbas + P;
   uint32_t* s_ovb  = s_room + P;
   __shared__ uint32_t s_warp[kBThreads / 32];
-  __shared__ uint32_t s_total;
+  __shared__ uint32_t s_total, s_ovf;
 
   const uint32_t t        = threadIdx.x;
-  const uint64_t capmask  = p.a.table.capacity - 1;
+  const uint32_t capmask  = (uint32_t)(p.a.table.capacity - 1);
   const uint32_t pmask    = P - 1;
   const uint32_t tiles_per_seg = MODE == 2 ? (p.seg_capacity + kBucketTile - 1) / kBucketTile : 1;
   const int64_t ntiles    = MODE == 2 ? (int64_t)p.num_segs * tiles_per_seg : (p.a.num_rows + kBucketTile - 1) / kBucketTile;
@@ -69,6 +84,7 @@ __global__ void __launch_bounds__(kBThreads, 2) bucket_scatter_kernel(const __gr
       nrows = p.a.num_rows - row0 < (int64_t)kBucketTile ? (uint32_t)(p.a.num_rows - row0) : kBucketTile;
     }
     for (uint32_t i = t; i < P; i += kBThreads) s_cnt[i] = 0;
+    if (t == 0) s_ovf = 0;
 
     // ---- keys (+ validity words) of this thread's rows; consecutive threads read consecutive rows
     uint64_t key[kBRows];
@@ -120,7 +136,7 @@ __global__ void __launch_bounds__(kBThreads, 2) bucket_scatter_kernel(const __gr
     uint32_t pid[kBRows], rank[kBRows];
 #pragma unroll
     for (int j = 0; j < kBRows; ++j) {
-      pid[j]  = (uint32_t)((hash_key(key[j], 0, 1) & capmask) >> p.slot_shift) & pmask;
+      pid[j]  = ((bucket_hash(key[j]) & capmask) >> p.slot_shift) & pmask;
       rank[j] = 0;
       if ((keep >> j) & 1u) rank[j] = atomicAdd(&s_cnt[pid[j]], 1u);
     }
@@ -141,15 +157,17 @@ __global__ void __launch_bounds__(kBThreads, 2) bucket_scatter_kernel(const __gr
 #pragma unroll
         for (int w = 0; w < kBThreads / 32; ++w) { uint32_t u = s_warp[w]; if (w < (int)(t >> 5)) woff += u; total += u; }
         if (i < P) {
-          s_off[i] = carry + woff + incl - v;
+          const uint32_t excl = carry + woff + incl - v;
+          s_off[i] = excl;
           if (v) {
             const uint32_t g    = atomicAdd(p.cursor + cbase + i, v);
             const uint32_t room = g < p.bucket_capacity ? p.bucket_capacity - g : 0;
-            s_gbas[i] = (cbase + i) * p.bucket_capacity + g;
-            s_room[i] = room;
+            s_gbas[i] = (cbase + i) * p.bucket_capacity + g - excl;  // destination row = staged position + this
+            s_room[i] = excl + room;                                 // staged positions from here on do not fit the bucket
             if (v > room) {
               const uint32_t e  = v - room;
               const uint32_t ob = atomicAdd(p.ov_cursor, e);
+              s_ovf = 1;
               if (ob > p.ov_capacity || e > p.ov_capacity - ob) { p.status[6] = 1; s_ovb[i] = kOvFail; }
               else s_ovb[i] = p.ov_base + ob;
             }
@@ -165,15 +183,17 @@ __global__ void __launch_bounds__(kBThreads, 2) bucket_scatter_kernel(const __gr
 
     // ---- destination row of every staged position, then column by column through `stage`
     uint32_t pos[kBRows];
+    const bool ovf = s_ovf != 0;  // CTA-uniform; only skewed inputs ever take the branch below
 #pragma unroll
     for (int j = 0; j < kBRows; ++j) {
       pos[j] = 0;
       if ((keep >> j) & 1u) {
         pos[j] = s_off[pid[j]] + rank[j];
-        const uint32_t room = s_room[pid[j]];
-        uint32_t d;
-        if (rank[j] < room) d = s_gbas[pid[j]] + rank[j];
-        else { const uint32_t ob = s_ovb[pid[j]]; d = ob == kOvFail ? p.ov_base + p.ov_capacity : ob + (rank[j] - room); }
+        uint32_t d = pos[j] + s_gbas[pid[j]];
+        if (ovf) {
+          const uint32_t lim = s_room[pid[j]];
+          if (pos[j] >= lim) { const uint32_t ob = s_ovb[pid[j]]; d = ob == kOvFail ? p.ov_base + p.ov_capacity : ob + (pos[j] - lim); }
+        }
         dst[pos[j]]   = d;
         stage[pos[j]] = p.key_in_low32 ? ((key[j] & 0xffffffffull) | ((uint64_t)vb[j] << 32)) : key[j];
       }
@@ -248,7 +268,7 @@ static cudaError_t launch_scatter_mode(const BucketScatterParams& p, int64_t nti
   const size_t smem = bucket_scatter_smem_bytes(p.log2_parts);
   cudaError_t e = cudaFuncSetAttribute(bucket_scatter_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  const int grid = (int)(ntiles < 2ll * num_sms ? ntiles : 2ll * num_sms);
+  const int grid = (int)(ntiles < (int64_t)kBCtasPerSm * num_sms ? ntiles : (int64_t)kBCtasPerSm * num_sms);
   bucket_scatter_kernel<MODE><<<grid, kBThreads, smem, s>>>(p);
   return note_launch();
 }
@@ -336,7 +356,7 @@ __device__ __forceinline__ void for_rows(uint32_t n, const uint16_t* s_loc, cons
   }
 }
 
-__global__ void __launch_bounds__(kAThreads, 2) bucket_aggregate_kernel(const __grid_constant__ BucketAggParams p)
+__global__ void __launch_bounds__(kAThreads, 3) bucket_aggregate_kernel(const __grid_constant__ BucketAggParams p)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   unsigned long long* s_keys = reinterpret_cast<unsigned long long*>(smem_raw);
@@ -374,39 +394,53 @@ __global__ void __launch_bounds__(kAThreads, 2) bucket_aggregate_kernel(const __
     }
     __syncthreads();
 
-    // ---- phase 1: key -> slot of the slice for every row (LDS probe, ATOMS.CAS only on the first row of a group)
+    // ---- phase 1: key -> slot of the slice for every row (LDS probe, ATOMS.CAS only on the first row of a group).
+    // A lane walks its kARows rows as ONE loop (a probe step per iteration, next row when the slot is found): the warp runs
+    // max-over-lanes of the SUMMED probe lengths instead of the sum over rows of the per-row maxima, and the rare insert
+    // branch exists once.
     for (uint32_t r0 = 0; r0 < n; r0 += kAThreads * kARows) {
-      uint64_t kw[kARows];
+      uint64_t kq[kARows];
+      uint32_t lq[kARows];
+      int cnt = 0;  // this lane's rows of the iteration are a prefix: r0 + j * kAThreads + t < n
 #pragma unroll
       for (int j = 0; j < kARows; ++j) {
         const uint32_t r = r0 + j * kAThreads + t;
-        kw[j] = 0;
-        if (r < n) kw[j] = __ldcs(reinterpret_cast<const unsigned long long*>(p.key) + base + r);
+        kq[j] = 0;
+        if (r < n) { kq[j] = __ldcs(reinterpret_cast<const unsigned long long*>(p.key) + base + r); cnt = j + 1; }
       }
 #pragma unroll
       for (int j = 0; j < kARows; ++j) {
         const uint32_t r = r0 + j * kAThreads + t;
-        if (r >= n) continue;
-        const uint32_t vb = p.vb_width ? row_vbits(p, kw[j], base + r) : 0;
-        const unsigned long long k = p.key_in_low32 ? (kw[j] & 0xffffffffull) : kw[j];
-        uint32_t loc = 0xFFFFu;
-        if (k == kEmpty) reserved_row(p, p.vb_width ? vb : 0xFFFFFFFFu, base + r);
-        else {
-          uint32_t l = (uint32_t)hash_key(k, 0, 1) & smask;
-          for (uint32_t probes = 0; probes <= smask; ++probes) {
-            const unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(s_keys + l);
-            if (cur == k) { loc = l; break; }
-            if (cur == kEmpty) {
-              const unsigned long long old = atomicCAS(s_keys + l, (unsigned long long)kEmpty, k);
-              if (old == kEmpty || old == k) { loc = l; break; }
-            }
-            l = (l + 1) & smask;
-          }
-          if (loc == 0xFFFFu) p.table.status[0] = 1;  // more distinct keys than slots: the host retries with a larger table
+        if (p.vb_width != 0 && r < n) {
+          const uint32_t vb = row_vbits(p, kq[j], base + r);
+          if (p.vb_width == 1) s_vb[r] = (uint8_t)vb; else reinterpret_cast<uint32_t*>(s_vb)[r] = vb;
         }
-        s_loc[r] = (uint16_t)loc;
-        if (p.vb_width == 1) s_vb[r] = (uint8_t)vb;
-        else if (p.vb_width == 4) reinterpret_cast<uint32_t*>(s_vb)[r] = vb;
+        if (p.key_in_low32) kq[j] &= 0xffffffffull;
+        lq[j] = bucket_hash(kq[j]) & smask;
+      }
+      uint32_t r = r0 + t, probes = 0;
+      while (cnt > 0) {
+        const unsigned long long k = kq[0];
+        uint32_t found = 0xFFFFFFFFu;  // 0xFFFF: row skipped
+        if (k == kEmpty) { reserved_row(p, p.vb_width == 0 ? 0xFFFFFFFFu : (p.vb_width == 1 ? (uint32_t)s_vb[r] : reinterpret_cast<uint32_t*>(s_vb)[r]), base + r); found = 0xFFFFu; }
+        else {
+          const unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(s_keys + lq[0]);
+          if (cur == k) found = lq[0];
+          else if (cur == kEmpty) {
+            const unsigned long long old = atomicCAS(s_keys + lq[0], (unsigned long long)kEmpty, k);
+            if (old == kEmpty || old == k) found = lq[0];
+          }
+          if (found == 0xFFFFFFFFu) {
+            lq[0] = (lq[0] + 1) & smask;
+            if (++probes > smask) { p.table.status[0] = 1; found = 0xFFFFu; }  // more distinct keys than slots: the host retries bigger
+          }
+        }
+        if (found != 0xFFFFFFFFu) {
+          s_loc[r] = (uint16_t)found;
+#pragma unroll
+          for (int j = 0; j + 1 < kARows; ++j) { kq[j] = kq[j + 1]; lq[j] = lq[j + 1]; }
+          r += kAThreads; --cnt; probes = 0;
+        }
       }
     }
     __syncthreads();
@@ -544,7 +578,7 @@ __device__ __forceinline__ uint64_t find_or_insert_sliced(const TableDesc& t, ui
   const uint64_t cap = t.capacity;
   if (k0 == kEmpty) { t.status[2] = 1; return cap; }
   const uint64_t smask = (1ull << log2_slice) - 1;
-  uint64_t slot = hash_key(k0, 0, 1) & (cap - 1);
+  uint64_t slot = bucket_hash(k0) & (cap - 1);
   unsigned long long* keys = reinterpret_cast<unsigned long long*>(t.keys);
   for (uint64_t probes = 0; probes <= smask; ++probes) {
     unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(keys + slot);
