@@ -131,6 +131,8 @@ int run_partitioned(bgb_groupby* h, int num_sms, bool& done)
   Plan& pl = h->plan;
   const int64_t N = pl.num_rows;
   if (pl.values.size() > (size_t)kMaxPartValues || N >= (1ll << 31)) return BGB_OK;
+  for (const AccPlan& a : pl.accs)
+    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX) return BGB_OK;  // the partition-ordered copy loses the row numbers ARG* report
   cudaStream_t s = h->stream;
   // partitions: table region of capacity/P slots (keys + all cells) around 16 MB, P in [16, 4096]
   size_t slot_bytes = 8 * (size_t)pl.key_words;

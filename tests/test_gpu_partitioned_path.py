@@ -76,3 +76,16 @@ def test_all_keys_null_and_tiny_inputs():
     G, _, _, path = gpu_util.run_gpu([k], [v], [(0, "sum", 1)], options={"force_path": 3})
     assert G == 0
     _check([H(np.array([5, 5, 7], dtype=np.int64))], [H(np.array([1, 2, 3], dtype=np.int64))], [(0, "sum", 1), (0, "count_all", 1)], name="tiny")
+
+
+@pytest.mark.parametrize("force_path", [3, 7])
+def test_argmin_argmax_keep_source_row_numbers(force_path):
+    # ARGMIN/ARGMAX report row numbers of the INPUT: a partition- or bucket-ordered copy cannot serve them, the call must
+    # take a path that sees the original rows
+    rng = np.random.default_rng(33)
+    n = 200_000
+    k = H(rng.integers(0, 30_000, n).astype(np.int64))
+    v = H(rng.permutation(n).astype(np.int32))  # unique values: no ties
+    G, path = gpu_util.compare_with_oracle([k], [v], [(0, "argmin", 1), (0, "argmax", 1), (0, "min", 1)], options={"force_path": force_path},
+                                           name=f"arg/{force_path}")
+    assert path == "global", path
