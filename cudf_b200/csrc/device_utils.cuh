@@ -132,24 +132,46 @@ __device__ __forceinline__ void cas128(uint64_t* addr, uint64_t c0, uint64_t c1,
 constexpr uint64_t kNoSlot       = ~0ull;
 constexpr uint32_t kMaxProbes    = 8192;  // beyond this the table is declared overloaded and the host retries bigger
 
+// Slot hash of the bucketed path (kernels_bucket.cu) and of tables merged from its output (kernels_peer.cu). A table is
+// only ever probed by the kernels that built it (compaction and emit read slots in order, whatever put the keys there), so
+// those kernels may use a cheaper hash than hash_key(): the SplitMix64 finaliser costs ~35 SASS instructions (two 64-bit
+// multiplies) and was a quarter of the scatter kernel. Here: Fibonacci product folded to 32 bits, then the murmur3 32-bit
+// finaliser (11 instructions). 32 bits index any table the hash path can build (capacity <= 2^32 slots).
+__device__ __forceinline__ uint32_t slot_hash32(uint64_t k)
+{
+  const uint64_t h = k * 0x9E3779B97F4A7C15ull;
+  uint32_t x = (uint32_t)(h >> 32) ^ (uint32_t)h;
+  x *= 0x85EBCA6Bu; x ^= x >> 13;
+  x *= 0xC2B2AE35u; x ^= x >> 16;
+  return x;
+}
+
+// one-word keys: linear probing from the slot a given hash names
+__device__ __forceinline__ uint64_t find_or_insert_from(const TableDesc& t, uint64_t k0, uint64_t hash)
+{
+  const uint64_t cap = t.capacity;
+  if (k0 == kEmpty) { t.status[2] = 1; return cap; }
+  uint64_t slot = hash & (cap - 1);
+  unsigned long long* keys = reinterpret_cast<unsigned long long*>(t.keys);
+  for (uint32_t probes = 0; probes < kMaxProbes; ++probes) {
+    unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(keys + slot);
+    if (cur == k0) return slot;
+    if (cur == kEmpty) {
+      unsigned long long old = atomicCAS(keys + slot, (unsigned long long)kEmpty, (unsigned long long)k0);
+      if (old == kEmpty || old == k0) return slot;
+    }
+    slot = (slot + 1) & (cap - 1);
+  }
+  t.status[0] = 1;
+  return kNoSlot;
+}
+
 // linear-probing find-or-insert in the HBM table; returns slot or kNoSlot (overflow flag set)
 __device__ __forceinline__ uint64_t find_or_insert(const TableDesc& t, uint64_t k0, uint64_t k1)
 {
   const uint64_t cap = t.capacity;
-  if (t.key_words == 1) {
-    if (k0 == kEmpty) { t.status[2] = 1; return cap; }
-    uint64_t slot = hash_key(k0, 0, 1) & (cap - 1);
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(t.keys);
-    for (uint32_t probes = 0; probes < kMaxProbes; ++probes) {
-      unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(keys + slot);
-      if (cur == k0) return slot;
-      if (cur == kEmpty) {
-        unsigned long long old = atomicCAS(keys + slot, (unsigned long long)kEmpty, (unsigned long long)k0);
-        if (old == kEmpty || old == k0) return slot;
-      }
-      slot = (slot + 1) & (cap - 1);
-    }
-  } else {
+  if (t.key_words == 1) return find_or_insert_from(t, k0, hash_key(k0, 0, 1));
+  {
     if (k0 == kEmpty && k1 == kEmpty) { t.status[2] = 1; return cap; }
     uint64_t slot = hash_key(k0, k1, 2) & (cap - 1);
     for (uint32_t probes = 0; probes < kMaxProbes; ++probes) {

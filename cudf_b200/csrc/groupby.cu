@@ -967,6 +967,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
     memset(&mp, 0, sizeof mp);
     mp.region = peer->buffer + kPeerHeaderBytes + (size_t)parity * peer->region_bytes;
     mp.cap = cap; mp.key1_off = key1_off; mp.key_words = pl.key_words; mp.num_accs = (int)na; mp.world = world;
+    mp.slot_hash32 = pl.key_words == 1 && h->path == "bucketed";
     for (int r = 0; r < world; ++r) mp.prefix[r + 1] = mp.prefix[r] + got[r];
     mp.table = h->table;
     for (size_t a = 0; a < na; ++a) {

@@ -23,20 +23,6 @@
 
 namespace bgb {
 
-// Slot hash of this path. The table a bucketed call builds is read back only by compaction/emit (slot order is not
-// observable) and by this file's own overflow kernel, so the path is free to use a cheaper hash than hash_key(): the
-// SplitMix64 finaliser costs ~35 SASS instructions (two 64-bit multiplies) and was a quarter of the scatter kernel. Here:
-// Fibonacci product folded to 32 bits, then the murmur3 32-bit finaliser (11 instructions). 32 bits index any table this
-// path can build (capacity <= 2^32 slots).
-__device__ __forceinline__ uint32_t bucket_hash(uint64_t k)
-{
-  const uint64_t h = k * 0x9E3779B97F4A7C15ull;
-  uint32_t x = (uint32_t)(h >> 32) ^ (uint32_t)h;
-  x *= 0x85EBCA6Bu; x ^= x >> 13;
-  x *= 0xC2B2AE35u; x ^= x >> 16;
-  return x;
-}
-
 namespace {
 constexpr int kBThreads = 512;
 constexpr int kBCtasPerSm = 2;
@@ -136,7 +122,7 @@ __global__ void __launch_bounds__(kBThreads, kBCtasPerSm) bucket_scatter_kernel(
     uint32_t pid[kBRows], rank[kBRows];
 #pragma unroll
     for (int j = 0; j < kBRows; ++j) {
-      pid[j]  = ((bucket_hash(key[j]) & capmask) >> p.slot_shift) & pmask;
+      pid[j]  = ((slot_hash32(key[j]) & capmask) >> p.slot_shift) & pmask;
       rank[j] = 0;
       if ((keep >> j) & 1u) rank[j] = atomicAdd(&s_cnt[pid[j]], 1u);
     }
@@ -416,7 +402,7 @@ __global__ void __launch_bounds__(kAThreads, 3) bucket_aggregate_kernel(const __
           if (p.vb_width == 1) s_vb[r] = (uint8_t)vb; else reinterpret_cast<uint32_t*>(s_vb)[r] = vb;
         }
         if (p.key_in_low32) kq[j] &= 0xffffffffull;
-        lq[j] = bucket_hash(kq[j]) & smask;
+        lq[j] = slot_hash32(kq[j]) & smask;
       }
       uint32_t r = r0 + t, probes = 0;
       while (cnt > 0) {
@@ -578,7 +564,7 @@ __device__ __forceinline__ uint64_t find_or_insert_sliced(const TableDesc& t, ui
   const uint64_t cap = t.capacity;
   if (k0 == kEmpty) { t.status[2] = 1; return cap; }
   const uint64_t smask = (1ull << log2_slice) - 1;
-  uint64_t slot = bucket_hash(k0) & (cap - 1);
+  uint64_t slot = slot_hash32(k0) & (cap - 1);
   unsigned long long* keys = reinterpret_cast<unsigned long long*>(t.keys);
   for (uint64_t probes = 0; probes <= smask; ++probes) {
     unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(keys + slot);

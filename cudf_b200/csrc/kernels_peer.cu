@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(kThreads) peer_merge_kernel(const __grid_const
     // .cg loads: the records were written by another GPU, never through this SM's L1
     const uint64_t k0 = __ldcg(reinterpret_cast<const unsigned long long*>(p.region) + idx);
     const uint64_t k1 = p.key_words == 2 ? __ldcg(reinterpret_cast<const unsigned long long*>(p.region + p.key1_off) + idx) : 0;
-    const uint64_t slot = find_or_insert(p.table, k0, k1);
+    const uint64_t slot = p.slot_hash32 ? find_or_insert_from(p.table, k0, slot_hash32(k0)) : find_or_insert(p.table, k0, k1);
     if (slot == kNoSlot) continue;
 #pragma unroll 1
     for (int a = 0; a < p.num_accs; ++a) {

@@ -49,6 +49,8 @@ struct PeerMergeParams {
   const uint8_t* region;  // my region for this parity
   uint64_t cap, key1_off;
   int32_t key_words, num_accs, world;
+  int32_t slot_hash32;             // != 0 (one-word keys): the final table is indexed by slot_hash32(), the hash of the bucketed
+                                   // local path, so that records arriving in local slot order sweep the final table in order
   uint32_t prefix[kMaxPeers + 1];  // records received from sources [0, s)
   TableDesc table;                 // final table
   PeerAcc acc[kMaxAccs];
