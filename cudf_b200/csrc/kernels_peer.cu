@@ -145,12 +145,18 @@ __device__ __forceinline__ void merge_cell(uint8_t op, void* cells, uint64_t slo
 
 __global__ void __launch_bounds__(kThreads) peer_merge_kernel(const __grid_constant__ PeerMergeParams p)
 {
-  const uint32_t total  = p.prefix[p.world];
-  const uint32_t stride = gridDim.x * kThreads;
-  for (uint32_t i = blockIdx.x * kThreads + threadIdx.x; i < total; i += stride) {
-    int src = 0;
-    while (i >= p.prefix[src + 1]) ++src;
-    const uint64_t idx = (uint64_t)src * p.cap + (i - p.prefix[src]);
+  // Sources are walked in LOCKSTEP, 32 records of one source per warp: every source wrote its records in the slot order of
+  // its local table, and the final table is indexed by the same hash, so all sources sweep the final table together and the
+  // world records of one group meet in L2 (source-by-source order re-read every table sector from HBM world times).
+  uint32_t longest = 0;
+  for (int r = 0; r < p.world; ++r) { const uint32_t c = p.prefix[r + 1] - p.prefix[r]; longest = c > longest ? c : longest; }
+  const uint64_t chunks = ((uint64_t)longest + 31) / 32 * (uint32_t)p.world;   // (chunk, source) pairs
+  const uint64_t warps  = (uint64_t)gridDim.x * (kThreads / 32);
+  for (uint64_t w = (uint64_t)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5); w < chunks; w += warps) {
+    const int src    = (int)(w % (uint32_t)p.world);
+    const uint32_t j = (uint32_t)(w / (uint32_t)p.world) * 32 + (threadIdx.x & 31);
+    if (j >= p.prefix[src + 1] - p.prefix[src]) continue;
+    const uint64_t idx = (uint64_t)src * p.cap + j;
     // .cg loads: the records were written by another GPU, never through this SM's L1
     const uint64_t k0 = __ldcg(reinterpret_cast<const unsigned long long*>(p.region) + idx);
     const uint64_t k1 = p.key_words == 2 ? __ldcg(reinterpret_cast<const unsigned long long*>(p.region + p.key1_off) + idx) : 0;
