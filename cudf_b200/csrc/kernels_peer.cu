@@ -29,7 +29,7 @@ __device__ __forceinline__ uint64_t global_timer_ns()
 constexpr int kSRows = 8;
 constexpr int kSTile = kThreads * kSRows;
 
-__global__ void __launch_bounds__(kThreads) peer_scatter_kernel(const __grid_constant__ PeerScatterParams p)
+__global__ void __launch_bounds__(kThreads) peer_scatter_kernel(const __grid_constant__ PeerScatterParams p, const uint32_t tile_rows)
 {
   __shared__ uint32_t s_cnt[kMaxPeers], s_off[kMaxPeers], s_base[kMaxPeers];
   __shared__ uint64_t stage[kSTile];
@@ -37,12 +37,13 @@ __global__ void __launch_bounds__(kThreads) peer_scatter_kernel(const __grid_con
   __shared__ uint8_t s_own[kSTile];
   const int64_t G  = p.num_groups;
   const uint32_t t = threadIdx.x;
-  for (int64_t tile = (int64_t)blockIdx.x * kSTile; tile < G; tile += (int64_t)gridDim.x * kSTile) {
+  // tile_rows <= kSTile: few groups are spread over many small tiles so that every SM has work (latency-bound exchange)
+  for (int64_t tile = (int64_t)blockIdx.x * tile_rows; tile < G; tile += (int64_t)gridDim.x * tile_rows) {
     if (t < (uint32_t)p.world) s_cnt[t] = 0;
     __syncthreads();
     uint32_t slot[kSRows], orank[kSRows];  // owner | rank << 8
     uint64_t k0[kSRows];
-    const uint32_t nrec = G - tile < (int64_t)kSTile ? (uint32_t)(G - tile) : (uint32_t)kSTile;
+    const uint32_t nrec = G - tile < (int64_t)tile_rows ? (uint32_t)(G - tile) : tile_rows;
 #pragma unroll
     for (int j = 0; j < kSRows; ++j) {
       const uint32_t r = j * kThreads + t;
@@ -130,9 +131,11 @@ __global__ void __launch_bounds__(kThreads) peer_scatter_kernel(const __grid_con
 cudaError_t launch_peer_scatter(const PeerScatterParams& p, cudaStream_t s)
 {
   if (p.num_groups <= 0) return cudaSuccess;
-  int64_t blocks = ((int64_t)p.num_groups + kSTile - 1) / kSTile;
+  uint32_t tile_rows = kSTile;
+  while (tile_rows > (uint32_t)kThreads && (int64_t)p.num_groups < 148ll * 2 * tile_rows) tile_rows /= 2;
+  int64_t blocks = ((int64_t)p.num_groups + tile_rows - 1) / tile_rows;
   if (blocks > 148 * 6) blocks = 148 * 6;
-  peer_scatter_kernel<<<(int)blocks, kThreads, 0, s>>>(p);
+  peer_scatter_kernel<<<(int)blocks, kThreads, 0, s>>>(p, tile_rows);
   return note_launch();
 }
 
