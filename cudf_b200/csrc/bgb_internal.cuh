@@ -37,12 +37,15 @@ enum AccOp : uint8_t {
   ACC_COUNT_VALID,
   ACC_COUNT_ALL,
   ACC_ARGMIN,     // (ordered value image << 32 | row) for <= 32-bit sources
-  ACC_ARGMAX
+  ACC_ARGMAX,
+  ACC_ARGROW_MIN, // ARGMIN / ARGMAX of 64-bit values: a 4-byte row-number cell filled by a SECOND pass over the rows once the
+  ACC_ARGROW_MAX  // group's MIN / MAX cell (AccDesc::aux) is final: smallest row whose value equals the extremum
 };
 
 __host__ __device__ inline int acc_cell_bytes(uint8_t op)
 {
-  return (op == ACC_SUM_F32 || op == ACC_SUMSQ_F32 || op == ACC_PROD_F32 || op == ACC_COUNT_VALID || op == ACC_COUNT_ALL) ? 4 : 8;
+  return (op == ACC_SUM_F32 || op == ACC_SUMSQ_F32 || op == ACC_PROD_F32 || op == ACC_COUNT_VALID || op == ACC_COUNT_ALL ||
+          op == ACC_ARGROW_MIN || op == ACC_ARGROW_MAX) ? 4 : 8;
 }
 
 struct KeyColDesc {
@@ -64,6 +67,7 @@ struct AccDesc {
   uint8_t byte_mask;      // mask points at one validity BYTE per row (partitioned copies) instead of a bitmask
   uint8_t pad;
   void* cells;            // capacity+1 cells
+  const void* aux;        // ACC_ARGROW_*: the MIN / MAX cells of the same value column
 };
 
 struct TableDesc {
@@ -146,6 +150,8 @@ __host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t seed, uint64_t 
 // host-side API of the kernel translation units
 cudaError_t launch_init_table(const AggParams& p, cudaStream_t s);
 cudaError_t launch_aggregate_global(const AggParams& p, cudaStream_t s);
+// second pass for ACC_ARGROW_* accumulators (after every row has been aggregated)
+cudaError_t launch_argrow(const AggParams& p, cudaStream_t s);
 cudaError_t launch_estimate_cardinality(const AggParams& p, int64_t sample_rows, uint64_t* scratch_set, uint64_t set_capacity,
                                         uint32_t* out_distinct /* 8 words */, uint64_t key_flip, cudaStream_t s);
 // compaction: fills group_slots[] with occupied slot ids (arbitrary order), status[1] = count

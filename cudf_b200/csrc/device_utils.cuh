@@ -294,6 +294,9 @@ __device__ __forceinline__ uint64_t acc_identity64(uint8_t op)
     default: return 0ull;  // sums, MAX (smallest ordered image), ARGMAX
   }
 }
-__device__ __forceinline__ uint32_t acc_identity32(uint8_t op) { return op == ACC_PROD_F32 ? 0x3f800000u : 0u; }
+__device__ __forceinline__ uint32_t acc_identity32(uint8_t op)
+{
+  return op == ACC_PROD_F32 ? 0x3f800000u : (op == ACC_ARGROW_MIN || op == ACC_ARGROW_MAX) ? 0xFFFFFFFFu : 0u;
+}
 
 }  // namespace bgb

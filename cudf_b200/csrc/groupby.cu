@@ -104,6 +104,7 @@ void fill_agg_params(const bgb_groupby& h, AggParams& p, size_t acc_begin, size_
     } else { d.data = nullptr; d.mask = nullptr; d.offset = 0; d.src = S_I32; }
     d.op    = ap.op;
     d.cells = ap.cells;
+    d.aux   = ap.aux_acc >= 0 ? pl.accs[ap.aux_acc].cells : nullptr;
   }
   p.table = h.table;
 }
@@ -132,7 +133,7 @@ int run_partitioned(bgb_groupby* h, int num_sms, bool& done)
   const int64_t N = pl.num_rows;
   if (pl.values.size() > (size_t)kMaxPartValues || N >= (1ll << 31)) return BGB_OK;
   for (const AccPlan& a : pl.accs)
-    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX) return BGB_OK;  // the partition-ordered copy loses the row numbers ARG* report
+    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX || a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX) return BGB_OK;  // the partition-ordered copy loses the row numbers ARG* report
   cudaStream_t s = h->stream;
   // partitions: table region of capacity/P slots (keys + all cells) around 16 MB, P in [16, 4096]
   size_t slot_bytes = 8 * (size_t)pl.key_words;
@@ -239,7 +240,7 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool& done
   auto mode_bytes = [](uint8_t m) -> size_t { return m == BM_COUNT ? 4 : m == BM_LIMBS ? 12 : m == BM_MINMAX ? 8 : 0; };
   size_t slot_bytes = 8;
   for (const AccPlan& a : pl.accs) {
-    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX) return BGB_OK;  // row numbers are lost by the scatter
+    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX || a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX) return BGB_OK;  // row numbers are lost by the scatter
     slot_bytes += mode_bytes(acc_mode(a.op));
   }
   int log2cap = 0; while ((1ull << log2cap) < h->table.capacity) ++log2cap;
@@ -545,6 +546,17 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
         FAIL_RC(check_cuda(launch_aggregate_global(p, s), "aggregate_global"));
       }
       h->prof.end();
+      bool argrow = false;
+      for (const AccPlan& a : pl.accs) argrow |= a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX;
+      if (argrow) {  // ARGMIN / ARGMAX of 64-bit values: the extrema are final now, find their rows
+        h->prof.begin("argrow");
+        for (size_t b = 0; b == 0 || b < na; b += kMaxAccs) {
+          AggParams p;
+          fill_agg_params(*h, p, b, std::min(na, b + kMaxAccs));
+          FAIL_RC(check_cuda(launch_argrow(p, s), "argrow"));
+        }
+        h->prof.end();
+      }
       path = "global";
     }
     h->path = path;
@@ -847,7 +859,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
     if (rc_ != BGB_OK) { h->free_all(); delete h; return rc_; } \
   } while (0)
   for (const AccPlan& a : pl.accs)
-    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX) FAIL_RC(set_error(BGB_UNSUPPORTED, "ARGMIN/ARGMAX have no cross-rank merge (row numbers are rank-local)"));
+    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX || a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX) FAIL_RC(set_error(BGB_UNSUPPORTED, "ARGMIN/ARGMAX have no cross-rank merge (row numbers are rank-local)"));
   if (pl.accs.size() > (size_t)kMaxAccs) FAIL_RC(set_error(BGB_UNSUPPORTED, "more than %d accumulators in one peer exchange", kMaxAccs));
 
   const int world = peer->world, me = peer->rank;

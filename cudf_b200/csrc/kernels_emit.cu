@@ -158,8 +158,10 @@ __global__ void __launch_bounds__(256) emit_kernel(const __grid_constant__ EmitP
         case OUT_MINMAX: bits = ordered_decode(reinterpret_cast<const uint64_t*>(d.a)[slot], d.src); valid = n > 0; break;
         case OUT_COUNT: bits = (uint32_t)reinterpret_cast<const int32_t*>(d.a)[slot]; break;
         case OUT_ARG: {
-          uint32_t lo = (uint32_t)reinterpret_cast<const uint64_t*>(d.a)[slot];
+          const bool rowcell = d.acc_op == ACC_ARGROW_MIN || d.acc_op == ACC_ARGROW_MAX;  // 64-bit values: the cell IS the row
+          uint32_t lo = rowcell ? reinterpret_cast<const uint32_t*>(d.a)[slot] : (uint32_t)reinterpret_cast<const uint64_t*>(d.a)[slot];
           valid       = n > 0;
+          if (rowcell) { bits = valid ? lo : 0xFFFFFFFFu; break; }
           bits        = !valid ? 0xFFFFFFFFu : (d.acc_op == ACC_ARGMAX ? 0xFFFFFFFFu - lo : lo);
           break;
         }

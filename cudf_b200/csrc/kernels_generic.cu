@@ -79,6 +79,39 @@ cudaError_t launch_aggregate_global(const AggParams& p, cudaStream_t s)
   return note_launch();
 }
 
+// ------------------------------------------------------------------ ARGMIN / ARGMAX of 64-bit values, second pass
+// The reference keeps a row index per group and CAS-loops on it while comparing the values it points at
+// (/root/reference/cpp/include/cudf/detail/aggregation/device_aggregators.cuh:131-160). Here the group's MIN / MAX cell is
+// already final when this kernel runs, so a row only has to compare its own value with it: equal -> atomicMin of the row
+// number (ties resolve to the smallest row, like the packed cells of the <= 32-bit case).
+__global__ void __launch_bounds__(256) argrow_kernel(const __grid_constant__ AggParams p)
+{
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < p.num_rows; row += stride) {
+    uint64_t k0, k1;
+    if (!pack_key(p, row, k0, k1)) continue;
+    const uint64_t slot = find_or_insert(p.table, k0, k1);  // the key is there: pure lookup
+    if (slot == kNoSlot) return;
+#pragma unroll 1
+    for (int a = 0; a < p.num_accs; ++a) {
+      const AccDesc& d = p.acc[a];
+      if (d.op != ACC_ARGROW_MIN && d.op != ACC_ARGROW_MAX) continue;
+      const int64_t idx = (int64_t)d.offset + row;
+      if (d.mask != nullptr && !bit_is_set(d.mask, idx)) continue;
+      const uint64_t img = ordered_image(load_raw(d.data, src_width(d.src), idx), d.src);
+      if (img == reinterpret_cast<const uint64_t*>(d.aux)[slot]) atomicMin(reinterpret_cast<unsigned int*>(d.cells) + slot, (unsigned int)row);
+    }
+  }
+}
+
+cudaError_t launch_argrow(const AggParams& p, cudaStream_t s)
+{
+  if (p.num_rows == 0) return cudaSuccess;
+  int64_t want = (p.num_rows + 255) / 256;
+  argrow_kernel<<<(int)(want < 148 * 8 ? want : 148 * 8), 256, 0, s>>>(p);
+  return note_launch();
+}
+
 // ------------------------------------------------------------------ cardinality estimator
 // Inserts the packed keys of `sample_rows` evenly spaced rows into a scratch set; out[0] = distinct, out[1] = sampled
 // rows that were not skipped. Only a regime hint: correctness never depends on it (overflow -> host retries bigger).

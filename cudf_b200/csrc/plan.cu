@@ -211,7 +211,14 @@ int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_nul
         case BGB_COUNT_VALID: o.acc_op = ACC_COUNT_VALID; o.acc_a = need_cnt(); o.op = OUT_COUNT; o.nullable = false; break;
         case BGB_COUNT_ALL: o.acc_op = ACC_COUNT_ALL; o.acc_a = get_acc(plan, -1, ACC_COUNT_ALL); o.op = OUT_COUNT; o.nullable = false; break;
         case BGB_ARGMIN: case BGB_ARGMAX:
-          if (type_width(rq.values.type_id) > 4) return set_error(BGB_UNSUPPORTED, "ARGMIN/ARGMAX of 64-bit values not served by the hash path yet");
+          if (type_width(rq.values.type_id) > 4) {
+            // 64-bit values do not fit a packed (value, row) cell: MIN / MAX first, then a second pass over the rows records
+            // the smallest row whose value equals the group's extremum (kernels_generic.cu: argrow_kernel)
+            const int ext = get_acc(plan, vc, kind == BGB_ARGMIN ? ACC_MIN : ACC_MAX);
+            o.acc_op = kind == BGB_ARGMIN ? ACC_ARGROW_MIN : ACC_ARGROW_MAX; o.acc_a = get_acc(plan, vc, o.acc_op); o.op = OUT_ARG;
+            plan.accs[o.acc_a].aux_acc = ext;
+            break;
+          }
           o.acc_op = kind == BGB_ARGMIN ? ACC_ARGMIN : ACC_ARGMAX; o.acc_a = get_acc(plan, vc, o.acc_op); o.op = OUT_ARG; break;
         case BGB_MEAN:
           // MEAN -> SUM + COUNT_VALID (extract_single_pass_aggs.cpp:62-73), finalised as double(sum)/count

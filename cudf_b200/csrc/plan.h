@@ -30,6 +30,7 @@ struct AccPlan {
   int value_col;    // index into values, -1 for COUNT_ALL
   uint8_t op;
   void* cells = nullptr;
+  int aux_acc = -1;  // ACC_ARGROW_*: index of the MIN / MAX accumulator it reads in the second pass
 };
 
 struct OutPlan {

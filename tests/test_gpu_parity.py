@@ -198,3 +198,21 @@ def test_sliced_columns_offsets():
     np.testing.assert_array_equal(kk[o], ko[0][0])
     np.testing.assert_array_equal(res[0].columns()[0].to_numpy()[0][o], ao[0][0])
     np.testing.assert_array_equal(res[0].columns()[1].to_numpy()[0][o], ao[1][0])
+
+
+@pytest.mark.parametrize("vtype", ["int64", "uint64", "float64"])
+def test_argmin_argmax_of_64bit_values(vtype):
+    # 64-bit values take the two-pass form (MIN / MAX first, then the smallest row holding the extremum); ties, nulls and an
+    # all-null group included. The reference serves these through its index CAS loop (device_aggregators.cuh:131-160).
+    rng = np.random.default_rng(77)
+    n = 150_000
+    k = orc.HostColumn(rng.integers(0, 5_000, n).astype(np.int64))
+    raw = rng.integers(-40, 40, n) if vtype != "uint64" else rng.integers(0, 80, n)  # few distinct values: many ties
+    valid = rng.random(n) > 0.15
+    valid[k.data == 7] = False  # a group without any valid value -> null result
+    v = orc.HostColumn(raw.astype(vtype), valid)
+    G, path = gpu_util.compare_with_oracle([k], [v], [(0, "argmin", 1), (0, "argmax", 1), (0, "min", 1), (0, "max", 1), (0, "sum", 1)],
+                                           name=f"arg64/{vtype}")
+    assert path == "global", path
+    w = orc.HostColumn(rng.permutation(n).astype(vtype))  # no nulls, no ties
+    gpu_util.compare_with_oracle([k], [w], [(0, "argmax", 1), (0, "argmin", 1)], name=f"arg64/{vtype}/unique")
