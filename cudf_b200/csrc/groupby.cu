@@ -222,7 +222,7 @@ int run_partitioned(bgb_groupby* h, int num_sms, bool& done)
 // Bucketed high-cardinality path (kernels_bucket.cu): one or two scatter levels into fixed-capacity buckets, one per
 // shared-memory-sized table slice, then a slice kernel that never touches the HBM table with atomics. `h->table` and the
 // accumulator cells are allocated (NOT initialised: every slice is stored whole). done=false when the plan does not fit.
-int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool& done)
+int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool one_level_only, bool& done)
 {
   done = false;
   Plan& pl = h->plan;
@@ -254,23 +254,43 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool& done
   const int vbw   = (nvb == 0 || in_low32) ? 0 : (nvb <= 8 ? 1 : 4);  // separate validity column between the levels
   const int vbw_s = nvb == 0 ? 0 : (nvb <= 8 ? 1 : 4);                // validity word per row in shared memory
   auto round16 = [](uint64_t x) { return (x + 15) & ~15ull; };
-  // rows a bucket of the LAST level can hold: expected rows + 12.5 % (one level) or + 27 % (two levels) + slack
-  auto last_capacity = [&](int bits) { return round16(bits <= 8 ? (uint64_t)((double)N / (double)(1u << bits) * 1.125) + 1024 : (uint64_t)((double)N / (double)(1u << bits) * 1.27) + 256); };
-  // shared memory of one bucket CTA: the slice + a 16-bit slot and the validity word of every row. Three CTAs per SM
-  // (<= 72 KB each) unless opt.bucket_slice_log2 fixes the slice (tests force several levels on small inputs); a bucket
-  // stays below 65536 rows (16-bit digits in 32-bit counters) and a slice below 65535 slots (16-bit slot numbers).
-  auto cta_bytes = [&](int ls_) { const uint64_t C = last_capacity(log2cap - ls_); return ((uint64_t)slot_bytes << ls_) + round16(C * 2) + round16(C * vbw_s); };
+  // rows a bucket of the LAST level can hold: expected rows + 25 % (one level) or + 27 % (two levels) + slack
+  constexpr int kOneLevelBits = 9;      // up to 512 buckets from one scatter level
+  constexpr uint64_t kChunkMax = 16384; // rows of a bucket whose slot numbers are held in shared memory at a time
+  auto last_capacity = [&](int bits) { return round16(bits <= kOneLevelBits ? (uint64_t)((double)N / (double)(1u << bits) * 1.25) + 1024 : (uint64_t)((double)N / (double)(1u << bits) * 1.27) + 256); };
+  int n_limbs = 0;
+  for (const AccPlan& a : pl.accs) n_limbs += acc_mode(a.op) == BM_LIMBS;
+  // long buckets (mid cardinalities: few slices, many rows each) are walked in chunks and fold their 16-bit digit sums into
+  // a 64-bit total (8 more bytes per slot and integer-sum accumulator) before 65536 addends have gone into them
+  auto long_bucket = [&](int bits) { return last_capacity(bits) > 60000; };
+  // shared memory of one bucket CTA: the slice + a 16-bit slot and the validity word of every row of a chunk. Three CTAs per SM
+  // (<= 72 KB each), or two (<= 108 KB) when that is what lets ONE scatter level reach the slices; opt.bucket_slice_log2
+  // fixes the slice instead (tests force several levels on small inputs). A slice has < 65535 slots (16-bit slot numbers).
+  auto cta_bytes = [&](int ls_) {
+    const int bits   = log2cap - ls_;
+    const uint64_t C = std::min<uint64_t>(last_capacity(bits), kChunkMax);
+    return ((uint64_t)(slot_bytes + (long_bucket(bits) ? 8 * n_limbs : 0)) << ls_) + round16(C * 2) + round16(C * vbw_s);
+  };
+  auto best_slice = [&](uint64_t budget) {
+    for (int c = std::min(15, log2cap - 1); c >= 4 && log2cap - c <= 18; --c)
+      if (cta_bytes(c) <= budget) return c;
+    return -1;
+  };
   int ls = -1;
   if (opt.bucket_slice_log2 > 0) {
     ls = std::min(opt.bucket_slice_log2, log2cap - 1);
-    if (ls < 4 || ls > 15 || log2cap - ls > 18 || cta_bytes(ls) > 200 * 1024 || last_capacity(log2cap - ls) > 65535) return BGB_OK;
+    if (ls < 4 || ls > 15 || log2cap - ls > 18 || cta_bytes(ls) > 200 * 1024) return BGB_OK;
   } else {
-    for (int c = std::min(15, log2cap - 1); c >= 4 && log2cap - c <= 18; --c)
-      if (cta_bytes(c) <= 72 * 1024 && last_capacity(log2cap - c) <= 65535) { ls = c; break; }
+    ls = best_slice(72 * 1024);
+    if (ls < 0 || log2cap - ls > kOneLevelBits) {
+      const int l2 = best_slice(108 * 1024);
+      if (l2 >= 0 && log2cap - l2 <= kOneLevelBits) ls = l2;
+    }
     if (ls < 0) return BGB_OK;
   }
   const int b  = log2cap - ls;
-  const int b1 = b <= 8 ? b : (b + 1) / 2, b2 = b - b1;
+  if (one_level_only && b > kOneLevelBits) return BGB_OK;
+  const int b1 = b <= kOneLevelBits ? b : (b + 1) / 2, b2 = b - b1;
   const uint32_t P1 = 1u << b1, NB = 1u << b;
   cudaStream_t s = h->stream;
 
@@ -324,13 +344,14 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool& done
       if ((pass == 0) != (mode == BM_MINMAX)) continue;
       BucketAcc& d = ap.acc[a];
       d.cells = acc.cells; d.op = acc.op; d.mode = mode; d.smem_off = off;
-      off += (uint32_t)(mode_bytes(mode) << ls);
+      off += (uint32_t)((mode_bytes(mode) + (mode == BM_LIMBS && long_bucket(b) ? 8 : 0)) << ls);
       if (acc.value_col >= 0) { d.data = LF.val[acc.value_col]; d.src = pl.values[acc.value_col].src; d.vbit = (int16_t)vbit[acc.value_col]; }
       else { d.data = nullptr; d.src = S_I32; d.vbit = -1; }
     }
-  const uint64_t CL = b2 ? C2 : C1;
+  const uint64_t CL = std::min<uint64_t>(b2 ? C2 : C1, kChunkMax);  // rows per chunk
   ap.loc_off = off; off += (uint32_t)round16(CL * 2);
   ap.vb_off = off; ap.vb_width = vbw_s; off += (uint32_t)round16(CL * vbw_s);
+  ap.chunk_rows = (uint32_t)CL; ap.limb_total = long_bucket(b);
   const size_t slice_smem = off;
   rc = check_cuda(launch_bucket_init_reserved(ap, s), "bucket_init_reserved");
 
@@ -520,8 +541,14 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
       for (const AccPlan& a : pl.accs) slot_bytes += acc_cell_bytes(a.op);
       // the table will not stay in L2: partition first (measured 3-5x faster than random HBM atomics at 1e8 groups)
       const bool big = (double)capacity * slot_bytes > 96e6 && N >= (1 << 22);
-      if ((opt.force_path == 7 || (opt.force_path == 0 && big)) && !no_bucket) {
-        FAIL_RC(run_bucketed(h, num_sms, opt, done));
+      // Mid cardinalities (past the shared-memory table, table still L2-sized) stay on the generic kernel: ONE scatter level +
+      // slices was measured SLOWER there (1e9 rows: 32 / 27 / 24 ms at 3e4 / 1e5 / 3e5 groups against 19-20 ms, profiles/
+      // r01_card_sweep_A9_mid.txt) -- with 64-512 buckets and one CTA per bucket most of the 444 CTA slots stay empty. It would
+      // need several CTAs per bucket and a keyed merge of their partial slices; BGB_BUCKET_MID=1 enables it for experiments.
+      static const bool mid_on = getenv("BGB_BUCKET_MID") != nullptr;
+      const bool mid = mid_on && !big && N >= (1 << 24) && capacity >= (1u << 16);
+      if ((opt.force_path == 7 || (opt.force_path == 0 && (big || mid))) && !no_bucket) {
+        FAIL_RC(run_bucketed(h, num_sms, opt, /*one_level_only=*/opt.force_path == 0 && !big, done));
         if (done) path = "bucketed";
       }
       if (!done && (opt.force_path == 3 || opt.force_path == 7 || big)) {

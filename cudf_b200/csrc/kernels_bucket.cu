@@ -353,9 +353,9 @@ __global__ void __launch_bounds__(kAThreads, 3) bucket_aggregate_kernel(const __
   uint8_t* s_vb        = smem_raw + p.vb_off;                                 // validity word of every row (1 or 4 bytes)
 
   for (uint32_t fb = blockIdx.x; fb < p.num_buckets; fb += gridDim.x) {
-    uint32_t n = __ldg(p.cursor + fb);
-    n = n < p.bucket_capacity ? n : p.bucket_capacity;
-    const int64_t base = (int64_t)fb * p.bucket_capacity;
+    uint32_t ntot = __ldg(p.cursor + fb);
+    ntot = ntot < p.bucket_capacity ? ntot : p.bucket_capacity;
+    const int64_t base0 = (int64_t)fb * p.bucket_capacity;
 
     // ---- EMPTY keys + identity cells (shared-memory accumulators here, BM_GLOBAL ones in the bucket's slice of the HBM table)
     for (uint32_t i = t; i < S / 2; i += kAThreads) reinterpret_cast<uint4*>(s_keys)[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
@@ -374,11 +374,18 @@ __global__ void __launch_bounds__(kAThreads, 3) bucket_aggregate_kernel(const __
         for (uint32_t i = t; i < S / 2; i += kAThreads) c[i] = make_ulonglong2(id, id);
       } else {
         uint4* c = reinterpret_cast<uint4*>(smem_raw + acc.smem_off);
-        const uint32_t words = acc.mode == BM_LIMBS ? 3 * S : S;
+        const uint32_t words = acc.mode == BM_LIMBS ? (p.limb_total ? 5 * S : 3 * S) : S;  // digit sums (+ the 64-bit running total)
         for (uint32_t i = t; i < words / 4; i += kAThreads) c[i] = make_uint4(0, 0, 0, 0);
       }
     }
     __syncthreads();
+
+    // A bucket is walked in chunks of chunk_rows rows (the 16-bit slot numbers of one chunk live in shared memory); the
+    // high-cardinality shapes have one chunk per bucket, mid cardinalities (few, long buckets) many.
+    uint32_t since_fold = 0;
+    for (uint32_t c0 = 0; c0 < ntot; c0 += p.chunk_rows) {
+    const uint32_t n   = ntot - c0 < p.chunk_rows ? ntot - c0 : p.chunk_rows;
+    const int64_t base = base0 + c0;
 
     // ---- phase 1: key -> slot of the slice for every row (LDS probe, ATOMS.CAS only on the first row of a group).
     // A lane walks its kARows rows as ONE loop (a probe step per iteration, next row when the slot is found): the warp runs
@@ -517,6 +524,23 @@ __global__ void __launch_bounds__(kAThreads, 3) bucket_aggregate_kernel(const __
       }
     }
     __syncthreads();
+    // the digit sums hold < 65536 addends each: fold them into the 64-bit totals before the next chunk could pass that
+    since_fold += n;
+    if (p.limb_total && c0 + n < ntot && since_fold + p.chunk_rows > 65535u) {
+#pragma unroll 1
+      for (int a = 0; a < p.num_accs; ++a) {
+        if (p.acc[a].mode != BM_LIMBS) continue;
+        uint32_t* c   = reinterpret_cast<uint32_t*>(smem_raw + p.acc[a].smem_off);
+        uint64_t* tot = reinterpret_cast<uint64_t*>(c + 3 * S);
+        for (uint32_t l = t; l < S; l += kAThreads) {
+          tot[l] += (uint64_t)(int64_t)(int32_t)c[l] + ((uint64_t)(int64_t)(int32_t)c[S + l] << 16) + ((uint64_t)c[2 * S + l] << 32);
+          c[l] = 0; c[S + l] = 0; c[2 * S + l] = 0;
+        }
+      }
+      since_fold = 0;
+      __syncthreads();
+    }
+    }  // chunks
 
     // ---- the finished slice -> HBM, 16 bytes per thread
     {
@@ -536,6 +560,7 @@ __global__ void __launch_bounds__(kAThreads, 3) bucket_aggregate_kernel(const __
             for (int h = 0; h < 2; ++h) {
               const uint32_t l = 2 * i + h;
               o[h] = (uint64_t)(int64_t)(int32_t)c[l] + ((uint64_t)(int64_t)(int32_t)c[S + l] << 16) + ((uint64_t)c[2 * S + l] << 32);
+              if (p.limb_total) o[h] += reinterpret_cast<const uint64_t*>(c + 3 * S)[l];
             }
             reinterpret_cast<ulonglong2*>(g)[i] = make_ulonglong2(o[0], o[1]);
           }

@@ -52,8 +52,9 @@ struct BucketScatterParams {
 enum BucketAccMode : uint8_t {
   BM_COUNT,    // u32 cell in shared memory
   BM_LIMBS,    // integer SUM / SUM_OF_SQUARES: three u32 arrays in shared memory holding the balanced 16-bit digits d0, d1 and
-               // the rest r2 of every addend (v = d0 + 2^16 d1 + 2^32 r2); a bucket has < 65536 rows, so no digit sum leaves
-               // 32 bits and sum mod 2^64 = s0 + 2^16 s1 + 2^32 s2 exactly, without carries between the arrays
+               // the rest r2 of every addend (v = d0 + 2^16 d1 + 2^32 r2); fewer than 65536 addends go into a digit sum before
+               // it is folded (one fold per bucket, or one every ~64K rows of a long bucket into a 64-bit total), so no digit
+               // sum leaves 32 bits and sum mod 2^64 = s0 + 2^16 s1 + 2^32 s2 exactly, without carries between the arrays
   BM_MINMAX,   // u64 ordered image in shared memory: plain load first, CAS loop only when the row improves the extremum
   BM_GLOBAL    // RED on the slice in the HBM table (float / double sums and sums of squares, products)
 };
@@ -80,6 +81,8 @@ struct BucketAggParams {
   uint32_t loc_off;          // shared memory: 16-bit slot of every row of the bucket (bucket_capacity entries)
   uint32_t vb_off;           // shared memory: validity word of every row (vb_width bytes each; only when some accumulator needs it)
   int32_t vb_width;          // 0: no masked value column
+  uint32_t chunk_rows;       // rows of a bucket processed per pass (= entries of the slot / validity arrays above)
+  int32_t limb_total;        // buckets may exceed 65535 rows: BM_LIMBS accumulators carry a 64-bit total behind their digit sums
   int32_t num_accs;
   // overflow pass: rows [ov_base, ov_base + min(*ov_cursor, ov_capacity)) through the HBM table
   const uint32_t* ov_cursor;

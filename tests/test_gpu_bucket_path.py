@@ -139,3 +139,19 @@ def test_automatic_choice_takes_the_bucketed_path_for_large_tables():
     G, path = gpu_util.compare_with_oracle([H(k)], [H(v)], [(0, "sum", 1), (0, "count_valid", 1)], name="auto")
     assert path == "bucketed", path
     assert G == len(np.unique(k))
+
+
+def test_long_buckets_are_walked_in_chunks():
+    # mid cardinality: few slices with > 65535 rows each -> chunks of 16384 rows, digit sums folded into 64-bit totals
+    rng = np.random.default_rng(9)
+    n, g = 6_000_000, 20_000
+    k = rng.integers(0, g, n).astype(np.int64)
+    v = rng.integers(-(1 << 40), 1 << 40, n).astype(np.int64)          # all three digit arrays in use
+    w = rng.integers(-30_000, 30_000, n).astype(np.int32)
+    x = H(rng.integers(0, 1000, n).astype(np.float64), rng.random(n) > 0.1)
+    aggs = [(0, "sum", 1), (0, "count_valid", 1), (0, "min", 1), (1, "sum_of_squares", 1), (1, "sum", 1), (2, "sum", 1), (2, "max", 1), (2, "mean", 1)]
+    _check([H(k)], [H(v), H(w), x], aggs, name="long buckets", capacity_log2=16, slice_log2=10)
+    # the same rows with every value at the extreme of its digit: 65535+ addends of -32768 / 32767 per group and digit
+    k2 = (np.arange(n) % 8).astype(np.int64)
+    v2 = np.where(np.arange(n) % 2 == 0, np.int64(-32768), np.int64(32767)).astype(np.int64) * np.int64(65537)
+    _check([H(k2)], [H(v2)], [(0, "sum", 1), (0, "count_valid", 1)], name="digit extremes", capacity_log2=12, slice_log2=8, expect=None)
