@@ -256,7 +256,9 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool one_l
   auto round16 = [](uint64_t x) { return (x + 15) & ~15ull; };
   // rows a bucket of the LAST level can hold: expected rows + 25 % (one level) or + 27 % (two levels) + slack
   constexpr int kOneLevelBits = 9;      // up to 512 buckets from one scatter level
-  constexpr uint64_t kChunkMax = 16384; // rows of a bucket whose slot numbers are held in shared memory at a time
+  static const uint64_t chunk_env = getenv("BGB_BUCKET_CHUNK") ? (uint64_t)atoll(getenv("BGB_BUCKET_CHUNK")) : 0;  // experiments
+  static const int slice_env = getenv("BGB_BUCKET_SLICE_LOG2") ? atoi(getenv("BGB_BUCKET_SLICE_LOG2")) : 0;
+  const uint64_t kChunkMax = chunk_env ? chunk_env : 16384; // rows of a bucket whose slot numbers are held in shared memory at a time
   auto last_capacity = [&](int bits) { return round16(bits <= kOneLevelBits ? (uint64_t)((double)N / (double)(1u << bits) * 1.25) + 1024 : (uint64_t)((double)N / (double)(1u << bits) * 1.27) + 256); };
   int n_limbs = 0;
   for (const AccPlan& a : pl.accs) n_limbs += acc_mode(a.op) == BM_LIMBS;
@@ -277,8 +279,8 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool one_l
     return -1;
   };
   int ls = -1;
-  if (opt.bucket_slice_log2 > 0) {
-    ls = std::min(opt.bucket_slice_log2, log2cap - 1);
+  if (opt.bucket_slice_log2 > 0 || slice_env > 0) {
+    ls = std::min(opt.bucket_slice_log2 > 0 ? opt.bucket_slice_log2 : slice_env, log2cap - 1);
     if (ls < 4 || ls > 15 || log2cap - ls > 18 || cta_bytes(ls) > 200 * 1024) return BGB_OK;
   } else {
     ls = best_slice(72 * 1024);
