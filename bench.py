@@ -43,6 +43,7 @@ WORKLOADS = {
     "A9": (1_000_000_000, 10_000, "single int64 key SUM/COUNT, 1e9 rows (north_star target shape)"),
     "B": (1_000_000_000, 100_000_000, "int32 key SUM/MIN/MAX float64 with 10% nulls, 1e9 rows, 1e8 groups (configs[2])"),
     "Q1": (600_000_000, 4, "TPC-H Q1-style two int8 keys MEAN/VAR/COUNT over 6e8 rows (configs[3])"),
+    "C1": (10_000_000, 1024, "df.groupby(['A','B']).mean(): two int64 keys in [0,32), two float64 values, 10M rows (configs[0] shape on the GPU)"),
 }
 
 
@@ -65,6 +66,8 @@ def algorithmic_bytes(workload: str, n: int, g: int) -> float:
         return 12.125 * n + (4 + 24 + 3 / 8) * g
     if workload == "Q1":
         return 18.0 * n
+    if workload == "C1":
+        return 32.0 * n + 32.0 * g
     raise ValueError(workload)
 
 
@@ -101,6 +104,12 @@ def make_device_inputs(workload: str, n: int, g: int, seed: int, device):
         _lib.check(L.bgb_gen_null_mask(C.c_void_p(mask.data_ptr()), n, seed + 2, 0, 10, C.byref(nc), s))
         v = cb.Column(vd, mask, nc.value)
         return cb.Table([k]), [cb.GroupByRequest(v, [A.sum(), A.min(), A.max()])]
+    if workload == "C1":
+        ka = cb.Column(gen_int(torch.int64, cb.TypeId.INT64, seed, 32))
+        kb = cb.Column(gen_int(torch.int64, cb.TypeId.INT64, seed + 1, 32))
+        c = cb.Column(gen_real(seed + 2, 1_000_000))
+        d = cb.Column(gen_real(seed + 3, 1_000_000))
+        return cb.Table([ka, kb]), [cb.GroupByRequest(c, [A.mean()]), cb.GroupByRequest(d, [A.mean()])]
     if workload == "Q1":
         # (returnflag, linestatus) joint weights (A,F) 24.7%, (N,F) 0.6%, (N,O) 50%, (R,F) 24.7%: one categorical draw
         # picks the pair, so both key columns come from the same x(seed,row)
@@ -130,6 +139,12 @@ def make_host_inputs_numpy(workload: str, n: int, g: int, seed: int):
         v = (orc.splitmix64(seed + 1, rows) % np.uint64(1_000_000)).astype(np.float64)
         valid = (orc.splitmix64(seed + 2, rows) % np.uint64(10)) != 0
         return [H(k)], [H(v, valid)], [(0, "sum", 1), (0, "min", 1), (0, "max", 1)]
+    if workload == "C1":
+        ka = (orc.splitmix64(seed, rows) % np.uint64(32)).astype(np.int64)
+        kb = (orc.splitmix64(seed + 1, rows) % np.uint64(32)).astype(np.int64)
+        c = (orc.splitmix64(seed + 2, rows) % np.uint64(1_000_000)).astype(np.float64)
+        d = (orc.splitmix64(seed + 3, rows) % np.uint64(1_000_000)).astype(np.float64)
+        return [H(ka), H(kb)], [H(c), H(d)], [(0, "mean", 1), (1, "mean", 1)]
     if workload == "Q1":
         x = (orc.splitmix64(seed, rows) & np.uint64(0xFFFF)).astype(np.int64)
         cum = [int(0.247 * 65536), int(0.253 * 65536), int(0.753 * 65536), 65536]

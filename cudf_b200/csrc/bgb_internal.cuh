@@ -121,7 +121,9 @@ struct OutDesc {
   // OUT_KEY only
   uint8_t shift;
   int8_t null_bit;
-  uint8_t pad[2];
+  uint8_t key_bits;       // != 0: the field is (value - key_base) in key_bits bits (repacked keys)
+  uint8_t pad;
+  uint64_t key_base;
 };
 
 struct EmitParams {
@@ -146,6 +148,33 @@ __host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t seed, uint64_t 
   uint64_t z = seed * 0x1000003ull + row + 0x9E3779B97F4A7C15ull;
   return mix64(z);
 }
+
+// ---- key repacking (kernels_repack.cu): several integer key columns whose packed image would need more than 64 bits are
+// range-compressed into ONE 64-bit key column, (value - column minimum) in just enough bits, so that every single-word fast
+// path serves them. The reference hashes and compares the key columns row by row whatever their ranges
+// (/root/reference/cpp/include/cudf/detail/row_operator/hashing.cuh:118-134, equality.cuh:59-89).
+struct RepackCol {
+  const uint8_t* data;
+  const uint32_t* mask;
+  int32_t offset;
+  uint8_t width;          // 1/2/4/8
+  uint8_t is_signed;      // sign-extend the element before subtracting the base
+  uint8_t is_bool;        // any non-zero byte is 1
+  uint8_t shift;          // bit position of the field in the packed word
+  int8_t null_bit;        // INCLUDE policy: position of the column's null flag, -1: none
+  uint64_t base;          // column minimum (as the sign- or zero-extended 64-bit value)
+};
+struct RepackParams {
+  RepackCol col[kMaxKeyCols];
+  int32_t num_cols;
+  int32_t drop_null_rows; // EXCLUDE policy: a row with a null key loses its bit in out_mask
+  int64_t num_rows;
+  uint64_t* minmax;       // [2 * num_cols]: min, max per column over the valid elements (minmax kernel output)
+  uint64_t* out;          // packed key column
+  uint32_t* out_mask;     // validity words of the packed column (EXCLUDE + some column has a mask), else nullptr
+};
+cudaError_t launch_repack_minmax(const RepackParams& p, cudaStream_t s);
+cudaError_t launch_repack_pack(const RepackParams& p, cudaStream_t s);
 
 // host-side API of the kernel translation units
 cudaError_t launch_init_table(const AggParams& p, cudaStream_t s);

@@ -34,6 +34,9 @@ struct bgb_groupby {
   int32_t num_groups = 0;
   std::string path = "empty";
   Profiler prof;
+  std::vector<KeyPlan> emit_keys;   // repacked keys: the caller's key columns and where each sits in the packed 64-bit image
+  void* repack_buf = nullptr;       // the packed key column (+ its validity words), released when the build is done
+  void* repack_mask = nullptr;
 
   void* dalloc(size_t bytes)
   {
@@ -422,6 +425,100 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool one_l
 
 }  // namespace
 
+// Key repacking: the caller's integer key columns would need a 128-bit image, but their exact value RANGES fit 64 bits
+// together: build one packed UINT64 key column ((value - minimum) of every column, null flags on top) and re-plan the call
+// on it, so that the single-word paths (shared-memory tables, tiny kernels, bucketed path) serve it instead of the generic
+// 128-bit CAS kernel. Costs one min/max pass and one packing pass over the key columns. done=false: plan left untouched.
+int try_repack_keys(bgb_groupby* h, const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
+                    const bgb_request* requests, int32_t num_requests, bool& done)
+{
+  done = false;
+  Plan& pl = h->plan;
+  const int64_t N = pl.num_rows;
+  cudaStream_t s = h->stream;
+  RepackParams rp;
+  memset(&rp, 0, sizeof rp);
+  rp.num_cols = num_keys; rp.num_rows = N;
+  bool any_mask = false;
+  for (int c = 0; c < num_keys; ++c) {
+    const uint8_t src = type_src(keys[c].type_id);
+    if (src == S_F32 || src == S_F64 || src == S_BAD) return BGB_OK;  // float keys keep their canonicalised bit images
+    RepackCol& rc = rp.col[c];
+    rc.data = (const uint8_t*)keys[c].data; rc.mask = keys[c].null_mask; rc.offset = keys[c].offset;
+    rc.width = (uint8_t)type_width(keys[c].type_id);
+    rc.is_signed = src == S_I8 || src == S_I16 || src == S_I32 || src == S_I64;
+    rc.is_bool = src == S_BOOL;
+    rc.null_bit = -1;
+    any_mask |= keys[c].null_mask != nullptr;
+  }
+  uint64_t* d_mm = (uint64_t*)h->dalloc(sizeof(uint64_t) * 2 * num_keys);
+  if (!d_mm) return set_error(BGB_OUT_OF_MEMORY, "repack scratch");
+  std::vector<uint64_t> mm(2 * num_keys);
+  for (int c = 0; c < num_keys; ++c) { mm[2 * c] = ~0ull; mm[2 * c + 1] = 0; }
+  int rc = check_cuda(cudaMemcpyAsync(d_mm, mm.data(), sizeof(uint64_t) * mm.size(), cudaMemcpyHostToDevice, s), "repack init");
+  rp.minmax = d_mm;
+  h->prof.begin("repack_minmax");
+  if (!rc) rc = check_cuda(launch_repack_minmax(rp, s), "repack_minmax");
+  h->prof.end();
+  if (!rc) rc = check_cuda(cudaMemcpyAsync(mm.data(), d_mm, sizeof(uint64_t) * mm.size(), cudaMemcpyDeviceToHost, s), "repack copy");
+  if (!rc) rc = check_cuda(cudaStreamSynchronize(s), "repack sync");
+  h->prof.resolve();
+  h->dfree(d_mm);
+  if (rc) return rc;
+  // field widths: the order images run from mm[2c] to mm[2c+1] (an all-null column keeps the initial min > max: one bit)
+  int bit = 0;
+  std::vector<KeyPlan> ek = pl.keys;
+  for (int c = 0; c < num_keys; ++c) {
+    const uint64_t lo = mm[2 * c], hi = mm[2 * c + 1];
+    const uint64_t range = lo <= hi ? hi - lo : 0;
+    int bits = 1; while (bits < 64 && (range >> bits) != 0) ++bits;
+    rp.col[c].base  = lo <= hi ? (rp.col[c].is_signed ? lo ^ 0x8000000000000000ull : lo) : 0;
+    rp.col[c].shift = (uint8_t)(bit & 63);
+    ek[c].shift = (uint8_t)(bit & 63); ek[c].base = rp.col[c].base; ek[c].bits = (uint8_t)bits; ek[c].null_bit = -1;
+    bit += bits;
+  }
+  for (int c = 0; c < num_keys; ++c)
+    if (ek[c].nullable_out) { if (bit < 64) { rp.col[c].null_bit = (int8_t)bit; ek[c].null_bit = (int8_t)bit; } ++bit; }
+  if (bit > 64) return BGB_OK;  // the ranges do not fit one word either: 128-bit path
+  if (pl.key_words == 2) {
+    // Two passes over the key columns only pay when the packed key opens a path the 128-bit image cannot take. The product
+    // of the column ranges bounds the group count: a handful of groups (tiny kernels), a shared-memory table for the
+    // SUM/COUNT shape, or a table that may exceed L2 on a large input (bucketed path instead of the partitioned one).
+    double gmax = 1.0;
+    for (int c = 0; c < num_keys; ++c) {
+      const uint64_t lo = mm[2 * c], hi = mm[2 * c + 1];
+      gmax *= (lo <= hi ? (double)(hi - lo) + 1.0 : 1.0) + (ek[c].nullable_out ? 1.0 : 0.0);
+    }
+    bool sum_count_shape = pl.values.size() <= 1;
+    for (const AccPlan& a : pl.accs) sum_count_shape &= a.op == ACC_SUM_I64 || a.op == ACC_COUNT_VALID || a.op == ACC_COUNT_ALL;
+    const bool worthwhile = gmax <= 24.0 || (gmax <= 16384.0 && sum_count_shape) || (N >= (1 << 24) && gmax >= 4194304.0);
+    if (!worthwhile) return BGB_OK;
+  }
+
+  rp.drop_null_rows = pl.skip_null_keys;
+  rp.out = (uint64_t*)h->dalloc((size_t)N * 8);
+  if (!rp.out) return set_error(BGB_OUT_OF_MEMORY, "packed key column (%lld rows)", (long long)N);
+  if (pl.skip_null_keys && any_mask) {
+    rp.out_mask = (uint32_t*)h->dalloc(sizeof(uint32_t) * (size_t)((N + 31) / 32));
+    if (!rp.out_mask) return set_error(BGB_OUT_OF_MEMORY, "packed key mask");
+  }
+  h->prof.begin("repack_pack");
+  rc = check_cuda(launch_repack_pack(rp, s), "repack_pack");
+  h->prof.end();
+  if (rc) return rc;
+  bgb_column_view pk{};
+  pk.type_id = BGB_UINT64; pk.size = (int32_t)N; pk.data = rp.out; pk.null_mask = rp.out_mask; pk.null_count = rp.out_mask ? 1 : 0;
+  Plan p2;
+  rc = make_plan(&pk, 1, include_null_keys, requests, num_requests, p2, false);
+  if (rc) return rc;
+  h->plan        = p2;
+  h->emit_keys   = ek;
+  h->repack_buf  = rp.out;
+  h->repack_mask = rp.out_mask;
+  done = true;
+  return BGB_OK;
+}
+
 static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
                        const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
                        const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups, bool rank_independent = false)
@@ -430,7 +527,9 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
   *out_handle = nullptr;
   *num_groups = 0;
   bgb_groupby* h = new bgb_groupby();
-  int rc = make_plan(keys, num_keys, include_null_keys, requests, num_requests, h->plan, rank_independent);
+  // key images wider than 128 bits are planned too when the call may repack them (the exact value ranges decide below)
+  const bool may_repack = !rank_independent && (!options || options->force_path == 0);
+  int rc = make_plan(keys, num_keys, include_null_keys, requests, num_requests, h->plan, rank_independent, may_repack);
   if (rc != BGB_OK) { delete h; return rc; }
   h->stream = (cudaStream_t)stream;
   if (alloc && alloc->allocate && alloc->deallocate) { h->alloc = *alloc; h->has_alloc = true; }
@@ -452,6 +551,12 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     if (rc_ != BGB_OK) { h->free_all(); delete h; return rc_; } \
   } while (0)
 
+  if (may_repack && (pl.key_words > 2 || (pl.key_words == 2 && N >= 65536))) {
+    bool repacked = false;
+    FAIL_RC(try_repack_keys(h, keys, num_keys, include_null_keys, requests, num_requests, repacked));
+    tr.mark("repack");
+  }
+  if (pl.key_words > 2) FAIL_RC(set_error(BGB_UNSUPPORTED, "packed key wider than 128 bits and the key ranges do not fit 64 bits"));
   uint32_t* status = (uint32_t*)h->dalloc(16 * sizeof(uint32_t));
   if (!status) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "status alloc"));
   h->table.status    = status;
@@ -638,6 +743,9 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     key_min = 1; key_max = 0;
   }
 #undef FAIL_RC
+  if (h->repack_buf) { h->dfree(h->repack_buf); h->repack_buf = nullptr; }   // stream-ordered: the kernels above are done with it
+  if (h->repack_mask) { h->dfree(h->repack_mask); h->repack_mask = nullptr; }
+  if (!h->emit_keys.empty()) h->path += "+repack";
   tr.mark("tail");
   tr.flush("build_local");
   g_tr = nullptr;
@@ -669,8 +777,10 @@ extern "C" int bgb_groupby_result_info(const bgb_groupby* h, int32_t request, in
 
 extern "C" int bgb_groupby_key_info(const bgb_groupby* h, int32_t key, int32_t* type_id, int32_t* scale, int32_t* nullable)
 {
-  if (!h || key < 0 || key >= (int)h->plan.keys.size()) return set_error(BGB_INVALID_ARGUMENT, "no key column %d", key);
-  const KeyPlan& k = h->plan.keys[key];
+  if (!h) return set_error(BGB_INVALID_ARGUMENT, "null handle");
+  const std::vector<KeyPlan>& ek = !h->emit_keys.empty() ? h->emit_keys : h->plan.keys;
+  if (key < 0 || key >= (int)ek.size()) return set_error(BGB_INVALID_ARGUMENT, "no key column %d", key);
+  const KeyPlan& k = ek[key];
   if (type_id) *type_id = k.v.type_id;
   if (scale) *scale = k.v.scale;
   if (nullable) *nullable = k.nullable_out;
@@ -683,7 +793,8 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
 {
   if (!h) return set_error(BGB_INVALID_ARGUMENT, "null handle");
   const Plan& pl = h->plan;
-  const int nk = (int)pl.keys.size(), nr = (int)pl.outs.size();
+  const std::vector<KeyPlan>& ekeys = h->emit_keys.empty() ? pl.keys : h->emit_keys;  // repacked: the caller's columns
+  const int nk = (int)ekeys.size(), nr = (int)pl.outs.size();
   if ((nk > 0 && !out_keys) || (nr > 0 && !out_results)) return set_error(BGB_INVALID_ARGUMENT, "null output arrays");
   for (int i = 0; i < nk; ++i) out_keys[i].null_count = 0;
   for (int i = 0; i < nr; ++i) out_results[i].null_count = 0;
@@ -696,7 +807,7 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
   // validate caller buffers
   for (int i = 0; i < nk; ++i) {
     if (out_keys[i].size < G || !out_keys[i].data) return set_error(BGB_INVALID_ARGUMENT, "out_keys[%d] too small", i);
-    if (pl.keys[i].nullable_out && !out_keys[i].null_mask) return set_error(BGB_INVALID_ARGUMENT, "out_keys[%d] needs a null mask", i);
+    if (ekeys[i].nullable_out && !out_keys[i].null_mask) return set_error(BGB_INVALID_ARGUMENT, "out_keys[%d] needs a null mask", i);
   }
   for (int i = 0; i < nr; ++i) {
     if (out_results[i].size < G || !out_results[i].data) return set_error(BGB_INVALID_ARGUMENT, "out_results[%d] too small", i);
@@ -711,10 +822,11 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
 
   std::vector<OutDesc> descs;
   for (int i = 0; i < nk; ++i) {
-    const KeyPlan& k = pl.keys[i];
+    const KeyPlan& k = ekeys[i];
     OutDesc d{};
     d.out = out_keys[i].data; d.out_mask = k.nullable_out ? out_keys[i].null_mask : nullptr; d.null_count = d_nulls + i;
     d.op = OUT_KEY; d.src = type_src(k.v.type_id); d.out_width = k.width; d.shift = k.shift; d.null_bit = k.null_bit;
+    d.key_bits = k.bits; d.key_base = k.base;
     any_nullable |= k.nullable_out;
     descs.push_back(d);
   }

@@ -149,6 +149,7 @@ __global__ void __launch_bounds__(256) emit_kernel(const __grid_constant__ EmitP
         case OUT_KEY: {
           if (d.null_bit >= 0) valid = !((d.null_bit < 64 ? (k0 >> d.null_bit) : (k1 >> (d.null_bit - 64))) & 1ull);
           uint64_t w = d.shift < 64 ? (k0 >> d.shift) : (k1 >> (d.shift - 64));
+          if (d.key_bits) w = (d.key_bits < 64 ? (w & ((1ull << d.key_bits) - 1)) : w) + d.key_base;  // repacked: value = base + field
           bits = d.out_width == 8 ? w : (w & ((1ull << (8 * d.out_width)) - 1));
           break;
         }

@@ -110,7 +110,7 @@ static bool same_column(const bgb_column_view& a, const bgb_column_view& b)
 }
 
 int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys, const bgb_request* requests,
-              int32_t num_requests, Plan& plan, bool rank_independent)
+              int32_t num_requests, Plan& plan, bool rank_independent, bool allow_wide)
 {
   if (num_keys <= 0 || keys == nullptr) return set_error(BGB_INVALID_ARGUMENT, "groupby needs at least one key column");
   if (num_requests < 0 || (num_requests > 0 && requests == nullptr)) return set_error(BGB_INVALID_ARGUMENT, "bad requests");
@@ -139,8 +139,8 @@ int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_nul
     if (keys[c].null_mask != nullptr) any_key_mask = true;
     if (plan.include_null_keys && (keys[c].null_mask != nullptr || rank_independent)) ++null_bits;
   }
-  if (total_bits + null_bits > 128) return set_error(BGB_UNSUPPORTED, "packed key wider than 128 bits (%d)", total_bits + null_bits);
-  plan.key_words      = (total_bits + null_bits > 64) ? 2 : 1;
+  if (total_bits + null_bits > 128 && !allow_wide) return set_error(BGB_UNSUPPORTED, "packed key wider than 128 bits (%d)", total_bits + null_bits);
+  plan.key_words      = (total_bits + null_bits + 63) / 64;
   plan.skip_null_keys = any_key_mask && !plan.include_null_keys;
 
   // pack widest fields first so no field straddles a 64-bit word; null flags go last

@@ -17,6 +17,9 @@ struct KeyPlan {
   uint8_t width, fclass, shift;
   int8_t null_bit;
   bool nullable_out;
+  // range-compressed image (key repacking, groupby.cu): the field holds (value - base) in `bits` bits; bits == 0: the element itself
+  uint64_t base = 0;
+  uint8_t bits  = 0;
 };
 
 struct ValuePlan {
@@ -67,6 +70,7 @@ int32_t target_type(int32_t type_id, int32_t kind);  // -1 invalid
 // mask on THIS rank (multi-GPU exchange: every rank packs keys and lays out records identically); every value column is
 // then treated as nullable and, under INCLUDE, every key column gets a null flag bit.
 int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys, const bgb_request* requests,
-              int32_t num_requests, Plan& plan, bool rank_independent = false);
+              int32_t num_requests, Plan& plan, bool rank_independent = false, bool allow_wide = false);
+// allow_wide: key images wider than 128 bits are planned anyway (key_words > 2): only valid as the input of key repacking
 
 }  // namespace bgb
