@@ -8,6 +8,7 @@
 
 #include "errors.h"
 #include "kernels_smem.h"
+#include "kernels_sorted.h"
 #include "kernels_tiny.h"
 
 namespace bgb {
@@ -21,6 +22,14 @@ SmemEligibility smem_eligibility(const Plan& pl)
 {
   SmemEligibility e;
   if (pl.key_words != 1 || pl.num_rows == 0) return e;
+  // key shape first: the estimator and the tile-sorting kernel use it whatever the accumulator set is
+  const KeyPlan& k0 = pl.keys[0];
+  e.integer_keys = true;
+  for (const KeyPlan& k : pl.keys) if (k.fclass != 0) e.integer_keys = false;
+  if (pl.keys.size() == 1 && k0.null_bit < 0) {
+    const uint8_t src = type_src(k0.v.type_id);
+    if (src == S_I8 || src == S_I16 || src == S_I32 || src == S_I64) e.key_flip = 1ull << (8 * k0.width - 1);
+  }
   for (size_t i = 0; i < pl.accs.size(); ++i) {
     const AccPlan& a = pl.accs[i];
     if (a.op == ACC_SUM_I64) { if (e.sum_acc >= 0) return e; e.sum_acc = (int)i; }
@@ -41,17 +50,10 @@ SmemEligibility smem_eligibility(const Plan& pl)
   }
   int key_bits = 0;
   for (const KeyPlan& k : pl.keys) key_bits = std::max(key_bits, std::max((int)k.shift + 8 * k.width, (int)k.null_bit + 1));
-  const KeyPlan& k0 = pl.keys[0];
   if (pl.keys.size() == 1 && (k0.width == 4 || k0.width == 8) && k0.null_bit < 0 && aligned_to(k0.v.data, k0.v.offset, k0.width, 2 * k0.width)) {
     e.key_mode = 1; e.smem_key_bytes = k0.width;
   } else {
     e.key_mode = 0; e.smem_key_bytes = key_bits <= 32 ? 4 : 8;
-  }
-  e.integer_keys = true;
-  for (const KeyPlan& k : pl.keys) if (k.fclass != 0) e.integer_keys = false;
-  if (pl.keys.size() == 1 && k0.null_bit < 0) {
-    const uint8_t src = type_src(k0.v.type_id);
-    if (src == S_I8 || src == S_I16 || src == S_I32 || src == S_I64) e.key_flip = 1ull << (8 * k0.width - 1);
   }
   e.ok = true;
   return e;
@@ -107,6 +109,81 @@ static int run_smem_path(const BuildContext& ctx, const SmemEligibility& e, uint
   }
   ctx.prof->begin("aggregate_smem");
   rc = check_cuda(launch_aggregate_smem(sp, e.smem_key_bytes, e.key_mode, e.value_width, ctx.num_sms, ctx.stream), "aggregate_smem");
+  ctx.prof->end();
+  return rc;
+}
+
+// ---- tile-sorting kernel (kernels_sorted.cu): dense integer key range, any accumulator set without ARGMIN/ARGMAX
+// (the key shape is checked by the caller: one-word integer keys with a known range)
+static bool sorted_plan(const Plan& pl, SortedParams* out)
+{
+  if (pl.accs.empty() || pl.accs.size() > (size_t)kMaxAccs) return false;
+  SortedParams local;
+  SortedParams& sp = out ? *out : local;
+  memset(&sp, 0, sizeof sp);
+  int col_of_value[64];
+  for (int& c : col_of_value) c = -1;
+  for (size_t i = 0; i < pl.accs.size(); ++i) {
+    const AccPlan& a = pl.accs[i];
+    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX || a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX) return false;
+    int col = -1;
+    if (a.value_col >= 0) {
+      if (a.value_col >= 64) return false;
+      if (col_of_value[a.value_col] < 0) {
+        if (sp.num_cols == kSortedMaxCols) return false;
+        const ValuePlan& v = pl.values[a.value_col];
+        sp.col[sp.num_cols] = SortedCol{(const uint8_t*)v.v.data, v.v.null_mask, v.v.offset, (uint8_t)type_width(v.v.type_id), v.src};
+        if (v.v.null_mask) sp.any_mask = 1;
+        col_of_value[a.value_col] = sp.num_cols++;
+      }
+      col = col_of_value[a.value_col];
+    }
+    sp.acc[i] = SortedAcc{a.cells, a.op, (int8_t)col};
+  }
+  sp.num_accs = (int)pl.accs.size();
+  return true;
+}
+
+uint32_t sorted_max_groups(const Plan& pl, bool forced)
+{
+  SortedParams sp;
+  if (!sorted_plan(pl, &sp)) return 0;
+  const int nc = std::max(1, sp.num_cols);
+  // automatic choice: two CTAs per SM and at most 4 groups per thread -- beyond that the per-tile walk over the owned groups
+  // costs more than the L2 atomics of the generic kernel (measured at 4000 groups: 5.2 ms against 4.2 ms per 1e8 rows)
+  const size_t budget = forced ? smem_table_max_bytes() : (size_t)112 * 1024;
+  uint32_t g = forced ? kSortedMaxGroups : kSortedMaxGroups / 2;
+  while (g > 0 && sorted_smem_bytes(g, sp.num_accs, nc) > budget) g -= 64;
+  return g;
+}
+
+static int run_sorted_path(const BuildContext& ctx, const SmemEligibility& e, SortedParams& sp, uint32_t groups, uint64_t key_base)
+{
+  const Plan& pl = *ctx.plan;
+  AggParams ip;
+  memset(&ip, 0, sizeof ip);
+  ip.table = ctx.table; ip.init_keys = 1; ip.num_accs = (int)pl.accs.size();
+  for (size_t i = 0; i < pl.accs.size(); ++i) { ip.acc[i].op = pl.accs[i].op; ip.acc[i].cells = pl.accs[i].cells; }
+  ctx.prof->begin("init_table");
+  int rc = check_cuda(launch_init_table(ip, ctx.stream), "init_table");
+  ctx.prof->end();
+  if (rc) return rc;
+  sp.a.num_rows = pl.num_rows; sp.a.num_key_cols = (int)pl.keys.size(); sp.a.skip_null_keys = pl.skip_null_keys;
+  for (size_t c = 0; c < pl.keys.size(); ++c) {
+    const KeyPlan& k = pl.keys[c];
+    sp.a.kc[c] = KeyColDesc{(const uint8_t*)k.v.data, k.v.null_mask, k.v.offset, k.width, k.fclass, k.shift, k.null_bit};
+  }
+  sp.a.table  = ctx.table;
+  sp.groups   = groups;
+  sp.key_flip = e.key_flip;
+  sp.key_base = key_base;
+  sp.key_mode = pl.keys.size() == 1 && pl.keys[0].v.null_mask == nullptr && pl.keys[0].fclass == 0 && pl.keys[0].null_bit < 0;
+  if (sp.key_mode == 1 && pl.keys[0].width == 8) sp.key_mode = 2;
+  sp.fast8 = sp.num_cols > 0;
+  for (int c = 0; c < sp.num_cols; ++c)
+    sp.fast8 &= sp.col[c].width == 8 && sp.col[c].mask == nullptr && (sp.col[c].src == S_I64 || sp.col[c].src == S_U64 || sp.col[c].src == S_F64);
+  ctx.prof->begin("aggregate_sorted");
+  rc = check_cuda(launch_aggregate_sorted(sp, ctx.num_sms, ctx.stream), "aggregate_sorted");
   ctx.prof->end();
   return rc;
 }
@@ -251,6 +328,22 @@ int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path)
       done = true; path = "smem";
       return BGB_OK;
     }
+  }
+  // (c) any other accumulator set over a dense integer key range of a few thousand ids: tile-sorting kernel
+  if (ctx.opt.force_path == 0 || ctx.opt.force_path == 8) {
+    SortedParams sp;
+    const uint32_t gmax    = sorted_max_groups(pl, ctx.opt.force_path == 8);
+    const bool range_known = ctx.key_min <= ctx.key_max;
+    const uint64_t range   = range_known ? ctx.key_max - ctx.key_min + 1 : ~0ull;
+    if (gmax != 0 && e.integer_keys && range_known && range <= gmax && (pl.num_rows >= 65536 || ctx.opt.force_path == 8) && sorted_plan(pl, &sp)) {
+      const uint64_t pad    = std::min<uint64_t>({(uint64_t)64, (gmax - range) / 2, ctx.key_min});
+      const uint32_t groups = (uint32_t)std::min<uint64_t>(gmax, range + 2 * pad + 64);
+      int rc = run_sorted_path(ctx, e, sp, groups, ctx.key_min - pad);
+      if (rc) return rc;
+      done = true; path = "sorted";
+      return BGB_OK;
+    }
+    if (ctx.opt.force_path == 8) return set_error(BGB_UNSUPPORTED, "force_path 8: the tile-sorting kernel needs one-word integer keys with a sampled range of at most %u ids and no ARGMIN/ARGMAX", gmax);
   }
   return BGB_OK;
 }

@@ -31,5 +31,8 @@ struct SmemEligibility {
 };
 SmemEligibility smem_eligibility(const Plan& plan);
 
+// tile-sorting kernel (kernels_sorted.cu): largest dense id range it holds for this plan's accumulators, 0 = plan not served
+uint32_t sorted_max_groups(const Plan& plan, bool forced = false);
+
 int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path);
 }

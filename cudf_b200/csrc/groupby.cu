@@ -483,7 +483,7 @@ int try_repack_keys(bgb_groupby* h, const bgb_column_view* keys, int32_t num_key
   if (pl.key_words == 2) {
     // Two passes over the key columns only pay when the packed key opens a path the 128-bit image cannot take. The product
     // of the column ranges bounds the group count: a handful of groups (tiny kernels), a shared-memory table for the
-    // SUM/COUNT shape, or a table that may exceed L2 on a large input (bucketed path instead of the partitioned one).
+    // SUM/COUNT shape, a few thousand dense ids for the tile-sorting kernel, or a table that may exceed L2 on a large input (bucketed path instead of the partitioned one).
     double gmax = 1.0;
     for (int c = 0; c < num_keys; ++c) {
       const uint64_t lo = mm[2 * c], hi = mm[2 * c + 1];
@@ -491,7 +491,9 @@ int try_repack_keys(bgb_groupby* h, const bgb_column_view* keys, int32_t num_key
     }
     bool sum_count_shape = pl.values.size() <= 1;
     for (const AccPlan& a : pl.accs) sum_count_shape &= a.op == ACC_SUM_I64 || a.op == ACC_COUNT_VALID || a.op == ACC_COUNT_ALL;
-    const bool worthwhile = gmax <= 24.0 || (gmax <= 16384.0 && sum_count_shape) || (N >= (1 << 24) && gmax >= 4194304.0);
+    // (the tile-sorting kernel indexes by the packed image itself: `bit` bits of dense ids, any accumulator set)
+    const bool sorted_fits = bit <= 20 && (1u << bit) <= sorted_max_groups(pl);
+    const bool worthwhile = gmax <= 24.0 || (gmax <= 16384.0 && sum_count_shape) || sorted_fits || (N >= (1 << 24) && gmax >= 4194304.0);
     if (!worthwhile) return BGB_OK;
   }
 

@@ -42,14 +42,23 @@ def test_two_int64_keys_few_groups_take_the_tiny_kernel():
     assert G == 6 and path.startswith("tiny"), path
 
 
-def test_baseline_config_1_shape_is_left_alone():
-    # BASELINE configs[0]: df.groupby(['A','B']).mean(), int64 keys in [0, 32), float64 values -> 1024 groups. No single-word
-    # path serves two float MEANs at 1024 groups, so the two extra passes would buy nothing: the call is not repacked.
+def test_baseline_config_1_shape_takes_the_tile_sorting_kernel():
+    # BASELINE configs[0]: df.groupby(['A','B']).mean(), int64 keys in [0, 32), float64 values -> 1024 groups: the packed image is
+    # a 10-bit dense id, which the tile-sorting kernel (kernels_sorted.cu) indexes directly
     rng = np.random.default_rng(42)
     a, b = rng.integers(0, 32, N).astype(np.int64), rng.integers(0, 32, N).astype(np.int64)
     c, d = rng.standard_normal(N), rng.standard_normal(N)
-    G, path = _check([H(a), H(b)], [H(c), H(d)], [(0, "mean", 1), (1, "mean", 1)], name="cfg1", repacked=False)
-    assert G == 1024
+    G, path = _check([H(a), H(b)], [H(c), H(d)], [(0, "mean", 1), (1, "mean", 1)], name="cfg1")
+    assert G == 1024 and path.startswith("sorted"), path
+
+
+def test_float_means_over_a_wide_packed_range_are_left_alone():
+    # 2 x 9 bits of dense ids exceed what the tile-sorting kernel holds, and no other single-word path serves two float MEANs at
+    # 1e5 groups faster than the L2-resident 128-bit table: the two extra passes would buy nothing
+    rng = np.random.default_rng(42)
+    a, b = rng.integers(0, 400, N).astype(np.int64), rng.integers(0, 400, N).astype(np.int64)
+    c, d = rng.standard_normal(N), rng.standard_normal(N)
+    _check([H(a), H(b)], [H(c), H(d)], [(0, "mean", 1), (1, "mean", 1)], name="wide float", repacked=False)
 
 
 @pytest.mark.parametrize("include", [False, True])
