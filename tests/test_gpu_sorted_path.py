@@ -138,3 +138,28 @@ def test_argmin_is_not_served():
     v = H(rng.standard_normal(N))
     with pytest.raises(cb.UnsupportedError):
         gpu_util.run_gpu([k], [v], [(0, "argmin", 1)], options={"force_path": 8})
+
+
+@pytest.mark.parametrize("include", [False, True])
+def test_repacked_nullable_key_columns(include):
+    # three nullable key columns of different widths whose exact ranges need 7 bits (+ 3 null flags under INCLUDE): repacked
+    # into one dense 64-bit image, which the tile-sorting kernel indexes directly
+    rng = np.random.default_rng(12)
+    k1 = H(rng.integers(-7_000_000_000, -6_999_999_992, N).astype(np.int64), rng.random(N) > 0.05)
+    k2 = H(rng.integers(-3, 5, N).astype(np.int64), rng.random(N) > 0.1)
+    k3 = H(rng.integers(200, 202, N).astype(np.uint8), rng.random(N) > 0.02)
+    v = H(rng.standard_normal(N), rng.random(N) > 0.1)
+    w = H(rng.integers(-50, 50, N).astype(np.int16))
+    aggs = [(0, "mean", 1), (0, "min", 1), (1, "sum", 1), (1, "max", 1)]
+    _check([k1, k2, k3], [v, w], aggs, include=include, name=f"repacked/include={include}", force=False, expect="sorted+repack")
+
+
+def test_repacked_keys_all_null_column():
+    rng = np.random.default_rng(13)
+    k1 = H(rng.integers(0, 100, N).astype(np.int64))
+    k2 = H(np.zeros(N, dtype=np.int64), np.zeros(N, dtype=bool))  # every element null
+    v = H(rng.standard_normal(N))
+    G = _check([k1, k2], [v], [(0, "mean", 1)], include=True, name="repacked/all-null column", force=False, expect="sorted+repack")
+    assert G == 100
+    G, path = gpu_util.compare_with_oracle([k1, k2], [v], [(0, "mean", 1)], include_null_keys=False, name="repacked/all-null column/exclude")
+    assert G == 0
