@@ -157,7 +157,19 @@ uint32_t sorted_max_groups(const Plan& pl, bool forced)
   return g;
 }
 
-static int run_sorted_path(const BuildContext& ctx, const SmemEligibility& e, SortedParams& sp, uint32_t groups, uint64_t key_base)
+// hashed variant: the largest power-of-two slot count whose tables fit (two CTAs per SM unless forced)
+static uint32_t sorted_max_slots(const Plan& pl, bool forced)
+{
+  SortedParams sp;
+  if (!sorted_plan(pl, &sp)) return 0;
+  const int nc = std::max(1, sp.num_cols);
+  const size_t budget = forced ? smem_table_max_bytes() : (size_t)112 * 1024;
+  uint32_t s = forced ? kSortedMaxGroups : kSortedMaxGroups / 2;
+  while (s >= 64 && sorted_smem_bytes(s, sp.num_accs, nc, true) > budget) s >>= 1;
+  return s >= 64 ? s : 0;
+}
+
+static int run_sorted_path(const BuildContext& ctx, const SmemEligibility& e, SortedParams& sp, uint32_t groups, uint64_t key_base, bool hashed = false)
 {
   const Plan& pl = *ctx.plan;
   AggParams ip;
@@ -175,8 +187,9 @@ static int run_sorted_path(const BuildContext& ctx, const SmemEligibility& e, So
   }
   sp.a.table  = ctx.table;
   sp.groups   = groups;
-  sp.key_flip = e.key_flip;
+  sp.key_flip = hashed ? 0 : e.key_flip;
   sp.key_base = key_base;
+  sp.hashed   = hashed;
   sp.key_mode = pl.keys.size() == 1 && pl.keys[0].v.null_mask == nullptr && pl.keys[0].fclass == 0 && pl.keys[0].null_bit < 0;
   if (sp.key_mode == 1 && pl.keys[0].width == 8) sp.key_mode = 2;
   sp.fast8 = sp.num_cols > 0;
@@ -343,7 +356,17 @@ int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path)
       done = true; path = "sorted";
       return BGB_OK;
     }
-    if (ctx.opt.force_path == 8) return set_error(BGB_UNSUPPORTED, "force_path 8: the tile-sorting kernel needs one-word integer keys with a sampled range of at most %u ids and no ARGMIN/ARGMAX", gmax);
+    // sparse integer keys, float keys, several key columns: the id is the key's slot in a small hash table of the CTA
+    const uint32_t smax = sorted_max_slots(pl, ctx.opt.force_path == 8);
+    if (smax != 0 && pl.key_words == 1 && (ctx.opt.force_path == 8 || (pl.num_rows >= 65536 && ctx.g_raw <= 0.6 * smax)) && sorted_plan(pl, &sp)) {
+      uint32_t slots = smax;
+      while (slots > 64 && ctx.g_raw <= 0.3 * slots) slots >>= 1;   // (a smaller table leaves more shared memory to the L1)
+      int rc = run_sorted_path(ctx, e, sp, slots, 0, true);
+      if (rc) return rc;
+      done = true; path = "sorted-hashed";
+      return BGB_OK;
+    }
+    if (ctx.opt.force_path == 8) return set_error(BGB_UNSUPPORTED, "force_path 8: the tile-sorting kernel needs a one-word key image, at most %d value columns and no ARGMIN/ARGMAX", kSortedMaxCols);
   }
   return BGB_OK;
 }

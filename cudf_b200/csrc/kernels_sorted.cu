@@ -12,6 +12,8 @@
 //   4. every thread folds the rows of the groups it owns, in registers, and adds the partials to the CTA's table with plain
 //      loads and stores -- it is the only thread that touches those cells. COUNTs of unmasked columns are the histogram.
 //      Groups with more than 64 rows in the tile (skewed keys) are left to a whole warp each (strided fold + shuffle tree).
+// Group ids are (key - minimum) when the sampled key range is dense, else the slot of the key in a small open-addressing table
+// of the CTA ("sorted-hashed": sparse integer keys, float keys, several key columns).
 // At the end the CTA merges its table into the HBM group table (find-or-insert + one atomic per cell and CTA).
 // The reference runs this shape through compute_shared_memory_aggs / global atomics
 // (/root/reference/cpp/src/groupby/hash/compute_shared_memory_aggs.cu, compute_global_memory_aggs.cuh).
@@ -212,7 +214,8 @@ __global__ void __launch_bounds__(kSortedThreads, 2) aggregate_sorted_kernel(con
   const uint32_t G     = p.groups;
   const int A          = p.num_accs;
   uint64_t* tab     = reinterpret_cast<uint64_t*>(smem_raw);           // [A][G] the CTA's accumulators
-  uint64_t* sval    = tab + (size_t)A * G;                              // [NC][T] canonical values of the tile, sorted by group
+  uint64_t* skey    = tab + (size_t)A * G;                              // [G] hashed mode: the key that owns each slot (kEmpty: free)
+  uint64_t* sval    = skey + (p.hashed ? G : 0);                        // [NC][T] canonical values of the tile, sorted by group
   uint32_t* cnt     = reinterpret_cast<uint32_t*>(sval + (size_t)NC * T);  // [G] rows per group in this tile
   uint32_t* start   = cnt + G;                                          // [G + 1] first sorted position of every group
   uint32_t* rows    = start + G + 1;                                    // [G] != 0: the CTA met the group
@@ -223,7 +226,7 @@ __global__ void __launch_bounds__(kSortedThreads, 2) aggregate_sorted_kernel(con
   const int tid  = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   for (uint32_t i = tid; i < (uint32_t)A * G; i += NT) tab[i] = sorted_identity(p.acc[i / G].op);
-  for (uint32_t g = tid; g < G; g += NT) { cnt[g] = 0; rows[g] = 0; }
+  for (uint32_t g = tid; g < G; g += NT) { cnt[g] = 0; rows[g] = 0; if (p.hashed) skey[g] = kEmpty; }
   if (tid == 0) { wsum[31] = 0; start[0] = 0; }
   const uint32_t gpt  = (G + NT - 1) / NT;   // groups owned per thread
   const uint32_t g0   = min(tid * gpt, G);
@@ -261,8 +264,24 @@ __global__ void __launch_bounds__(kSortedThreads, 2) aggregate_sorted_kernel(con
     for (int r = 0; r < kSortedRows; ++r) {
       gid[r] = kNone; vb[r] = 0; rank[r] = 0;
       if ((ok >> r) & 1) {
-        const uint64_t d = (k[r] ^ p.key_flip) - p.key_base;
-        if (d < G) gid[r] = (uint32_t)d; else byp |= 1u << r;
+        if (p.hashed) {
+          // the group id is the SLOT of the key in the CTA's open-addressing table (64-bit ATOMS.CAS only for the first row of
+          // a group); a key that finds no slot within 32 probes (more groups than estimated) goes to the HBM table
+          uint32_t slot = slot_hash32(k[r]) & (G - 1);
+          gid[r] = kNone;
+          if (k[r] != kEmpty) {
+            for (int probe = 0; probe < 32; ++probe) {
+              unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(skey + slot);
+              if (cur == kEmpty) cur = atomicCAS(reinterpret_cast<unsigned long long*>(skey + slot), (unsigned long long)kEmpty, (unsigned long long)k[r]);
+              if (cur == k[r] || cur == kEmpty) { gid[r] = slot; break; }
+              slot = (slot + 1) & (G - 1);
+            }
+          }
+          if (gid[r] == kNone) byp |= 1u << r;
+        } else {
+          const uint64_t d = (k[r] ^ p.key_flip) - p.key_base;
+          if (d < G) gid[r] = (uint32_t)d; else byp |= 1u << r;
+        }
       }
     }
 #pragma unroll
@@ -370,7 +389,7 @@ __global__ void __launch_bounds__(kSortedThreads, 2) aggregate_sorted_kernel(con
   for (uint32_t i = tid; i < G; i += NT) {
     const uint32_t g = (uint32_t)(((uint64_t)i + (uint64_t)blockIdx.x * 61u) % G);
     if (rows[g] == 0) continue;
-    const uint64_t key  = (p.key_base + g) ^ p.key_flip;
+    const uint64_t key  = p.hashed ? skey[g] : (p.key_base + g) ^ p.key_flip;
     const uint64_t slot = find_or_insert(p.a.table, key, 0);
     if (slot == kNoSlot) continue;
     for (int a = 0; a < A; ++a) atomic_fold(p.acc[a].op, p.acc[a].cells, slot, tab[a * G + g]);
@@ -379,9 +398,9 @@ __global__ void __launch_bounds__(kSortedThreads, 2) aggregate_sorted_kernel(con
 
 }  // namespace
 
-size_t sorted_smem_bytes(uint32_t groups, int num_accs, int num_cols)
+size_t sorted_smem_bytes(uint32_t groups, int num_accs, int num_cols, bool hashed)
 {
-  return (size_t)num_accs * groups * 8 + (size_t)num_cols * kSortedTile * 8 + (size_t)groups * 4 + ((size_t)groups + 1) * 4 +
+  return (size_t)num_accs * groups * 8 + (hashed ? (size_t)groups * 8 : 0) + (size_t)num_cols * kSortedTile * 8 + (size_t)groups * 4 + ((size_t)groups + 1) * 4 +
          (size_t)groups * 4 + 32 * 4 + (kSortedTile / kSortedHeavy) * 2 + kSortedTile + 16;
 }
 
@@ -395,7 +414,7 @@ cudaError_t launch_aggregate_sorted(const SortedParams& p, int num_sms, cudaStre
     case 4: kern = aggregate_sorted_kernel<4>; break;
     default: return cudaErrorInvalidValue;
   }
-  const size_t bytes = sorted_smem_bytes(p.groups, p.num_accs, p.num_cols < 1 ? 1 : p.num_cols);
+  const size_t bytes = sorted_smem_bytes(p.groups, p.num_accs, p.num_cols < 1 ? 1 : p.num_cols, p.hashed != 0);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
   if (e != cudaSuccess) return e;
   int per_sm = 1;

@@ -31,14 +31,15 @@ struct SortedParams {
   SortedCol col[kSortedMaxCols];
   SortedAcc acc[kMaxAccs];
   int32_t num_cols, num_accs;
-  uint32_t groups;           // dense ids [0, groups): id = (key ^ key_flip) - key_base
+  uint32_t groups;           // dense ids [0, groups): id = (key ^ key_flip) - key_base; hashed: slots of the CTA's key table (power of two)
+  int32_t hashed;            // != 0: id = slot of the key in a shared-memory open-addressing table (any one-word key image)
   int32_t key_mode;          // 2: one unmasked 8-byte integer key column, 1: one unmasked integer-like key column, 0: pack_key
   uint64_t key_flip, key_base;
   int32_t any_mask;          // some value column carries a validity mask
   int32_t fast8;             // every value column is 8 bytes wide without a mask (int64 / uint64 / float64): plain 64-bit loads
 };
 
-size_t sorted_smem_bytes(uint32_t groups, int num_accs, int num_cols);
+size_t sorted_smem_bytes(uint32_t groups, int num_accs, int num_cols, bool hashed = false);
 cudaError_t launch_aggregate_sorted(const SortedParams& p, int num_sms, cudaStream_t s);
 
 }  // namespace bgb

@@ -118,8 +118,8 @@ typedef struct bgb_options {
   int32_t force_path;        /* 0 auto, 1 global-table kernel only, 2 shared-memory hashed pre-aggregation, 3 partitioned,
                                 4 shared-memory (direct-address variant allowed), 5 tiny-cardinality kernel (shared-memory
                                 accumulators), 6 tiny-cardinality kernel with register accumulators (<= 8 groups), 7 bucketed (radix scatter
-                                into fixed-capacity buckets + one shared-memory table slice per bucket), 8 tile-sorting kernel (dense integer
-                                key range of a few thousand ids, any accumulators but ARGMIN/ARGMAX) */
+                                into fixed-capacity buckets + one shared-memory table slice per bucket), 8 tile-sorting kernel (one-word key image:
+                                dense integer range of a few thousand ids, else a per-CTA hash table; any accumulators but ARGMIN/ARGMAX) */
   int32_t capacity_log2;     /* 0 auto; else global table has 2^capacity_log2 slots */
   int32_t sample_rows;       /* 0 auto (65536) rows sampled by the cardinality estimator */
   int32_t profile;           /* != 0: bracket every kernel with CUDA events on the call's stream (bgb_groupby_profile) */

@@ -64,14 +64,8 @@ def test_masked_keys_several_key_columns(include):
     k2 = H(rng.integers(0, 7, N).astype(np.int8))
     v = H(rng.standard_normal(N), rng.random(N) > 0.1)
     w = H(rng.integers(-1000, 1000, N).astype(np.int64))
-    # int16 + int8 fields leave holes in the packed image: a 24-bit range does not fit the dense ids unless the sample is narrow
-    # -> this shape is served only when the packed range fits; forced runs must say so instead of guessing
-    import cudf_b200 as cb
-    try:
-        _check([k1, k2], [v, w], [(0, "mean", 1), (0, "min", 1), (1, "sum", 1), (1, "count_all", 1)], include=include, name="2 keys")
-    except cb.UnsupportedError:
-        G, path = gpu_util.compare_with_oracle([k1, k2], [v, w], [(0, "mean", 1), (0, "min", 1), (1, "sum", 1), (1, "count_all", 1)], include_null_keys=include)
-        assert path != "sorted"
+    # int16 + int8 fields leave holes in the packed image (a 24-bit range): not dense, so the ids come from the CTA's hash table
+    _check([k1, k2], [v, w], [(0, "mean", 1), (0, "min", 1), (1, "sum", 1), (1, "count_all", 1)], include=include, name="2 keys", expect="sorted-hashed")
 
 
 def test_single_masked_key_column_exclude_and_include():
@@ -81,7 +75,7 @@ def test_single_masked_key_column_exclude_and_include():
     _check([k], [v], [(0, "sum", 1), (0, "mean", 1), (0, "max", 1)], include=False, name="masked key/exclude")
     # INCLUDE puts the null flag at bit 32 of the image: the range no longer fits, the automatic plan takes another path
     G, path = gpu_util.compare_with_oracle([k], [v], [(0, "sum", 1)], include_null_keys=True, name="masked key/include")
-    assert G == 1001 and path != "sorted"
+    assert G == 1001 and path == "sorted-hashed", path
 
 
 def test_skewed_keys_heavy_groups_take_a_warp():
@@ -163,3 +157,58 @@ def test_repacked_keys_all_null_column():
     assert G == 100
     G, path = gpu_util.compare_with_oracle([k1, k2], [v], [(0, "mean", 1)], include_null_keys=False, name="repacked/all-null column/exclude")
     assert G == 0
+
+
+# ---- hashed variant: the group id is the key's slot in a small shared-memory hash table of the CTA
+
+def test_hashed_sparse_integer_keys_automatic():
+    rng = np.random.default_rng(20)
+    pool = rng.integers(-(1 << 60), 1 << 60, 500).astype(np.int64)
+    k = H(pool[rng.integers(0, 500, N)])
+    v = H(rng.standard_normal(N), rng.random(N) > 0.1)
+    w = H(rng.integers(-1000, 1000, N).astype(np.int32))
+    aggs = [(0, "mean", 1), (0, "std", 1), (0, "min", 1), (1, "sum", 1), (1, "max", 1)]
+    assert _check([k], [v, w], aggs, name="hashed/sparse", force=False, expect="sorted-hashed") == 500
+
+
+@pytest.mark.parametrize("include", [False, True])
+def test_hashed_float_keys_with_nan_and_negative_zero(include):
+    # float32 keys: -0.0 == +0.0 and every NaN payload is one key (the image is canonicalised before it is hashed)
+    rng = np.random.default_rng(21)
+    pool = np.concatenate([rng.standard_normal(300), [0.0, -0.0, np.nan, np.inf, -np.inf]]).astype(np.float32)
+    kd = pool[rng.integers(0, len(pool), N)]
+    other_nan = np.frombuffer(np.uint32(0xFFC00001).tobytes(), dtype=np.float32)[0]
+    kd[np.isnan(kd) & (rng.random(N) < 0.5)] = other_nan
+    k = H(kd, rng.random(N) > 0.03)
+    v = H(rng.integers(0, 1000, N).astype(np.float64))
+    _check([k], [v], [(0, "sum", 1), (0, "max", 1), (0, "count_all", 1)], include=include, name=f"hashed/float keys/{include}", force=False, expect="sorted-hashed")
+
+
+@pytest.mark.parametrize("include", [False, True])
+def test_hashed_two_key_columns_with_masks(include):
+    rng = np.random.default_rng(22)
+    k1 = H(rng.integers(0, 50, N).astype(np.int16), rng.random(N) > 0.05)
+    k2 = H(rng.integers(0, 7, N).astype(np.int8), rng.random(N) > 0.5)
+    v = H(rng.standard_normal(N), rng.random(N) > 0.1)
+    w = H(rng.integers(-1000, 1000, N).astype(np.int64))
+    _check([k1, k2], [v, w], [(0, "mean", 1), (0, "min", 1), (1, "sum", 1), (1, "count_all", 1)], include=include, name="hashed/2 keys", expect="sorted-hashed")
+
+
+def test_hashed_more_groups_than_slots_overflow_to_the_hbm_table():
+    # 20 000 distinct sparse keys against at most 4096 slots per CTA: most rows bypass to the HBM table; still exact
+    rng = np.random.default_rng(23)
+    pool = rng.integers(-(1 << 60), 1 << 60, 20_000).astype(np.int64)
+    pool[:2] = [-1, 0]  # -1: image of the EMPTY sentinel
+    k = H(pool[rng.integers(0, 20_000, N)])
+    v = H(rng.integers(-100, 100, N).astype(np.int64), rng.random(N) > 0.2)
+    G = _check([k], [v], [(0, "sum", 1), (0, "count_valid", 1), (0, "min", 1), (0, "sum_of_squares", 1)], name="hashed/overflow", expect="sorted-hashed")
+    assert G == len(np.unique(k.data))
+
+
+def test_hashed_skewed_keys():
+    rng = np.random.default_rng(24)
+    pool = rng.integers(-(1 << 40), 1 << 40, 500).astype(np.int64)
+    kd = pool[rng.integers(0, 500, N)]
+    kd[rng.random(N) < 0.7] = pool[3]
+    v = H(rng.integers(0, 1000, N).astype(np.float64), rng.random(N) > 0.25)
+    _check([H(kd)], [v], [(0, "sum", 1), (0, "variance", 1), (0, "max", 1)], name="hashed/skew", force=False, expect="sorted-hashed")

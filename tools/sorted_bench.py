@@ -49,3 +49,10 @@ for g in (300, 1000, 1900):
     run(f"1 int64 key, {g} groups, f64 SUM+MIN+MAX", keys, [cb.GroupByRequest(c, [A.sum(), A.min(), A.max()])])
 keys = cb.Table([gen(1, 32), gen(2, 32)])
 run("C1: 2 int64 keys 32x32, 2 f64 MEAN", keys, [cb.GroupByRequest(c, [A.mean()]), cb.GroupByRequest(d, [A.mean()])])
+# sparse keys: ids come from the CTA's hash table ("sorted-hashed")
+for g in (300, 600):
+    t = torch.empty(n, dtype=torch.int64, device=dev)
+    _lib.check(L.bgb_gen_uniform_int(C.c_void_p(t.data_ptr()), cb.TypeId.INT64, n, 5, 0, g, 0, s))
+    t.mul_(0x9E3779B97F4A7C15 - (1 << 64)).bitwise_xor_(t >> 29)   # spread the ids over the whole int64 range
+    keys = cb.Table([cb.Column(t)])
+    run(f"1 sparse int64 key, {g} groups, 2 f64 MEAN", keys, [cb.GroupByRequest(c, [A.mean()]), cb.GroupByRequest(d, [A.mean()])])
