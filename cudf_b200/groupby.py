@@ -92,7 +92,7 @@ def emit_handle(L, handle, G, nk, aggs_per_request, device, stream):
             t, sc, nl = C.c_int32(), C.c_int32(), C.c_int32()
             _lib.check(L.bgb_groupby_key_info(handle, i, C.byref(t), C.byref(sc), C.byref(nl)))
             data = torch.empty(G, dtype=torch_dtype(t.value), device=device)
-            mask = torch.zeros((G + 31) // 32, dtype=torch.int32, device=device) if nl.value else None
+            mask = torch.empty((G + 31) // 32, dtype=torch.int32, device=device) if nl.value else None  # emit writes every word
             key_cols.append(Column(data, mask, 0, t.value, scale=sc.value))
             okeys[i] = _lib.MutableColumn(t.value, G, data.data_ptr() if G else None,
                                           mask.data_ptr() if mask is not None and G else None, 0, 0)
@@ -106,7 +106,7 @@ def emit_handle(L, handle, G, nk, aggs_per_request, device, stream):
                 t, sc, nl = C.c_int32(), C.c_int32(), C.c_int32()
                 _lib.check(L.bgb_groupby_result_info(handle, ri, ai, C.byref(t), C.byref(sc), C.byref(nl)))
                 data = torch.empty(G, dtype=torch_dtype(t.value), device=device)
-                mask = torch.zeros((G + 31) // 32, dtype=torch.int32, device=device) if nl.value else None
+                mask = torch.empty((G + 31) // 32, dtype=torch.int32, device=device) if nl.value else None  # emit writes every word
                 cols.append(Column(data, mask, 0, t.value, scale=sc.value))
                 ores[k] = _lib.MutableColumn(t.value, G, data.data_ptr() if G else None,
                                              mask.data_ptr() if mask is not None and G else None, 0, 0)
