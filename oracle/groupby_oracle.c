@@ -78,6 +78,12 @@ int orc_target_type(int t, int k)
       if (is_integral(t)) return ORC_INT64;
       if (is_floating(t)) return t;
       return -1;
+    /* SUM_OVERFLOW: struct{sum: Source, overflow: bool} for signed integers and decimals
+     * (device_aggregators.cuh:131-160, output_utils.cu:83-104; decimal128 is outside this path) */
+    case ORC_SUM_OVERFLOW:
+      return (t == ORC_INT8 || t == ORC_INT16 || t == ORC_INT32 || t == ORC_INT64 || is_decimal(t)) ? t : -1;
+    case ORC_SUM_OVERFLOW_FLAG:
+      return (t == ORC_INT8 || t == ORC_INT16 || t == ORC_INT32 || t == ORC_INT64 || is_decimal(t)) ? ORC_BOOL8 : -1;
     case ORC_MEAN:
       if (is_timestamp(t)) return -1;
       if (is_duration(t) || is_decimal(t)) return t;
@@ -226,6 +232,17 @@ static inline void acc_update(acc_t* a, int kind, const orc_column* v, int64_t r
       else if (cls == CLS_F32) { float x = load_f32(v, r); a->f += x; a->f2 += x * x; }
       else { uint64_t x = (uint64_t)load_i64(v, r); a->i += x; a->i2 += x * x; }
       break;
+    case ORC_SUM_OVERFLOW: case ORC_SUM_OVERFLOW_FLAG: {
+      /* The reference adds with atomic_add and raises the flag when an add overflows the Source type, after which the group
+       * ignores further rows (device_aggregators.cuh:150-158): which prefix overflows depends on the order the atomics land
+       * in. The oracle keeps the EXACT total (i2:i as a 128-bit integer) and reports the order-independent outcome: the flag
+       * is set iff the total does not fit the Source type -- every order overflows then, and when it fits some order of the
+       * atomics sees no overflow at all. The sum child of an overflowed group is unspecified in the reference. */
+      __int128 tot = (__int128)(((unsigned __int128)a->i2 << 64) | a->i);
+      tot += (__int128)load_i64(v, r);
+      a->i = (uint64_t)tot; a->i2 = (uint64_t)((unsigned __int128)tot >> 64);
+      break;
+    }
     case ORC_PRODUCT:
       if (cls == CLS_F64) a->d *= load_f64(v, r); else if (cls == CLS_F32) a->f *= load_f32(v, r);
       else a->i *= (uint64_t)load_i64(v, r);
@@ -263,6 +280,12 @@ static void acc_merge(acc_t* a, const acc_t* b, int kind, const orc_column* v)
 {
   cls_t cls = type_class(v->type_id);
   switch (kind) {
+    case ORC_SUM_OVERFLOW: case ORC_SUM_OVERFLOW_FLAG: {
+      __int128 ta = (__int128)(((unsigned __int128)a->i2 << 64) | a->i), tb = (__int128)(((unsigned __int128)b->i2 << 64) | b->i);
+      ta += tb;
+      a->i = (uint64_t)ta; a->i2 = (uint64_t)((unsigned __int128)ta >> 64);
+      break;
+    }
     case ORC_PRODUCT: a->i *= b->i; a->d *= b->d; a->f *= b->f; break;
     case ORC_MIN:
       if (cls == CLS_F64) { if (b->d < a->d) a->d = b->d; } else if (cls == CLS_F32) { if (b->f < a->f) a->f = b->f; }
@@ -508,6 +531,15 @@ int orc_groupby(const orc_column* keys, int n_keys, int include_null_keys, const
           valid = has_nulls ? (A->n > 0) : 1;
           break;
         case ORC_ARGMIN: case ORC_ARGMAX: ri = (uint64_t)(int64_t)A->arg; valid = has_nulls ? (A->n > 0) : 1; break;
+        case ORC_SUM_OVERFLOW: case ORC_SUM_OVERFLOW_FLAG: {
+          __int128 tot = (__int128)(((unsigned __int128)A->i2 << 64) | A->i);
+          int bits = 8 * orc_type_size(v->type_id);
+          __int128 lo = -((__int128)1 << (bits - 1)), hi = ((__int128)1 << (bits - 1)) - 1;
+          if (kind == ORC_SUM_OVERFLOW) ri = (uint64_t)tot; /* low bits; store_typed keeps the Source width */
+          else ri = (tot < lo || tot > hi) ? 1 : 0;
+          valid = has_nulls ? (A->n > 0) : 1;
+          break;
+        }
         case ORC_MEAN: {
           /* hash_compound_agg_finalizer.cu:94-133: double(sum)/double(count), null where count == 0 */
           if (tt == ORC_FLOAT64) {

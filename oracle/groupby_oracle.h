@@ -38,7 +38,10 @@ enum {
 /* cudf::aggregation::Kind values (cpp/include/cudf/aggregation.hpp:78-121) */
 enum {
   ORC_SUM = 0, ORC_SUM_OVERFLOW = 1, ORC_PRODUCT = 2, ORC_MIN = 3, ORC_MAX = 4, ORC_COUNT_VALID = 5, ORC_COUNT_ALL = 6,
-  ORC_SUM_OF_SQUARES = 9, ORC_MEAN = 10, ORC_M2 = 11, ORC_VARIANCE = 12, ORC_STD = 13, ORC_ARGMAX = 16, ORC_ARGMIN = 17
+  ORC_SUM_OF_SQUARES = 9, ORC_MEAN = 10, ORC_M2 = 11, ORC_VARIANCE = 12, ORC_STD = 13, ORC_ARGMAX = 16, ORC_ARGMIN = 17,
+  /* oracle-internal: the BOOL8 `overflow` child of a SUM_OVERFLOW result (ORC_SUM_OVERFLOW itself yields the `sum` child,
+   * typed like the values; the struct's validity is the validity of either) */
+  ORC_SUM_OVERFLOW_FLAG = 101
 };
 
 /* host-memory column: same field meaning as cudf::column_view (column_view.hpp:236-243) */

@@ -27,7 +27,10 @@ NP_OF_TYPE_ID = {
 }
 # cudf::aggregation::Kind (cpp/include/cudf/aggregation.hpp:78-121)
 KIND = {"sum": 0, "product": 2, "min": 3, "max": 4, "count_valid": 5, "count_all": 6, "sum_of_squares": 9,
-        "mean": 10, "m2": 11, "variance": 12, "std": 13, "argmax": 16, "argmin": 17}
+        "mean": 10, "m2": 11, "variance": 12, "std": 13, "argmax": 16, "argmin": 17,
+        # SUM_OVERFLOW yields struct{sum, overflow}: "sum_overflow" is the sum child (typed like the values), "sum_overflow_flag" the
+        # BOOL8 overflow child; both carry the struct's validity
+        "sum_overflow": 1, "sum_overflow_flag": 101}
 
 
 class _Col(C.Structure):
