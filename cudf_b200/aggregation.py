@@ -23,6 +23,7 @@ class Aggregation:
 
 
 def sum(): return Aggregation(Kind.SUM)  # noqa: A001,E704
+def sum_overflow(): return Aggregation(Kind.SUM_OVERFLOW)  # noqa: E704  (struct{sum, overflow} result: Column.children)
 def product(): return Aggregation(Kind.PRODUCT)  # noqa: E704
 def min(): return Aggregation(Kind.MIN)  # noqa: A001,E704
 def max(): return Aggregation(Kind.MAX)  # noqa: A001,E704

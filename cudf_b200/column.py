@@ -65,6 +65,7 @@ class Column:
         self.size = (data.numel() - offset) if size is None else size
         self.null_count = null_count if mask is not None else 0
         self.scale = scale
+        self.children = []  # STRUCT columns (SUM_OVERFLOW results): [sum Column, overflow Column]; `data` is then empty
 
     # -- construction helpers (tests, examples)
     @staticmethod

@@ -39,7 +39,11 @@ enum AccOp : uint8_t {
   ACC_ARGMIN,     // (ordered value image << 32 | row) for <= 32-bit sources
   ACC_ARGMAX,
   ACC_ARGROW_MIN, // ARGMIN / ARGMAX of 64-bit values: a 4-byte row-number cell filled by a SECOND pass over the rows once the
-  ACC_ARGROW_MAX  // group's MIN / MAX cell (AccDesc::aux) is final: smallest row whose value equals the extremum
+  ACC_ARGROW_MAX, // group's MIN / MAX cell (AccDesc::aux) is final: smallest row whose value equals the extremum
+  // SUM_OVERFLOW keeps the EXACT total of a signed column as two wrapping 64-bit sums, total = hi * 2^32 + lo (neither can wrap
+  // below 2^31 rows), so the overflow flag does not depend on the order the atomics land in
+  ACC_SUM_LO32,   // sum of the low 32 bits of every value, zero-extended
+  ACC_SUM_HI32    // sum of (value >> 32), arithmetic
 };
 
 __host__ __device__ inline int acc_cell_bytes(uint8_t op)
@@ -103,7 +107,9 @@ enum OutOp : uint8_t {
   OUT_M2,
   OUT_VAR,
   OUT_STD,
-  OUT_ARG         // low 32 bits of the packed (value,row) cell
+  OUT_ARG,        // low 32 bits of the packed (value,row) cell
+  OUT_SUMOV_SUM,  // SUM_OVERFLOW child 0: low bits of hi * 2^32 + lo in the source width (a = lo cells, b = hi cells); carries the struct mask
+  OUT_SUMOV_FLAG  // SUM_OVERFLOW child 1 (BOOL8): the exact total does not fit the source type (shift = source width in bytes)
 };
 
 struct OutDesc {

@@ -278,6 +278,8 @@ __device__ __forceinline__ void apply_value(uint8_t op, uint8_t src, void* cells
     case ACC_PROD_F32: atomic_mul_f32(c32, __uint_as_float((uint32_t)raw)); break;
     case ACC_MIN: { unsigned long long v = ordered_image(raw, src); if (v < *reinterpret_cast<volatile unsigned long long*>(c64)) atomicMin(c64, v); break; }
     case ACC_MAX: { unsigned long long v = ordered_image(raw, src); if (v > *reinterpret_cast<volatile unsigned long long*>(c64)) atomicMax(c64, v); break; }
+    case ACC_SUM_LO32: atomicAdd(c64, (unsigned long long)(uint32_t)raw_to_i64(raw, src)); break;
+    case ACC_SUM_HI32: atomicAdd(c64, (unsigned long long)(raw_to_i64(raw, src) >> 32)); break;
     case ACC_ARGMIN: atomicMin(c64, (unsigned long long)((ordered_image(raw, src) << 32) | (uint32_t)row)); break;
     case ACC_ARGMAX: atomicMax(c64, (unsigned long long)((ordered_image(raw, src) << 32) | (0xFFFFFFFFu - (uint32_t)row))); break;
     default: break;

@@ -126,6 +126,7 @@ static bool sorted_plan(const Plan& pl, SortedParams* out)
   for (size_t i = 0; i < pl.accs.size(); ++i) {
     const AccPlan& a = pl.accs[i];
     if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX || a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX) return false;
+    if (a.op == ACC_SUM_LO32 || a.op == ACC_SUM_HI32) return false;  // SUM_OVERFLOW: generic / bucketed kernels
     int col = -1;
     if (a.value_col >= 0) {
       if (a.value_col >= 64) return false;

@@ -813,6 +813,13 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
   }
   for (int i = 0; i < nr; ++i) {
     if (out_results[i].size < G || !out_results[i].data) return set_error(BGB_INVALID_ARGUMENT, "out_results[%d] too small", i);
+    if (pl.outs[i].op == OUT_SUMOV_SUM) {  // STRUCT result: data = the caller's two child descriptors {sum, overflow}
+      bgb_mutable_column* ch = (bgb_mutable_column*)out_results[i].data;
+      for (int c = 0; c < 2; ++c) {
+        if (ch[c].size < G || !ch[c].data) return set_error(BGB_INVALID_ARGUMENT, "out_results[%d]: struct child %d too small", i, c);
+        ch[c].null_count = 0;
+      }
+    }
     if (pl.outs[i].nullable && !out_results[i].null_mask) return set_error(BGB_INVALID_ARGUMENT, "out_results[%d] needs a null mask", i);
   }
   const int total = nk + nr;
@@ -841,6 +848,12 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
     d.cnt = o.acc_cnt >= 0 ? (const int32_t*)pl.accs[o.acc_cnt].cells : nullptr;
     d.ddof = o.ddof; d.op = o.op; d.src = o.src; d.out_width = o.out_width; d.acc_op = o.acc_op; d.null_bit = -1;
     any_nullable |= o.nullable;
+    if (o.op == OUT_SUMOV_SUM) {  // two children: the sum (it also writes the struct's mask) and the BOOL8 overflow flag
+      const bgb_mutable_column* ch = (const bgb_mutable_column*)out_results[i].data;
+      d.out = ch[0].data;
+      descs.push_back(d);
+      d.op = OUT_SUMOV_FLAG; d.out = ch[1].data; d.out_mask = nullptr; d.null_count = nullptr; d.shift = o.out_width; d.out_width = 1;
+    }
     descs.push_back(d);
   }
   h->prof.begin("emit");

@@ -113,6 +113,7 @@ extern "C" int bgb_groupby_host(const bgb_column_view* host_keys, int32_t num_ke
   if (!hk || !hr) return fail(set_error(BGB_OUT_OF_MEMORY, "host result arrays"));
   const size_t words = ((size_t)G + 31) / 32;
   auto prepare = [&](bgb_mutable_column& m, bgb_host_column& hc, int32_t type_id, int32_t nullable) -> int {
+    if (type_id == BGB_STRUCT) return set_error(BGB_UNSUPPORTED, "bgb_groupby_host: struct results (SUM_OVERFLOW) are served by bgb_groupby_build / emit only");
     const int w = type_width(type_id);
     m = bgb_mutable_column{type_id, G, nullptr, nullptr, 0, 0};
     hc.type_id = type_id; hc.size = G;

@@ -158,6 +158,17 @@ __global__ void __launch_bounds__(256) emit_kernel(const __grid_constant__ EmitP
         case OUT_COPY_F32: bits = reinterpret_cast<const uint32_t*>(d.a)[slot]; valid = n > 0; break;
         case OUT_MINMAX: bits = ordered_decode(reinterpret_cast<const uint64_t*>(d.a)[slot], d.src); valid = n > 0; break;
         case OUT_COUNT: bits = (uint32_t)reinterpret_cast<const int32_t*>(d.a)[slot]; break;
+        case OUT_SUMOV_SUM: case OUT_SUMOV_FLAG: {
+          const uint64_t lo = reinterpret_cast<const uint64_t*>(d.a)[slot];
+          const int64_t hi  = (int64_t)reinterpret_cast<const uint64_t*>(d.b)[slot];
+          valid = n > 0;
+          if (d.op == OUT_SUMOV_SUM) { bits = ((uint64_t)hi << 32) + lo; break; }
+          const __int128 total = ((__int128)hi << 32) + (__int128)lo;
+          const int vbits      = 8 * (int)d.shift;
+          const __int128 vmin = -((__int128)1 << (vbits - 1)), vmax = ((__int128)1 << (vbits - 1)) - 1;
+          bits = (total < vmin || total > vmax) ? 1 : 0;
+          break;
+        }
         case OUT_ARG: {
           const bool rowcell = d.acc_op == ACC_ARGROW_MIN || d.acc_op == ACC_ARGROW_MAX;  // 64-bit values: the cell IS the row
           uint32_t lo = rowcell ? reinterpret_cast<const uint32_t*>(d.a)[slot] : (uint32_t)reinterpret_cast<const uint64_t*>(d.a)[slot];

@@ -81,8 +81,9 @@ int32_t target_type(int32_t t, int32_t k)
 
 static bool kind_is_hash_capable(int32_t k)
 {
-  // is_hash_aggregation (/root/reference/cpp/src/groupby/common/utils.hpp:66-86) minus SUM_OVERFLOW (not built yet)
+  // is_hash_aggregation (/root/reference/cpp/src/groupby/common/utils.hpp:66-86)
   switch (k) {
+    case BGB_SUM_OVERFLOW:
     case BGB_SUM: case BGB_PRODUCT: case BGB_MIN: case BGB_MAX: case BGB_COUNT_VALID: case BGB_COUNT_ALL: case BGB_SUM_OF_SQUARES:
     case BGB_MEAN: case BGB_M2: case BGB_VARIANCE: case BGB_STD: case BGB_ARGMIN: case BGB_ARGMAX: case BGB_MERGE_COUNT: return true;
     default: return false;
@@ -220,6 +221,15 @@ int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_nul
             break;
           }
           o.acc_op = kind == BGB_ARGMIN ? ACC_ARGMIN : ACC_ARGMAX; o.acc_a = get_acc(plan, vc, o.acc_op); o.op = OUT_ARG; break;
+        case BGB_SUM_OVERFLOW:
+          // struct{sum: Source, overflow: bool} (device_aggregators.cuh:131-160, output_utils.cu:83-104). The reference raises the
+          // flag when one atomic add overflows, which depends on the order the adds land in; here the EXACT total is kept (two
+          // 64-bit sums) and the flag says whether it fits the Source type -- the outcome every order agrees on when it is set.
+          if (rank_independent) return set_error(BGB_UNSUPPORTED, "SUM_OVERFLOW is not served by the streaming / distributed tables");
+          if (o.type_id != BGB_STRUCT) return set_error(BGB_INVALID_ARGUMENT, "request %d: SUM_OVERFLOW needs a signed integer or decimal32/64 column", r);
+          o.acc_op = ACC_SUM_LO32; o.acc_a = get_acc(plan, vc, ACC_SUM_LO32); o.acc_b = get_acc(plan, vc, ACC_SUM_HI32);
+          o.op = OUT_SUMOV_SUM; o.out_width = (uint8_t)type_width(rq.values.type_id);
+          break;
         case BGB_MEAN:
           // MEAN -> SUM + COUNT_VALID (extract_single_pass_aggs.cpp:62-73), finalised as double(sum)/count
           o.acc_op = sum_op(src); o.acc_a = get_acc(plan, vc, o.acc_op); o.acc_cnt = need_cnt();

@@ -13,7 +13,7 @@ import torch
 
 from . import _lib
 from .aggregation import NullPolicy
-from .column import Column, Table, torch_dtype
+from .column import Column, Table, TypeId, torch_dtype
 
 
 class GroupByRequest:
@@ -72,7 +72,8 @@ class GroupBy:
                                                C.byref(handle), C.byref(ngroups)))
             try:
                 self.last_path = L.bgb_groupby_path(handle).decode()
-                key_cols, res_cols = emit_handle(L, handle, ngroups.value, nk, [len(r._aggregations) for r in requests], device, stream)
+                key_cols, res_cols = emit_handle(L, handle, ngroups.value, nk, [len(r._aggregations) for r in requests], device, stream,
+                                                 struct_child_types=[r._values.type_id for r in requests])
                 if opt.profile:
                     self.last_profile = _read_profile(L, handle)
             finally:
@@ -81,10 +82,11 @@ class GroupBy:
         return Table(key_cols), [Table(cols) for cols in res_cols]
 
 
-def emit_handle(L, handle, G, nk, aggs_per_request, device, stream):
+def emit_handle(L, handle, G, nk, aggs_per_request, device, stream, struct_child_types=None):
     """Caller-allocated outputs (the role of the caller's rmm memory resource) + bgb_groupby_emit for a built handle.
     Returns ([key Column], [[result Column] per request])."""
     sptr = C.c_void_p(stream.cuda_stream)
+    keep_alive = []
     with torch.cuda.stream(stream):
         okeys = (_lib.MutableColumn * max(nk, 1))()
         key_cols = []
@@ -105,8 +107,21 @@ def emit_handle(L, handle, G, nk, aggs_per_request, device, stream):
             for ai in range(na):
                 t, sc, nl = C.c_int32(), C.c_int32(), C.c_int32()
                 _lib.check(L.bgb_groupby_result_info(handle, ri, ai, C.byref(t), C.byref(sc), C.byref(nl)))
-                data = torch.empty(G, dtype=torch_dtype(t.value), device=device)
                 mask = torch.empty((G + 31) // 32, dtype=torch.int32, device=device) if nl.value else None  # emit writes every word
+                if t.value == TypeId.STRUCT:
+                    # SUM_OVERFLOW: struct{sum: value type, overflow: BOOL8}; `data` = the two child descriptors (bgb.h)
+                    vt = struct_child_types[ri] if struct_child_types else None
+                    kids = [torch.empty(G, dtype=torch_dtype(vt), device=device), torch.empty(G, dtype=torch.bool, device=device)]
+                    cdesc = (_lib.MutableColumn * 2)(_lib.MutableColumn(vt, G, kids[0].data_ptr() if G else None, None, 0, 0),
+                                                     _lib.MutableColumn(TypeId.BOOL8, G, kids[1].data_ptr() if G else None, None, 0, 0))
+                    keep_alive.append(cdesc)
+                    col = Column(torch.empty(0, dtype=torch.int8, device=device), mask, 0, t.value, size=G)
+                    col.children = [Column(kids[0], None, 0, vt, scale=sc.value), Column(kids[1], None, 0, TypeId.BOOL8)]
+                    cols.append(col)
+                    ores[k] = _lib.MutableColumn(t.value, G, C.cast(cdesc, C.c_void_p), mask.data_ptr() if mask is not None and G else None, 0, 0)
+                    k += 1
+                    continue
+                data = torch.empty(G, dtype=torch_dtype(t.value), device=device)
                 cols.append(Column(data, mask, 0, t.value, scale=sc.value))
                 ores[k] = _lib.MutableColumn(t.value, G, data.data_ptr() if G else None,
                                              mask.data_ptr() if mask is not None and G else None, 0, 0)

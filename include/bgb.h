@@ -93,6 +93,14 @@ typedef struct bgb_request {
   int32_t reserved;
 } bgb_request;
 
+/* A result of type BGB_STRUCT (SUM_OVERFLOW: struct{sum, overflow}, cudf/aggregation.hpp make_sum_overflow_aggregation,
+ * /root/reference/cpp/src/groupby/hash/output_utils.cu:83-104) is passed to bgb_groupby_emit as a bgb_mutable_column whose `data`
+ * points to an array of TWO caller-owned bgb_mutable_column children in HOST memory -- [0] the sum, typed like the values
+ * column, [1] the overflow flag, BGB_BOOL8 -- and whose null_mask is the struct's mask (children carry none).
+ * The overflow flag is set iff the EXACT total of the group does not fit the values type: the reference raises it when one
+ * of its atomic adds overflows (device_aggregators.cuh:150-158), which depends on the order the adds land in whenever only a
+ * prefix overflows; this library reports the outcome every order agrees on. The sum of an overflowed group is the wrapped
+ * total (unspecified in the reference). */
 /* caller-owned output column: data/null_mask sized for `size` rows (mask words = (size+31)/32, zero-filled not required).
  * null_mask may be NULL when bgb_groupby_result_info said nullable == 0. null_count is written by emit. */
 typedef struct bgb_mutable_column {

@@ -13,7 +13,7 @@ KIND_TO_AGG = {
     "sum": agg_mod.sum, "product": agg_mod.product, "min": agg_mod.min, "max": agg_mod.max,
     "count_valid": lambda: agg_mod.count(cb.NullPolicy.EXCLUDE), "count_all": lambda: agg_mod.count(cb.NullPolicy.INCLUDE),
     "sum_of_squares": agg_mod.sum_of_squares, "mean": agg_mod.mean, "m2": agg_mod.m2, "argmin": agg_mod.argmin,
-    "argmax": agg_mod.argmax,
+    "argmax": agg_mod.argmax, "sum_overflow": agg_mod.sum_overflow,
 }
 
 
