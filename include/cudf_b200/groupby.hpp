@@ -8,7 +8,9 @@
 
 #include <cuda_runtime_api.h>
 
+#include <array>
 #include <cstdint>
+#include <deque>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -154,6 +156,10 @@ class column {
   bool nullable() const { return _mask != nullptr; }
   void set_null_count(size_type n) { _null_count = n; }
   bgb_mutable_column abi_mutable() { return {static_cast<int32_t>(_type.id()), _size, _data, _mask, 0, 0}; }
+  // STRUCT columns (SUM_OVERFLOW results, column::child in cudf/column/column.hpp): children own their buffers, the parent the mask
+  size_type num_children() const { return static_cast<size_type>(_children.size()); }
+  column const& child(size_type i) const { return *_children.at(i); }
+  column& add_child(std::unique_ptr<column> c) { _children.push_back(std::move(c)); return *_children.back(); }
 
  private:
   data_type _type;
@@ -162,6 +168,7 @@ class column {
   uint32_t* _mask{nullptr};
   size_type _null_count{0};
   cudaStream_t _stream;
+  std::vector<std::unique_ptr<column>> _children;
 };
 
 class table_view {
@@ -196,6 +203,8 @@ struct groupby_aggregation {
 };
 inline std::unique_ptr<groupby_aggregation> make_agg(int32_t kind, int32_t ddof = 1) { return std::unique_ptr<groupby_aggregation>(new groupby_aggregation{kind, ddof}); }
 inline auto make_sum_aggregation() { return make_agg(BGB_SUM); }
+// struct{sum, overflow} result (cudf/aggregation.hpp make_sum_overflow_aggregation): child 0 typed like the values, child 1 BOOL8
+inline auto make_sum_overflow_aggregation() { return make_agg(BGB_SUM_OVERFLOW); }
 inline auto make_product_aggregation() { return make_agg(BGB_PRODUCT); }
 inline auto make_min_aggregation() { return make_agg(BGB_MIN); }
 inline auto make_max_aggregation() { return make_agg(BGB_MAX); }
@@ -254,12 +263,20 @@ class groupby {
       km.push_back(kcols.back()->abi_mutable());
     }
     std::vector<aggregation_result> results(requests.size());
+    std::deque<std::array<bgb_mutable_column, 2>> struct_children;  // (a deque keeps the descriptors where they are)
     for (size_t i = 0; i < requests.size(); ++i)
       for (size_t j = 0; j < requests[i].aggregations.size(); ++j) {
         int32_t t, s, nl;
         detail::throw_on(bgb_groupby_result_info(h, (int32_t)i, (int32_t)j, &t, &s, &nl));
         results[i].results.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream));
         rm.push_back(results[i].results.back()->abi_mutable());
+        if (static_cast<type_id>(t) == type_id::STRUCT) {  // SUM_OVERFLOW: `data` = the two child descriptors (bgb.h)
+          column& parent = *results[i].results.back();
+          column& sum    = parent.add_child(std::make_unique<column>(data_type{requests[i].values.type().id(), s}, n, false, stream));
+          column& flag   = parent.add_child(std::make_unique<column>(data_type{type_id::BOOL8}, n, false, stream));
+          struct_children.push_back({sum.abi_mutable(), flag.abi_mutable()});
+          rm.back().data = struct_children.back().data();
+        }
       }
     detail::throw_on(bgb_groupby_emit(h, km.data(), rm.data(), stream));
     for (size_t i = 0; i < kcols.size(); ++i) kcols[i]->set_null_count(km[i].null_count);

@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <limits>
 #include <numeric>
 
 #include "cudf_b200/groupby.hpp"
@@ -144,6 +145,28 @@ int main()
     reqs[0].aggregations.push_back(make_sum_aggregation());
     auto [tbl, res] = gb.aggregate(reqs);
     CHECK(tbl->num_rows() == 0 && res[0].results.size() == 2 && res[0].results[1]->type().id() == type_id::FLOAT32);
+  }
+  {  // sum_overflow_tests.cpp OverflowDetection (int32): struct{sum, overflow}; flags {true,false,true,true}, group 2 sums to 100
+    constexpr int32_t mx = std::numeric_limits<int32_t>::max(), mn = std::numeric_limits<int32_t>::min();
+    auto keys = column::from_host<K>(type_id::INT32, {1, 2, 3, 4, 1, 2, 2, 1, 3, 3, 2, 4, 4});
+    auto vals = column::from_host<int32_t>(type_id::INT32, {mx - 5, 10, 20, mn + 5, 10, 20, 30, mx - 5, mx - 5, 1, 40, -10, mn + 5});
+    groupby::groupby gb(table_view({keys->view()}));
+    std::vector<groupby::aggregation_request> reqs(1);
+    reqs[0].values = vals->view();
+    reqs[0].aggregations.push_back(make_sum_overflow_aggregation());
+    auto [tbl, res] = gb.aggregate(reqs);
+    column const& st = *res[0].results[0];
+    CHECK(st.type().id() == type_id::STRUCT && st.num_children() == 2 && !st.nullable());
+    CHECK(st.child(0).type().id() == type_id::INT32 && st.child(1).type().id() == type_id::BOOL8);
+    auto [k, kv] = tbl->get_column(0).to_host<K>();
+    auto [sum, sv] = st.child(0).to_host<int32_t>();
+    auto [flag, fv] = st.child(1).to_host<uint8_t>();
+    std::vector<std::pair<K, int>> got;
+    int32_t sum2 = 0;
+    for (size_t i = 0; i < k.size(); ++i) { got.push_back({k[i], (int)flag[i]}); if (k[i] == 2) sum2 = sum[i]; }
+    std::sort(got.begin(), got.end());
+    CHECK((got == std::vector<std::pair<K, int>>{{1, 1}, {2, 0}, {3, 1}, {4, 1}}));
+    CHECK(sum2 == 100);
   }
   {  // streaming_groupby_test.cpp MergeTwoObjects: worker1 {1,2,1}/{10,20,30} + worker2 {2,3}/{40,50} -> {1,2,3} / {40,60,50}
     auto mk = [] {
