@@ -54,3 +54,21 @@ def test_target_type_rules_match_oracle_and_reference(tid, kind, expect):
     assert L.bgb_target_type(tid, kind) == expect
     if tid != 23:
         assert orc.lib().orc_target_type(tid, kind) == expect
+
+
+@pytest.mark.parametrize("tid,expect", [(1, 28), (2, 28), (3, 28), (4, 28), (25, 28), (26, 28), (7, -1), (11, -1), (10, -1), (13, -1)])
+def test_sum_overflow_target_type_and_eligibility(tid, expect):
+    # SUM_OVERFLOW -> STRUCT{sum, overflow} for signed integers and decimal32/64 only (sum_overflow_tests.cpp:496-561: bool and
+    # unsigned types are rejected); the hash path says so without touching a GPU
+    from cudf_b200 import _lib
+    L = _lib.lib()
+    assert L.bgb_target_type(tid, 1) == expect
+    keys = (_lib.ColumnView * 1)(_lib.ColumnView(3, 0, 4, 0, 0, 0, None, None))
+    aggs = (_lib.Aggregation * 1)(_lib.Aggregation(1, 1))
+    reqs = (_lib.Request * 1)(_lib.Request(_lib.ColumnView(tid, 0, 4, 0, 0, 0, None, None), aggs, 1, 0))
+    ok = C.c_int32(-1)
+    rc = L.bgb_can_use_hash_groupby(keys, 1, reqs, 1, C.byref(ok))
+    if expect == 28:
+        assert rc == 0 and ok.value == 1
+    else:
+        assert ok.value == 0 or rc != 0
