@@ -217,6 +217,18 @@ __device__ __forceinline__ uint64_t ordered_decode(uint64_t img, int src)
   }
 }
 
+// 32-bit order image of a source of at most 32 bits (the packed (value, row) cell of ARGMIN / ARGMAX): the sign flip must
+// sit in bit 31, not in bit 63 where ordered_image() puts it and where `<< 32` would drop it
+__device__ __forceinline__ uint32_t ordered_image32(uint64_t raw, int src)
+{
+  switch (src) {
+    case S_I8: return (uint32_t)(int32_t)(int8_t)raw ^ 0x80000000u;
+    case S_I16: return (uint32_t)(int32_t)(int16_t)raw ^ 0x80000000u;
+    case S_I32: return (uint32_t)raw ^ 0x80000000u;
+    default: return (uint32_t)ordered_image(raw, src);  // F32, unsigned, bool: already 32-bit images
+  }
+}
+
 __device__ __forceinline__ int src_width(int src)
 {
   switch (src) {
@@ -280,8 +292,8 @@ __device__ __forceinline__ void apply_value(uint8_t op, uint8_t src, void* cells
     case ACC_MAX: { unsigned long long v = ordered_image(raw, src); if (v > *reinterpret_cast<volatile unsigned long long*>(c64)) atomicMax(c64, v); break; }
     case ACC_SUM_LO32: atomicAdd(c64, (unsigned long long)(uint32_t)raw_to_i64(raw, src)); break;
     case ACC_SUM_HI32: atomicAdd(c64, (unsigned long long)(raw_to_i64(raw, src) >> 32)); break;
-    case ACC_ARGMIN: atomicMin(c64, (unsigned long long)((ordered_image(raw, src) << 32) | (uint32_t)row)); break;
-    case ACC_ARGMAX: atomicMax(c64, (unsigned long long)((ordered_image(raw, src) << 32) | (0xFFFFFFFFu - (uint32_t)row))); break;
+    case ACC_ARGMIN: atomicMin(c64, (unsigned long long)(((uint64_t)ordered_image32(raw, src) << 32) | (uint32_t)row)); break;
+    case ACC_ARGMAX: atomicMax(c64, (unsigned long long)(((uint64_t)ordered_image32(raw, src) << 32) | (0xFFFFFFFFu - (uint32_t)row))); break;
     default: break;
   }
 }

@@ -216,3 +216,27 @@ def test_argmin_argmax_of_64bit_values(vtype):
     assert path == "global", path
     w = orc.HostColumn(rng.permutation(n).astype(vtype))  # no nulls, no ties
     gpu_util.compare_with_oracle([k], [w], [(0, "argmax", 1), (0, "argmin", 1)], name=f"arg64/{vtype}/unique")
+
+
+@pytest.mark.parametrize("vtype", ["int8", "int16", "int32", "uint8", "uint16", "uint32", "float32"])
+@pytest.mark.parametrize("nullable", [False, True])
+def test_argmin_argmax_of_narrow_values_mixed_sign(vtype, nullable):
+    # values of at most 32 bits travel as one packed (order image, row) cell: the image must order NEGATIVE values below
+    # positive ones (round-1 advisor finding: the sign flip of the 64-bit image was shifted out of the cell)
+    rng = np.random.default_rng(91)
+    n = 120_000
+    k = orc.HostColumn(rng.integers(0, 3_000, n).astype(np.int64))
+    signed = vtype.startswith("int") or vtype == "float32"
+    raw = rng.integers(-100, 100, n) if signed else rng.integers(0, 200, n)
+    valid = None
+    if nullable:
+        valid = rng.random(n) > 0.2
+        valid[k.data == 11] = False
+    v = orc.HostColumn(raw.astype(vtype), valid)
+    gpu_util.compare_with_oracle([k], [v], [(0, "argmin", 1), (0, "argmax", 1), (0, "min", 1), (0, "max", 1)], name=f"arg32/{vtype}")
+    # two rows only, {-1, 1}: ARGMIN must be the row of -1
+    if signed:
+        k2 = orc.HostColumn(np.zeros(2, dtype=np.int64))
+        v2 = orc.HostColumn(np.array([1, -1]).astype(vtype))
+        G, kg, ag, _ = gpu_util.run_gpu([k2], [v2], [(0, "argmin", 1), (0, "argmax", 1)])
+        assert G == 1 and ag[0][0][0] == 1 and ag[1][0][0] == 0
