@@ -110,6 +110,8 @@ def lib():
     L.bgb_hash_partition.argtypes = [C.POINTER(ColumnView), C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32, C.c_uint32,
                                      C.POINTER(MutableColumn), C.POINTER(C.c_int32), C.c_void_p]
     L.bgb_bytes_to_bitmask.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_int32), C.c_void_p]
+    L.bgb_bytes_to_bitmask_noalloc.argtypes = L.bgb_bytes_to_bitmask.argtypes
+    L.bgb_bytes_to_bitmask_noalloc_max_rows.restype = C.c_int64
     L.bgb_finalize_moments.argtypes = [C.c_int32, C.c_int32, C.POINTER(ColumnView), C.POINTER(ColumnView), C.POINTER(ColumnView),
                                        C.POINTER(MutableColumn), C.c_void_p]
     L.bgb_is_streaming_groupby_supported.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_int32)]

@@ -263,6 +263,17 @@ int bgb_hash_partition(const bgb_column_view* input, int32_t num_cols, const int
 /* validity bytes (1 = valid) -> cudf bitmask words ((n + 31) / 32 of them); *null_count_host = number of zero bytes */
 int bgb_bytes_to_bitmask(const uint8_t* valid_bytes, int64_t n, uint32_t* mask_words, int32_t* null_count_host, void* stream);
 
+/* The same conversion for callers that CANNOT ALLOCATE (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc). No counterpart in the reference. It calls no
+ * cudaMalloc / cudaFree / memory-pool routine: its scratch (a ticket, the total, one partial null count per 8192-row tile) is
+ * a file-scope __device__ array of 262 400 bytes that every GPU loading the library holds until the process exits
+ * (cudf_b200/csrc/noalloc.cu). Limit: n <= bgb_bytes_to_bitmask_noalloc_max_rows() = 536 870 912 rows, beyond which the call
+ * returns BGB_INVALID_ARGUMENT. All calls on one device share the array (the call clears what must start at zero), so calls
+ * that OVERLAP on the GPU -- different streams without an ordering between them -- race; calls in stream order are safe.
+ * null_count_host == NULL makes the call fully asynchronous on `stream` (no read-back, no synchronisation). */
+int bgb_bytes_to_bitmask_noalloc(const uint8_t* valid_bytes, int64_t n, uint32_t* mask_words, int32_t* null_count_host, void* stream);
+int64_t bgb_bytes_to_bitmask_noalloc_max_rows(void);
+
 /* MEAN / M2 / VARIANCE / STD from MERGED partial columns: sum (and sumsq, unused for MEAN) are the merged SUM /
  * SUM_OF_SQUARES columns (INT64, UINT64, FLOAT32, FLOAT64, or a duration type for MEAN), count the merged INT32 count.
  * out->data receives n FLOAT64 values (the duration type for a duration MEAN); out->null_mask, when not NULL, receives
