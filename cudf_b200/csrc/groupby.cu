@@ -13,6 +13,7 @@
 #include "errors.h"
 #include "fastpaths.h"
 #include "kernels_bucket.h"
+#include "kernels_hc.h"
 #include "kernels_partition.h"
 #include "kernels_peer.h"
 #include "plan.h"
@@ -37,6 +38,7 @@ struct bgb_groupby {
   std::vector<KeyPlan> emit_keys;   // repacked keys: the caller's key columns and where each sits in the packed 64-bit image
   void* repack_buf = nullptr;       // the packed key column (+ its validity words), released when the build is done
   void* repack_mask = nullptr;
+  bool dense = false;               // the build wrote the groups densely at [0, G) and filled group_slots itself (kernels_hc.cu)
 
   void* dalloc(size_t bytes)
   {
@@ -423,6 +425,163 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool one_l
   return BGB_OK;
 }
 
+// Records form of the bucketed path (kernels_hc.cu): TMA-fed scatter levels over 16- to 32-byte records, then one CTA per
+// table slice with DENSE group output -- no HBM hash table, no compaction pass. `h->table` and the accumulator cells are
+// allocated (capacity + 1 entries each); on success h->group_slots is allocated and filled and h->dense is set.
+// done=false when the plan does not fit (the caller then tries the column-form kernels of kernels_bucket.cu).
+int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, bool& done)
+{
+  done = false;
+  Plan& pl = h->plan;
+  const int64_t N = pl.num_rows;
+  static const bool off = getenv("BGB_NO_HC") != nullptr;
+  if (off || pl.key_words != 1 || pl.accs.size() > (size_t)kMaxAccs || N >= (1ll << 31) || N < 1) return BGB_OK;
+  size_t slot_bytes = 8;
+  for (const AccPlan& a : pl.accs) {
+    if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX || a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX) return BGB_OK;  // row numbers are lost by the scatter
+    slot_bytes += acc_cell_bytes(a.op);
+  }
+  // record layout
+  int nvb = 0;
+  std::vector<int> vbit(pl.values.size(), -1);
+  for (size_t c = 0; c < pl.values.size(); ++c) if (pl.values[c].v.null_mask != nullptr) vbit[c] = nvb++;
+  int key_bits = 0;
+  for (const KeyPlan& k : pl.keys) key_bits = std::max(key_bits, std::max((int)k.shift + 8 * k.width, (int)k.null_bit + 1));
+  const bool in_low32 = nvb > 0 && key_bits <= 32;
+  const int W = 1 + (int)pl.values.size() + ((nvb > 0 && !in_low32) ? 1 : 0);
+  if (W > kHcMaxWords || nvb > 32) return BGB_OK;
+  const int vbits_word = (nvb > 0 && !in_low32) ? W - 1 : -1;
+  int log2cap = 0; while ((1ull << log2cap) < h->table.capacity) ++log2cap;
+  auto round16 = [](uint64_t x) { return (x + 15) & ~15ull; };
+
+  // slice: the largest power of two of slots that leaves two CTAs per SM (measured: 8.3 ms per 1e9 rows at 2 x 4096 slots
+  // against 12.6 ms at 1 x 8192); at least ~1000 buckets so that every SM has slices to work on
+  int ls;
+  if (opt.bucket_slice_log2 > 0) {
+    ls = std::min(opt.bucket_slice_log2, log2cap - 1);
+    if (ls < 4 || (slot_bytes << ls) > 220 * 1024) return BGB_OK;
+  } else {
+    ls = 4;
+    while (ls + 1 < log2cap && (slot_bytes << (ls + 1)) <= 112 * 1024) ++ls;
+    if (log2cap - ls < 10) ls = std::max(6, log2cap - 10);
+    if (ls >= log2cap) return BGB_OK;
+  }
+  const int b = log2cap - ls;
+  if (b < 1 || b > 20) return BGB_OK;
+  const int b2 = b <= 10 ? 0 : b / 2, b1 = b - b2;
+  const uint32_t P1 = 1u << b1, NB = 1u << b;
+  // rows a final bucket can hold: its groups are a Poisson draw (relative sigma 1 / sqrt(groups per bucket)) of groups whose
+  // own sizes vary, so the margin is 27 % at the ~1500 groups per bucket of the high-cardinality shapes and grows as buckets
+  // hold fewer groups; beyond +100 % the plan is left to the other paths
+  const double gpb    = std::max(1.0, std::min(g_est, (double)N) / (double)NB);
+  const double margin = std::max(0.27, 6.0 / std::sqrt(gpb));
+  if (margin > 1.0 && opt.force_path != 7) return BGB_OK;
+  const uint64_t CL = round16((uint64_t)((double)N / NB * (1.0 + std::min(margin, 1.0))) + 256);  // last level
+  const uint64_t C1 = b2 ? round16((uint64_t)((double)N / P1 * 1.125) + 1024) : CL;
+  const uint64_t rows1 = (uint64_t)P1 * C1, rows2 = b2 ? (uint64_t)NB * CL : 0;
+  if (rows1 >= (1ull << 32) || rows2 >= (1ull << 32)) return BGB_OK;
+  cudaStream_t s = h->stream;
+
+  std::vector<void*> scratch;
+  auto grab = [&](size_t bytes) { void* p = h->dalloc(bytes); if (p) scratch.push_back(p); return p; };
+  auto release = [&]() { for (void* p : scratch) h->dfree(p); scratch.clear(); };
+  constexpr uint32_t kHotStride = 64;  // level-1 cursors 256 B apart: every (tile, bucket) reservation is an atomic on one of P1 words
+  const size_t ncur = (size_t)P1 * kHotStride + (b2 ? NB : 0) + 4;
+  uint32_t* counters = (uint32_t*)grab(sizeof(uint32_t) * ncur);
+  uint64_t* L1 = (uint64_t*)grab(rows1 * W * 8 + 64);
+  uint64_t* L2 = b2 ? (uint64_t*)grab(rows2 * W * 8 + 64) : nullptr;
+  const uint64_t max_groups = std::min<uint64_t>(h->table.capacity + 1, (uint64_t)N + 1);
+  h->group_slots = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
+  if (!counters || !L1 || (b2 && !L2) || !h->group_slots) {
+    release();
+    if (h->group_slots) { h->dfree(h->group_slots); h->group_slots = nullptr; }
+    return set_error(BGB_OUT_OF_MEMORY, "record buffers of the bucketed path (%lld rows)", (long long)N);
+  }
+  uint32_t* cursor1 = counters;
+  uint32_t* cursor2 = counters + (size_t)P1 * kHotStride;
+  unsigned long long* gcount = reinterpret_cast<unsigned long long*>(counters + ((ncur - 4 + 1) & ~(size_t)1));
+  TR("hc alloc");
+  int rc = check_cuda(cudaMemsetAsync(counters, 0, sizeof(uint32_t) * ncur, s), "hc counters");
+
+  // ---- slices: accumulators in shared memory, 8-byte cells first
+  HcSliceParams sp;
+  memset(&sp, 0, sizeof sp);
+  sp.table = h->table;
+  sp.words = W; sp.key_in_low32 = in_low32; sp.vbits_word = vbits_word;
+  sp.log2_slice = ls; sp.num_buckets = NB; sp.num_accs = (int)pl.accs.size();
+  sp.group_slots = h->group_slots; sp.gcount = gcount; sp.max_groups = max_groups;
+  uint32_t off_b = (uint32_t)(8u << ls);
+  for (int pass = 0; pass < 2; ++pass)
+    for (size_t a = 0; a < pl.accs.size(); ++a) {
+      const AccPlan& acc = pl.accs[a];
+      const int cb = acc_cell_bytes(acc.op);
+      if ((pass == 0) != (cb == 8)) continue;
+      HcAcc& d = sp.acc[a];
+      d.cells = acc.cells; d.op = acc.op; d.cell_bytes = (uint8_t)cb; d.smem_off = off_b;
+      off_b += (uint32_t)cb << ls;
+      switch (acc.op) {
+        case ACC_COUNT_VALID: case ACC_COUNT_ALL: d.mode = HM_COUNT; break;
+        case ACC_SUM_I64: case ACC_SUMSQ_I64: case ACC_SUM_LO32: case ACC_SUM_HI32: d.mode = HM_ISUM; break;
+        case ACC_MIN: case ACC_MAX: d.mode = HM_MINMAX; break;
+        default: d.mode = HM_OTHER; break;
+      }
+      if (acc.value_col >= 0) { d.word = (uint8_t)(1 + acc.value_col); d.src = pl.values[acc.value_col].src; d.vbit = (int16_t)vbit[acc.value_col]; }
+      else { d.word = 0; d.src = S_I32; d.vbit = -1; }
+    }
+  const size_t slice_smem = off_b;
+  if (!rc) rc = check_cuda(launch_hc_init(sp, s), "hc_init");
+
+  // ---- level 1
+  HcScatterParams s1;
+  memset(&s1, 0, sizeof s1);
+  fill_agg_params(*h, s1.a, 0, 0);
+  s1.level = 1; s1.words = W; s1.key_in_low32 = in_low32; s1.vbits_word = vbits_word;
+  s1.num_vals = (int)pl.values.size();
+  bool tma = pl.keys.size() == 1 && pl.keys[0].v.null_mask == nullptr && pl.keys[0].fclass == 0 &&
+             ((uintptr_t)pl.keys[0].v.data + (size_t)pl.keys[0].v.offset * pl.keys[0].width) % 16 == 0;
+  for (size_t c = 0; c < pl.values.size(); ++c) {
+    const ValuePlan& v = pl.values[c];
+    const int w = type_width(v.v.type_id);
+    s1.val[c] = HcValue{(const uint8_t*)v.v.data, v.v.null_mask, v.v.offset, w, vbit[c], 0};
+    tma = tma && ((uintptr_t)v.v.data + (size_t)v.v.offset * w) % 16 == 0;
+    if (v.v.null_mask) tma = tma && v.v.offset % 128 == 0 && ((uintptr_t)v.v.null_mask + (size_t)v.v.offset / 8) % 16 == 0;
+  }
+  static const bool no_tma = getenv("BGB_HC_NO_TMA") != nullptr;
+  s1.tma_src = tma && !no_tma;
+  s1.out = L1; s1.cursor = cursor1; s1.cursor_stride = kHotStride; s1.bucket_capacity = (uint32_t)C1;
+  s1.log2_parts = b1; s1.slot_shift = log2cap - b1; s1.status = h->table.status;
+  h->prof.begin("hc_scatter1");
+  if (!rc) rc = check_cuda(launch_hc_scatter(s1, num_sms, s), "hc_scatter1");
+  h->prof.end();
+
+  // ---- level 2: every level-1 bucket is a segment
+  if (b2 && !rc) {
+    HcScatterParams s2 = s1;
+    s2.level = 2; s2.tma_src = 0;
+    s2.in = L1; s2.seg_cursor = cursor1; s2.seg_cursor_stride = kHotStride; s2.seg_capacity = (uint32_t)C1; s2.num_segs = P1;
+    s2.out = L2; s2.cursor = cursor2; s2.cursor_stride = 1; s2.bucket_capacity = (uint32_t)CL;
+    s2.log2_parts = b2; s2.slot_shift = log2cap - b;
+    h->prof.begin("hc_scatter2");
+    rc = check_cuda(launch_hc_scatter(s2, num_sms, s), "hc_scatter2");
+    h->prof.end();
+  }
+
+  // ---- slices + group count
+  sp.rec = b2 ? L2 : L1;
+  sp.cursor = b2 ? cursor2 : cursor1; sp.cursor_stride = b2 ? 1 : kHotStride;
+  sp.bucket_capacity = (uint32_t)(b2 ? CL : C1);
+  h->prof.begin("hc_slices");
+  if (!rc) rc = check_cuda(launch_hc_slices(sp, slice_smem, num_sms, s), "hc_slices");
+  h->prof.end();
+  if (!rc) rc = check_cuda(launch_hc_finish(sp, s), "hc_finish");
+  TR("hc launches");
+  release();  // stream-ordered
+  if (rc) { h->dfree(h->group_slots); h->group_slots = nullptr; return rc; }
+  h->dense = true;
+  done = true;
+  return BGB_OK;
+}
+
 }  // namespace
 
 // Key repacking: the caller's integer key columns would need a 128-bit image, but their exact value RANGES fit 64 bits
@@ -629,7 +788,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     if (capacity > cap_max) capacity = cap_max;
   }
 
-  bool skip_tiny = false, no_bucket = false;
+  bool skip_tiny = false, no_bucket = false, no_hc = false;
   for (int attempt = 0;; ++attempt) {
     h->table.capacity = capacity;
     const uint64_t slots = capacity + 1;
@@ -642,7 +801,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     // init + aggregate, kMaxAccs accumulators per launch (the first launch also initialises the keys)
     TR("table alloc");
     std::string path;
-    bool done = false;
+    bool done = false, was_hc_attempt = false;
     BuildContext ctx{&pl, h->table, opt, g_raw, max_abs, key_min, key_max, s, &h->prof, num_sms, skip_tiny};
     FAIL_RC(try_fast_paths(ctx, done, path));
     if (!done && opt.force_path != 1 && opt.force_path != 2 && opt.force_path != 4) {
@@ -657,7 +816,9 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
       static const bool mid_on = getenv("BGB_BUCKET_MID") != nullptr;
       const bool mid = mid_on && !big && N >= (1 << 24) && capacity >= (1u << 16);
       if ((opt.force_path == 7 || (opt.force_path == 0 && (big || mid))) && !no_bucket) {
-        FAIL_RC(run_bucketed(h, num_sms, opt, /*one_level_only=*/opt.force_path == 0 && !big, done));
+        if (!no_hc) FAIL_RC(run_hc(h, num_sms, opt, g_raw, done));  // records form first; plans it does not take go through the column form
+        was_hc_attempt = done;
+        if (!done) FAIL_RC(run_bucketed(h, num_sms, opt, /*one_level_only=*/opt.force_path == 0 && !big, done));
         if (done) path = "bucketed";
       }
       if (!done && (opt.force_path == 3 || opt.force_path == 7 || big)) {
@@ -698,13 +859,16 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     h->path = path;
     // compaction: occupied slots -> dense group list (+ group count)
     const uint64_t max_groups = std::min<uint64_t>(slots, (uint64_t)N);
-    h->group_slots            = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
-    uint32_t* scan_state      = (uint32_t*)h->dalloc(compact_scan_state_bytes(capacity));
-    if (!h->group_slots || !scan_state) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "compaction scratch"));
-    TR("compact alloc");
-    h->prof.begin("compact");
-    FAIL_RC(check_cuda(launch_compact(h->table, h->group_slots, scan_state, s), "compact"));
-    h->prof.end();
+    uint32_t* scan_state      = nullptr;
+    if (!h->dense) {  // (the records form of the bucketed path wrote dense groups and their slot list itself)
+      h->group_slots = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
+      scan_state     = (uint32_t*)h->dalloc(compact_scan_state_bytes(capacity));
+      if (!h->group_slots || !scan_state) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "compaction scratch"));
+      TR("compact alloc");
+      h->prof.begin("compact");
+      FAIL_RC(check_cuda(launch_compact(h->table, h->group_slots, scan_state, s), "compact"));
+      h->prof.end();
+    }
     TR("compact launch");
     uint32_t st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     FAIL_RC(check_cuda(cudaMemcpyAsync(st, status, sizeof st, cudaMemcpyDeviceToHost, s), "status copy"));
@@ -712,11 +876,13 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     FAIL_RC(check_cuda(cudaStreamSynchronize(s), "build sync"));
     tr.mark("build sync");
     h->prof.resolve();
-    h->dfree(scan_state);
+    if (scan_state) h->dfree(scan_state);
+    h->dense = false;  // (a retry below starts from scratch)
     if (getenv("BGB_DEBUG")) fprintf(stderr, "[bgb] path=%s groups=%u overflow=%u bypass_rows=%u flushes=%u\n", path.c_str(), st[1], st[0], st[4], st[5]);
     if (st[6] != 0 && path == "bucketed") {
-      // skewed keys filled the buckets' overflow region: same table size, exact-offset partitioned path
-      no_bucket = true;
+      // skewed keys filled a bucket of the records form (no overflow region there): column form, whose overflow region takes
+      // moderate skew; if that fills too: same table size, exact-offset partitioned path
+      if (was_hc_attempt) no_hc = true; else no_bucket = true;
       h->dfree(h->group_slots); h->group_slots = nullptr;
       h->dfree(h->table.keys); h->table.keys = nullptr;
       for (AccPlan& a : pl.accs) { h->dfree(a.cells); a.cells = nullptr; }
