@@ -7,12 +7,22 @@ columns that are already resident in HBM; `e2e` is the same call through the C A
 (bgb_groupby_host) with pinned HOST columns, H2D/D2H inside the timed region.
 
 Workloads (BASELINE.json configs / SURVEY.md 8d):
-  A      int64 key x%1e4, int64 value, SUM+COUNT, N=1e8            (default at N=1: configs[1])
-  A9     as A with N=1e9 and --groups 10000 | 100000000             (north_star target shapes)
-  B      int32 key x%1e8, float64 value 10% null, SUM+MIN+MAX, N=1e9
-  Q1     2 int8 keys (4 groups), 2 float64 values, MEAN+VAR+COUNT each, N=6e8
-At N>1 every rank aggregates its own shard of the same per-GPU workload (weak scaling), the per-rank partial groups are
-hash-partitioned by key and exchanged with one NCCL all-to-all, and merged by a second groupby on the owner rank.
+  A9g    int64 key x%1e8, int64 value, SUM+COUNT, N=1e9     <- HEADLINE at --gpus 1: the largest single-GPU configuration, the
+                                                               shape north_star's target is quoted on (1e9 rows, 1e8 groups)
+  A9     as A9g with 1e4 groups                              (north_star's other target shape)
+  A      as A9 with N=1e8                                    (configs[1])
+  AS     as A with SPARSE key values (splitmix64 of x%1e4)   (the shared-memory table cannot direct-address these)
+  B      int32 key x%1e8, float64 value 10% null, SUM+MIN+MAX, N=1e9   (configs[2])
+  Q1     2 int8 keys (4 groups), 2 float64 values, MEAN+VAR+COUNT each, N=6e8   (configs[3])
+  C1     2 int64 keys 32x32, 2 float64 MEANs, N=1e7          (configs[0]'s shape on the GPU)
+  MG     configs[4]: 8 shards x 1e9 rows (shard s = seed 42+s), int64 key x%1e8, SUM+COUNT -- STRONG scaling: the 8 shards
+         are spread over the N ranks (8/N each; at N=1 every shard is fed as two 5e8-row halves so that inputs + scratch
+         fit 180 GB), per-shard partials are folded on the rank, the folded table is exchanged by owner rank (peer-memory
+         stores over NVLink, or --exchange nccl for the all-to-all) and merged. This is what --gpus N>1 runs.
+With no --workload, --gpus 1 times A9g as the headline and then A9, B, Q1, C1, A, AS as a "sweep" array in the same JSON line
+(the reference's own precedent for one run across cardinalities: cpp/benchmarks/groupby/group_max.cpp:79-165).
+Every workload's result is VERIFIED outside the timed region: per-group against the CPU oracle on a prefix of the rows
+(>= 5e7 where the workload has them) and through sum / count / unique-key invariants on the full result.
 
 `--impl reference` times the CPU restatement of the reference algorithm (oracle/, all host threads) on a bounded sample
 of the same workload: libcudf itself cannot be built offline, so the oracle port is the reference arm.
@@ -23,7 +33,6 @@ import argparse
 import json
 import os
 import statistics
-import subprocess
 import sys
 import threading
 import time
@@ -38,13 +47,18 @@ METRIC = "groupby_agg_rows_per_sec"
 UNIT = "rows/s"
 
 WORKLOADS = {
-    # name: (rows, groups, description)
-    "A": (100_000_000, 10_000, "single int64 key SUM/COUNT, 100M rows, 1e4 groups (BASELINE.json configs[1])"),
-    "A9": (1_000_000_000, 10_000, "single int64 key SUM/COUNT, 1e9 rows (north_star target shape)"),
-    "B": (1_000_000_000, 100_000_000, "int32 key SUM/MIN/MAX float64 with 10% nulls, 1e9 rows, 1e8 groups (configs[2])"),
-    "Q1": (600_000_000, 4, "TPC-H Q1-style two int8 keys MEAN/VAR/COUNT over 6e8 rows (configs[3])"),
-    "C1": (10_000_000, 1024, "df.groupby(['A','B']).mean(): two int64 keys in [0,32), two float64 values, 10M rows (configs[0] shape on the GPU)"),
+    # name: (rows, groups, dtype, description)
+    "A9g": (1_000_000_000, 100_000_000, "int64", "single int64 key SUM/COUNT, 1e9 rows, 1e8 groups (north_star target shape; largest single-GPU configuration)"),
+    "A9": (1_000_000_000, 10_000, "int64", "single int64 key SUM/COUNT, 1e9 rows, 1e4 groups (north_star target shape)"),
+    "A": (100_000_000, 10_000, "int64", "single int64 key SUM/COUNT, 100M rows, 1e4 groups (BASELINE.json configs[1])"),
+    "AS": (100_000_000, 10_000, "int64", "as A with sparse key values: key = splitmix64(x % 1e4) (hashed shared-memory regime)"),
+    "B": (1_000_000_000, 100_000_000, "f64", "int32 key SUM/MIN/MAX float64 with 10% nulls, 1e9 rows, 1e8 groups (configs[2])"),
+    "Q1": (600_000_000, 4, "f64", "TPC-H Q1-style two int8 keys MEAN/VAR/COUNT over 6e8 rows (configs[3])"),
+    "C1": (10_000_000, 1024, "f64", "df.groupby(['A','B']).mean(): two int64 keys in [0,32), two float64 values, 10M rows (configs[0] shape on the GPU)"),
+    "MG": (8_000_000_000, 100_000_000, "int64", "int64 key SUM/COUNT, 8e9 rows as 8 shards x 1e9, 1e8 groups, partials exchanged by owner rank (configs[4])"),
 }
+SWEEP = ["A9", "B", "Q1", "C1", "A", "AS"]
+SPARSE_SEED = 7_777
 
 
 def peaks():
@@ -60,7 +74,7 @@ def peaks():
 # ------------------------------------------------------------------------------------------------ synthetic inputs
 def algorithmic_bytes(workload: str, n: int, g: int) -> float:
     """minimum reads + minimum writes of one call."""
-    if workload in ("A", "A9"):
+    if workload in ("A", "A9", "A9g", "AS", "MG"):
         return 16.0 * n + 20.0 * g
     if workload == "B":
         return 12.125 * n + (4 + 24 + 3 / 8) * g
@@ -71,7 +85,19 @@ def algorithmic_bytes(workload: str, n: int, g: int) -> float:
     raise ValueError(workload)
 
 
-def make_device_inputs(workload: str, n: int, g: int, seed: int, device):
+def _torch_mix64(z):
+    """SplitMix64 finaliser on int64 tensors (wrapping arithmetic; logical shifts through masks)."""
+    import torch
+    def lsr(x, k):
+        return (x >> k) & ((1 << (64 - k)) - 1)
+    c1 = torch.tensor(-4658895280553007687, dtype=torch.int64, device=z.device)   # 0xBF58476D1CE4E5B9
+    c2 = torch.tensor(-7723592293110705685, dtype=torch.int64, device=z.device)   # 0x94D049BB133111EB
+    z = (z ^ lsr(z, 30)) * c1
+    z = (z ^ lsr(z, 27)) * c2
+    return z ^ lsr(z, 31)
+
+
+def make_device_inputs(workload: str, n: int, g: int, seed: int, device, first_row: int = 0):
     """Columns generated ON the device by the library's counter-based SplitMix64 generators (bit-identical to the oracle's)."""
     import ctypes as C
 
@@ -84,16 +110,21 @@ def make_device_inputs(workload: str, n: int, g: int, seed: int, device):
 
     def gen_int(dtype, tid, sd, mod, add=0):
         t = torch.empty(n, dtype=dtype, device=device)
-        _lib.check(L.bgb_gen_uniform_int(C.c_void_p(t.data_ptr()), tid, n, sd, 0, mod, add, s))
+        _lib.check(L.bgb_gen_uniform_int(C.c_void_p(t.data_ptr()), tid, n, sd, first_row, mod, add, s))
         return t
 
     def gen_real(sd, mod, add=0.0):
         t = torch.empty(n, dtype=torch.float64, device=device)
-        _lib.check(L.bgb_gen_uniform_real(C.c_void_p(t.data_ptr()), cb.TypeId.FLOAT64, n, sd, 0, mod, add, s))
+        _lib.check(L.bgb_gen_uniform_real(C.c_void_p(t.data_ptr()), cb.TypeId.FLOAT64, n, sd, first_row, mod, add, s))
         return t
 
-    if workload in ("A", "A9"):
-        k = cb.Column(gen_int(torch.int64, cb.TypeId.INT64, seed, g))
+    if workload in ("A", "A9", "A9g", "AS", "MG"):
+        kt = gen_int(torch.int64, cb.TypeId.INT64, seed, g)
+        if workload == "AS":
+            step = 1 << 26
+            for lo in range(0, n, step):  # in place, chunked: the mix needs a few temporaries
+                kt[lo:lo + step] = _torch_mix64(kt[lo:lo + step] + (SPARSE_SEED * 0x1000003 + 0x9E3779B97F4A7C15 - (1 << 64)))
+        k = cb.Column(kt)
         v = cb.Column(gen_int(torch.int64, cb.TypeId.INT64, seed + 1, 2001, -1000))
         return cb.Table([k]), [cb.GroupByRequest(v, [A.sum(), A.count()])]
     if workload == "B":
@@ -101,7 +132,7 @@ def make_device_inputs(workload: str, n: int, g: int, seed: int, device):
         vd = gen_real(seed + 1, 1_000_000)
         mask = torch.empty((n + 31) // 32, dtype=torch.int32, device=device)
         nc = C.c_int32(0)
-        _lib.check(L.bgb_gen_null_mask(C.c_void_p(mask.data_ptr()), n, seed + 2, 0, 10, C.byref(nc), s))
+        _lib.check(L.bgb_gen_null_mask(C.c_void_p(mask.data_ptr()), n, seed + 2, first_row, 10, C.byref(nc), s))
         v = cb.Column(vd, mask, nc.value)
         return cb.Table([k]), [cb.GroupByRequest(v, [A.sum(), A.min(), A.max()])]
     if workload == "C1":
@@ -116,8 +147,8 @@ def make_device_inputs(workload: str, n: int, g: int, seed: int, device):
         cum = (C.c_int32 * 4)(int(0.247 * 65536), int(0.253 * 65536), int(0.753 * 65536), 65536)
         rf = torch.empty(n, dtype=torch.int8, device=device)
         ls = torch.empty(n, dtype=torch.int8, device=device)
-        _lib.check(L.bgb_gen_categorical_i8(C.c_void_p(rf.data_ptr()), n, seed, 0, cum, bytes([0, 1, 1, 2]), 4, s))
-        _lib.check(L.bgb_gen_categorical_i8(C.c_void_p(ls.data_ptr()), n, seed, 0, cum, bytes([0, 0, 1, 0]), 4, s))
+        _lib.check(L.bgb_gen_categorical_i8(C.c_void_p(rf.data_ptr()), n, seed, first_row, cum, bytes([0, 1, 1, 2]), 4, s))
+        _lib.check(L.bgb_gen_categorical_i8(C.c_void_p(ls.data_ptr()), n, seed, first_row, cum, bytes([0, 0, 1, 0]), 4, s))
         q = cb.Column(gen_real(seed + 1, 50, 1.0))
         p = cb.Column(gen_real(seed + 2, 104_100, 900.0))
         aggs = lambda: [A.mean(), A.variance(1), A.count()]  # noqa: E731
@@ -126,14 +157,16 @@ def make_device_inputs(workload: str, n: int, g: int, seed: int, device):
 
 
 def make_host_inputs_numpy(workload: str, n: int, g: int, seed: int):
-    """The same columns on the host (numpy), for the CPU legs. Identical values to make_device_inputs."""
+    """The same columns on the host (numpy), for the CPU legs and the checker. Identical values to make_device_inputs."""
     from oracle import oracle as orc
     rows = np.arange(n, dtype=np.uint64)
     H = orc.HostColumn
-    if workload in ("A", "A9"):
-        k = (orc.splitmix64(seed, rows) % np.uint64(g)).astype(np.int64)
+    if workload in ("A", "A9", "A9g", "AS", "MG"):
+        k = orc.splitmix64(seed, rows) % np.uint64(g)
+        if workload == "AS":
+            k = orc.splitmix64(SPARSE_SEED, k)
         v = (orc.splitmix64(seed + 1, rows) % np.uint64(2001)).astype(np.int64) - 1000
-        return [H(k)], [H(v)], [(0, "sum", 1), (0, "count_valid", 1)]
+        return [H(k.astype(np.int64))], [H(v)], [(0, "sum", 1), (0, "count_valid", 1)]
     if workload == "B":
         k = (orc.splitmix64(seed, rows) % np.uint64(g)).astype(np.int32)
         v = (orc.splitmix64(seed + 1, rows) % np.uint64(1_000_000)).astype(np.float64)
@@ -200,33 +233,44 @@ def pandas_leg(workload: str, n_full: int, g: int, seed: int, sample_rows: int):
     return {"value": n / dt, "unit": UNIT, "cores": 1, "rows": n, "pandas": pd.__version__}
 
 
+def default_workload(args):
+    if args.workload:
+        return args.workload
+    return "A9g" if args.gpus <= 1 and int(os.environ.get("WORLD_SIZE", "1")) <= 1 else "MG"
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    wl = args.workload or "A"
-    n, g, desc = WORKLOADS[wl]
+    wl = default_workload(args)
+    n, g, dtype, desc = WORKLOADS[wl]
     n = args.rows or n
     g = args.groups or g
+    # each step = a bounded sample of the workload (the whole --steps/--warmup run has to end within a few minutes on 16
+    # host cores): the first `sample` rows with the workload's key domain, i.e. the same cardinality regime
     sample = min(n, args.cpu_sample_rows)
-    keys, vals, aggs = make_host_inputs_numpy(wl, sample, g, 42)
+    gen_wl = "A9g" if wl == "MG" else wl
+    keys, vals, aggs = make_host_inputs_numpy(gen_wl, sample, g, 42)
     from oracle import oracle as orc
     cores = os.cpu_count() or 1
-    for _ in range(args.warmup):
+    for _ in range(min(args.warmup, 1)):
         orc.groupby(keys, vals, aggs, threads=cores, sort=False)
+    steps = max(1, min(args.steps, 5))
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         orc.groupby(keys, vals, aggs, threads=cores, sort=False)
-    dt = (time.perf_counter() - t0) / args.steps
+    dt = (time.perf_counter() - t0) / steps
     value = sample / dt
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "int64" if wl in ("A", "A9") else "f64", "data": "synthetic",
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "strong" if wl == "MG" else "weak", "vs_baseline": None,
+        "dtype": dtype, "data": "synthetic",
         "config": {"workload": f"{wl}: {desc}", "rows": n, "groups": g, "sample_rows_per_step": sample},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"each step = first {sample} rows of the workload; libcudf cannot be built offline, "
-                                   "so the reference arm is the CPU restatement in oracle/ (OpenMP, all host cores)"},
+                         "sample": f"each step = first {sample} rows of the workload (same {g}-value key domain); libcudf cannot be built "
+                                   "offline, so the reference arm is the CPU restatement in oracle/ (OpenMP, all host cores)"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -293,7 +337,7 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self.h is not None else "unavailable"}
 
 
-# ------------------------------------------------------------------------------------------------ our arm
+# ------------------------------------------------------------------------------------------------ output plumbing
 _REAL_STDOUT = None
 
 
@@ -316,6 +360,184 @@ def emit_line(line):
         os.write(_REAL_STDOUT, data)
 
 
+def log(*a):
+    print("[bench]", *a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ verification (checker)
+def _combined_key(cols):
+    """key column tensors -> ONE int64 tensor that orders and identifies the groups (bench keys are one int64 / int32 column or
+    two small-integer columns)"""
+    import torch
+    if len(cols) == 1:
+        return cols[0].to(torch.int64)
+    out = cols[0].to(torch.int64)
+    for c in cols[1:]:
+        out = out * (1 << 20) + c.to(torch.int64)
+    return out
+
+
+def verify_workload(wl, keys, reqs, n, g, seed, prefix_rows, force_path=0):
+    """(a) per-group comparison with the CPU oracle on the first `prefix_rows` rows (the checker, never the thing measured):
+    both results are ordered by key ON THE DEVICE (torch.sort) and compared there -- keys, counts, integer sums, MIN / MAX
+    bit-exact, float results within 1e-9 relative (north_star's tolerance);
+    (b) invariants on the FULL result: sum of counts == valid rows, sum of sums == column total, every key once.
+    Returns (ok, details)."""
+    import torch
+
+    import cudf_b200 as cb
+    from oracle import oracle as orc
+    details = {}
+    t0 = time.perf_counter()
+    dev = keys.columns()[0].data.device
+    # ---- (a) prefix against the oracle
+    p = min(n, prefix_rows)
+    pkeys = cb.Table([c.sliced(0, p) for c in keys.columns()])
+    preqs = [cb.GroupByRequest(r._values.sliced(0, p), r._aggregations) for r in reqs]
+    kt, rts = cb.GroupBy(pkeys, options={"force_path": force_path}).aggregate(preqs)
+    gkey = _combined_key([c.data for c in kt.columns()])
+    gorder = torch.argsort(gkey)
+    hk, hv, aggs = make_host_inputs_numpy(wl, p, g, seed)
+    t1 = time.perf_counter()
+    Go, ko, ao = orc.groupby(hk, hv, aggs, threads=os.cpu_count() or 1, sort=False)
+    t2 = time.perf_counter()
+    ok = kt.num_rows() == Go
+    if ok:
+        okey = _combined_key([torch.from_numpy(np.ascontiguousarray(d)).to(dev) for d, *_ in ko])
+        oorder = torch.argsort(okey)
+        ok = bool(torch.equal(gkey[gorder], okey[oorder]))
+        flat = [c for t in rts for c in t.columns()]
+        for i, c in enumerate(flat):
+            od = torch.from_numpy(np.ascontiguousarray(ao[i][0])).to(dev)[oorder]
+            ov = torch.from_numpy(np.ascontiguousarray(ao[i][1])).to(dev)[oorder]
+            gd = c.data[gorder]
+            if c.mask is not None:
+                words = c.mask
+                idx = gorder.to(torch.int64)
+                gv = ((words[idx >> 5] >> (idx & 31).to(torch.int32)) & 1).to(torch.bool)
+            else:
+                gv = torch.ones(gd.numel(), dtype=torch.bool, device=dev)
+            ok = ok and bool(torch.equal(gv, ov))
+            if not ok:
+                break
+            a, b2 = gd[gv], od[ov]
+            if a.dtype.is_floating_point:
+                ok = ok and bool(torch.allclose(a, b2.to(a.dtype), rtol=1e-9, atol=0.0))
+            else:
+                ok = ok and a.dtype == b2.dtype and bool(torch.equal(a, b2))
+        del flat
+    details["oracle_seconds"] = round(t2 - t1, 2)
+    details["oracle_prefix_rows"] = p
+    details["oracle_prefix_groups"] = int(Go)
+    details["oracle_prefix_ok"] = bool(ok)
+    del kt, rts, hk, hv, ko, ao
+    # ---- (b) full-size invariants
+    kt, rts = cb.GroupBy(keys, options={"force_path": force_path}).aggregate(reqs)
+    G = kt.num_rows()
+    inv = True
+    k0 = kt.columns()[0].data
+    if kt.num_columns() == 1:
+        inv = inv and int(torch.unique(k0).numel()) == G
+    else:
+        combo = kt.columns()[0].data.to(torch.int64) * 65536 + kt.columns()[1].data.to(torch.int64)
+        inv = inv and int(torch.unique(combo).numel()) == G
+    for r, t in zip(reqs, rts):
+        vcol = r._values
+        valid_rows = n - (vcol.null_count if vcol.mask is not None else 0)
+        for a, c in zip(r._aggregations, t.columns()):
+            if a.kind == cb.aggregation.Kind.COUNT_VALID:
+                inv = inv and int(c.data.sum(dtype=torch.int64).item()) == valid_rows
+            elif a.kind == cb.aggregation.Kind.SUM:
+                if vcol.mask is None:
+                    tot = vcol.data.sum(dtype=vcol.data.dtype if vcol.data.dtype.is_floating_point else torch.int64)
+                    got = c.data.sum(dtype=c.data.dtype)
+                    inv = inv and (tot.item() == got.item())  # int64: exact (wrapping); f64: whole-number inputs, exact below 2^53
+    for r, t in zip(reqs, rts):
+        kinds = [a.kind for a in r._aggregations]
+        if cb.aggregation.Kind.MIN in kinds and cb.aggregation.Kind.MAX in kinds:
+            cmin, cmax = t.columns()[kinds.index(cb.aggregation.Kind.MIN)], t.columns()[kinds.index(cb.aggregation.Kind.MAX)]
+            both = torch.ones(G, dtype=torch.bool, device=cmin.data.device) if cmin.mask is None else None
+            if both is not None:
+                inv = inv and bool((cmin.data <= cmax.data).all().item())
+            else:
+                inv = inv and cmin.null_count == cmax.null_count
+    details["full_groups"] = int(G)
+    details["full_invariants_ok"] = bool(inv)
+    details["seconds"] = round(time.perf_counter() - t0, 2)
+    return bool(ok and inv), details
+
+
+# ------------------------------------------------------------------------------------------------ single-GPU measurement
+def measure_single(wl, n, g, seed, device, steps, warmup, force_path, L):
+    """Timed region: `steps` calls with kernel profiling OFF (CUDA events around the region on the call's stream); kernel
+    times come from a separate profiled pass."""
+    import torch
+
+    import cudf_b200 as cb
+    keys, reqs = make_device_inputs(wl, n, g, seed, device)
+    torch.cuda.synchronize()
+    gb = cb.GroupBy(keys, options={"force_path": force_path})
+    for _ in range(max(warmup, 3)):
+        gb.aggregate(reqs)
+    torch.cuda.synchronize()
+    launches0 = L.bgb_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    host_ms = []
+    e0.record()
+    for _ in range(steps):
+        th = time.perf_counter()
+        gb.aggregate(reqs)
+        host_ms.append((time.perf_counter() - th) * 1e3)
+    e1.record()
+    torch.cuda.synchronize()
+    total_ms = e0.elapsed_time(e1)
+    launches = L.bgb_kernel_launches() - launches0
+    # separate profiled pass: per-kernel device times (events on the launch stream around every kernel)
+    gp = cb.GroupBy(keys, options={"force_path": force_path, "profile": 1})
+    acc = {}
+    for _ in range(3):
+        gp.aggregate(reqs)
+        for name, ms in gp.last_profile:
+            acc.setdefault(name, []).append(ms)
+    kern_ms = {k: sum(v) / len(v) for k, v in acc.items()}
+    return {"keys": keys, "reqs": reqs, "ms_per_step": total_ms / steps, "path": gb.last_path, "kernels_ms": kern_ms,
+            "launches": int(launches), "host_ms": host_ms}
+
+
+def roofline_of(wl, n, g, m, peak, peak_src):
+    kern_ms = m["kernels_ms"]
+    dom = max(kern_ms, key=kern_ms.get) if kern_ms else None
+    alg = algorithmic_bytes(wl, n, g)
+    if not dom:
+        return None
+    ach = alg / (kern_ms[dom] * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "peak_source": peak_src, "kernel_ms": kern_ms[dom], "algorithmic_bytes": alg, "traffic": None,
+            "frac_of_nominal_8000": ach / 8000.0,
+            "whole_call": {"achieved": alg / (m["ms_per_step"] * 1e-3) / 1e9, "frac": alg / (m["ms_per_step"] * 1e-3) / 1e9 / peak},
+            "kernels_ms": {k: round(v, 4) for k, v in kern_ms.items()},
+            "kernels_note": "per-kernel times from a separate profiled pass (profiling is off in the timed steps)"}
+    tr = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr):
+        try:
+            t = json.load(open(tr))
+            roof["traffic"] = t.get(f"{wl}:{dom}")
+            roof["traffic_source"] = "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture (profiles/traffic.json), not measured in this run"
+        except Exception:
+            pass
+    return roof
+
+
+def free_device_memory(L):
+    import gc
+
+    import torch
+    gc.collect()
+    torch.cuda.synchronize()
+    L.bgb_release_cached_memory()
+    torch.cuda.empty_cache()
+
+
 def main():
     _quiet_stdout()
     ap = argparse.ArgumentParser()
@@ -324,12 +546,18 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
-    ap.add_argument("--rows", type=int, default=0, help="override rows per GPU")
+    ap.add_argument("--rows", type=int, default=0, help="override rows (per shard for MG)")
     ap.add_argument("--groups", type=int, default=0, help="override key cardinality")
     ap.add_argument("--cpu-sample-rows", type=int, default=50_000_000)
+    ap.add_argument("--verify-rows", type=int, default=50_000_000, help="rows of the prefix checked per group against the oracle")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg")
+    ap.add_argument("--no-sweep", action="store_true", help="headline workload only")
+    ap.add_argument("--no-verify", action="store_true", help="skip the result checks (experiments only: the line then says verified: null)")
     ap.add_argument("--force-path", type=int, default=0)
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"])
+    ap.add_argument("--shards", type=int, default=8, help="MG: total number of shards of the job")
+    ap.add_argument("--pieces", type=int, default=0, help="MG: pieces every shard is fed as (0 = auto)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
@@ -338,140 +566,98 @@ def main():
 
     import torch
 
-    import cudf_b200 as cb
     from cudf_b200 import _lib
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the product path")
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.gpus != world and world > 1:
         args.gpus = world
-    device = torch.device("cuda", local_rank)
-    torch.cuda.set_device(device)
-    dist = None
+    wl = default_workload(args)
+    if wl == "MG":
+        run_multi(args, world)
+        return
     if world > 1:
-        import torch.distributed as dist_mod
-        dist = dist_mod
-        dist.init_process_group("nccl", device_id=device)
+        raise SystemExit("single-GPU workloads run with --gpus 1; --gpus N>1 runs MG (configs[4])")
+    device = torch.device("cuda", 0)
+    torch.cuda.set_device(device)
     L = _lib.lib()
-
-    wl = args.workload or "A"
-    n, g, desc = WORKLOADS[wl]
+    peak, peak_src = peaks()
+    n, g, dtype, desc = WORKLOADS[wl]
     n = args.rows or n
     g = args.groups or g
-    seed = 42 + rank
-    keys, reqs = make_device_inputs(wl, n, g, seed, device)
-    torch.cuda.synchronize()
-    opts = {"profile": 1, "force_path": args.force_path}
-    gb = cb.GroupBy(keys, options=opts)
-    dgb = None
-    if world > 1:
-        from cudf_b200 import distributed as D
-        dgb = D.DistributedGroupBy(keys, options=opts)
 
-    def step():
-        if dgb is not None:
-            return dgb.aggregate(reqs)
-        return gb.aggregate(reqs)
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(args.warmup, 3)):
-        step()
-    barrier()
-    launches0 = L.bgb_kernel_launches()
-    clocks = ClockSampler(local_rank)
-    if rank == 0:
-        clocks.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    prof_acc = {}
-    barrier()
-    e0.record()
-    host_ms = []
-    for it in range(args.steps):
-        th = time.perf_counter()
-        step()
-        host_ms.append((time.perf_counter() - th) * 1e3)
-        src = dgb.last_profile if dgb is not None else gb.last_profile
-        for name, ms in src:
-            prof_acc.setdefault(name, []).append(ms)
-    e1.record()
-    if rank == 0 and not clocks.samples:
-        # region shorter than the sampler's 20 ms period: one sample while the GPU is still finishing the last step. Taken
-        # after e1 is recorded because an NVML query from the launching thread costs ~2 ms (it would be billed to the steps).
+    # ---- headline
+    clocks = ClockSampler(0)
+    clocks.start()
+    m = measure_single(wl, n, g, 42, device, args.steps, args.warmup, args.force_path, L)
+    if not clocks.samples:
         clocks.sample()
-    barrier()
-    total_ms = e0.elapsed_time(e1)
-    launches = L.bgb_kernel_launches() - launches0
-    clk = clocks.stop() if rank == 0 else None
-    if dist is not None:
-        t = torch.tensor([total_ms], device=device, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
-    ms_per_step = total_ms / args.steps
-    value = world * n / (ms_per_step * 1e-3)
-    path = (dgb.last_path if dgb is not None else gb.last_path)
-
-    # ---- roofline of the dominant kernel (CUDA events on the call's stream, recorded inside the timed steps)
-    peak, peak_src = peaks()
-    kern_ms = {k: sum(v) / len(v) for k, v in prof_acc.items()}
-    local_ms = {k: v for k, v in kern_ms.items() if not k.startswith("dist_")}  # dist_* are whole phases, not kernels
-    dom = max(local_ms, key=local_ms.get) if local_ms else None
-    alg = algorithmic_bytes(wl, n, g)
-    roof = None
-    if dom:
-        ach = alg / (kern_ms[dom] * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "peak_source": peak_src, "kernel_ms": kern_ms[dom], "algorithmic_bytes": alg, "traffic": None,
-                "frac_of_nominal_8000": ach / 8000.0,
-                "whole_call": {"achieved": alg / (ms_per_step * 1e-3) / 1e9, "frac": alg / (ms_per_step * 1e-3) / 1e9 / peak},
-                "kernels_ms": {k: round(v, 4) for k, v in kern_ms.items()}}
-        tr = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tr):
-            try:
-                roof["traffic"] = json.load(open(tr)).get(f"{wl}:{dom}")
-            except Exception:
-                pass
-
-    # ---- end to end through the host-buffer C ABI call (pinned host columns; H2D + D2H inside the timed region)
+    clk = clocks.stop()
+    value = n / (m["ms_per_step"] * 1e-3)
+    roof = roofline_of(wl, n, g, m, peak, peak_src)
+    log(f"{wl}: {m['ms_per_step']:.3f} ms/step  path={m['path']}  kernels={ {k: round(v, 3) for k, v in m['kernels_ms'].items()} }")
+    verified, vdetails = None, None
+    if not args.no_verify:
+        verified, vdetails = verify_workload(wl, m["keys"], m["reqs"], n, g, 42, args.verify_rows, args.force_path)
+        log(f"{wl}: verified={verified} {vdetails}")
     e2e = None
-    if not args.no_e2e and world == 1:
-        e2e = run_e2e(wl, keys, reqs, n, args, device)
-    elif not args.no_e2e:
-        e2e = run_e2e_distributed(wl, keys, reqs, n, args, device, dist, world)
+    if not args.no_e2e:
+        e2e = run_e2e(m["keys"], m["reqs"], n, args)
+        log(f"{wl}: e2e {e2e['ms_per_step']:.1f} ms/step")
+    alg = algorithmic_bytes(wl, n, g)
+    del m["keys"], m["reqs"]
+    free_device_memory(L)
+
+    # ---- sweep: the other single-GPU workloads, same method, fewer steps
+    sweep = None
+    if not args.workload and not args.no_sweep:
+        sweep = []
+        for sw in SWEEP:
+            sn, sg, sdtype, sdesc = WORKLOADS[sw]
+            sm = measure_single(sw, sn, sg, 42, device, max(3, min(args.steps, 5)), 3, 0, L)
+            sroof = roofline_of(sw, sn, sg, sm, peak, peak_src)
+            ent = {"workload": sw, "description": sdesc, "rows": sn, "groups": sg, "dtype": sdtype, "ms_per_step": sm["ms_per_step"],
+                   "value": sn / (sm["ms_per_step"] * 1e-3), "path": sm["path"], "kernel": sroof["kernel"] if sroof else None,
+                   "kernel_ms": sroof["kernel_ms"] if sroof else None, "frac": sroof["frac"] if sroof else None,
+                   "whole_call_frac": sroof["whole_call"]["frac"] if sroof else None,
+                   "kernels_ms": sroof["kernels_ms"] if sroof else None, "gpu_launches": sm["launches"]}
+            if not args.no_verify:
+                ok, det = verify_workload(sw, sm["keys"], sm["reqs"], sn, sg, 42, args.verify_rows)
+                ent["verified"] = ok
+                ent["verify"] = det
+            log(f"sweep {sw}: {sm['ms_per_step']:.3f} ms  path={sm['path']}  frac={ent['frac']}  verified={ent.get('verified')}")
+            sweep.append(ent)
+            del sm
+            free_device_memory(L)
 
     cpu = None
     pandas_b = None
-    if rank == 0 and world == 1 and not args.no_cpu:
+    if not args.no_cpu:
         v, cores, sample, secs = cpu_leg(wl, n, g, 42, args.cpu_sample_rows)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "seconds": secs}
         pandas_b = pandas_leg(wl, n, g, 42, min(args.cpu_sample_rows, 20_000_000))
 
-    if rank == 0:
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "int64" if wl in ("A", "A9") else "f64", "data": "synthetic",
-            "config": {"workload": f"{wl}: {desc}", "rows_per_gpu": n, "groups": g, "path": path,
-                       "l2": "inputs (%.1f GB per step) are larger than the 126 MB L2; no flush needed" % (alg / 1e9),
-                       "parallelism": f"shard{world}" if world > 1 else "single"},
-            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
-            # host wall-clock of each call (every call ends in a stream sync, so this tracks device time): spread of the steps
-            "step_ms": {"median": statistics.median(host_ms), "min": min(host_ms), "max": max(host_ms)},
-        }
-        if pandas_b:
-            line["pandas_baseline"] = pandas_b
-        emit_line(line)
-    if dist is not None:
-        dist.destroy_process_group()
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": dtype, "data": "synthetic",
+        "config": {"workload": f"{wl}: {desc}", "rows_per_gpu": n, "groups": g, "path": m["path"],
+                   "l2": "inputs (%.1f GB per step) are larger than the 126 MB L2; no flush needed" % (alg / 1e9),
+                   "parallelism": "single"},
+        "verified": verified, "verify": vdetails,
+        "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": m["launches"], "clocks": clk,
+        # host wall-clock of each call (every call ends in a stream sync, so this tracks device time): spread of the steps
+        "step_ms": {"median": statistics.median(m["host_ms"]), "min": min(m["host_ms"]), "max": max(m["host_ms"])},
+    }
+    if sweep is not None:
+        line["sweep"] = sweep
+    if pandas_b:
+        line["pandas_baseline"] = pandas_b
+    emit_line(line)
 
 
 def _pinned_like(col):
-    """device Column -> pinned host numpy views (data, mask words)"""
+    """device Column -> pinned host tensors (data, mask words)"""
     import torch
     d = torch.empty(col.data.shape, dtype=col.data.dtype, pin_memory=True)
     d.copy_(col.data)
@@ -482,7 +668,9 @@ def _pinned_like(col):
     return d, m
 
 
-def run_e2e(wl, keys, reqs, n, args, device):
+def run_e2e(keys, reqs, n, args):
+    """The same metric through bgb_groupby_host: pinned HOST columns in, host results out; the H2D copy of every input byte
+    and the D2H copy of the result are inside the timed region."""
     import torch
 
     import cudf_b200 as cb
@@ -497,10 +685,9 @@ def run_e2e(wl, keys, reqs, n, args, device):
     hreqs = [(host_view(r._values), r._aggregations) for r in reqs]
     torch.cuda.synchronize()
     h2d = sum(d.numel() * d.element_size() + (m.numel() * 4 if m is not None else 0) for d, m in hold)
-    steps = max(1, min(args.steps, 5))
-    out = None
-    for _ in range(1):
-        out = cb.groupby_host(hkeys, hreqs, options={"force_path": args.force_path})
+    steps = max(1, min(args.steps, 3))
+    for _ in range(2):  # two untimed calls: the library's pinned result buffers are cached once two result sets exist (the previous
+        out = cb.groupby_host(hkeys, hreqs, options={"force_path": args.force_path})   # result is still referenced while the next call runs)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(steps):
@@ -514,15 +701,262 @@ def run_e2e(wl, keys, reqs, n, args, device):
             "steps": steps, "groups_out": int(G), "api": "bgb_groupby_host (C ABI, pinned host columns)"}
 
 
-def run_e2e_distributed(wl, keys, reqs, n, args, device, dist, world):
-    """N>1: every rank runs the host-buffer call on its shard, then the distributed exchange+merge of the partials."""
+# ------------------------------------------------------------------------------------------------ configs[4]: strong scaling
+def run_multi(args, world):
+    """BASELINE configs[4] at any number of GPUs (see the module docstring): the job is `--shards` shards of `rows` rows."""
     import torch
-    e = run_e2e(wl, keys, reqs, n, args, device)
-    t = torch.tensor([e["ms_per_step"]], device=device, dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    e.update({"value": world * n / (ms * 1e-3), "ms_per_step": ms, "note": "per-rank host-buffer call, max over ranks"})
-    return e
+
+    import cudf_b200 as cb
+    from cudf_b200 import _lib
+    from cudf_b200 import distributed as D
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=device)
+    L = _lib.lib()
+    peak, peak_src = peaks()
+    _, g, dtype, desc = WORKLOADS["MG"]
+    g = args.groups or g
+    shard_rows = args.rows or 1_000_000_000
+    nshards = args.shards
+    if nshards % world != 0:
+        raise SystemExit(f"--shards {nshards} must be a multiple of the number of ranks ({world})")
+    mine = list(range(rank * nshards // world, (rank + 1) * nshards // world))
+    # one GPU holding all 8 shards (128 GB) has ~50 GB left: a 1e9-row call needs 44 GB of scratch + table, so every shard is fed as halves
+    pieces_per_shard = args.pieces or (2 if world == 1 and shard_rows * nshards > 4_000_000_000 else 1)
+    shards, total_sum, total_rows = [], 0, 0
+    for sidx in mine:
+        keys, reqs = make_device_inputs("MG", shard_rows, g, 42 + 2 * sidx, device)  # (seed, seed + 1) per shard: key and value streams never collide
+        total_sum += int(reqs[0]._values.data.sum(dtype=torch.int64).item())
+        total_rows += shard_rows
+        if pieces_per_shard == 1:
+            shards.append((keys, reqs))
+        else:
+            h = shard_rows // pieces_per_shard
+            for pc in range(pieces_per_shard):
+                lo = pc * h
+                sz = h if pc < pieces_per_shard - 1 else shard_rows - lo
+                shards.append((cb.Table([c.sliced(lo, sz) for c in keys.columns()]),
+                               [cb.GroupByRequest(r._values.sliced(lo, sz), r._aggregations) for r in reqs]))
+    torch.cuda.synchronize()
+    region = 64 << 20
+    if world > 1:
+        # receive region: every source sends ~G / world^2 records of 20 bytes to this rank; x2 headroom
+        region = max(region, int(2.0 * 20 * g / world) + (8 << 20))
+
+    def make_dgb(profile):
+        return D.DistributedGroupBy(shards[0][0], options={"profile": profile, "force_path": args.force_path}, exchange=args.exchange,
+                                    peer_region_bytes=region)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    dgb = make_dgb(0)
+    out = None
+    for _ in range(max(args.warmup, 3) if world > 1 else max(min(args.warmup, 3), 1)):
+        out = dgb.aggregate_shards(shards)
+    barrier()
+    launches0 = L.bgb_kernel_launches()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    steps = args.steps if world > 1 else max(1, min(args.steps, 5))
+    barrier()
+    e0.record()
+    for _ in range(steps):
+        out = dgb.aggregate_shards(shards)
+    e1.record()
+    if rank == 0 and not clocks.samples:
+        clocks.sample()
+    barrier()
+    total_ms = e0.elapsed_time(e1)
+    launches = L.bgb_kernel_launches() - launches0
+    clk = clocks.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([total_ms], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    ms_per_step = total_ms / steps
+    n_total = shard_rows * nshards
+    value = n_total / (ms_per_step * 1e-3)
+
+    # ---- verification of the last result: every key once over all ranks, counts and sums add up to the whole job
+    okeys, ores = out
+    G_local = okeys.num_rows()
+    cnt = int(ores[0].columns()[1].data.sum(dtype=torch.int64).item())
+    sm = int(ores[0].columns()[0].data.sum(dtype=torch.int64).item())
+    uniq = int(torch.unique(okeys.columns()[0].data).numel()) == G_local
+    stats = torch.tensor([G_local, cnt, sm, total_rows, total_sum, int(uniq)], device=device, dtype=torch.int64)
+    if dist is not None:
+        allst = [torch.zeros_like(stats) for _ in range(world)]
+        dist.all_gather(allst, stats)
+        stats_all = torch.stack(allst).cpu().numpy()
+    else:
+        stats_all = stats.cpu().numpy()[None, :]
+    G_total = int(stats_all[:, 0].sum())
+    verified = bool(stats_all[:, 1].sum() == stats_all[:, 3].sum() and stats_all[:, 2].sum() == stats_all[:, 4].sum() and stats_all[:, 5].all()
+                    and G_total <= g)
+    # owner partition: a key belongs to exactly one rank iff the per-rank unique key sets add up to the distinct keys of the job
+    expected_groups = g if n_total >= 20 * g else None   # with >= 20 rows per key value every value occurs (P(miss) < 1e-8 each)
+    if expected_groups is not None:
+        verified = verified and G_total == expected_groups
+
+    # ---- phases (separate profiled pass) and the exchange's NVLink rate
+    pg = make_dgb(1)
+    pg.aggregate_shards(shards)
+    pg.aggregate_shards(shards)
+    prof = {}
+    for name, ms in pg.last_profile:
+        prof[name] = prof.get(name, 0.0) + ms
+    barrier()
+    rec_bytes = 20
+    out_bytes = None
+    nvlink = None
+    if world > 1:
+        # every rank holds ~all g groups after its local fold and keeps 1/world of them: (world-1)/world * G_fold records leave
+        g_fold = min(g, shard_rows * len(mine))
+        out_bytes = rec_bytes * g_fold * (world - 1) / world
+        ps = prof.get("peer_scatter")
+        if ps:
+            nvlink = {"bytes_out_per_gpu": out_bytes, "peer_scatter_ms": ps, "GBps_out_per_gpu": out_bytes / (ps * 1e-3) / 1e9,
+                      "peak_GBps": 900.0, "measured_peer_copy_GBps": 770.0}
+    # dominant local kernel against the HBM roofline (per call of the local path: one piece of one shard)
+    local = {k: v for k, v in prof.items() if not k.startswith("dist_") and not k.startswith("peer_")}
+    calls = len(shards)
+    roof = None
+    if local:
+        dom = max(local, key=local.get)
+        piece_rows = shards[0][0].num_rows()
+        alg = algorithmic_bytes("MG", piece_rows, min(g, piece_rows))
+        kms = local[dom] / calls
+        ach = alg / (kms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src,
+                "kernel_ms": kms, "algorithmic_bytes": alg, "traffic": None,
+                "whole_call": {"achieved": algorithmic_bytes("MG", n_total / world, g) / (ms_per_step * 1e-3) / 1e9,
+                               "frac": algorithmic_bytes("MG", n_total / world, g) / (ms_per_step * 1e-3) / 1e9 / peak},
+                "kernels_ms": {k: round(v, 4) for k, v in prof.items()},
+                "kernels_note": "sums over the rank's local calls in one step, from a separate profiled pass; dist_* are whole phases"}
+
+    # ---- e2e: the same job through DistributedGroupBy with HOST-resident shards: H2D of every shard inside the timed region,
+    # D2H of the rank's result columns at the end of the step
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e_multi(args, world, rank, device, dist, shards, shard_rows * len(mine), n_total, region)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": max(args.warmup, 3) if world > 1 else max(min(args.warmup, 3), 1),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": dtype, "data": "synthetic",
+            "config": {"workload": f"MG: {desc}", "rows_total": n_total, "shards": nshards, "rows_per_shard": shard_rows, "groups": g,
+                       "shards_per_gpu": len(mine), "pieces_per_shard": pieces_per_shard, "path": dgb.last_path, "exchange": dgb.last_exchange,
+                       "l2": "inputs (16 GB per shard) are larger than the 126 MB L2; no flush needed",
+                       "parallelism": f"shard{world}: local pre-aggregation per shard, fold on the rank, owner-rank exchange ({dgb.last_exchange}), merge"},
+            "verified": verified,
+            "verify": {"groups_total": G_total, "expected_groups": expected_groups, "rows_counted": int(stats_all[:, 1].sum()),
+                       "rows_total": int(stats_all[:, 3].sum()), "sums_match": bool(stats_all[:, 2].sum() == stats_all[:, 4].sum()),
+                       "keys_unique_per_rank": bool(stats_all[:, 5].all()),
+                       "method": "sum of counts == rows of the job, sum of sums == sum of every value column (int64, exact), every rank's keys unique, "
+                                 "groups over all ranks == distinct key values; per-group parity of the same code path is in tests/"},
+            "roofline": roof, "nvlink": nvlink, "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
+        }
+        emit_line(line)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def run_e2e_multi(args, world, rank, device, dist, shards, rows_local, n_total, region):
+    """End to end at N GPUs: every piece of this rank's shards starts in PINNED HOST memory; a step copies each piece to the
+    device (H2D inside the timed region), runs the whole distributed groupby (local aggregation, fold, exchange, merge) and
+    copies the rank's result columns back to the host. Pieces are staged one at a time (two device buffers), so the device
+    holds one piece, not the shard set."""
+    import torch
+
+    import cudf_b200 as cb
+    from cudf_b200 import distributed as D
+    # pinned copies of the pieces: at most 4 are materialised on the host and cycled (pinning 128 GB for the N=1 leg takes
+    # minutes; the bytes copied and the device work per step are those of the whole job either way)
+    keep = min(len(shards), 4)
+    host = []
+    for keys, reqs in shards[:keep]:
+        kc = keys.columns()[0]
+        vc = reqs[0]._values
+        hk = torch.empty(kc.size, dtype=kc.data.dtype, pin_memory=True)
+        hv = torch.empty(vc.size, dtype=vc.data.dtype, pin_memory=True)
+        hk.copy_(kc.data[kc.offset:kc.offset + kc.size])
+        hv.copy_(vc.data[vc.offset:vc.offset + vc.size])
+        host.append((hk, hv))
+    torch.cuda.synchronize()
+    aggs = shards[0][1][0]._aggregations
+    piece_rows = [s[0].num_rows() for s in shards]
+    stream = torch.cuda.current_stream(device)
+
+    class HostShards:
+        """iterable of (keys, requests): piece i + 1 is copied from pinned host memory on a side stream while piece i is
+        aggregated (two device buffers; a piece's call has returned before its buffer is reused)"""
+        def __init__(self):
+            self.bufs = [(torch.empty(max(piece_rows), dtype=torch.int64, device=device), torch.empty(max(piece_rows), dtype=torch.int64, device=device))
+                         for _ in range(2)]
+            self.copy_stream = torch.cuda.Stream(device)
+        def _issue(self, i):
+            hk, hv = host[i % keep]
+            dk, dv = self.bufs[i % 2]
+            nrow = piece_rows[i]
+            self.copy_stream.wait_stream(torch.cuda.current_stream(device))
+            with torch.cuda.stream(self.copy_stream):
+                dk[:nrow].copy_(hk[:nrow], non_blocking=True)
+                dv[:nrow].copy_(hv[:nrow], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self.copy_stream)
+            return ev
+        def __iter__(self):
+            ev = self._issue(0)
+            for i in range(len(shards)):
+                nxt = self._issue(i + 1) if i + 1 < len(shards) else None
+                torch.cuda.current_stream(device).wait_event(ev)
+                dk, dv = self.bufs[i % 2]
+                nrow = piece_rows[i]
+                yield (cb.Table([cb.Column(dk[:nrow])]), [cb.GroupByRequest(cb.Column(dv[:nrow]), aggs)])
+                ev = nxt
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    hs = HostShards()
+    dgb = D.DistributedGroupBy(shards[0][0], options={"force_path": args.force_path}, exchange=args.exchange, peer_region_bytes=region)
+
+    def step():
+        okeys, ores = dgb.aggregate_shards(hs)
+        res = [okeys.columns()[0].data.cpu()] + [c.data.cpu() for c in ores[0].columns()]
+        return res
+
+    res = step()
+    barrier()
+    steps = 2 if world == 1 else max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        res = step()
+    barrier()
+    dt = (time.perf_counter() - t0) / steps
+    if dist is not None:
+        t = torch.tensor([dt], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    h2d = 16 * sum(piece_rows)
+    d2h = sum(x.numel() * x.element_size() for x in res)
+    return {"value": n_total / dt, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": dt * 1e3,
+            "steps": steps, "groups_out_this_rank": int(res[0].numel()),
+            "api": "DistributedGroupBy.aggregate_shards over pinned host pieces (per-rank bytes; max over ranks of the wall time, barrier on both sides)"}
 
 
 if __name__ == "__main__":

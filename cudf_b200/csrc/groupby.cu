@@ -724,7 +724,9 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
   h->table.key_words = pl.key_words;
 
   // ---- capacity: explicit, or from the sampled cardinality estimate (one small kernel + one read-back)
-  const uint64_t cap_max = next_pow2((uint64_t)(2 * N < 1024 ? 1024 : 2 * N));
+  // (group_slots are 32-bit and the reserved slot's index is `capacity`: never more than 2^31 slots, load <= 0.5 for N < 2^30,
+  //  <= 1.0 beyond -- N < 2^31 always)
+  const uint64_t cap_max = std::min<uint64_t>(1ull << 31, next_pow2((uint64_t)(2 * N < 1024 ? 1024 : 2 * N)));
   uint64_t capacity      = 0;
   double g_est           = (double)N, g_raw = (double)N;
   uint64_t max_abs       = ~0ull, key_min = 1, key_max = 0;  // key_min > key_max: range not sampled
@@ -1356,6 +1358,8 @@ struct bgb_stream {
   uint32_t* new_keys = nullptr;   // device counter of distinct keys
   int32_t distinct = 0;
   cudaStream_t last_stream = nullptr;
+  bool invalidated = false;       // a fold failed part-way (distinct keys beyond the limit): the table holds a partial batch, so the
+                                  // object refuses every further use, like the reference (streaming_groupby/aggregate.cu:26, merge.cu:93)
 };
 
 static bool stream_kind_supported(int32_t kind)
@@ -1434,16 +1438,19 @@ static int stream_fold(bgb_stream* st, const TableDesc& src, const uint32_t* src
   if (!rc) rc = check_cuda(cudaMemcpyAsync(&host[0], st->new_keys, sizeof(uint32_t), cudaMemcpyDeviceToHost, s), "distinct copy");
   if (!rc) rc = check_cuda(cudaMemcpyAsync(&host[1], st->table.status, sizeof(uint32_t), cudaMemcpyDeviceToHost, s), "status copy");
   if (!rc) rc = check_cuda(cudaStreamSynchronize(s), "stream fold sync");
-  if (rc) return rc;
+  if (rc) { st->invalidated = true; return rc; }
   st->distinct = (int32_t)host[0];
-  if (host[1] != 0 || host[0] > (uint32_t)st->max_keys)
+  if (host[1] != 0 || host[0] > (uint32_t)st->max_keys) {
+    st->invalidated = true;
     return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: cumulative distinct keys (%u) exceed max_distinct_keys (%d)", host[0], st->max_keys);
+  }
   return BGB_OK;
 }
 
 extern "C" int bgb_stream_aggregate(bgb_stream* st, const bgb_column_view* columns, int32_t num_columns, void* stream, const bgb_options* options)
 {
   if (!st || (num_columns > 0 && !columns)) return set_error(BGB_INVALID_ARGUMENT, "null argument");
+  if (st->invalidated) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: the object was invalidated by a failed aggregate() / merge() and cannot be used");
   std::vector<bgb_column_view> keys;
   for (int32_t k : st->key_indices) {
     if (k < 0 || k >= num_columns) return set_error(BGB_INVALID_ARGUMENT, "key index %d out of range (%d columns)", k, num_columns);
@@ -1509,6 +1516,8 @@ extern "C" int bgb_stream_aggregate(bgb_stream* st, const bgb_column_view* colum
 extern "C" int bgb_stream_merge(bgb_stream* st, const bgb_stream* other, void* stream)
 {
   if (!st || !other) return set_error(BGB_INVALID_ARGUMENT, "null argument");
+  if (st->invalidated) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: the object was invalidated by a failed aggregate() / merge() and cannot be used");
+  if (other->invalidated) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: the other object was invalidated by a failed aggregate() / merge()");
   if (!st->initialized) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: merge() needs an object that has seen at least one aggregate()");
   if (!other->initialized || other->distinct == 0) return BGB_OK;
   if (!plans_compatible(st->master, other->master)) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: the two objects have different aggregation requests or column types");
@@ -1537,6 +1546,7 @@ extern "C" int bgb_stream_finalize(const bgb_stream* st, void* stream, bgb_group
   if (!st || !out_handle || !num_groups) return set_error(BGB_INVALID_ARGUMENT, "null argument");
   *out_handle = nullptr;
   *num_groups = 0;
+  if (st->invalidated) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: the object was invalidated by a failed aggregate() / merge() and cannot be used");
   if (!st->initialized) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: no data has been accumulated");
   bgb_groupby* h = new bgb_groupby();
   h->plan   = st->master;

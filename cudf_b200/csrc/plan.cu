@@ -258,8 +258,10 @@ extern "C" int32_t bgb_target_type(int32_t values_type_id, int32_t kind) { retur
 extern "C" int bgb_can_use_hash_groupby(const bgb_column_view* keys, int32_t num_keys, const bgb_request* requests,
                                         int32_t num_requests, int32_t* out)
 {
+  // same eligibility as bgb_groupby_build: key images wider than 128 bits are planned (build serves them by key repacking or
+  // through row-index slots); the null policy does not change the answer
   bgb::Plan p;
-  int rc = bgb::make_plan(keys, num_keys, 0, requests, num_requests, p);
+  int rc = bgb::make_plan(keys, num_keys, 0, requests, num_requests, p, false, /*allow_wide=*/true);
   if (out) *out = (rc == BGB_OK);
   return rc == BGB_UNSUPPORTED ? BGB_OK : rc;
 }

@@ -132,6 +132,17 @@ void pool_free_async(void* p, cudaStream_t s)
   }
 }
 
+void pool_release_stream(cudaStream_t s)
+{
+  std::lock_guard<std::mutex> lock(g_mu);
+  DeviceCache* c = current_cache();
+  if (!c) return;
+  auto it = c->free_blocks.find(s);
+  if (it == c->free_blocks.end()) return;
+  for (FreeBlock& b : it->second) { cudaFreeAsync(b.p, s); c->cached_bytes -= b.bytes; }
+  c->free_blocks.erase(it);  // a destroyed stream's handle must never be used again (flush_locked frees on the key)
+}
+
 void pool_trim()
 {
   std::lock_guard<std::mutex> lock(g_mu);

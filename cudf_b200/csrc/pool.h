@@ -9,4 +9,5 @@ namespace bgb {
 void* pool_alloc_async(size_t bytes, cudaStream_t s);   // nullptr on failure (error state cleared)
 void pool_free_async(void* p, cudaStream_t s);
 void pool_trim();  // hand every cached block of the current device back to the driver
+void pool_release_stream(cudaStream_t s);  // hand back the blocks cached for stream `s` (call before destroying the stream)
 }  // namespace bgb

@@ -32,7 +32,8 @@ from .column import Column, Table, torch_dtype
 
 
 _MERGE_KIND = {Kind.SUM: Kind.SUM, Kind.PRODUCT: Kind.PRODUCT, Kind.MIN: Kind.MIN, Kind.MAX: Kind.MAX,
-               Kind.SUM_OF_SQUARES: Kind.SUM, Kind.COUNT_VALID: Kind.MERGE_COUNT, Kind.COUNT_ALL: Kind.MERGE_COUNT}
+               Kind.SUM_OF_SQUARES: Kind.SUM, Kind.COUNT_VALID: Kind.MERGE_COUNT, Kind.COUNT_ALL: Kind.MERGE_COUNT,
+               Kind.MERGE_COUNT: Kind.MERGE_COUNT}  # (merging merged partials: the sum of counts again)
 
 
 @dataclass
@@ -55,7 +56,7 @@ def decompose(aggregations) -> RequestPlan:
     rp = RequestPlan()
     for a in aggregations:
         k = a.kind
-        if k in (Kind.SUM, Kind.PRODUCT, Kind.MIN, Kind.MAX, Kind.SUM_OF_SQUARES, Kind.COUNT_VALID, Kind.COUNT_ALL):
+        if k in (Kind.SUM, Kind.PRODUCT, Kind.MIN, Kind.MAX, Kind.SUM_OF_SQUARES, Kind.COUNT_VALID, Kind.COUNT_ALL, Kind.MERGE_COUNT):
             rp.recipes.append(("copy", rp.partial(k)))
         elif k == Kind.MEAN:
             rp.recipes.append(("mean", rp.partial(Kind.SUM), rp.partial(Kind.COUNT_VALID)))
@@ -438,6 +439,92 @@ class DistributedGroupBy:
         self.last_merge_path = merger.last_path
 
         # (5) finalise: copy-through or MEAN / M2 / VARIANCE / STD from the merged SUM / SUMSQ / COUNT columns
+        results = self._finalize(requests, plans, merged, device)
+        self._phase_end(tok, device)
+        return okeys, results
+
+
+    # -- several shards per rank (strong scaling: BASELINE configs[4] holds 8 shards whatever the number of GPUs)
+    def aggregate_shards(self, shards):
+        """shards: [(keys Table, [GroupByRequest])] -- the pieces of this rank's rows, each at most 2^31-1 rows (cudf::size_type),
+        all with the same column types and aggregations. Every shard is pre-aggregated with the single-GPU path into PARTIAL
+        columns (decompose()), the shards' partial tables are folded together on this rank with the merge kinds (a running
+        table, so only two partial tables are alive at a time), and the folded table goes through the ordinary distributed
+        merge (peer-memory or NCCL exchange by owner rank). One shard is exactly aggregate(). The decomposition is the one
+        cudf_polars uses across partitions (/root/reference/python/cudf_polars/cudf_polars/streaming/groupby.py:322-435); the
+        fold is streaming_groupby::merge (/root/reference/cpp/src/groupby/streaming_groupby/merge.cu:30-144)."""
+        from .groupby import GroupBy, GroupByRequest
+        it = iter(shards)  # consumed lazily: a caller may stage shard i + 1 (host -> device) while shard i is aggregated
+        first = next(it)
+        second = next(it, None)
+        if second is None:
+            self._keys = first[0]
+            return self.aggregate(first[1])
+        requests0 = first[1]
+        plans = [decompose(r._aggregations) for r in requests0]
+        device = first[0].columns()[0].data.device
+        self._phase_events = []
+        self._local_profile = []
+        nk = first[0].num_columns()
+
+        def chain():
+            yield first
+            yield second
+            yield from it
+        merge_opts = {kk: v for kk, v in self._options.items() if kk in ("profile",)}
+
+        def merge_requests(cols):
+            reqs, k = [], nk
+            for p in plans:
+                for kind in p.partial_kinds:
+                    reqs.append(GroupByRequest(cols[k], [agg.Aggregation(merge_kind(kind))]))
+                    k += 1
+            return reqs
+
+        def concat(a, b):
+            """two partial tables (lists of Columns with offset 0) -> one; validity through bytes when any side carries a mask"""
+            out = []
+            for ca, cb_ in zip(a, b):
+                data = torch.cat([ca.data[:ca.size], cb_.data[:cb_.size]])
+                if ca.mask is None and cb_.mask is None:
+                    out.append(Column(data, None, 0, ca.type_id, scale=ca.scale))
+                    continue
+                vb = torch.cat([_valid_bytes(ca), _valid_bytes(cb_)])
+                out.append(column_from_wire(data, vb, ca.type_id, ca.scale))
+            return out
+
+        running = None
+        for keys, reqs in chain():
+            local_reqs = [GroupByRequest(r._values, [agg.Aggregation(k) for k in p.partial_kinds]) for r, p in zip(reqs, plans)]
+            tok = self._phase("dist_local", device)
+            local = GroupBy(keys, self._null_handling, options=self._options)
+            pkeys, presults = local.aggregate(local_reqs)
+            self._phase_end(tok, device)
+            self._local_profile.extend(local.last_profile)
+            self.last_path = local.last_path
+            flat = list(pkeys.columns()) + [c for t in presults for c in t.columns()]
+            if running is None:
+                running = flat
+                continue
+            tok = self._phase("dist_fold", device)
+            cols = concat(running, flat)
+            del running, flat, pkeys, presults
+            fk, fr = GroupBy(Table(cols[:nk]), self._null_handling, options=merge_opts).aggregate(merge_requests(cols))
+            running = list(fk.columns()) + [t.columns()[0] for t in fr]
+            del cols, fk, fr
+            self._phase_end(tok, device)
+
+        # the folded partial table through the distributed merge (its requests are merge kinds of single partial columns)
+        dg = DistributedGroupBy(Table(running[:nk]), self._null_handling, options=merge_opts, comm=self._comm, exchange=self._exchange,
+                                peer_region_bytes=self._peer_region_bytes)
+        okeys, merged = dg.aggregate(merge_requests(running))
+        self.last_exchange = dg.last_exchange
+        self._local_profile.extend(dg._local_profile)
+        self._phase_events.extend(dg._phase_events)
+        return okeys, self._finalize(requests0, plans, merged, device)
+
+    def _finalize(self, requests, plans, merged, device):
+        """merged: one single-column Table per partial column, request-major -> one result Table per request"""
         results, k = [], 0
         for r, p in zip(requests, plans):
             part = [merged[k + j].columns()[0] for j in range(len(p.partial_kinds))]
@@ -447,12 +534,21 @@ class DistributedGroupBy:
                 if rec[0] == "copy":
                     outs.append(part[rec[1]])
                 elif rec[0] == "mean":
-                    s, c = part[rec[1]], part[rec[2]]
+                    s_, c_ = part[rec[1]], part[rec[2]]
                     out_type = _lib.lib().bgb_target_type(r._values.type_id, Kind.MEAN)
-                    outs.append(finalize_moments(Kind.MEAN, 0, s, None, c, s.mask is not None, out_type))
+                    outs.append(finalize_moments(Kind.MEAN, 0, s_, None, c_, s_.mask is not None, out_type))
                 else:
                     _, kind, ddof, si, qi, ci = rec
                     outs.append(finalize_moments(kind, ddof, part[si], part[qi], part[ci], kind != Kind.M2))
             results.append(Table(outs))
-        self._phase_end(tok, device)
-        return okeys, results
+        return results
+
+
+def _valid_bytes(col: Column) -> torch.Tensor:
+    """validity of a Column (offset 0) as one byte per row (1 = valid)"""
+    n = col.size
+    if col.mask is None:
+        return torch.ones(n, dtype=torch.uint8, device=col.data.device)
+    words = col.mask.view(torch.int32)
+    idx = torch.arange(n, device=col.data.device, dtype=torch.int64)
+    return ((words[idx >> 5] >> (idx & 31).to(torch.int32)) & 1).to(torch.uint8)

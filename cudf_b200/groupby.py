@@ -168,7 +168,8 @@ def groupby_host(keys, requests, null_handling: int = NullPolicy.EXCLUDE, option
     """End-to-end call on HOST columns through the C ABI's bgb_groupby_host: H2D staging, build, emit, D2H.
 
     keys: [HostColumnView]; requests: [(HostColumnView, [Aggregation])].
-    Returns (num_groups, [(data, mask_words|None, null_count)] keys, [[...] per request]) as numpy arrays (copied)."""
+    Returns (num_groups, [(data, mask_words|None, null_count)] keys, [[...] per request]) as numpy arrays that VIEW the host
+    buffers the library allocated (no copy); the buffers are released when the last array is garbage-collected."""
     import numpy as np
     from .column import _NP_OF_TYPE
     L = _lib.lib()
@@ -195,25 +196,37 @@ def groupby_host(keys, requests, null_handling: int = NullPolicy.EXCLUDE, option
                                   C.byref(hr), C.byref(nres)))
     G = ng.value
 
+    class _Owner:
+        """keeps the C result alive while any returned array views it; frees it (bgb_free_host_result) afterwards"""
+        def __init__(self):
+            self.hk, self.hr, self.nk, self.nres = hk, hr, nk, nres.value
+        def __del__(self):
+            L.bgb_free_host_result(self.hk, self.nk)
+            L.bgb_free_host_result(self.hr, self.nres)
+
+    owner = _Owner()
+
+    def view(ptr, nbytes, dt):
+        buf = (C.c_uint8 * nbytes).from_address(ptr)
+        buf._owner = owner  # the numpy array references `buf` (buffer protocol), `buf` references the owner
+        return np.frombuffer(buf, dtype=dt)
+
     def take(hc):
         dt = np.dtype(_NP_OF_TYPE[hc.type_id])
         if G == 0:
             return np.empty(0, dt), None, 0
-        data = np.ctypeslib.as_array(C.cast(hc.data, C.POINTER(C.c_uint8)), shape=(G * dt.itemsize,)).view(dt).copy()
+        data = view(hc.data, G * dt.itemsize, dt)   # zero-copy: the library's host buffer
         mask = None
         if hc.null_mask:
-            mask = np.ctypeslib.as_array(C.cast(hc.null_mask, C.POINTER(C.c_uint32)), shape=((G + 31) // 32,)).copy()
+            mask = view(hc.null_mask, ((G + 31) // 32) * 4, np.uint32)
         return data, mask, hc.null_count
 
-    try:
-        kout = [take(hk[i]) for i in range(nk)]
-        rout, k = [], 0
-        for _, aggs in requests:
-            rout.append([take(hr[k + j]) for j in range(len(aggs))])
-            k += len(aggs)
-    finally:
-        L.bgb_free_host_result(hk, nk)
-        L.bgb_free_host_result(hr, nres.value)
+    kout = [take(hk[i]) for i in range(nk)]
+    rout, k = [], 0
+    for _, aggs in requests:
+        rout.append([take(hr[k + j]) for j in range(len(aggs))])
+        k += len(aggs)
+    del owner
     return G, kout, rout
 
 

@@ -182,13 +182,13 @@ int64_t bgb_kernel_launches(void);
 /* ---- host-buffer convenience (end-to-end measurement and simple callers) ------------------------------------- */
 
 /* Same call with HOST columns (pinned or pageable): copies inputs H2D in chunks overlapped with aggregation,
- * runs build+emit, copies the results D2H into host buffers the library allocates with malloc
- * (*out_keys / *out_results, release with bgb_free_host_result). */
+ * runs build+emit, copies the results D2H into host buffers the library allocates (*out_keys / *out_results: pinned host memory
+ * from a cache of released result blocks, pageable memory when pinning fails; release ONLY with bgb_free_host_result). */
 typedef struct bgb_host_column {
   int32_t type_id;
   int32_t size;
-  void* data;          /* malloc'ed, size elements */
-  uint32_t* null_mask; /* malloc'ed or NULL */
+  void* data;          /* library-owned, size elements */
+  uint32_t* null_mask; /* library-owned or NULL */
   int32_t null_count;
   int32_t reserved;
 } bgb_host_column;

@@ -430,6 +430,42 @@ def test_peer_two_steps_reuse_the_context():
         np.testing.assert_array_equal(gc[order], np.bincount(inv))
 
 
+@pytest.mark.parametrize("exchange", EXCHANGES)
+@pytest.mark.parametrize("nshards,null_frac", [(2, 0.0), (3, 0.3), (5, 0.0)])
+def test_aggregate_shards_on_one_rank(exchange, nshards, null_frac):
+    # several shards per rank (strong scaling of BASELINE configs[4]): per-shard partials folded on the rank, then the ordinary
+    # distributed merge; the result is the groupby of the concatenated shards (the reference's verify_against_groupby idea,
+    # cpp/tests/groupby/streaming_groupby_test.cpp:60-110)
+    shards = int_shards(nshards, 20_000, 700, null_frac=null_frac, seed=5)
+    if null_frac:
+        shards[1][1][0].valid[shards[1][0][0].data == 3] = False  # a group that is all-null in one shard only
+    aggs = [(0, "sum", 1), (0, "count_valid", 1), (0, "count_all", 1), (0, "min", 1), (0, "max", 1), (0, "mean", 1), (0, "variance", 1),
+            (0, "std", 0), (0, "m2", 1)]
+    keys, values = concat_shards(shards)
+    Go, ko, ao = orc.groupby(keys, values, aggs, threads=4)
+    dev_shards = []
+    for k, v in shards:
+        dk, dv = [to_device(c) for c in k], [to_device(c) for c in v]
+        dev_shards.append((cb.Table(dk), [cb.GroupByRequest(dv[0], [make_agg(kind, d) for _, kind, d in aggs])]))
+    dgb = D.DistributedGroupBy(dev_shards[0][0], comm=D.SingleComm(), exchange=exchange, peer_region_bytes=8 << 20)
+    kt, rts = dgb.aggregate_shards(dev_shards)
+    ctx = getattr(dgb._comm, "_bgb_peer_ctx", None)
+    kd, kv = kt.columns()[0].to_numpy()
+    order = np.argsort(kd)
+    assert len(kd) == Go
+    np.testing.assert_array_equal(kd[order], ko[0][0])
+    for a in range(len(aggs)):
+        d, v = rts[0].columns()[a].to_numpy()
+        np.testing.assert_array_equal(v[order], ao[a][1], err_msg=f"agg {aggs[a]} validity")
+        got, exp = d[order][ao[a][1]], ao[a][0][ao[a][1]]
+        if got.dtype.kind == "f":
+            np.testing.assert_allclose(got, exp, rtol=1e-9, atol=0, err_msg=f"agg {aggs[a]}")
+        else:
+            np.testing.assert_array_equal(got, exp, err_msg=f"agg {aggs[a]}")
+    if ctx is not None:
+        ctx.close()
+
+
 def test_unsupported_kind_raises():
     k = cb.Column.from_numpy(np.arange(10, dtype=np.int64))
     dgb = D.DistributedGroupBy(cb.Table([k]), comm=D.SingleComm())
