@@ -16,8 +16,8 @@ Workloads (BASELINE.json configs / SURVEY.md 8d):
   Q1     2 int8 keys (4 groups), 2 float64 values, MEAN+VAR+COUNT each, N=6e8   (configs[3])
   C1     2 int64 keys 32x32, 2 float64 MEANs, N=1e7          (configs[0]'s shape on the GPU)
   MG     configs[4]: 8 shards x 1e9 rows (shard s = seed 42+s), int64 key x%1e8, SUM+COUNT -- STRONG scaling: the 8 shards
-         are spread over the N ranks (8/N each; at N=1 every shard is fed as two 5e8-row halves so that inputs + scratch
-         fit 180 GB), per-shard partials are folded on the rank, the folded table is exchanged by owner rank (peer-memory
+         are spread over the N ranks (8/N each; at N=1 every shard is fed as four 2.5e8-row quarters so that inputs +
+         scratch fit the GPU), per-shard partials are folded on the rank, the folded table is exchanged by owner rank (peer-memory
          stores over NVLink, or --exchange nccl for the all-to-all) and merged. This is what --gpus N>1 runs.
 With no --workload, --gpus 1 times A9g as the headline and then A9, B, Q1, C1, A, AS as a "sweep" array in the same JSON line
 (the reference's own precedent for one run across cardinalities: cpp/benchmarks/groupby/group_max.cpp:79-165).
@@ -713,6 +713,10 @@ def run_multi(args, world):
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     device = torch.device("cuda", local_rank)
     torch.cuda.set_device(device)
+    if world == 1:
+        # one GPU holds all 128 GB of inputs: the library's pool and its block cache are bounded so that torch's allocator (outputs,
+        # concatenations) and the pool do not starve each other of the remaining ~60 GB
+        pass
     dist = None
     if world > 1:
         import torch.distributed as dist_mod
@@ -727,8 +731,9 @@ def run_multi(args, world):
     if nshards % world != 0:
         raise SystemExit(f"--shards {nshards} must be a multiple of the number of ranks ({world})")
     mine = list(range(rank * nshards // world, (rank + 1) * nshards // world))
-    # one GPU holding all 8 shards (128 GB) has ~50 GB left: a 1e9-row call needs 44 GB of scratch + table, so every shard is fed as halves
-    pieces_per_shard = args.pieces or (2 if world == 1 and shard_rows * nshards > 4_000_000_000 else 1)
+    # one GPU holding all 8 shards (128 GB of 192) has ~60 GB left: a 1e9-row call needs 44 GB of scratch + table, a 2.5e8-row call
+    # 15 GB, and partial tables, their concatenation and the fold need room too: every shard is fed as quarters
+    pieces_per_shard = args.pieces or (4 if world == 1 and shard_rows * nshards > 4_000_000_000 else 1)
     shards, total_sum, total_rows = [], 0, 0
     for sidx in mine:
         keys, reqs = make_device_inputs("MG", shard_rows, g, 42 + 2 * sidx, device)  # (seed, seed + 1) per shard: key and value streams never collide
@@ -749,9 +754,12 @@ def run_multi(args, world):
         # receive region: every source sends ~G / world^2 records of 20 bytes to this rank; x2 headroom
         region = max(region, int(2.0 * 20 * g / world) + (8 << 20))
 
+    comm = D.TorchComm() if dist is not None else D.SingleComm()   # ONE communicator: its peer-memory context is created once
+    fold_rows = 190_000_000 if world == 1 else 450_000_000          # one GPU holding 128 GB of inputs keeps fewer partial tables pending
+
     def make_dgb(profile):
-        return D.DistributedGroupBy(shards[0][0], options={"profile": profile, "force_path": args.force_path}, exchange=args.exchange,
-                                    peer_region_bytes=region)
+        return D.DistributedGroupBy(shards[0][0], options={"profile": profile, "force_path": args.force_path, "fold_rows": fold_rows},
+                                    exchange=args.exchange, peer_region_bytes=region, comm=comm)
 
     def barrier():
         if dist is not None:
@@ -785,6 +793,8 @@ def run_multi(args, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms = float(t.item())
     ms_per_step = total_ms / steps
+    log(f"rank {rank}: {ms_per_step:.1f} ms/step; torch reserved {torch.cuda.memory_reserved(device) / 1e9:.1f} GB, allocated {torch.cuda.memory_allocated(device) / 1e9:.1f} GB, "
+        f"max allocated {torch.cuda.max_memory_allocated(device) / 1e9:.1f} GB")
     n_total = shard_rows * nshards
     value = n_total / (ms_per_step * 1e-3)
 
@@ -803,11 +813,20 @@ def run_multi(args, world):
         stats_all = stats.cpu().numpy()[None, :]
     G_total = int(stats_all[:, 0].sum())
     verified = bool(stats_all[:, 1].sum() == stats_all[:, 3].sum() and stats_all[:, 2].sum() == stats_all[:, 4].sum() and stats_all[:, 5].all()
-                    and G_total <= g)
-    # owner partition: a key belongs to exactly one rank iff the per-rank unique key sets add up to the distinct keys of the job
-    expected_groups = g if n_total >= 20 * g else None   # with >= 20 rows per key value every value occurs (P(miss) < 1e-8 each)
-    if expected_groups is not None:
-        verified = verified and G_total == expected_groups
+                    and 0 < G_total <= g)
+    # owner partition: the ranks' key sets are disjoint iff the union of all keys has as many elements as the ranks hold together
+    if dist is not None:
+        gmax = int(stats_all[:, 0].max())
+        padded = torch.full((gmax,), -1, dtype=torch.int64, device=device)
+        padded[:G_local] = okeys.columns()[0].data
+        gathered = [torch.empty(gmax, dtype=torch.int64, device=device) for _ in range(world)] if rank == 0 else None
+        dist.gather(padded, gathered, dst=0)
+        if rank == 0:
+            allk = torch.cat([gathered[r][:int(stats_all[r, 0])] for r in range(world)])
+            verified = verified and int(torch.unique(allk).numel()) == G_total
+            del allk, gathered
+        del padded
+    expected_groups = None
 
     # ---- phases (separate profiled pass) and the exchange's NVLink rate
     pg = make_dgb(1)
@@ -848,8 +867,24 @@ def run_multi(args, world):
     # ---- e2e: the same job through DistributedGroupBy with HOST-resident shards: H2D of every shard inside the timed region,
     # D2H of the rank's result columns at the end of the step
     e2e = None
+    shards_per_gpu, last_path, last_exchange = len(mine), dgb.last_path, dgb.last_exchange
     if not args.no_e2e:
-        e2e = run_e2e_multi(args, world, rank, device, dist, shards, shard_rows * len(mine), n_total, region)
+        # pinned host copies of (at most 4 of) the pieces, then the device-resident inputs are released: the e2e leg stages from the host
+        keep = min(len(shards), 4)
+        host = []
+        for keys, reqs in shards[:keep]:
+            kc, vc = keys.columns()[0], reqs[0]._values
+            hk = torch.empty(kc.size, dtype=kc.data.dtype, pin_memory=True)
+            hv = torch.empty(vc.size, dtype=vc.data.dtype, pin_memory=True)
+            hk.copy_(kc.data[kc.offset:kc.offset + kc.size])
+            hv.copy_(vc.data[vc.offset:vc.offset + vc.size])
+            host.append((hk, hv))
+        piece_rows = [sh[0].num_rows() for sh in shards]
+        aggs = shards[0][1][0]._aggregations
+        torch.cuda.synchronize()
+        del shards, keys, reqs, out, okeys, ores, dgb, pg
+        free_device_memory(L)
+        e2e = run_e2e_multi(args, world, rank, device, dist, host, piece_rows, aggs, n_total, region, comm)
 
     if rank == 0:
         line = {
@@ -857,15 +892,16 @@ def run_multi(args, world):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": dtype, "data": "synthetic",
             "config": {"workload": f"MG: {desc}", "rows_total": n_total, "shards": nshards, "rows_per_shard": shard_rows, "groups": g,
-                       "shards_per_gpu": len(mine), "pieces_per_shard": pieces_per_shard, "path": dgb.last_path, "exchange": dgb.last_exchange,
+                       "shards_per_gpu": shards_per_gpu, "pieces_per_shard": pieces_per_shard, "path": last_path, "exchange": last_exchange,
                        "l2": "inputs (16 GB per shard) are larger than the 126 MB L2; no flush needed",
-                       "parallelism": f"shard{world}: local pre-aggregation per shard, fold on the rank, owner-rank exchange ({dgb.last_exchange}), merge"},
+                       "parallelism": f"shard{world}: local pre-aggregation per shard, fold on the rank, owner-rank exchange ({last_exchange}), merge"},
             "verified": verified,
             "verify": {"groups_total": G_total, "expected_groups": expected_groups, "rows_counted": int(stats_all[:, 1].sum()),
                        "rows_total": int(stats_all[:, 3].sum()), "sums_match": bool(stats_all[:, 2].sum() == stats_all[:, 4].sum()),
                        "keys_unique_per_rank": bool(stats_all[:, 5].all()),
                        "method": "sum of counts == rows of the job, sum of sums == sum of every value column (int64, exact), every rank's keys unique, "
-                                 "groups over all ranks == distinct key values; per-group parity of the same code path is in tests/"},
+                                 "the union of all ranks' keys (gathered on rank 0) has as many elements as the ranks hold together (owner sets are "
+                                 "disjoint); per-group parity of the same code path against the oracle is in tests/"},
             "roofline": roof, "nvlink": nvlink, "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
         }
         emit_line(line)
@@ -873,31 +909,18 @@ def run_multi(args, world):
         dist.destroy_process_group()
 
 
-def run_e2e_multi(args, world, rank, device, dist, shards, rows_local, n_total, region):
-    """End to end at N GPUs: every piece of this rank's shards starts in PINNED HOST memory; a step copies each piece to the
-    device (H2D inside the timed region), runs the whole distributed groupby (local aggregation, fold, exchange, merge) and
-    copies the rank's result columns back to the host. Pieces are staged one at a time (two device buffers), so the device
-    holds one piece, not the shard set."""
+def run_e2e_multi(args, world, rank, device, dist, host, piece_rows, aggs, n_total, region, comm):
+    """End to end at N GPUs: every piece of this rank's shards starts in PINNED HOST memory (`host`: the pinned copies, cycled when
+    the rank has more pieces than copies -- pinning 128 GB for the N=1 leg would take minutes; the bytes copied and the device
+    work per step are those of the whole job either way); a step copies each piece to the device (H2D inside the timed region,
+    piece i + 1 while piece i is aggregated), runs the whole distributed groupby (local aggregation, fold, exchange, merge) and
+    copies the rank's result columns back to the host."""
     import torch
 
     import cudf_b200 as cb
     from cudf_b200 import distributed as D
-    # pinned copies of the pieces: at most 4 are materialised on the host and cycled (pinning 128 GB for the N=1 leg takes
-    # minutes; the bytes copied and the device work per step are those of the whole job either way)
-    keep = min(len(shards), 4)
-    host = []
-    for keys, reqs in shards[:keep]:
-        kc = keys.columns()[0]
-        vc = reqs[0]._values
-        hk = torch.empty(kc.size, dtype=kc.data.dtype, pin_memory=True)
-        hv = torch.empty(vc.size, dtype=vc.data.dtype, pin_memory=True)
-        hk.copy_(kc.data[kc.offset:kc.offset + kc.size])
-        hv.copy_(vc.data[vc.offset:vc.offset + vc.size])
-        host.append((hk, hv))
-    torch.cuda.synchronize()
-    aggs = shards[0][1][0]._aggregations
-    piece_rows = [s[0].num_rows() for s in shards]
-    stream = torch.cuda.current_stream(device)
+    keep = len(host)
+    npieces = len(piece_rows)
 
     class HostShards:
         """iterable of (keys, requests): piece i + 1 is copied from pinned host memory on a side stream while piece i is
@@ -919,8 +942,8 @@ def run_e2e_multi(args, world, rank, device, dist, shards, rows_local, n_total, 
             return ev
         def __iter__(self):
             ev = self._issue(0)
-            for i in range(len(shards)):
-                nxt = self._issue(i + 1) if i + 1 < len(shards) else None
+            for i in range(npieces):
+                nxt = self._issue(i + 1) if i + 1 < npieces else None
                 torch.cuda.current_stream(device).wait_event(ev)
                 dk, dv = self.bufs[i % 2]
                 nrow = piece_rows[i]
@@ -933,7 +956,8 @@ def run_e2e_multi(args, world, rank, device, dist, shards, rows_local, n_total, 
         torch.cuda.synchronize()
 
     hs = HostShards()
-    dgb = D.DistributedGroupBy(shards[0][0], options={"force_path": args.force_path}, exchange=args.exchange, peer_region_bytes=region)
+    dgb = D.DistributedGroupBy(None, options={"force_path": args.force_path, "fold_rows": 190_000_000 if world == 1 else 450_000_000},
+                               exchange=args.exchange, peer_region_bytes=region, comm=comm)
 
     def step():
         okeys, ores = dgb.aggregate_shards(hs)

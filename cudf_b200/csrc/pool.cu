@@ -11,6 +11,7 @@
 
 #include <mutex>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <unordered_map>
 #include <vector>
@@ -31,6 +32,9 @@ struct DeviceCache {
 
 std::mutex g_mu;
 DeviceCache g_cache[64];
+// diagnostics (BGB_TRACE): how often the block cache missed and how often the driver ran out of memory
+size_t g_hits = 0, g_driver_allocs = 0, g_oom_flushes = 0, g_driver_bytes = 0;
+struct PoolReport { ~PoolReport() { if (getenv("BGB_TRACE")) fprintf(stderr, "[bgb pool] cache hits %zu, driver allocations %zu (%.1f GB), out-of-memory flushes %zu\n", g_hits, g_driver_allocs, g_driver_bytes / 1e9, g_oom_flushes); } } g_report;
 
 DeviceCache* current_cache()
 {
@@ -44,7 +48,13 @@ DeviceCache* current_cache()
     props.location.type = cudaMemLocationTypeDevice;
     props.location.id   = dev;
     if (cudaMemPoolCreate(&c.pool, &props) != cudaSuccess) { cudaGetLastError(); c.pool = nullptr; }
-    else { uint64_t keep = ~0ull; cudaMemPoolSetAttribute(c.pool, cudaMemPoolAttrReleaseThreshold, &keep); }
+    else {
+      // BGB_POOL_KEEP_MB: bytes the driver pool may keep reserved across synchronisations (default: everything); a process that
+      // shares the device with other allocators near its capacity sets a bound so that unused pool memory goes back to the driver
+      uint64_t keep = ~0ull;
+      if (const char* e = getenv("BGB_POOL_KEEP_MB")) keep = (uint64_t)atoll(e) << 20;
+      cudaMemPoolSetAttribute(c.pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); total_b = 64ull << 30; }
     c.limit_bytes = total_b / 10 * 4;  // keep at most 40 % of the device cached
@@ -76,6 +86,14 @@ void flush_locked(DeviceCache& c)
 void* pool_alloc_async(size_t bytes, cudaStream_t s)
 {
   bytes = ((bytes ? bytes : 16) + 255) & ~(size_t)255;
+  if (bytes >= ((size_t)64 << 20)) {
+    // size classes for large blocks (1/8 of the leading power of two, <= 12.5 % waste): calls whose row counts differ by a few
+    // per cent (the folds of a multi-shard job) then ask for the SAME size and re-use each other's blocks; exact sizes made every
+    // such call miss the cache and grow the pool until the driver ran out of memory
+    size_t step = (size_t)1 << 26;
+    while ((step << 4) <= bytes) step <<= 1;
+    bytes = (bytes + step - 1) & ~(step - 1);
+  }
   std::lock_guard<std::mutex> lock(g_mu);
   DeviceCache* c = current_cache();
   if (!c) return nullptr;
@@ -93,11 +111,14 @@ void* pool_alloc_async(size_t bytes, cudaStream_t s)
       v.pop_back();
       c->cached_bytes -= b.bytes;
       c->live[b.p] = b.bytes;
+      ++g_hits;
       return b.p;
     }
   }
   void* p = driver_alloc(*c, bytes, s);
+  ++g_driver_allocs; g_driver_bytes += bytes;
   if (!p) {  // out of memory: return the cache to the driver and try once more
+    ++g_oom_flushes;
     flush_locked(*c);
     cudaStreamSynchronize(s);
     p = driver_alloc(*c, bytes, s);

@@ -448,8 +448,8 @@ class DistributedGroupBy:
     def aggregate_shards(self, shards):
         """shards: [(keys Table, [GroupByRequest])] -- the pieces of this rank's rows, each at most 2^31-1 rows (cudf::size_type),
         all with the same column types and aggregations. Every shard is pre-aggregated with the single-GPU path into PARTIAL
-        columns (decompose()), the shards' partial tables are folded together on this rank with the merge kinds (a running
-        table, so only two partial tables are alive at a time), and the folded table goes through the ordinary distributed
+        columns (decompose()), the shards' partial tables are folded together on this rank with the merge kinds (in batches
+        of ~4.5e8 pending rows: options["fold_rows"]), and the folded table goes through the ordinary distributed
         merge (peer-memory or NCCL exchange by owner rank). One shard is exactly aggregate(). The decomposition is the one
         cudf_polars uses across partitions (/root/reference/python/cudf_polars/cudf_polars/streaming/groupby.py:322-435); the
         fold is streaming_groupby::merge (/root/reference/cpp/src/groupby/streaming_groupby/merge.cu:30-144)."""
@@ -481,19 +481,41 @@ class DistributedGroupBy:
                     k += 1
             return reqs
 
-        def concat(a, b):
-            """two partial tables (lists of Columns with offset 0) -> one; validity through bytes when any side carries a mask"""
+        def concat(tables):
+            """partial tables (lists of Columns with offset 0) -> one, ONE torch.cat per column (no pairwise intermediates: every
+            intermediate would stay in torch's block cache, out of reach of the library's pool); validity through bytes when any
+            table carries a mask"""
             out = []
-            for ca, cb_ in zip(a, b):
-                data = torch.cat([ca.data[:ca.size], cb_.data[:cb_.size]])
-                if ca.mask is None and cb_.mask is None:
-                    out.append(Column(data, None, 0, ca.type_id, scale=ca.scale))
+            for ci in range(len(tables[0])):
+                cs = [t[ci] for t in tables]
+                data = torch.cat([c.data[:c.size] for c in cs])
+                if all(c.mask is None for c in cs):
+                    out.append(Column(data, None, 0, cs[0].type_id, scale=cs[0].scale))
                     continue
-                vb = torch.cat([_valid_bytes(ca), _valid_bytes(cb_)])
-                out.append(column_from_wire(data, vb, ca.type_id, ca.scale))
+                vb = torch.cat([_valid_bytes(c) for c in cs])
+                out.append(column_from_wire(data, vb, cs[0].type_id, cs[0].scale))
             return out
 
-        running = None
+        def fold(tables):
+            """several partial tables -> one (concatenate, then ONE merge groupby)"""
+            cols = concat(tables)
+            tables.clear()  # the concatenation replaces them
+            reqs_m = merge_requests(cols)
+            try:
+                fk, fr = GroupBy(Table(cols[:nk]), self._null_handling, options=merge_opts).aggregate(reqs_m)
+            except _lib.CudaError as e:
+                if e.status != 5:  # BGB_OUT_OF_MEMORY: hand torch's and the library's cached blocks back to the driver, once
+                    raise
+                torch.cuda.synchronize(device)
+                torch.cuda.empty_cache()
+                _lib.lib().bgb_release_cached_memory()
+                fk, fr = GroupBy(Table(cols[:nk]), self._null_handling, options=merge_opts).aggregate(reqs_m)
+            return list(fk.columns()) + [t.columns()[0] for t in fr]
+
+        # partial tables wait for each other until ~fold_rows rows are pending, then one fold replaces them (one merge groupby over
+        # 4e8 rows costs about as much as one over 2e8, so folding pairwise would pay it once per shard)
+        fold_rows = int(self._options.get("fold_rows", 450_000_000))
+        pending, pending_rows = [], 0
         for keys, reqs in chain():
             local_reqs = [GroupByRequest(r._values, [agg.Aggregation(k) for k in p.partial_kinds]) for r, p in zip(reqs, plans)]
             tok = self._phase("dist_local", device)
@@ -503,17 +525,24 @@ class DistributedGroupBy:
             self._local_profile.extend(local.last_profile)
             self.last_path = local.last_path
             flat = list(pkeys.columns()) + [c for t in presults for c in t.columns()]
-            if running is None:
-                running = flat
-                continue
+            pending.append(flat)
+            pending_rows += flat[0].size
+            del pkeys, presults, flat
+            if len(pending) > 1 and pending_rows >= fold_rows:
+                tok = self._phase("dist_fold", device)
+                pending = [fold(pending)]
+                pending_rows = pending[0][0].size
+                self._phase_end(tok, device)
+        if len(pending) > 1:
             tok = self._phase("dist_fold", device)
-            cols = concat(running, flat)
-            del running, flat, pkeys, presults
-            fk, fr = GroupBy(Table(cols[:nk]), self._null_handling, options=merge_opts).aggregate(merge_requests(cols))
-            running = list(fk.columns()) + [t.columns()[0] for t in fr]
-            del cols, fk, fr
+            pending = [fold(pending)]
             self._phase_end(tok, device)
+        running = pending[0]
 
+        if self._comm.world == 1:
+            # one rank: the folded table already holds every group once -- nothing to exchange, nothing to merge
+            self.last_exchange = "none"
+            return Table(running[:nk]), self._finalize(requests0, plans, [Table([c]) for c in running[nk:]], device)
         # the folded partial table through the distributed merge (its requests are merge kinds of single partial columns)
         dg = DistributedGroupBy(Table(running[:nk]), self._null_handling, options=merge_opts, comm=self._comm, exchange=self._exchange,
                                 peer_region_bytes=self._peer_region_bytes)
