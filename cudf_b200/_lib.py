@@ -35,6 +35,10 @@ class PeerOverflow(BgbError):    # BGB_PEER_OVERFLOW: every rank of the exchange
     pass
 
 
+class PeerAborted(CudaError):    # BGB_PEER_ABORTED: another rank failed in this step (every other rank raises this together)
+    pass
+
+
 class ColumnView(C.Structure):
     _fields_ = [("type_id", C.c_int32), ("scale", C.c_int32), ("size", C.c_int32), ("null_count", C.c_int32),
                 ("offset", C.c_int32), ("reserved", C.c_int32), ("data", C.c_void_p), ("null_mask", C.c_void_p)]
@@ -146,4 +150,6 @@ def check(status: int):
         raise UnsupportedError(status, msg)
     if status == 6:
         raise PeerOverflow(status, msg)
+    if status == 7:
+        raise PeerAborted(status, msg)
     raise CudaError(status, msg)

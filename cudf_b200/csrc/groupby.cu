@@ -1086,6 +1086,7 @@ struct bgb_peer {
   bool same_process = false;             // some peer was attached with bgb_peer_attach_local
   uint32_t epoch = 0;
   uint64_t timeout_ns = 20ull * 1000 * 1000 * 1000;
+  bool poisoned = false;                 // a wait timed out or the abort signal could not be sent: epochs may differ between ranks
 };
 
 extern "C" int bgb_peer_create(int32_t rank, int32_t world, int64_t region_bytes, bgb_peer** out)
@@ -1172,11 +1173,31 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
   if (!peer) return set_error(BGB_INVALID_ARGUMENT, "null peer context");
   for (int r = 0; r < peer->world; ++r)
     if (!peer->peer_buffer[r]) return set_error(BGB_INVALID_ARGUMENT, "rank %d is not attached", r);
+  if (peer->poisoned) return set_error(BGB_CUDA_ERROR, "this peer context is out of step with its peers (an earlier exchange timed out): create a new one");
+  if (!out_handle || !num_groups) return set_error(BGB_INVALID_ARGUMENT, "null output pointer");
   bgb_groupby* h = nullptr;
   int32_t g_local = 0;
+  // The step's epoch is taken BEFORE anything that can fail, and a rank that fails before it has signalled still signals --
+  // with the abort word -- so every rank leaves the step at the same epoch and nobody waits for the time-out.
+  const int world = peer->world, me = peer->rank;
+  const uint32_t epoch = ++peer->epoch;
+  const int parity     = (int)(epoch & 1u);
+  bool signalled       = false;
+  auto signal_abort = [&]() {
+    if (signalled) return;
+    signalled = true;
+    PeerSignalParams gp;
+    memset(&gp, 0, sizeof gp);
+    for (int r = 0; r < world; ++r) gp.header[r] = (PeerHeader*)peer->peer_buffer[r];
+    gp.cursors = nullptr; gp.cap = 0; gp.world = world; gp.me = me; gp.parity = parity; gp.epoch = epoch; gp.abort = 1;
+    if (launch_peer_signal(gp, (cudaStream_t)stream) != cudaSuccess || cudaStreamSynchronize((cudaStream_t)stream) != cudaSuccess) {
+      cudaGetLastError();
+      peer->poisoned = true;  // the peers will time out on this step
+    }
+  };
   // ---- (1) this rank's rows through the single-GPU path
   int rc = build_local(keys, num_keys, include_null_keys, requests, num_requests, stream, alloc, options, &h, &g_local, /*rank_independent=*/true);
-  if (rc) return rc;  // NOTE: an error here leaves the other ranks waiting until their timeout
+  if (rc) { const std::string msg = bgb_last_error(); signal_abort(); return set_error(rc, "%s", msg.c_str()); }
   HostTrace tr;
   *out_handle = nullptr;
   *num_groups = 0;
@@ -1185,15 +1206,12 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
 #define FAIL_RC(expr)            \
   do {                           \
     int rc_ = (expr);            \
-    if (rc_ != BGB_OK) { h->free_all(); delete h; return rc_; } \
+    if (rc_ != BGB_OK) { const std::string msg_ = bgb_last_error(); signal_abort(); h->free_all(); delete h; return set_error(rc_, "%s", msg_.c_str()); } \
   } while (0)
   for (const AccPlan& a : pl.accs)
     if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX || a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX) FAIL_RC(set_error(BGB_UNSUPPORTED, "ARGMIN/ARGMAX have no cross-rank merge (row numbers are rank-local)"));
   if (pl.accs.size() > (size_t)kMaxAccs) FAIL_RC(set_error(BGB_UNSUPPORTED, "more than %d accumulators in one peer exchange", kMaxAccs));
 
-  const int world = peer->world, me = peer->rank;
-  const uint32_t epoch = ++peer->epoch;
-  const int parity     = (int)(epoch & 1u);
   // ---- record layout inside a region: key word arrays, then one array per accumulator, each world * cap entries
   size_t record_bytes = 8 * (size_t)pl.key_words;
   for (const AccPlan& a : pl.accs) record_bytes += acc_cell_bytes(a.op);
@@ -1233,6 +1251,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
     for (int r = 0; r < world; ++r) gp.header[r] = (PeerHeader*)peer->peer_buffer[r];
     gp.cursors = cursors; gp.cap = cap; gp.world = world; gp.me = me; gp.parity = parity; gp.epoch = epoch;
     FAIL_RC(check_cuda(launch_peer_signal(gp, s), "peer_signal"));
+    signalled = true;  // from here on a failure is this rank's alone: its peers have what they need from it
   }
   h->prof.end();
 
@@ -1270,10 +1289,11 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
   }
   tr.mark("wait+sync");
   h->prof.resolve();
-  if (got[2 * world]) FAIL_RC(set_error(BGB_CUDA_ERROR, "peer exchange timed out waiting for another rank (epoch %u)", epoch));
+  if (got[2 * world]) { peer->poisoned = true; FAIL_RC(set_error(BGB_CUDA_ERROR, "peer exchange timed out waiting for another rank (epoch %u)", epoch)); }
   uint64_t total = 0;
-  bool overflow  = false;
-  for (int r = 0; r < world; ++r) { total += got[r]; overflow |= got[world + r] != 0; }
+  bool overflow  = false, aborted = false;
+  for (int r = 0; r < world; ++r) { total += got[r]; overflow |= got[world + r] == 1; aborted |= got[world + r] == 2; }
+  if (aborted) FAIL_RC(set_error(BGB_PEER_ABORTED, "another rank failed in this step of the peer exchange (epoch %u)", epoch));
   // the local partial table is no longer needed (its records are in the owners' regions)
   if (h->group_slots) { h->dfree(h->group_slots); h->group_slots = nullptr; }
   if (h->table.keys) { h->dfree(h->table.keys); h->table.keys = nullptr; }

@@ -145,11 +145,11 @@ __global__ void peer_signal_kernel(const __grid_constant__ PeerSignalParams p)
 {
   const int d = threadIdx.x;
   if (d >= p.world) return;
-  const uint32_t produced = p.cursors[d];
+  const uint32_t produced = p.abort ? 0u : p.cursors[d];
   PeerHeader* h           = p.header[d];
-  // an overflow towards ANY destination is reported to EVERY rank, so that all ranks fail the step together
-  uint32_t overflow = 0;
-  for (int r = 0; r < p.world; ++r) overflow |= p.cursors[r] > p.cap ? 1u : 0u;
+  // an overflow towards ANY destination is reported to EVERY rank, so that all ranks fail the step together; so is an abort
+  uint32_t overflow = p.abort ? 2u : 0u;
+  if (!p.abort) for (int r = 0; r < p.world; ++r) overflow |= p.cursors[r] > p.cap ? 1u : 0u;
   h->count[p.parity][p.me]    = produced < p.cap ? produced : (uint32_t)p.cap;
   h->overflow[p.parity][p.me] = overflow;
   __threadfence_system();

@@ -12,7 +12,7 @@ constexpr int kMaxPeers = 64;
 struct PeerHeader {
   uint32_t flag[2][kMaxPeers];      // epoch of the last completed scatter from that source
   uint32_t count[2][kMaxPeers];     // records that source wrote into its segment
-  uint32_t overflow[2][kMaxPeers];  // source had more records for this rank than a segment holds
+  uint32_t overflow[2][kMaxPeers];  // 1: source had more records for this rank than a segment holds; 2: the source aborted the step
 };
 constexpr size_t kPeerHeaderBytes = 4096;
 static_assert(sizeof(PeerHeader) <= kPeerHeaderBytes, "header must fit its page");
@@ -43,6 +43,7 @@ struct PeerSignalParams {
   uint64_t cap;
   int32_t world, me, parity;
   uint32_t epoch;
+  int32_t abort;                  // != 0: this rank failed before it could scatter: counts 0, overflow word 2 to every destination
 };
 
 struct PeerMergeParams {

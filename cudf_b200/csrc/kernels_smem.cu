@@ -9,9 +9,14 @@
 // With 1e4 groups this gives S = 24K index slots (load 0.41) + 11K dense rows in 227 KB; storing keys and accumulators
 // in the probed slots (16 B each) would cap the table at 14.5K slots (load 0.69), where the longest of a warp's 32
 // linear-probe sequences is ~11 steps (measured with ncu: profiles/r01_smem_kernel_v2_notes.txt).
-// Rows are streamed from HBM with 128-bit coalesced loads, software-pipelined one chunk ahead in registers (the whole
-// shared memory belongs to the table, so there is no room for a TMA staging ring here; the TMA-staged kernels are the
-// tiny-cardinality and partition kernels). Per row: LDS.U16 index probe + LDS key compare, ATOMS.ADD(lo) with return to
+// Rows are streamed from HBM in one of two ways. TMA ring (round 2): when the table leaves room for at least two stages of
+// 4096 rows (true for the direct-address table at 1e4 groups: 83 KB of 227) and the key / value columns are plain 16-byte
+// aligned arrays, thread 0 keeps the other stages in flight with cp.async.bulk + mbarrier (full / empty barrier per stage),
+// every thread takes its four rows of a stage with 128-bit LDS and the warp's lane 0 releases the stage; no load instruction,
+// no address arithmetic and no load registers in the consumer loop (the streaming microbenchmark reaches 7.3 TB/s this way
+// against 6.1-6.4 TB/s for LDG.128 under a large shared-memory reservation, profiles/r01_microbench2_stream_vs_smem.txt).
+// (4096-row stages: 64 KB at 16 B per row.) Otherwise (hashed table filling the shared memory, masked or unaligned columns): 128-bit coalesced loads, software-
+// pipelined one chunk ahead in registers. Per row: LDS.U16 index probe + LDS key compare, ATOMS.ADD(lo) with return to
 // catch the carry, ATOMS.ADD(hi|count). 64-bit shared atomics do not exist in hardware (ATOMS.CAST.SPIN loop, 3x
 // slower, see profiles/r01_microbench.txt), hence the split. Values outside [-2^m, 2^m) go straight to the HBM table
 // with global atomics, as do keys that no longer fit once the dense rows are used up, so any input is aggregated
@@ -21,6 +26,7 @@
 // Replaces the reference's shared-memory path: compute_mapping_indices + single_pass_shmem_aggs_kernel
 // (/root/reference/cpp/src/groupby/hash/compute_mapping_indices.cuh:23-151,
 //  /root/reference/cpp/src/groupby/hash/compute_shared_memory_aggs.cu:121-353), which caps out at 128 groups per block.
+#include <cstdlib>
 #include <type_traits>
 
 #include "device_utils.cuh"
@@ -59,11 +65,26 @@ template <int SK> struct SKey;
 template <> struct SKey<8> { using type = unsigned long long; };
 template <> struct SKey<4> { using type = unsigned int; };
 
-struct RowBuf {
-  uint64_t k[kRowsPerThread];
-  uint64_t v[kRowsPerThread];
+template <int ROWS>
+struct RowBufT {
+  uint64_t k[ROWS];
+  uint64_t v[ROWS];
   uint32_t flags;  // bit i: row i present and key usable; bit 8+i: value valid
 };
+
+// TMA ring plumbing (cp.async.bulk global -> shared, completion counted in bytes on an mbarrier)
+__device__ __forceinline__ void mbar_init(uint32_t b, int c) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(b), "r"(c)); }
+__device__ __forceinline__ void mbar_expect(uint32_t b, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint32_t b) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(b) : "memory"); }
+__device__ __forceinline__ void mbar_wait(uint32_t b, uint32_t parity)
+{
+  asm volatile("{\n.reg .pred p;\nWAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(b), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+constexpr int kTmaRows = 4096;  // rows per stage: four per thread (two 128-bit LDS of keys, two of values)
 
 
 // ---- shared-window accessors on 32-bit addresses (keeps the probe loop free of generic->shared address arithmetic)
@@ -150,10 +171,13 @@ __device__ __noinline__ uint32_t smem_insert_key(const SmemParams& p, uint64_t k
 
 }  // namespace
 
-template <int SK, int KEYMODE, int VW, bool DIRECT>
+template <int SK, int KEYMODE, int VW, bool DIRECT, bool TMA>
 __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_constant__ SmemParams p)
 {
   using skey_t = typename SKey<SK>::type;
+  constexpr int ROWS  = kRowsPerThread;
+  constexpr int CHUNK = kThreads * ROWS;
+  using RowBuf = RowBufT<ROWS>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const uint32_t S = p.slots;   // index slots (even)
   const uint32_t D = p.dense;   // dense group rows
@@ -173,7 +197,7 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
 
   const AggParams& a   = p.a;
   const int64_t n      = a.num_rows;
-  const int64_t nchunk = (n + kChunk - 1) / kChunk;
+  const int64_t nchunk = (n + CHUNK - 1) / CHUNK;
   const int c_bits     = p.cnt_bits;
   const uint32_t c_mask = (1u << c_bits) - 1u;
   const int m_bits     = p.val_bits;
@@ -185,8 +209,8 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
     constexpr bool FULL = decltype(full_tag)::value;
     rb.flags = 0;
 #pragma unroll
-    for (int pr = 0; pr < kRowsPerThread / 2; ++pr) {
-      const int64_t r = c * kChunk + (int64_t)pr * (kThreads * 2) + (int64_t)threadIdx.x * 2;
+    for (int pr = 0; pr < ROWS / 2; ++pr) {
+      const int64_t r = c * CHUNK + (int64_t)pr * (kThreads * 2) + (int64_t)threadIdx.x * 2;
       const int i0 = pr * 2;
       rb.k[i0] = rb.k[i0 + 1] = 0; rb.v[i0] = rb.v[i0 + 1] = 0;
       if (!FULL && r >= n) continue;
@@ -242,8 +266,8 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
     const bool plain = kc0.fclass == 0 && kc0.mask == nullptr && p.v_mask == nullptr && !(VW == 4 && p.v_signed);
     if (plain) return;
 #pragma unroll
-    for (int pr = 0; pr < kRowsPerThread / 2; ++pr) {
-      const int64_t r = c * kChunk + (int64_t)pr * (kThreads * 2) + (int64_t)threadIdx.x * 2;
+    for (int pr = 0; pr < ROWS / 2; ++pr) {
+      const int64_t r = c * CHUNK + (int64_t)pr * (kThreads * 2) + (int64_t)threadIdx.x * 2;
       const int i0 = pr * 2;
       uint32_t present = (rb.flags >> i0) & 3u, vvalid = (rb.flags >> (8 + i0)) & 3u;
       if (kc0.fclass) { rb.k[i0] = canon_key_bits(rb.k[i0], kc0.fclass); rb.k[i0 + 1] = canon_key_bits(rb.k[i0 + 1], kc0.fclass); }
@@ -263,7 +287,7 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
     }
   };
   auto load_chunk = [&](int64_t c, RowBuf& rb) {
-    if ((c + 1) * kChunk <= n) load_chunk_impl(c, rb, std::true_type{});
+    if ((c + 1) * CHUNK <= n) load_chunk_impl(c, rb, std::true_type{});
     else load_chunk_impl(c, rb, std::false_type{});
   };
 
@@ -271,19 +295,19 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
   uint32_t idx_end = idx_a + 2 * S;
   // pin the window addresses in registers (otherwise they are re-derived from SR_CgaCtaId inside the probe loop)
   asm volatile("" : "+r"(kd_a), "+r"(lo_a), "+r"(hc_a), "+r"(idx_a), "+r"(idx_end));
-  const uint64_t m_bias  = 1ull << m_bits;
+  const uint64_t m_bias  = 1ull << m_bits, m_range = m_bits >= 63 ? ~0ull : (2ull << m_bits);
 
   // ---- one chunk: (1) every lane finds the dense id of each of its rows (divergent probe loops, inserts and bypasses
   // are rare), (2) the warp re-joins, (3) the shared atomics of all rows issue as full warps
   auto process = [&](const RowBuf& rb) {
-    uint32_t id[kRowsPerThread];
+    uint32_t id[ROWS];
 #pragma unroll
-    for (int i = 0; i < kRowsPerThread; ++i) {
+    for (int i = 0; i < ROWS; ++i) {
       const uint64_t k = rb.k[i], v = rb.v[i];
       const bool present = (rb.flags >> i) & 1u, vvalid = (rb.flags >> (8 + i)) & 1u;
       id[i] = kIdSkip;
       if (present) {
-        const bool in_range = VW == 0 || ((v + m_bias) >> (m_bits + 1)) == 0;
+        const bool in_range = VW == 0 || (v + m_bias) < m_range;  // -2^m <= v < 2^m as ONE unsigned compare
         const uint64_t didx = (k ^ p.key_flip) - p.key_base;  // direct mode: order-preserving image minus the base
         if (!in_range || (DIRECT && didx >= D)) { smem_global_row(p, k, v, vvalid, VW != 0, &s_abort); }
         else if (DIRECT) {
@@ -312,7 +336,7 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
     }
     if (DIRECT) __syncwarp();
 #pragma unroll
-    for (int i = 0; i < kRowsPerThread; ++i) {
+    for (int i = 0; i < ROWS; ++i) {
       if (id[i] < kIdEmpty) {
         uint32_t hi_delta = 0;
         if (VW != 0) {
@@ -357,9 +381,81 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
     }
   };
 
+  uint32_t rows_since_flush = 0;
+  if (TMA) {
+    // ---- TMA ring behind the table: [full[NS] | empty[NS]] barriers, then NS stages of keys[2048] | values[2048]
+    const int NS = p.tma_stages;
+    constexpr uint32_t kStageBytes = kTmaRows * (SK + VW);
+    const uint32_t bar_a   = smem_addr(smem_raw + p.tma_offset);
+    const uint32_t stage_a = bar_a + 128;
+    const int64_t nfull    = n / CHUNK;  // whole stages; the tail (< 2048 rows) goes through the register loader below
+    if (threadIdx.x == 0) {
+      for (int s = 0; s < NS; ++s) { mbar_init(bar_a + 8 * s, 1); mbar_init(bar_a + 64 + 8 * s, kThreads / 32); }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const uint8_t* kbase = kc0.data + (int64_t)kc0.offset * SK;
+    const uint8_t* vbase = VW ? p.v_data + (int64_t)p.v_offset * VW : nullptr;
+    // producer state (thread 0): next chunk of this CTA to request, its stage and the parity its stage's EMPTY barrier must show
+    int64_t pc = blockIdx.x;
+    int ps = 0;
+    uint32_t pph = 1;  // first pass over the ring: nothing to wait for (parity 1 = "the phase before the first" is complete)
+    auto issue = [&]() {
+      if (pc >= nfull) return;
+      mbar_wait(bar_a + 64 + 8 * ps, pph);
+      mbar_expect(bar_a + 8 * ps, kStageBytes);
+      const uint32_t dst = stage_a + (uint32_t)ps * kStageBytes;
+      tma_g2s(dst, kbase + pc * CHUNK * SK, kTmaRows * SK, bar_a + 8 * ps);
+      if (VW) tma_g2s(dst + kTmaRows * SK, vbase + pc * CHUNK * VW, kTmaRows * VW, bar_a + 8 * ps);
+      pc += gridDim.x;
+      if (++ps == NS) { ps = 0; pph ^= 1u; }
+    };
+    if (threadIdx.x == 0) for (int j = 0; j < NS; ++j) issue();
+    int cs = 0;
+    uint32_t cph = 0;
+    bool aborted = false;
+    for (int64_t c = blockIdx.x; c < nfull; c += gridDim.x) {
+      mbar_wait(bar_a + 8 * cs, cph);
+      RowBuf rb;
+      const uint32_t src = stage_a + (uint32_t)cs * kStageBytes;
+      // thread t owns rows {2t, 2t+1} and {2048 + 2t, 2048 + 2t + 1} of the stage: conflict-free 128-bit (64-bit) LDS
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const uint32_t ko = src + (uint32_t)h * (kTmaRows / 2) * SK, vo = src + kTmaRows * SK + (uint32_t)h * (kTmaRows / 2) * VW;
+        if (SK == 8) { asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(rb.k[2 * h]), "=l"(rb.k[2 * h + 1]) : "r"(ko + threadIdx.x * 16) : "memory"); }
+        else { uint32_t x, y; asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(x), "=r"(y) : "r"(ko + threadIdx.x * 8) : "memory"); rb.k[2 * h] = x; rb.k[2 * h + 1] = y; }
+        rb.v[2 * h] = rb.v[2 * h + 1] = 0;
+        if (VW == 8) { asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(rb.v[2 * h]), "=l"(rb.v[2 * h + 1]) : "r"(vo + threadIdx.x * 16) : "memory"); }
+        else if (VW == 4) {
+          uint32_t x, y;
+          asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(x), "=r"(y) : "r"(vo + threadIdx.x * 8) : "memory");
+          rb.v[2 * h] = p.v_signed ? (uint64_t)(int64_t)(int32_t)x : x; rb.v[2 * h + 1] = p.v_signed ? (uint64_t)(int64_t)(int32_t)y : y;
+        }
+      }
+      rb.flags = 0x0F0Fu;
+      __syncwarp();
+      if ((threadIdx.x & 31) == 0) mbar_arrive(bar_a + 64 + 8 * cs);  // this warp is done with the stage
+      if (threadIdx.x == 0) issue();                                  // refill it once every warp has released it
+      if (++cs == NS) { cs = 0; cph ^= 1u; }
+      if (aborted) continue;  // (table overflow: the host retries bigger; keep draining the ring -- a CTA must not exit with bulk copies in flight)
+      process(rb);
+      rows_since_flush += CHUNK;
+      if (rows_since_flush + CHUNK > c_mask) {
+        flush();
+        rows_since_flush = 0;
+        if (*reinterpret_cast<volatile int*>(&s_abort)) aborted = true;
+      }
+    }
+    // tail rows (n % 4096) through the register loader, on the CTA whose turn it would be
+    if (nfull * CHUNK < n && (int64_t)blockIdx.x == nfull % gridDim.x) {
+      RowBuf rb;
+      load_chunk(nfull, rb);
+      decode_chunk(nfull, rb);
+      process(rb);
+    }
+  } else {
   RowBuf cur, nxt;
   int64_t c = blockIdx.x;
-  uint32_t rows_since_flush = 0;
   if (c < nchunk) load_chunk(c, cur);
   for (; c < nchunk; c += gridDim.x) {
     __syncwarp();  // the trip count is block-uniform: re-join lanes that drifted apart in the previous iteration
@@ -368,12 +464,13 @@ __global__ void __launch_bounds__(kThreads, 1) agg_smem_kernel(const __grid_cons
     decode_chunk(c, cur);
     process(cur);
     cur = nxt;
-    rows_since_flush += kChunk;
-    if (rows_since_flush + kChunk > c_mask) {  // block-uniform: count field would overflow
+    rows_since_flush += CHUNK;
+    if (rows_since_flush + CHUNK > c_mask) {  // block-uniform: count field would overflow
       flush();
       rows_since_flush = 0;
       if (*reinterpret_cast<volatile int*>(&s_abort)) break;
     }
+  }
   }
   flush();
   if (threadIdx.x == 0 && s_abort) a.table.status[0] = 1;
@@ -392,31 +489,51 @@ size_t smem_table_max_bytes()
   return 232448 - 64;
 }
 
-template <int SK, int KEYMODE, int VW, bool DIRECT>
+template <int SK, int KEYMODE, int VW, bool DIRECT, bool TMA = false>
 static cudaError_t launch_one(const SmemParams& p, int grid, size_t smem, cudaStream_t s)
 {
-  auto kern = agg_smem_kernel<SK, KEYMODE, VW, DIRECT>;
+  auto kern = agg_smem_kernel<SK, KEYMODE, VW, DIRECT, TMA>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   kern<<<grid, kThreads, smem, s>>>(p);
   return note_launch();
 }
 
-cudaError_t launch_aggregate_smem(const SmemParams& p, int smem_key_bytes, int key_mode, int value_width, int num_sms, cudaStream_t s)
+cudaError_t launch_aggregate_smem(const SmemParams& p_in, int smem_key_bytes, int key_mode, int value_width, int num_sms, cudaStream_t s)
 {
-  if (p.a.num_rows == 0) return cudaSuccess;
+  if (p_in.a.num_rows == 0) return cudaSuccess;
+  SmemParams p = p_in;
   const bool direct = p.direct != 0;
-  const size_t smem = smem_table_bytes(p.slots, p.dense, smem_key_bytes, direct);
-  const int64_t nchunk = (p.a.num_rows + kChunk - 1) / kChunk;
+  size_t smem = smem_table_bytes(p.slots, p.dense, smem_key_bytes, direct);
+  // ---- TMA ring when the columns are plain, aligned arrays and the table leaves room for >= 2 stages of 2048 rows
+  static const bool no_tma = getenv("BGB_SMEM_NO_TMA") != nullptr;
+  const KeyColDesc& kc = p.a.kc[0];
+  const size_t stage = (size_t)kTmaRows * (smem_key_bytes + value_width);
+  const size_t ring0 = (smem + 127) & ~(size_t)127;
+  int stages = (int)((smem_table_max_bytes() - 1024 - ring0 - 128) / stage);
+  if (stages > 3) stages = 3;
+  bool tma = !no_tma && key_mode == 1 && stages >= 2 && kc.mask == nullptr && kc.fclass == 0 && p.v_mask == nullptr &&
+             ((uintptr_t)kc.data + (size_t)kc.offset * smem_key_bytes) % 16 == 0 &&
+             (value_width == 0 || ((uintptr_t)p.v_data + (size_t)p.v_offset * value_width) % 16 == 0) && p.a.num_rows >= 4 * kTmaRows;
+  p.tma_stages = 0; p.tma_offset = 0;
+  const int rows_per_chunk = tma ? kTmaRows : kChunk;
+  if (tma) { p.tma_stages = stages; p.tma_offset = (uint32_t)ring0; smem = ring0 + 128 + (size_t)stages * stage; }
+  const int64_t nchunk = (p.a.num_rows + rows_per_chunk - 1) / rows_per_chunk;
   const int grid = (int)(nchunk < num_sms ? nchunk : num_sms);
 #define BGB_SMEM_CASE(SK, KM, VW) \
   if (smem_key_bytes == SK && key_mode == KM && value_width == VW)       \
     return direct ? launch_one<SK, KM, VW, true>(p, grid, smem, s) : launch_one<SK, KM, VW, false>(p, grid, smem, s);
+#define BGB_SMEM_TMA_CASE(SK, VW) \
+  if (tma && smem_key_bytes == SK && value_width == VW)       \
+    return direct ? launch_one<SK, 1, VW, true, true>(p, grid, smem, s) : launch_one<SK, 1, VW, false, true>(p, grid, smem, s);
+  BGB_SMEM_TMA_CASE(8, 8) BGB_SMEM_TMA_CASE(8, 4) BGB_SMEM_TMA_CASE(8, 0)
+  BGB_SMEM_TMA_CASE(4, 8) BGB_SMEM_TMA_CASE(4, 4) BGB_SMEM_TMA_CASE(4, 0)
   BGB_SMEM_CASE(8, 1, 8) BGB_SMEM_CASE(8, 1, 4) BGB_SMEM_CASE(8, 1, 0)
   BGB_SMEM_CASE(4, 1, 8) BGB_SMEM_CASE(4, 1, 4) BGB_SMEM_CASE(4, 1, 0)
   BGB_SMEM_CASE(8, 0, 8) BGB_SMEM_CASE(8, 0, 4) BGB_SMEM_CASE(8, 0, 0)
   BGB_SMEM_CASE(4, 0, 8) BGB_SMEM_CASE(4, 0, 4) BGB_SMEM_CASE(4, 0, 0)
 #undef BGB_SMEM_CASE
+#undef BGB_SMEM_TMA_CASE
   return cudaErrorInvalidValue;
 }
 

@@ -21,6 +21,8 @@ struct SmemParams {
   uint64_t key_base;
   int32_t debug;                  // count bypassed rows / flushes in status[4], status[5]
   int32_t val_bits;               // m: values in [-2^m, 2^m) take the shared-memory path; c + m <= 63 - c
+  int32_t tma_stages;             // set by the launcher: > 0 = rows arrive through a TMA ring of that many 2048-row stages
+  uint32_t tma_offset;            // byte offset of the ring (barriers, then stages) in the dynamic shared memory
 };
 
 size_t smem_table_max_bytes();

@@ -41,8 +41,11 @@ typedef enum bgb_status {
   BGB_CUDA_ERROR = 3,       /* cudf::cuda_error */
   BGB_NCCL_ERROR = 4,
   BGB_OUT_OF_MEMORY = 5,
-  BGB_PEER_OVERFLOW = 6     /* bgb_groupby_build_peer: a receive segment was too small; every rank reports it, the caller
+  BGB_PEER_OVERFLOW = 6,    /* bgb_groupby_build_peer: a receive segment was too small; every rank reports it, the caller
                                re-creates the peer context with a larger region (or uses the NCCL exchange) */
+  BGB_PEER_ABORTED = 7      /* bgb_groupby_build_peer: ANOTHER rank failed in this step and said so through the exchange header;
+                               every other rank returns this in the same step (no rank is left waiting for the time-out) and
+                               the context stays usable: all ranks have advanced to the same epoch */
 } bgb_status;
 
 /* cudf::type_id, same numeric values (/root/reference/cpp/include/cudf/types.hpp:185-217) */

@@ -14,6 +14,7 @@
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <utility>
 #include <vector>
 
@@ -34,6 +35,79 @@ enum class null_policy : bool { EXCLUDE = false, INCLUDE = true };
 struct logic_error : std::logic_error { using std::logic_error::logic_error; };     // cudf::logic_error
 struct cuda_error : std::runtime_error { using std::runtime_error::runtime_error; };  // cudf::cuda_error
 struct unsupported_error : std::runtime_error { using std::runtime_error::runtime_error; };  // "take the sort path"
+
+// ---- stand-ins for the three vocabulary types of the reference signature that live outside libcudf (CCCL / rmm are not
+// vendored here): same call shape as cudf/groupby.hpp:181-184
+//   aggregate(std::span<aggregation_request const>, cuda::stream_ref, rmm::device_async_resource_ref)
+// A build that HAS those headers passes the real objects: stream_ref converts from cudaStream_t (cuda::stream_ref::get()),
+// device_async_resource_ref wraps anything with allocate_async / deallocate_async (rmm's resource_ref interface).
+struct stream_ref {
+  cudaStream_t s{nullptr};
+  stream_ref() = default;
+  stream_ref(cudaStream_t st) : s(st) {}  // NOLINT: implicit like cuda::stream_ref
+  cudaStream_t get() const { return s; }
+};
+inline stream_ref get_default_stream() { return stream_ref{}; }  // cudf::get_default_stream()
+
+class device_async_resource_ref {
+ public:
+  // (not for device_async_resource_ref itself: a non-const lvalue copy must stay a copy, not a reference to a reference)
+  template <typename Resource, typename = std::enable_if_t<!std::is_same<std::decay_t<Resource>, device_async_resource_ref>::value>>
+  device_async_resource_ref(Resource& r)  // NOLINT: implicit like rmm::device_async_resource_ref
+    : _obj(&r),
+      _alloc([](void* o, size_t b, cudaStream_t s) { return static_cast<Resource*>(o)->allocate_async(b, s); }),
+      _free([](void* o, void* p, size_t b, cudaStream_t s) { static_cast<Resource*>(o)->deallocate_async(p, b, s); })
+  {
+  }
+  void* allocate_async(size_t bytes, cudaStream_t s) const { return _alloc(_obj, bytes, s); }
+  void deallocate_async(void* p, size_t bytes, cudaStream_t s) const { _free(_obj, p, bytes, s); }
+  // the bgb_allocator view of this resource (scratch of the C ABI call comes from the caller's resource, like
+  // cpp/src/groupby/hash/compute_groupby.cu:66,76,80 use the current device resource)
+  bgb_allocator abi() const
+  {
+    return bgb_allocator{[](size_t b, void* s, void* ctx) { return static_cast<device_async_resource_ref const*>(ctx)->allocate_async(b, (cudaStream_t)s); },
+                         [](void* p, size_t b, void* s, void* ctx) { static_cast<device_async_resource_ref const*>(ctx)->deallocate_async(p, b, (cudaStream_t)s); },
+                         const_cast<device_async_resource_ref*>(this)};
+  }
+
+ private:
+  void* _obj;
+  void* (*_alloc)(void*, size_t, cudaStream_t);
+  void (*_free)(void*, void*, size_t, cudaStream_t);
+};
+// rmm::mr::cuda_async_memory_resource's role: stream-ordered allocation from the device's default pool
+struct cuda_async_resource {
+  void* allocate_async(size_t bytes, cudaStream_t s)
+  {
+    void* p = nullptr;
+    if (cudaMallocAsync(&p, bytes ? bytes : 1, s) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+  }
+  void deallocate_async(void* p, size_t, cudaStream_t s) { cudaFreeAsync(p, s); }
+};
+inline device_async_resource_ref get_current_device_resource_ref()  // cudf::get_current_device_resource_ref()
+{
+  static cuda_async_resource r;
+  return device_async_resource_ref(r);
+}
+// std::span<T const> of the reference signature (C++20); this header is C++17
+template <typename T>
+class host_span {
+ public:
+  host_span() = default;
+  host_span(T* p, size_t n) : _p(p), _n(n) {}
+  template <typename V, typename = decltype(std::declval<V const&>().data())>
+  host_span(V const& v) : _p(v.data()), _n(v.size()) {}  // NOLINT: std::vector / std::array / std::span
+  T* data() const { return _p; }
+  size_t size() const { return _n; }
+  T& operator[](size_t i) const { return _p[i]; }
+  T* begin() const { return _p; }
+  T* end() const { return _p + _n; }
+
+ private:
+  T* _p{nullptr};
+  size_t _n{0};
+};
 
 namespace detail {
 inline void throw_on(int status)
@@ -104,18 +178,20 @@ class column_view {
 // owning device column (stream-ordered allocation)
 class column {
  public:
-  column(data_type type, size_type size, bool with_mask, cudaStream_t stream) : _type(type), _size(size), _stream(stream)
+  column(data_type type, size_type size, bool with_mask, cudaStream_t stream, device_async_resource_ref mr = get_current_device_resource_ref())
+    : _type(type), _size(size), _stream(stream), _mr(mr)
   {
-    size_t bytes = static_cast<size_t>(size) * detail::width_of(type.id());
-    if (bytes) detail::cuda_try(cudaMallocAsync(&_data, bytes, stream));
-    if (with_mask && size) detail::cuda_try(cudaMallocAsync(reinterpret_cast<void**>(&_mask), sizeof(uint32_t) * ((size + 31) / 32), stream));
+    _bytes      = static_cast<size_t>(size) * detail::width_of(type.id());
+    _mask_bytes = (with_mask && size) ? sizeof(uint32_t) * ((size + 31) / 32) : 0;
+    if (_bytes && !(_data = _mr.allocate_async(_bytes, stream))) throw cuda_error("out of device memory (column data)");
+    if (_mask_bytes && !(_mask = static_cast<uint32_t*>(_mr.allocate_async(_mask_bytes, stream)))) throw cuda_error("out of device memory (column mask)");
   }
   column(column const&)            = delete;
   column& operator=(column const&) = delete;
   ~column()
   {
-    if (_data) cudaFreeAsync(_data, _stream);
-    if (_mask) cudaFreeAsync(_mask, _stream);
+    if (_data) _mr.deallocate_async(_data, _bytes, _stream);
+    if (_mask) _mr.deallocate_async(_mask, _mask_bytes, _stream);
   }
   // host -> device convenience for tests and examples (cudf::test::fixed_width_column_wrapper's role)
   template <typename T>
@@ -168,6 +244,8 @@ class column {
   uint32_t* _mask{nullptr};
   size_type _null_count{0};
   cudaStream_t _stream;
+  device_async_resource_ref _mr;
+  size_t _bytes{0}, _mask_bytes{0};
   std::vector<std::unique_ptr<column>> _children;
 };
 
@@ -236,7 +314,7 @@ class groupby {
   explicit groupby(table_view const& keys, null_policy null_handling = null_policy::EXCLUDE) : _keys(keys), _null_handling(null_handling) {}
 
   // detail::hash::can_use_hash_groupby (hash/groupby.cu:115-131) for this library
-  bool can_use_hash_groupby(std::vector<aggregation_request> const& requests) const
+  bool can_use_hash_groupby(host_span<aggregation_request const> requests) const
   {
     marshalled m(_keys, requests);
     int32_t ok = 0;
@@ -245,21 +323,26 @@ class groupby {
   }
 
   // groupby::aggregate (cudf/groupby.hpp:148-184): unique keys (arbitrary order) + one aggregation_result per request
-  std::pair<std::unique_ptr<table>, std::vector<aggregation_result>> aggregate(std::vector<aggregation_request> const& requests,
-                                                                               cudaStream_t stream = nullptr) const
+  // Same call shape as the reference (cudf/groupby.hpp:181-184): requests as a span, the stream, and the memory resource that
+  // serves BOTH the returned columns and the call's scratch (group table, record buffers) through the C ABI's bgb_allocator.
+  std::pair<std::unique_ptr<table>, std::vector<aggregation_result>> aggregate(host_span<aggregation_request const> requests,
+                                                                               stream_ref stream_              = get_default_stream(),
+                                                                               device_async_resource_ref mr    = get_current_device_resource_ref()) const
   {
+    cudaStream_t stream = stream_.get();
     marshalled m(_keys, requests);
     bgb_groupby* h = nullptr;
     int32_t n      = 0;
+    bgb_allocator const scratch = mr.abi();
     detail::throw_on(bgb_groupby_build(m.keys.data(), (int32_t)m.keys.size(), _null_handling == null_policy::INCLUDE, m.reqs.data(),
-                                       (int32_t)m.reqs.size(), stream, nullptr, nullptr, &h, &n));
+                                       (int32_t)m.reqs.size(), stream, &scratch, nullptr, &h, &n));
     struct guard { bgb_groupby* h; ~guard() { bgb_groupby_destroy(h); } } g{h};
     std::vector<std::unique_ptr<column>> kcols;
     std::vector<bgb_mutable_column> km, rm;
     for (int32_t i = 0; i < (int32_t)m.keys.size(); ++i) {
       int32_t t, s, nl;
       detail::throw_on(bgb_groupby_key_info(h, i, &t, &s, &nl));
-      kcols.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream));
+      kcols.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream, mr));
       km.push_back(kcols.back()->abi_mutable());
     }
     std::vector<aggregation_result> results(requests.size());
@@ -268,12 +351,12 @@ class groupby {
       for (size_t j = 0; j < requests[i].aggregations.size(); ++j) {
         int32_t t, s, nl;
         detail::throw_on(bgb_groupby_result_info(h, (int32_t)i, (int32_t)j, &t, &s, &nl));
-        results[i].results.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream));
+        results[i].results.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream, mr));
         rm.push_back(results[i].results.back()->abi_mutable());
         if (static_cast<type_id>(t) == type_id::STRUCT) {  // SUM_OVERFLOW: `data` = the two child descriptors (bgb.h)
           column& parent = *results[i].results.back();
-          column& sum    = parent.add_child(std::make_unique<column>(data_type{requests[i].values.type().id(), s}, n, false, stream));
-          column& flag   = parent.add_child(std::make_unique<column>(data_type{type_id::BOOL8}, n, false, stream));
+          column& sum    = parent.add_child(std::make_unique<column>(data_type{requests[i].values.type().id(), s}, n, false, stream, mr));
+          column& flag   = parent.add_child(std::make_unique<column>(data_type{type_id::BOOL8}, n, false, stream, mr));
           struct_children.push_back({sum.abi_mutable(), flag.abi_mutable()});
           rm.back().data = struct_children.back().data();
         }
@@ -291,7 +374,7 @@ class groupby {
     std::vector<bgb_column_view> keys;
     std::vector<std::vector<bgb_aggregation>> aggs;
     std::vector<bgb_request> reqs;
-    marshalled(table_view const& k, std::vector<aggregation_request> const& requests) : aggs(requests.size())
+    marshalled(table_view const& k, host_span<aggregation_request const> requests) : aggs(requests.size())
     {
       for (auto const& c : k) keys.push_back(c.abi());
       for (size_t i = 0; i < requests.size(); ++i) {
@@ -348,8 +431,10 @@ class streaming_groupby {
     return n;
   }
   // does not modify the state; aggregate() may be called again afterwards
-  std::pair<std::unique_ptr<table>, std::vector<aggregation_result>> finalize(cudaStream_t stream = nullptr) const
+  std::pair<std::unique_ptr<table>, std::vector<aggregation_result>> finalize(stream_ref stream_           = get_default_stream(),
+                                                                              device_async_resource_ref mr = get_current_device_resource_ref()) const
   {
+    cudaStream_t stream = stream_.get();
     bgb_groupby* h = nullptr;
     int32_t n      = 0;
     detail::throw_on(bgb_stream_finalize(_h, stream, &h, &n));
@@ -359,14 +444,14 @@ class streaming_groupby {
     for (int32_t i = 0; i < _nk; ++i) {
       int32_t t, s, nl;
       detail::throw_on(bgb_groupby_key_info(h, i, &t, &s, &nl));
-      kcols.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream));
+      kcols.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream, mr));
       km.push_back(kcols.back()->abi_mutable());
     }
     std::vector<aggregation_result> results(_nreq);
     for (int32_t i = 0; i < _nreq; ++i) {
       int32_t t, s, nl;
       detail::throw_on(bgb_groupby_result_info(h, i, 0, &t, &s, &nl));
-      results[i].results.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream));
+      results[i].results.push_back(std::make_unique<column>(data_type{static_cast<type_id>(t), s}, n, nl != 0, stream, mr));
       rm.push_back(results[i].results.back()->abi_mutable());
     }
     detail::throw_on(bgb_groupby_emit(h, km.data(), rm.data(), stream));

@@ -208,6 +208,40 @@ int main()
     CHECK(threw);
     CHECK(groupby::is_streaming_groupby_supported(data_type{type_id::FLOAT64}, BGB_STD));
   }
+  // the reference's call shape (cudf/groupby.hpp:181-184): span of requests, stream, memory resource -- and the resource really
+  // serves BOTH the returned columns and the call's scratch (the C ABI's bgb_allocator): every byte it hands out comes back
+  {
+    struct counting_resource {
+      long allocs = 0, frees = 0; size_t live = 0, peak = 0;
+      void* allocate_async(size_t b, cudaStream_t s) { void* p = nullptr; if (cudaMallocAsync(&p, b ? b : 1, s) != cudaSuccess) return nullptr; ++allocs; live += b; peak = std::max(peak, live); return p; }
+      void deallocate_async(void* p, size_t b, cudaStream_t s) { cudaFreeAsync(p, s); ++frees; live -= b; }
+    } res_mr;
+    cudaStream_t st;
+    cudaStreamCreate(&st);
+    {
+      std::vector<K> kk(50000);
+      std::vector<int64_t> vv(50000);
+      for (size_t i = 0; i < kk.size(); ++i) { kk[i] = (K)(i % 977); vv[i] = (int64_t)i; }
+      auto keys = column::from_host<K>(type_id::INT32, kk);
+      auto vals = column::from_host<int64_t>(type_id::INT64, vv);
+      groupby::groupby gb(table_view({keys->view()}));
+      std::vector<groupby::aggregation_request> reqs(1);
+      reqs[0].values = vals->view();
+      reqs[0].aggregations.push_back(make_sum_aggregation());
+      reqs[0].aggregations.push_back(make_count_aggregation());
+      auto [tbl, res] = gb.aggregate(reqs, stream_ref(st), device_async_resource_ref(res_mr));
+      CHECK(tbl->num_rows() == 977);
+      auto [s, sv] = res[0].results[0]->to_host<int64_t>();
+      int64_t total = 0;
+      for (auto x : s) total += x;
+      CHECK(total == (int64_t)50000 * 49999 / 2);
+      CHECK(res_mr.allocs >= 5);   // 3 output columns + the table and its scratch
+      CHECK(res_mr.live > 0);      // the outputs are alive, the scratch is back
+    }
+    cudaStreamSynchronize(st);
+    CHECK(res_mr.live == 0 && res_mr.allocs == res_mr.frees);
+    cudaStreamDestroy(st);
+  }
   std::printf(g_fail ? "%d check(s) FAILED\n" : "all C++ host-layer checks passed\n", g_fail);
   return g_fail ? 1 : 0;
 }

@@ -430,6 +430,62 @@ def test_peer_two_steps_reuse_the_context():
         np.testing.assert_array_equal(gc[order], np.bincount(inv))
 
 
+def test_peer_rank_failure_is_broadcast_and_the_context_survives():
+    """One rank fails before it can scatter (its value column is shorter than its keys: cudf::logic_error, groupby.cu:186-229): it
+    still signals -- with the abort word -- so the other rank returns BGB_PEER_ABORTED in the SAME step instead of spinning until
+    the 20 s time-out, both ranks are at the same epoch afterwards, and the next step on the same contexts is correct
+    (round-1 advisor finding: a single failing rank desynchronised the exchange for good)."""
+    import time
+    world = 2
+    shared = _Shared(world)
+    comms = [ThreadComm(shared, r) for r in range(world)]
+    out, raised, errors = {}, {}, []
+
+    def work(rank):
+        try:
+            with torch.cuda.stream(torch.cuda.Stream()):
+                for step in range(3):
+                    rng = np.random.default_rng(77 * step + rank)
+                    k = rng.integers(0, 300, 10_000).astype(np.int64)
+                    v = rng.integers(-5, 5, 10_000).astype(np.int64)
+                    vcol = cb.Column.from_numpy(v[:-1] if (step == 1 and rank == 1) else v)   # step 1, rank 1: size mismatch
+                    dgb = D.DistributedGroupBy(cb.Table([cb.Column.from_numpy(k)]), comm=comms[rank], exchange="peer", peer_region_bytes=1 << 20)
+                    t0 = time.perf_counter()
+                    try:
+                        kt, rts = dgb.aggregate([cb.GroupByRequest(vcol, [agg.sum(), agg.count()])])
+                        torch.cuda.current_stream().synchronize()
+                        out[(step, rank)] = (k, v, kt.columns()[0].to_numpy()[0], rts[0].columns()[0].to_numpy()[0])
+                    except _lib.BgbError as e:
+                        raised[(step, rank)] = (e, time.perf_counter() - t0)
+        except BaseException as e:  # noqa: BLE001
+            errors.append(e)
+            shared.barrier.abort()
+
+    threads = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for c in shared.ctxs:
+        if c is not None:
+            c.close()
+    if errors:
+        raise errors[0]
+    assert set(raised) == {(1, 0), (1, 1)}, raised
+    assert isinstance(raised[(1, 1)][0], cb.LogicError)                       # the failing rank reports its own error
+    assert isinstance(raised[(1, 0)][0], _lib.PeerAborted), raised[(1, 0)][0]   # its peer is told, in the same step
+    assert raised[(1, 0)][1] < 5.0, "the healthy rank waited for the time-out"
+    for step in (0, 2):                                                         # the steps around the failure are exact
+        k = np.concatenate([out[(step, r)][0] for r in range(world)])
+        v = np.concatenate([out[(step, r)][1] for r in range(world)])
+        gk = np.concatenate([out[(step, r)][2] for r in range(world)])
+        gs = np.concatenate([out[(step, r)][3] for r in range(world)])
+        order = np.argsort(gk)
+        uk, inv = np.unique(k, return_inverse=True)
+        np.testing.assert_array_equal(gk[order], uk)
+        np.testing.assert_array_equal(gs[order], np.bincount(inv, weights=v).astype(np.int64))
+
+
 @pytest.mark.parametrize("exchange", EXCHANGES)
 @pytest.mark.parametrize("nshards,null_frac", [(2, 0.0), (3, 0.3), (5, 0.0)])
 def test_aggregate_shards_on_one_rank(exchange, nshards, null_frac):
