@@ -388,7 +388,11 @@ template <int W> __device__ __noinline__ void hc_reserved_row(const HcSliceParam
 
 }  // namespace
 
-template <int W, int THREADS>
+// LEAN: every accumulator is a COUNT or a plain 64-bit integer SUM and no validity bit is looked at (the SUM / COUNT shapes of
+// BASELINE configs[1], [4] and the north-star target): the other accumulator forms are compiled out -- the general kernel's
+// code does not fit the instruction cache well (5 % of its stall samples were instruction fetches) and its descriptor-driven
+// accumulator section cost ~250 of ~930 warp instructions per 128 rows.
+template <int W, int THREADS, bool LEAN>
 __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_constant__ HcSliceParams p)
 {
   constexpr int U = W <= 2 ? 4 : 2;
@@ -410,10 +414,12 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
 #pragma unroll
   for (int j = 0; j < U; ++j) { const uint32_t r = j * THREADS + t; if (r < n) load_rec<W>(rows + (uint64_t)r * W, nxt[j]); }
   bool overflow = false;
+  bool any_vbit = false;  // some accumulator looks at a validity bit (else the validity word of a row is never extracted)
+  for (int a = 0; a < p.num_accs; ++a) any_vbit |= p.acc[a].vbit >= 0 && p.acc[a].op != ACC_COUNT_ALL;
 
   while (fb < p.num_buckets) {
     // ---- EMPTY keys + identity cells
-    for (uint32_t i = t; i < S; i += THREADS) s_key[i] = kEmptyK;
+    for (uint32_t i = t; i < S / 2; i += THREADS) reinterpret_cast<uint4*>(s_key)[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
 #pragma unroll 1
     for (int a = 0; a < p.num_accs; ++a) {
       const HcAcc& acc = p.acc[a];
@@ -439,15 +445,18 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
 #pragma unroll
         for (int j = 0; j < U; ++j) { const uint32_t r = j * THREADS + t; if (r < n_next) load_rec<W>(rows_next + (uint64_t)r * W, nxt[j]); }
       }
-      // ---- key -> slot
+      // ---- key -> slot. The table is probed in PAIRS of slots (one 128-bit LDS per step; home pair = hash & (S/2 - 1), linear in
+      // pairs): a step resolves a row when either slot holds its key or is EMPTY (CAS), which halves the probe steps of linear
+      // probing -- the warp pays for the LONGEST of its 32 x U probe sequences, so the tail is what costs
       uint32_t slot[U], vb[U];
-      unsigned long long key[U], cur[U];
+      unsigned long long key[U];
       uint32_t pend = 0, act = 0;
+      const uint32_t pmask = (S >> 1) - 1;
 #pragma unroll
       for (int j = 0; j < U; ++j) {
         key[j] = p.key_in_low32 ? (rec[j][0] & 0xffffffffull) : rec[j][0];
-        vb[j]  = p.key_in_low32 ? (uint32_t)(rec[j][0] >> 32) : (p.vbits_word > 0 ? (uint32_t)pick_word<W>(rec[j], p.vbits_word) : 0xFFFFFFFFu);
-        slot[j] = slot_hash32(key[j]) & smask;
+        vb[j]  = (LEAN || !any_vbit) ? 0xFFFFFFFFu : p.key_in_low32 ? (uint32_t)(rec[j][0] >> 32) : (uint32_t)pick_word<W>(rec[j], p.vbits_word);
+        slot[j] = (slot_hash32(key[j]) & pmask) << 1;
         if (r0 + j * THREADS + t < n) {
           if (key[j] == kEmptyK) {  // cold: a copy, so that the rows themselves never have their address taken
             uint64_t tmp[W];
@@ -457,24 +466,66 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
           } else act |= 1u << j;
         }
       }
-#pragma unroll
-      for (int j = 0; j < U; ++j) cur[j] = lds64v(a_key + slot[j] * 8);
-#pragma unroll
-      for (int j = 0; j < U; ++j) if (((act >> j) & 1u) && cur[j] != key[j]) pend |= 1u << j;
-      uint32_t guard = 0;
-      while (__ballot_sync(0xffffffffu, pend != 0)) {  // warp-converged: a probe step per iteration for the rows still looking
-#pragma unroll
-        for (int j = 0; j < U; ++j) {
-          if ((pend >> j) & 1u) {
-            bool hit = false;
-            if (cur[j] == kEmptyK) { const unsigned long long old = atoms_cas64(a_key + slot[j] * 8, kEmptyK, key[j]); hit = old == kEmptyK || old == key[j]; }
-            if (!hit) { slot[j] = (slot[j] + 1) & smask; cur[j] = lds64v(a_key + slot[j] * 8); hit = cur[j] == key[j]; }
-            if (hit) pend &= ~(1u << j);
-          }
+      // One probe step on (k, sl): true when sl is final. Written with ONE divergent branch (the CAS): every path a lane of the warp
+      // takes is paid by the whole warp, and the five-way if-chain this replaces cost ~45 instructions per call.
+      auto step = [&](unsigned long long k, uint32_t& sl) -> bool {
+        unsigned long long c0, c1;
+        asm volatile("ld.volatile.shared.v2.u64 {%0, %1}, [%2];" : "=l"(c0), "=l"(c1) : "r"(a_key + sl * 8) : "memory");
+        const bool hit0 = c0 == k, hit1 = c1 == k, e0 = c0 == kEmptyK, e1 = c1 == kEmptyK;
+        bool found = hit0 || hit1;
+        uint32_t add = hit0 ? 0u : 1u;                 // slot of the pair the key sits in (or would be inserted at)
+        const bool try_cas = !found && (e0 || e1);     // first EMPTY slot in probe order: c0 before c1
+        if (try_cas) {
+          add = e0 ? 0u : 1u;
+          const unsigned long long old = atoms_cas64(a_key + (sl + add) * 8, kEmptyK, k);
+          found = old == kEmptyK || old == k;          // lost to another key: the pair is looked at again
         }
-        if (++guard > S + 1) { overflow = true; act &= ~pend; pend = 0; }  // more distinct keys than slots: the host retries bigger
+        if (found) sl += add;
+        else if (!try_cas) sl = (sl + 2) & smask;      // both slots hold other keys: next pair
+        return found;
+      };
+#pragma unroll
+      for (int j = 0; j < U; ++j) if (((act >> j) & 1u) && !step(key[j], slot[j])) pend |= 1u << j;
+      // rows still looking: each lane works on ITS lowest pending row, one probe step per iteration, so the warp pays
+      // max-over-lanes of the lane's remaining steps with ONE step body per iteration (not U bodies per iteration)
+      uint32_t guard = 0;
+      while (__ballot_sync(0xffffffffu, pend != 0)) {
+        if (pend) {
+          const int j = __ffs(pend) - 1;
+          unsigned long long k = key[0];
+          uint32_t sl = slot[0];
+#pragma unroll
+          for (int x = 1; x < U; ++x) if (j == x) { k = key[x]; sl = slot[x]; }
+          const bool done = step(k, sl);
+#pragma unroll
+          for (int x = 0; x < U; ++x) if (j == x) slot[x] = sl;
+          if (done) pend &= pend - 1;
+        }
+        if (++guard > 4 * S + 8) { overflow = true; act &= ~pend; pend = 0; }  // more distinct keys than slots: the host retries bigger
       }
       // ---- accumulators, one at a time over the U rows
+      if (LEAN) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+          if (a >= p.num_accs) break;
+          const uint32_t a_cells = smem_u32(smem + p.acc[a].smem_off);
+          if (p.acc[a].mode == HM_COUNT) {
+#pragma unroll
+            for (int j = 0; j < U; ++j) if ((act >> j) & 1u) reds_add(a_cells + slot[j] * 4, 1u);
+          } else {
+            const int word = p.acc[a].word;
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+              if (!((act >> j) & 1u)) continue;
+              const uint64_t v   = pick_word<W>(rec[j], word);
+              const uint32_t vlo = (uint32_t)v, vhi = (uint32_t)(v >> 32);
+              const uint32_t old = atoms_add_ret(a_cells + slot[j] * 8, vlo);
+              const uint32_t add = vhi + ((uint32_t)(old + vlo) < old ? 1u : 0u);
+              if (add) reds_add(a_cells + slot[j] * 8 + 4, add);
+            }
+          }
+        }
+      } else
 #pragma unroll 1
       for (int a = 0; a < p.num_accs; ++a) {
         const HcAcc& acc = p.acc[a];
@@ -603,26 +654,43 @@ cudaError_t launch_hc_init(const HcSliceParams& p, cudaStream_t s)
   return note_launch();
 }
 
-template <int W, int THREADS>
-static cudaError_t launch_slices_wt(const HcSliceParams& p, size_t smem_bytes, int num_sms, cudaStream_t s)
+template <int W, int THREADS, bool LEAN>
+static cudaError_t launch_slices_wtl(const HcSliceParams& p, size_t smem_bytes, int num_sms, cudaStream_t s)
 {
-  cudaError_t e = cudaFuncSetAttribute(hc_slice_kernel<W, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  cudaError_t e = cudaFuncSetAttribute(hc_slice_kernel<W, THREADS, LEAN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
   int occ = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, hc_slice_kernel<W, THREADS>, THREADS, smem_bytes);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, hc_slice_kernel<W, THREADS, LEAN>, THREADS, smem_bytes);
   if (e != cudaSuccess) return e;
   if (occ < 1) return cudaErrorInvalidConfiguration;
   const uint32_t grid = p.num_buckets < (uint32_t)(occ * num_sms) ? p.num_buckets : (uint32_t)(occ * num_sms);
-  hc_slice_kernel<W, THREADS><<<grid, THREADS, smem_bytes, s>>>(p);
+  hc_slice_kernel<W, THREADS, LEAN><<<grid, THREADS, smem_bytes, s>>>(p);
   return note_launch();
 }
 template <int W>
 static cudaError_t launch_slices_w(const HcSliceParams& p, size_t smem_bytes, int num_sms, cudaStream_t s)
 {
-  static const int thr = getenv("BGB_HC_SLICE_THREADS") ? atoi(getenv("BGB_HC_SLICE_THREADS")) : 384;
-  if (thr == 512) return launch_slices_wt<W, 512>(p, smem_bytes, num_sms, s);
-  if (thr == 256) return launch_slices_wt<W, 256>(p, smem_bytes, num_sms, s);
-  return launch_slices_wt<W, 384>(p, smem_bytes, num_sms, s);
+  // threads per CTA (two CTAs per SM): measured per 1e9 rows on B200 -- SUM + COUNT (lean kernel): 8.4 ms at 512, 9.5 at 384, 9.6 at
+  // 256; float64 SUM + MIN + MAX (general kernel, 78 registers): 17.2-17.9 ms whatever the count (its CAS-loop accumulators bound it)
+  static const int thr_env = getenv("BGB_HC_SLICE_THREADS") ? atoi(getenv("BGB_HC_SLICE_THREADS")) : 0;
+  bool lean = p.num_accs <= 3 && W <= 2;
+  for (int a = 0; a < p.num_accs; ++a) {
+    const HcAcc& acc = p.acc[a];
+    const bool count = acc.mode == HM_COUNT && (acc.vbit < 0 || acc.op == ACC_COUNT_ALL);
+    const bool isum  = acc.mode == HM_ISUM && acc.op == ACC_SUM_I64 && (acc.src == S_I64 || acc.src == S_U64) && acc.vbit < 0;
+    lean = lean && (count || isum);
+  }
+  static const bool no_lean = getenv("BGB_HC_NO_LEAN") != nullptr;
+  lean = lean && !no_lean;
+  const int thr = thr_env ? thr_env : (lean ? 512 : 384);
+  if (lean) {
+    if (thr == 256) return launch_slices_wtl<W, 256, true>(p, smem_bytes, num_sms, s);
+    if (thr == 384) return launch_slices_wtl<W, 384, true>(p, smem_bytes, num_sms, s);
+    return launch_slices_wtl<W, 512, true>(p, smem_bytes, num_sms, s);
+  }
+  if (thr == 256) return launch_slices_wtl<W, 256, false>(p, smem_bytes, num_sms, s);
+  if (thr == 512) return launch_slices_wtl<W, 512, false>(p, smem_bytes, num_sms, s);
+  return launch_slices_wtl<W, 384, false>(p, smem_bytes, num_sms, s);
 }
 
 cudaError_t launch_hc_slices(const HcSliceParams& p, size_t smem_bytes, int num_sms, cudaStream_t s)
