@@ -39,6 +39,8 @@ struct bgb_groupby {
   void* repack_buf = nullptr;       // the packed key column (+ its validity words), released when the build is done
   void* repack_mask = nullptr;
   bool dense = false;               // the build wrote the groups densely at [0, G) and filled group_slots itself (kernels_hc.cu)
+  bool peer_fused = false;          // ... or wrote them straight into the owner ranks' exchange regions (no local groups at all)
+  uint32_t* peer_cursors = nullptr; // records produced per destination by the fused slices
 
   void* dalloc(size_t bytes)
   {
@@ -64,6 +66,41 @@ struct bgb_groupby {
     while (!blocks.empty()) dfree(blocks.back().p);
   }
 };
+
+struct bgb_peer {
+  int rank = 0, world = 1, device = 0;
+  uint8_t* buffer = nullptr;          // header page + two regions (double-buffered by step parity)
+  size_t region_bytes = 0;
+  uint8_t* peer_buffer[kMaxPeers] = {};  // every rank's buffer as mapped into this process (own buffer at [rank])
+  bool opened[kMaxPeers] = {};           // mapped through cudaIpcOpenMemHandle (must be closed)
+  bool same_process = false;             // some peer was attached with bgb_peer_attach_local
+  uint32_t epoch = 0;
+  uint64_t timeout_ns = 20ull * 1000 * 1000 * 1000;
+  bool poisoned = false;                 // a wait timed out or the abort signal could not be sent: epochs may differ between ranks
+};
+
+// record layout of the peer exchange inside a region: key word arrays, then one array per accumulator, each world * cap entries
+struct PeerLayout {
+  size_t record_bytes = 0;
+  uint64_t cap = 0, entries = 0, key1_off = 0;
+  std::vector<uint64_t> acc_off;
+};
+static bool peer_layout(const bgb::Plan& pl, const bgb_peer* peer, PeerLayout& L)
+{
+  L.record_bytes = 8 * (size_t)pl.key_words;
+  for (const bgb::AccPlan& a : pl.accs) L.record_bytes += bgb::acc_cell_bytes(a.op);
+  L.cap = (uint64_t)((peer->region_bytes / ((size_t)peer->world * L.record_bytes)) & ~(size_t)31);
+  if (L.cap == 0) return false;
+  L.entries = (uint64_t)peer->world * L.cap;
+  uint64_t off = 8 * L.entries;
+  L.key1_off = off;
+  if (pl.key_words == 2) off += 8 * L.entries;
+  L.acc_off.assign(pl.accs.size(), 0);
+  for (size_t a = 0; a < pl.accs.size(); ++a) { L.acc_off[a] = off; off += (uint64_t)bgb::acc_cell_bytes(pl.accs[a].op) * L.entries; }
+  return true;
+}
+// build_local on behalf of bgb_groupby_build_peer: the records-form slices may write their groups straight into the owners' regions
+struct PeerFuse { bgb_peer* peer; int parity; };
 
 namespace {
 
@@ -429,7 +466,7 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool one_l
 // table slice with DENSE group output -- no HBM hash table, no compaction pass. `h->table` and the accumulator cells are
 // allocated (capacity + 1 entries each); on success h->group_slots is allocated and filled and h->dense is set.
 // done=false when the plan does not fit (the caller then tries the column-form kernels of kernels_bucket.cu).
-int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, bool& done)
+int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, const PeerFuse* fuse, bool& done)
 {
   done = false;
   Plan& pl = h->plan;
@@ -441,6 +478,11 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, bo
     if (a.op == ACC_ARGMIN || a.op == ACC_ARGMAX || a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX) return BGB_OK;  // row numbers are lost by the scatter
     slot_bytes += acc_cell_bytes(a.op);
   }
+  // multi-GPU: fuse the exchange into the slices' flush (every finished slice goes straight to its owners over NVLink)
+  static const bool no_fuse = getenv("BGB_NO_PEER_FUSE") != nullptr;
+  PeerLayout playout;
+  const bool fused = fuse && !no_fuse && fuse->peer->world > 1 && fuse->peer->world <= kHcMaxPeers && peer_layout(pl, fuse->peer, playout);
+  if (fused) slot_bytes += 3;  // owner-ordered permutation of the slice (u16 + u8 per slot) behind the table
   // record layout
   int nvb = 0;
   std::vector<int> vbit(pl.values.size(), -1);
@@ -533,6 +575,19 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, bo
       if (acc.value_col >= 0) { d.word = (uint8_t)(1 + acc.value_col); d.src = pl.values[acc.value_col].src; d.vbit = (int16_t)vbit[acc.value_col]; }
       else { d.word = 0; d.src = S_I32; d.vbit = -1; }
     }
+  if (fused) {
+    bgb_peer* peer = fuse->peer;
+    uint32_t* cursors = (uint32_t*)h->dalloc(sizeof(uint32_t) * kMaxPeers);
+    if (!cursors) { release(); h->dfree(h->group_slots); h->group_slots = nullptr; return set_error(BGB_OUT_OF_MEMORY, "peer cursors"); }
+    if (!rc) rc = check_cuda(cudaMemsetAsync(cursors, 0, sizeof(uint32_t) * kMaxPeers, s), "peer cursors");
+    h->peer_cursors = cursors;
+    sp.peer.world = peer->world; sp.peer.me = peer->rank; sp.peer.cap = playout.cap; sp.peer.cursors = cursors;
+    for (int r = 0; r < peer->world; ++r) sp.peer.region[r] = peer->peer_buffer[r] + kPeerHeaderBytes + (size_t)fuse->parity * peer->region_bytes;
+    for (size_t a = 0; a < pl.accs.size(); ++a) sp.peer.acc_off[a] = playout.acc_off[a];
+    off_b = (off_b + 15u) & ~15u;
+    sp.peer.perm_off = off_b;
+    off_b += (uint32_t)(3u << ls);
+  }
   const size_t slice_smem = off_b;
   if (!rc) rc = check_cuda(launch_hc_init(sp, s), "hc_init");
 
@@ -583,7 +638,128 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, bo
   release();  // stream-ordered
   if (rc) { h->dfree(h->group_slots); h->group_slots = nullptr; return rc; }
   h->dense = true;
+  h->peer_fused = fused;
   done = true;
+  return BGB_OK;
+}
+
+int num_sms_of_current_device()
+{
+  int num_sms = 148, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+  return num_sms;
+}
+
+// Final merge of the peer exchange through the records-form kernels: level 1 reads the received records (MODE 3 of
+// hc_scatter_kernel), the slices ADD partial cells (sum of sums, sum of counts, min of mins ... the merges of
+// /root/reference/cpp/src/groupby/streaming_groupby/merge.cu:30-144) and write the owner's groups densely. `h->table` and the
+// accumulator cells are allocated for `capacity`; on success group_slots is allocated + filled. merged=false: shape not taken.
+int run_hc_merge(bgb_groupby* h, int num_sms, const uint8_t* region, uint64_t cap, int world, const std::vector<uint32_t>& prefix,
+                 const std::vector<uint64_t>& acc_off, uint64_t total, bool& merged)
+{
+  merged = false;
+  Plan& pl = h->plan;
+  if (pl.key_words != 1 || pl.accs.size() > (size_t)(kHcMaxWords - 1) || world > kHcMaxPeers || total >= (1ull << 31)) return BGB_OK;
+  const int W = 1 + (int)pl.accs.size();
+  size_t slot_bytes = 8;
+  for (const AccPlan& a : pl.accs) slot_bytes += acc_cell_bytes(a.op);
+  int log2cap = 0; while ((1ull << log2cap) < h->table.capacity) ++log2cap;
+  auto round16 = [](uint64_t x) { return (x + 15) & ~15ull; };
+  int ls = 4;
+  while (ls + 1 < log2cap && (slot_bytes << (ls + 1)) <= 112 * 1024) ++ls;
+  if (log2cap - ls < 10) ls = std::max(6, log2cap - 10);
+  if (ls >= log2cap) return BGB_OK;
+  const int b = log2cap - ls;
+  if (b < 1 || b > 20) return BGB_OK;
+  const int b2 = b <= 10 ? 0 : b / 2, b1 = b - b2;
+  const uint32_t P1 = 1u << b1, NB = 1u << b;
+  const int64_t N = (int64_t)total;
+  // every group arrives once per source that saw it: a bucket's rows are ~world records of each of its groups
+  const double gpb    = std::max(1.0, (double)N / std::max(1, world) / (double)NB);
+  const double margin = std::max(0.27, 6.0 / std::sqrt(gpb));
+  if (margin > 1.0) return BGB_OK;
+  const uint64_t CL = round16((uint64_t)((double)N / NB * (1.0 + margin)) + 256);
+  const uint64_t C1 = b2 ? round16((uint64_t)((double)N / P1 * 1.125) + 1024) : CL;
+  const uint64_t rows1 = (uint64_t)P1 * C1, rows2 = b2 ? (uint64_t)NB * CL : 0;
+  if (rows1 >= (1ull << 32) || rows2 >= (1ull << 32)) return BGB_OK;
+  cudaStream_t s = h->stream;
+  constexpr uint32_t kHotStride = 64;
+  const size_t ncur = (size_t)P1 * kHotStride + (b2 ? NB : 0) + 4;
+  auto up256 = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  const size_t cur_bytes = up256(sizeof(uint32_t) * ncur), l1_bytes = up256(rows1 * W * 8 + 64), l2_bytes = b2 ? up256(rows2 * W * 8 + 64) : 0;
+  uint8_t* arena = (uint8_t*)h->dalloc(cur_bytes + l1_bytes + l2_bytes);
+  const uint64_t max_groups = std::min<uint64_t>(h->table.capacity + 1, (uint64_t)N + 1);
+  h->group_slots = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
+  if (!arena || !h->group_slots) {
+    if (arena) h->dfree(arena);
+    if (h->group_slots) { h->dfree(h->group_slots); h->group_slots = nullptr; }
+    return set_error(BGB_OUT_OF_MEMORY, "record buffers of the merge (%lld records)", (long long)N);
+  }
+  uint32_t* counters = (uint32_t*)arena;
+  uint64_t* L1 = (uint64_t*)(arena + cur_bytes);
+  uint64_t* L2 = b2 ? (uint64_t*)(arena + cur_bytes + l1_bytes) : nullptr;
+  uint32_t* cursor1 = counters;
+  uint32_t* cursor2 = counters + (size_t)P1 * kHotStride;
+  unsigned long long* gcount = reinterpret_cast<unsigned long long*>(counters + ((ncur - 4 + 1) & ~(size_t)1));
+  int rc = check_cuda(cudaMemsetAsync(counters, 0, sizeof(uint32_t) * ncur, s), "merge counters");
+
+  HcSliceParams sp;
+  memset(&sp, 0, sizeof sp);
+  sp.table = h->table;
+  sp.words = W; sp.key_in_low32 = 0; sp.vbits_word = -1;
+  sp.log2_slice = ls; sp.num_buckets = NB; sp.num_accs = (int)pl.accs.size();
+  sp.group_slots = h->group_slots; sp.gcount = gcount; sp.max_groups = max_groups;
+  uint32_t off_b = (uint32_t)(8u << ls);
+  for (int pass = 0; pass < 2; ++pass)
+    for (size_t a = 0; a < pl.accs.size(); ++a) {
+      const AccPlan& acc = pl.accs[a];
+      const int cb = acc_cell_bytes(acc.op);
+      if ((pass == 0) != (cb == 8)) continue;
+      HcAcc& d = sp.acc[a];
+      d.cells = acc.cells; d.cell_bytes = (uint8_t)cb; d.smem_off = off_b; d.vbit = -1; d.word = (uint8_t)(1 + a);
+      off_b += (uint32_t)cb << ls;
+      switch (acc.op) {  // merge of two partial cells of this accumulator
+        case ACC_COUNT_VALID: case ACC_COUNT_ALL: d.mode = HM_ADD32; d.op = acc.op; d.src = S_U32; break;
+        case ACC_SUM_I64: case ACC_SUMSQ_I64: case ACC_SUM_LO32: case ACC_SUM_HI32: d.mode = HM_ISUM; d.op = ACC_SUM_I64; d.src = S_I64; break;
+        case ACC_MIN: case ACC_MAX: d.mode = HM_MINMAX; d.op = acc.op; d.src = S_U64; break;   // cells are order images already
+        case ACC_SUM_F64: case ACC_SUMSQ_F64: d.mode = HM_OTHER; d.op = ACC_SUM_F64; d.src = S_F64; break;
+        case ACC_SUM_F32: case ACC_SUMSQ_F32: d.mode = HM_OTHER; d.op = ACC_SUM_F32; d.src = S_F32; break;
+        case ACC_PROD_I64: d.mode = HM_OTHER; d.op = ACC_PROD_I64; d.src = S_I64; break;
+        case ACC_PROD_F64: d.mode = HM_OTHER; d.op = ACC_PROD_F64; d.src = S_F64; break;
+        case ACC_PROD_F32: d.mode = HM_OTHER; d.op = ACC_PROD_F32; d.src = S_F32; break;
+        default: h->dfree(arena); h->dfree(h->group_slots); h->group_slots = nullptr; return BGB_OK;
+      }
+    }
+  const size_t slice_smem = off_b;
+  if (!rc) rc = check_cuda(launch_hc_init(sp, s), "hc_init");
+
+  HcScatterParams s1;
+  memset(&s1, 0, sizeof s1);
+  s1.a.num_rows = N; s1.a.table = h->table;
+  s1.level = 1; s1.words = W; s1.key_in_low32 = 0; s1.vbits_word = -1; s1.num_vals = 0;
+  s1.peer_in.region = region; s1.peer_in.cap = cap; s1.peer_in.world = world; s1.peer_in.num_accs = (int)pl.accs.size();
+  for (int r = 0; r <= world; ++r) s1.peer_in.prefix[r] = prefix[r];
+  for (size_t a = 0; a < pl.accs.size(); ++a) { s1.peer_in.acc_off[a] = acc_off[a]; s1.peer_in.cell_bytes[a] = (uint8_t)acc_cell_bytes(pl.accs[a].op); }
+  s1.out = L1; s1.cursor = cursor1; s1.cursor_stride = kHotStride; s1.bucket_capacity = (uint32_t)C1;
+  s1.log2_parts = b1; s1.slot_shift = log2cap - b1; s1.status = h->table.status;
+  if (!rc) rc = check_cuda(launch_hc_scatter(s1, num_sms, s), "hc_merge_scatter1");
+  if (b2 && !rc) {
+    HcScatterParams s2 = s1;
+    s2.level = 2; s2.peer_in.region = nullptr;
+    s2.in = L1; s2.seg_cursor = cursor1; s2.seg_cursor_stride = kHotStride; s2.seg_capacity = (uint32_t)C1; s2.num_segs = P1;
+    s2.out = L2; s2.cursor = cursor2; s2.cursor_stride = 1; s2.bucket_capacity = (uint32_t)CL;
+    s2.log2_parts = b2; s2.slot_shift = log2cap - b;
+    rc = check_cuda(launch_hc_scatter(s2, num_sms, s), "hc_merge_scatter2");
+  }
+  sp.rec = b2 ? L2 : L1;
+  sp.cursor = b2 ? cursor2 : cursor1; sp.cursor_stride = b2 ? 1 : kHotStride;
+  sp.bucket_capacity = (uint32_t)(b2 ? CL : C1);
+  if (!rc) rc = check_cuda(launch_hc_slices(sp, slice_smem, num_sms, s), "hc_merge_slices");
+  if (!rc) rc = check_cuda(launch_hc_finish(sp, s), "hc_finish");
+  h->dfree(arena);  // stream-ordered
+  if (rc) { h->dfree(h->group_slots); h->group_slots = nullptr; return rc; }
+  merged = true;
   return BGB_OK;
 }
 
@@ -687,7 +863,8 @@ int try_repack_keys(bgb_groupby* h, const bgb_column_view* keys, int32_t num_key
 
 static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
                        const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
-                       const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups, bool rank_independent = false)
+                       const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups, bool rank_independent = false,
+                       const PeerFuse* fuse = nullptr)
 {
   if (!out_handle || !num_groups) return set_error(BGB_INVALID_ARGUMENT, "null output pointer");
   *out_handle = nullptr;
@@ -823,7 +1000,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
       static const bool mid_on = getenv("BGB_BUCKET_MID") != nullptr;
       const bool mid = mid_on && !big && N >= (1 << 24) && capacity >= (1u << 16);
       if ((opt.force_path == 7 || (opt.force_path == 0 && (big || mid))) && !no_bucket) {
-        if (!no_hc) FAIL_RC(run_hc(h, num_sms, opt, g_raw, done));  // records form first; plans it does not take go through the column form
+        if (!no_hc) FAIL_RC(run_hc(h, num_sms, opt, g_raw, fuse, done));  // records form first; plans it does not take go through the column form
         was_hc_attempt = done;
         if (!done) FAIL_RC(run_bucketed(h, num_sms, opt, /*one_level_only=*/opt.force_path == 0 && !big, done));
         if (done) path = "bucketed";
@@ -884,19 +1061,22 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     tr.mark("build sync");
     h->prof.resolve();
     if (scan_state) h->dfree(scan_state);
+    const bool was_fused = h->peer_fused;
     h->dense = false;  // (a retry below starts from scratch)
     if (getenv("BGB_DEBUG")) fprintf(stderr, "[bgb] path=%s groups=%u overflow=%u bypass_rows=%u flushes=%u\n", path.c_str(), st[1], st[0], st[4], st[5]);
     if (st[6] != 0 && path == "bucketed") {
       // skewed keys filled a bucket of the records form (no overflow region there): column form, whose overflow region takes
       // moderate skew; if that fills too: same table size, exact-offset partitioned path
       if (was_hc_attempt) no_hc = true; else no_bucket = true;
+      h->peer_fused = false;  // (records a fused attempt already wrote are dead: the cursors that count them are replaced)
       h->dfree(h->group_slots); h->group_slots = nullptr;
       h->dfree(h->table.keys); h->table.keys = nullptr;
       for (AccPlan& a : pl.accs) { h->dfree(a.cells); a.cells = nullptr; }
       --attempt;
       continue;
     }
-    if (st[0] == 0 && st[3] == 0) { h->num_groups = (int32_t)st[1]; break; }
+    if (st[0] == 0 && st[3] == 0) { h->num_groups = (int32_t)st[1]; h->peer_fused = was_fused; break; }
+    h->peer_fused = false;
     if (st[0] == 0 && st[3] != 0 && !skip_tiny) {
       // the tiny-cardinality kernel met more distinct keys than it has rows for: same table, general path
       if (opt.force_path == 5 || opt.force_path == 6) opt.force_path = 0;
@@ -1077,17 +1257,6 @@ extern "C" void bgb_groupby_destroy(bgb_groupby* h)
 // Peer-memory multi-GPU build: local aggregation -> records scattered into the owners' regions over NVLink -> merge.
 // =====================================================================================================================
 
-struct bgb_peer {
-  int rank = 0, world = 1, device = 0;
-  uint8_t* buffer = nullptr;          // header page + two regions (double-buffered by step parity)
-  size_t region_bytes = 0;
-  uint8_t* peer_buffer[kMaxPeers] = {};  // every rank's buffer as mapped into this process (own buffer at [rank])
-  bool opened[kMaxPeers] = {};           // mapped through cudaIpcOpenMemHandle (must be closed)
-  bool same_process = false;             // some peer was attached with bgb_peer_attach_local
-  uint32_t epoch = 0;
-  uint64_t timeout_ns = 20ull * 1000 * 1000 * 1000;
-  bool poisoned = false;                 // a wait timed out or the abort signal could not be sent: epochs may differ between ranks
-};
 
 extern "C" int bgb_peer_create(int32_t rank, int32_t world, int64_t region_bytes, bgb_peer** out)
 {
@@ -1196,7 +1365,8 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
     }
   };
   // ---- (1) this rank's rows through the single-GPU path
-  int rc = build_local(keys, num_keys, include_null_keys, requests, num_requests, stream, alloc, options, &h, &g_local, /*rank_independent=*/true);
+  const PeerFuse fuse{peer, parity};
+  int rc = build_local(keys, num_keys, include_null_keys, requests, num_requests, stream, alloc, options, &h, &g_local, /*rank_independent=*/true, &fuse);
   if (rc) { const std::string msg = bgb_last_error(); signal_abort(); return set_error(rc, "%s", msg.c_str()); }
   HostTrace tr;
   *out_handle = nullptr;
@@ -1213,26 +1383,20 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
   if (pl.accs.size() > (size_t)kMaxAccs) FAIL_RC(set_error(BGB_UNSUPPORTED, "more than %d accumulators in one peer exchange", kMaxAccs));
 
   // ---- record layout inside a region: key word arrays, then one array per accumulator, each world * cap entries
-  size_t record_bytes = 8 * (size_t)pl.key_words;
-  for (const AccPlan& a : pl.accs) record_bytes += acc_cell_bytes(a.op);
-  const uint64_t cap = (uint64_t)bgb_peer_segment_capacity(peer, (int32_t)record_bytes);
-  if (cap == 0) FAIL_RC(set_error(BGB_INVALID_ARGUMENT, "peer region too small for %d ranks of %zu-byte records", world, record_bytes));
-  const uint64_t entries = (uint64_t)world * cap;
-  uint64_t off           = 8 * entries;
-  const uint64_t key1_off = off;
-  if (pl.key_words == 2) off += 8 * entries;
-  std::vector<uint64_t> acc_off(pl.accs.size());
-  for (size_t a = 0; a < pl.accs.size(); ++a) { acc_off[a] = off; off += (uint64_t)acc_cell_bytes(pl.accs[a].op) * entries; }
+  PeerLayout playout;
+  if (!peer_layout(pl, peer, playout)) FAIL_RC(set_error(BGB_INVALID_ARGUMENT, "peer region too small for %d ranks of %zu-byte records", world, playout.record_bytes));
+  const uint64_t cap = playout.cap, key1_off = playout.key1_off;
+  const std::vector<uint64_t>& acc_off = playout.acc_off;
 
   uint32_t* scratch = (uint32_t*)h->dalloc(sizeof(uint32_t) * (3 * kMaxPeers + 4));  // cursors | wait output
   if (!scratch) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "peer scratch"));
-  uint32_t* cursors  = scratch;
+  uint32_t* cursors  = h->peer_fused ? h->peer_cursors : scratch;   // fused: the slices of the local build already counted (and wrote) the records
   uint32_t* wait_out = scratch + kMaxPeers;
-  FAIL_RC(check_cuda(cudaMemsetAsync(cursors, 0, sizeof(uint32_t) * kMaxPeers, s), "peer cursors"));
+  if (!h->peer_fused) FAIL_RC(check_cuda(cudaMemsetAsync(cursors, 0, sizeof(uint32_t) * kMaxPeers, s), "peer cursors"));
 
   // ---- (2) scatter the local groups into their owners' regions, then publish counts + epoch
-  h->prof.begin("peer_scatter");
-  if (g_local > 0) {
+  h->prof.begin(h->peer_fused ? "peer_signal" : "peer_scatter");
+  if (g_local > 0 && !h->peer_fused) {
     PeerScatterParams sp;
     memset(&sp, 0, sizeof sp);
     sp.keys = h->table.keys; sp.group_slots = h->group_slots; sp.num_groups = g_local;
@@ -1315,49 +1479,75 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
     a.cells = h->dalloc(slots * acc_cell_bytes(a.op));
     if (!a.cells) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "final table accumulators"));
   }
-  h->prof.begin("peer_merge");
-  {
-    size_t na = pl.accs.size();
-    for (size_t b = 0; b == 0 || b < na; b += kMaxAccs) {
-      AggParams p;
-      fill_agg_params(*h, p, b, std::min(na, b + kMaxAccs));
-      p.init_keys = (b == 0);
-      FAIL_RC(check_cuda(launch_init_table(p, s), "init_table"));
+  // The received records are merged like rows of a groupby whose "values" are partial cells: through the records-form slices
+  // when the shape fits (one key word, <= 3 accumulators, enough records to fill the machine), else with HBM atomics
+  static const bool no_hc_merge = getenv("BGB_NO_HC_MERGE") != nullptr;
+  uint64_t hc_merge_min = 1u << 22;  // below this the HBM-table merge is a few microseconds anyway
+  if (const char* e = getenv("BGB_HC_MERGE_MIN")) hc_merge_min = (uint64_t)atoll(e);
+  bool try_hc = !no_hc_merge && total >= hc_merge_min;
+  uint32_t st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (;;) {
+    bool merged = false;
+    if (try_hc) {
+      std::vector<uint32_t> prefix(world + 1, 0);
+      for (int r = 0; r < world; ++r) prefix[r + 1] = prefix[r] + got[r];
+      h->prof.begin("peer_merge_hc");
+      FAIL_RC(run_hc_merge(h, num_sms_of_current_device(), peer->buffer + kPeerHeaderBytes + (size_t)parity * peer->region_bytes, cap, world, prefix, acc_off,
+                           total, merged));
+      h->prof.end();
     }
-    PeerMergeParams mp;
-    memset(&mp, 0, sizeof mp);
-    mp.region = peer->buffer + kPeerHeaderBytes + (size_t)parity * peer->region_bytes;
-    mp.cap = cap; mp.key1_off = key1_off; mp.key_words = pl.key_words; mp.num_accs = (int)na; mp.world = world;
-    mp.slot_hash32 = pl.key_words == 1 && h->path == "bucketed";
-    for (int r = 0; r < world; ++r) mp.prefix[r + 1] = mp.prefix[r] + got[r];
-    mp.table = h->table;
-    for (size_t a = 0; a < na; ++a) {
-      mp.acc[a].cells = pl.accs[a].cells; mp.acc[a].region_off = acc_off[a]; mp.acc[a].op = pl.accs[a].op;
-      mp.acc[a].cell_bytes = (uint8_t)acc_cell_bytes(pl.accs[a].op);
+    uint32_t* scan_state = nullptr;
+    if (!merged) {
+      h->prof.begin("peer_merge");
+      size_t na = pl.accs.size();
+      for (size_t b = 0; b == 0 || b < na; b += kMaxAccs) {
+        AggParams p;
+        fill_agg_params(*h, p, b, std::min(na, b + kMaxAccs));
+        p.init_keys = (b == 0);
+        FAIL_RC(check_cuda(launch_init_table(p, s), "init_table"));
+      }
+      PeerMergeParams mp;
+      memset(&mp, 0, sizeof mp);
+      mp.region = peer->buffer + kPeerHeaderBytes + (size_t)parity * peer->region_bytes;
+      mp.cap = cap; mp.key1_off = key1_off; mp.key_words = pl.key_words; mp.num_accs = (int)na; mp.world = world;
+      mp.slot_hash32 = pl.key_words == 1 && h->path == "bucketed";
+      for (int r = 0; r < world; ++r) mp.prefix[r + 1] = mp.prefix[r] + got[r];
+      mp.table = h->table;
+      for (size_t a = 0; a < na; ++a) {
+        mp.acc[a].cells = pl.accs[a].cells; mp.acc[a].region_off = acc_off[a]; mp.acc[a].op = pl.accs[a].op;
+        mp.acc[a].cell_bytes = (uint8_t)acc_cell_bytes(pl.accs[a].op);
+      }
+      FAIL_RC(check_cuda(launch_peer_merge(mp, s), "peer_merge"));
+      h->prof.end();
+      const uint64_t max_groups = std::max<uint64_t>(1, std::min<uint64_t>(slots, total));
+      h->group_slots            = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
+      scan_state                = (uint32_t*)h->dalloc(compact_scan_state_bytes(capacity));
+      if (!h->group_slots || !scan_state) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "compaction scratch"));
+      h->prof.begin("compact_final");
+      FAIL_RC(check_cuda(launch_compact(h->table, h->group_slots, scan_state, s), "compact"));
+      h->prof.end();
     }
-    FAIL_RC(check_cuda(launch_peer_merge(mp, s), "peer_merge"));
+    FAIL_RC(check_cuda(cudaMemcpyAsync(st, status, sizeof st, cudaMemcpyDeviceToHost, s), "status copy"));
+    tr.mark("merge launches");
+    FAIL_RC(check_cuda(cudaStreamSynchronize(s), "peer build sync"));
+    tr.mark("final sync");
+    h->prof.resolve();
+    if (scan_state) h->dfree(scan_state);
+    if (merged && (st[0] || st[6])) {  // a bucket of the merge overflowed (skewed keys): once more with the HBM-table merge
+      h->dfree(h->group_slots); h->group_slots = nullptr;
+      try_hc = false;
+      continue;
+    }
+    h->dense = merged;
+    break;
   }
-  h->prof.end();
-  const uint64_t max_groups = std::max<uint64_t>(1, std::min<uint64_t>(slots, total));
-  h->group_slots            = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
-  uint32_t* scan_state      = (uint32_t*)h->dalloc(compact_scan_state_bytes(capacity));
-  if (!h->group_slots || !scan_state) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "compaction scratch"));
-  h->prof.begin("compact_final");
-  FAIL_RC(check_cuda(launch_compact(h->table, h->group_slots, scan_state, s), "compact"));
-  h->prof.end();
-  uint32_t st[4] = {0, 0, 0, 0};
-  FAIL_RC(check_cuda(cudaMemcpyAsync(st, status, sizeof st, cudaMemcpyDeviceToHost, s), "status copy"));
-  tr.mark("merge launches");
-  FAIL_RC(check_cuda(cudaStreamSynchronize(s), "peer build sync"));
-  tr.mark("final sync");
-  h->prof.resolve();
-  h->dfree(scan_state);
   h->dfree(scratch);
   if (st[0]) FAIL_RC(set_error(BGB_CUDA_ERROR, "final table overflow during the merge"));
 #undef FAIL_RC
   tr.flush("build_peer");
   h->num_groups = (int32_t)st[1];
-  h->path += "+peer";
+  h->path += h->peer_fused ? "+peer-fused" : "+peer";       // how the records travelled
+  if (h->dense) h->path += "+slices";                        // how they were merged (else: HBM-table atomics + compaction)
   *num_groups = h->num_groups;
   *out_handle = h;
   return BGB_OK;

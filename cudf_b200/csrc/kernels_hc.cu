@@ -25,6 +25,7 @@
 
 #include "device_utils.cuh"
 #include "kernels_hc.h"
+#include "kernels_peer.h"
 
 namespace bgb {
 
@@ -78,7 +79,8 @@ size_t hc_scatter_smem_bytes(int words, int log2_parts)
   return T * words * 8 + T * 2 + (size_t)(4u << log2_parts) * 4 + 64;
 }
 
-// MODE 0: level 1, generic packer (LDG -> records in the stage); 1: level 1, raw column tiles by TMA; 2: level 2 (records by TMA)
+// MODE 0: level 1, generic packer (LDG -> records in the stage); 1: level 1, raw column tiles by TMA; 2: level 2 (records by TMA);
+// 3: level 1 of a MERGE pass: row r is record (source, j) of the received region (word 0 key, one word per accumulator cell)
 template <int W, int MODE>
 __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_constant__ HcScatterParams p)
 {
@@ -107,13 +109,14 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
     for (int c = 0; c < kHcMaxWords - 1; ++c) { moff[c] = o; if (c < p.num_vals && p.val[c].vbit >= 0) o += T / 8; }
   }
 
-  if (MODE != 0 && t == 0) { mbar_init(full, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  if ((MODE == 1 || MODE == 2) && t == 0) { mbar_init(full, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
   for (uint32_t i = t; i < P; i += kHcThreads) s_cnt[i] = 0;
   __syncthreads();
 
   const uint32_t tiles_per_seg = MODE == 2 ? (p.seg_capacity + T - 1) / T : 1;
   const int64_t ntiles = MODE == 2 ? (int64_t)p.num_segs * tiles_per_seg : (p.a.num_rows + T - 1) / T;
   uint32_t phase = 0;
+  (void)phase;
   bool overflow = false;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     int64_t row0;
@@ -192,7 +195,26 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
       if (r < nrows) {
         uint64_t k;
         bool keep = true;
-        if (MODE == 0) {
+        if (MODE == 3) {
+          const uint32_t row = (uint32_t)(row0 + r);
+          int src = 0;
+          while (src + 1 < p.peer_in.world && row >= p.peer_in.prefix[src + 1]) ++src;   // world <= 64 sources
+          const uint64_t idx = (uint64_t)src * p.peer_in.cap + (row - p.peer_in.prefix[src]);
+          uint64_t w[W];
+          // .cg loads: the records were written by another GPU, never through this SM's L1
+          w[0] = __ldcg(reinterpret_cast<const unsigned long long*>(p.peer_in.region) + idx);
+#pragma unroll
+          for (int c = 0; c < W - 1; ++c) {
+            w[(c + 1) % W] = 0;
+            if (c < p.peer_in.num_accs) {
+              const uint8_t* base = p.peer_in.region + p.peer_in.acc_off[c];
+              w[(c + 1) % W] = p.peer_in.cell_bytes[c] == 8 ? __ldcg(reinterpret_cast<const unsigned long long*>(base) + idx)
+                                                            : (uint64_t)__ldcg(reinterpret_cast<const unsigned int*>(base) + idx);
+            }
+          }
+          k = w[0];
+          store_rec<W>(reinterpret_cast<uint64_t*>(stage) + (size_t)r * W, w);
+        } else if (MODE == 0) {
           const int64_t row = row0 + r;
           uint64_t k1;
           keep = pack_key(p.a, row, k, k1);
@@ -335,6 +357,12 @@ static cudaError_t launch_scatter_w(const HcScatterParams& p, int num_sms, cudaS
   ntiles = (p.a.num_rows + T - 1) / T;
   if (ntiles == 0) return cudaSuccess;
   const int grid = (int)(ntiles < 2ll * num_sms ? ntiles : 2ll * num_sms);
+  if (p.peer_in.region != nullptr) {
+    e = cudaFuncSetAttribute(hc_scatter_kernel<W, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    hc_scatter_kernel<W, 3><<<grid, kHcThreads, smem, s>>>(p);
+    return note_launch();
+  }
   if (p.tma_src) {
     e = cudaFuncSetAttribute(hc_scatter_kernel<W, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -382,6 +410,7 @@ template <int W> __device__ __noinline__ void hc_reserved_row(const HcSliceParam
   for (int a = 0; a < p.num_accs; ++a) {
     const HcAcc& acc = p.acc[a];
     if (!(acc.op == ACC_COUNT_ALL || acc.vbit < 0 || ((vb >> acc.vbit) & 1u))) continue;
+    if (acc.mode == HM_ADD32) { atomicAdd(reinterpret_cast<unsigned int*>(acc.cells) + p.table.capacity, (unsigned int)pick_word<W>(w, acc.word)); continue; }  // merge pass: a partial count
     apply_value(acc.op, acc.src, acc.cells, p.table.capacity, pick_word<W>(w, acc.word), 0);
   }
 }
@@ -401,6 +430,7 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
   unsigned long long* s_key = reinterpret_cast<unsigned long long*>(smem);
   __shared__ uint32_t s_warp[THREADS / 32];
   __shared__ unsigned long long s_base;
+  __shared__ uint32_t s_pcnt[kHcMaxPeers], s_pfill[kHcMaxPeers], s_poff[kHcMaxPeers + 1], s_pbase[kHcMaxPeers];
   const uint32_t t = threadIdx.x;
   const uint32_t a_key = smem_u32(s_key);
   constexpr unsigned long long kEmptyK = ~0ull;
@@ -512,6 +542,10 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
           if (p.acc[a].mode == HM_COUNT) {
 #pragma unroll
             for (int j = 0; j < U; ++j) if ((act >> j) & 1u) reds_add(a_cells + slot[j] * 4, 1u);
+          } else if (p.acc[a].mode == HM_ADD32) {
+            const int word = p.acc[a].word;
+#pragma unroll
+            for (int j = 0; j < U; ++j) if ((act >> j) & 1u) reds_add(a_cells + slot[j] * 4, (uint32_t)pick_word<W>(rec[j], word));
           } else {
             const int word = p.acc[a].word;
 #pragma unroll
@@ -539,6 +573,9 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
         if (acc.mode == HM_COUNT) {
 #pragma unroll
           for (int j = 0; j < U; ++j) if ((on >> j) & 1u) reds_add(a_cells + slot[j] * 4, 1u);
+        } else if (acc.mode == HM_ADD32) {
+#pragma unroll
+          for (int j = 0; j < U; ++j) if ((on >> j) & 1u) reds_add(a_cells + slot[j] * 4, (uint32_t)pick_word<W>(rec[j], acc.word));
         } else if (acc.mode == HM_ISUM) {
           // lo += vlo with the old value returned: the add carried iff the new low word is smaller than the old one
           auto add64 = [&](uint32_t cell, uint64_t v) {
@@ -591,6 +628,48 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
     }
     __syncthreads();
 
+    if (p.peer.world > 0) {
+      // ---- fused exchange: the slice's groups go straight into their OWNER ranks' regions (peer stores over NVLink), ordered by
+      // owner in shared memory so that consecutive threads write consecutive records of one region
+      uint16_t* s_perm = reinterpret_cast<uint16_t*>(smem + p.peer.perm_off);
+      uint8_t* s_own   = reinterpret_cast<uint8_t*>(s_perm + S);
+      const int world  = p.peer.world;
+      if (t < (uint32_t)world) { s_pcnt[t] = 0; s_pfill[t] = 0; }
+      __syncthreads();
+      for (uint32_t l = t; l < S; l += THREADS) {
+        const unsigned long long k = s_key[l];
+        if (k != kEmptyK) atomicAdd(&s_pcnt[owner_mix(hash_key(k, 0, 1), (uint32_t)world)], 1u);
+      }
+      __syncthreads();
+      if (t == 0) { uint32_t run = 0; for (int o = 0; o < world; ++o) { s_poff[o] = run; run += s_pcnt[o]; } s_poff[world] = run; }
+      if (t < (uint32_t)world) s_pbase[t] = s_pcnt[t] ? atomicAdd(p.peer.cursors + t, s_pcnt[t]) : 0u;
+      __syncthreads();
+      for (uint32_t l = t; l < S; l += THREADS) {
+        const unsigned long long k = s_key[l];
+        if (k == kEmptyK) continue;
+        const uint32_t owner = owner_mix(hash_key(k, 0, 1), (uint32_t)world);
+        const uint32_t i     = s_poff[owner] + atomicAdd(&s_pfill[owner], 1u);
+        s_perm[i] = (uint16_t)l;
+        s_own[i]  = (uint8_t)owner;
+      }
+      __syncthreads();
+      const uint32_t total = s_poff[world];
+      const uint64_t seg   = (uint64_t)p.peer.me * p.peer.cap;
+      for (uint32_t i = t; i < total; i += THREADS) {
+        const uint32_t l = s_perm[i], owner = s_own[i];
+        const uint64_t pos = (uint64_t)s_pbase[owner] + (i - s_poff[owner]);
+        if (pos >= p.peer.cap) continue;  // over capacity: counted (the signal kernel reports the overflow to every rank), not written
+        uint8_t* region = p.peer.region[owner];
+        reinterpret_cast<uint64_t*>(region)[seg + pos] = s_key[l];
+#pragma unroll 1
+        for (int a = 0; a < p.num_accs; ++a) {
+          const HcAcc& acc = p.acc[a];
+          if (acc.cell_bytes == 8) reinterpret_cast<uint64_t*>(region + p.peer.acc_off[a])[seg + pos] = reinterpret_cast<const uint64_t*>(smem + acc.smem_off)[l];
+          else reinterpret_cast<uint32_t*>(region + p.peer.acc_off[a])[seg + pos] = reinterpret_cast<const uint32_t*>(smem + acc.smem_off)[l];
+        }
+      }
+      __syncthreads();
+    } else {
     // ---- dense output: occupied slots of the slice, appended to the group arrays
     uint32_t mine = 0;
     for (uint32_t l = t; l < S; l += THREADS) mine += s_key[l] != kEmptyK;
@@ -619,6 +698,7 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
       ++o;
     }
     __syncthreads();
+    }
     fb = fb_next; n = n_next; rows = rows_next;
   }
   if (overflow) p.table.status[0] = 1;
@@ -643,6 +723,24 @@ __global__ void hc_init_kernel(const __grid_constant__ HcSliceParams p)
 
 __global__ void hc_finish_kernel(const __grid_constant__ HcSliceParams p)
 {
+  if (p.peer.world > 0) {  // fused exchange: the group of the all-ones key (reserved slot) travels like any other record
+    if (p.table.status[2] != 0) {
+      const uint64_t cap   = p.table.capacity;
+      const uint32_t owner = owner_mix(hash_key(kEmpty, 0, 1), (uint32_t)p.peer.world);
+      const uint64_t pos   = atomicAdd(p.peer.cursors + owner, 1u);
+      if (pos < p.peer.cap) {
+        uint8_t* region    = p.peer.region[owner];
+        const uint64_t seg = (uint64_t)p.peer.me * p.peer.cap;
+        reinterpret_cast<uint64_t*>(region)[seg + pos] = kEmpty;
+        for (int a = 0; a < p.num_accs; ++a) {
+          if (p.acc[a].cell_bytes == 8) reinterpret_cast<uint64_t*>(region + p.peer.acc_off[a])[seg + pos] = reinterpret_cast<const uint64_t*>(p.acc[a].cells)[cap];
+          else reinterpret_cast<uint32_t*>(region + p.peer.acc_off[a])[seg + pos] = reinterpret_cast<const uint32_t*>(p.acc[a].cells)[cap];
+        }
+      }
+    }
+    p.table.status[1] = 0;
+    return;
+  }
   unsigned long long g = *p.gcount;
   if (p.table.status[2] != 0) { p.group_slots[g] = (uint32_t)p.table.capacity; ++g; }
   p.table.status[1] = (uint32_t)g;
@@ -676,7 +774,7 @@ static cudaError_t launch_slices_w(const HcSliceParams& p, size_t smem_bytes, in
   bool lean = p.num_accs <= 3 && W <= 2;
   for (int a = 0; a < p.num_accs; ++a) {
     const HcAcc& acc = p.acc[a];
-    const bool count = acc.mode == HM_COUNT && (acc.vbit < 0 || acc.op == ACC_COUNT_ALL);
+    const bool count = (acc.mode == HM_COUNT || acc.mode == HM_ADD32) && (acc.vbit < 0 || acc.op == ACC_COUNT_ALL);
     const bool isum  = acc.mode == HM_ISUM && acc.op == ACC_SUM_I64 && (acc.src == S_I64 || acc.src == S_U64) && acc.vbit < 0;
     lean = lean && (count || isum);
   }

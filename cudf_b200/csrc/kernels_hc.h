@@ -19,6 +19,32 @@ constexpr int kHcMaxWords = 4;     // record words: key + up to 3 value / validi
 constexpr int kHcMaxParts = 1024;  // buckets per scatter level
 constexpr int kHcThreads  = 512;
 
+// Multi-GPU fusion (kernels_hc.cu, hc_slice_kernel flush): instead of appending a finished slice to the local dense table, the
+// CTA writes one record per group STRAIGHT INTO THE OWNER RANK'S exchange region over NVLink (peer stores, ordered by owner in
+// shared memory so that consecutive threads write consecutive positions of one region). The record layout is the one
+// peer_merge / the merge-mode scatter read: key array, then one array per accumulator, each world x cap entries.
+constexpr int kHcMaxPeers = 64;
+struct HcPeerOut {
+  int32_t world;             // 0: not fused (dense local output)
+  int32_t me;
+  uint64_t cap;              // records per (source, destination) segment
+  uint32_t* cursors;         // [world] records produced for each destination (local memory, zeroed)
+  uint8_t* region[kHcMaxPeers];
+  uint64_t acc_off[kMaxAccs];  // byte offset of every accumulator's array inside a region (key array at 0)
+  uint32_t perm_off;         // shared memory: u16 perm[S] then u8 own[S] behind the slice
+};
+
+// Final merge of the peer exchange as an hc pass: level 1 reads RECEIVED RECORDS (world segments of a region) instead of columns
+struct HcPeerIn {
+  const uint8_t* region;     // nullptr: not a merge pass
+  uint64_t cap;
+  int32_t world;
+  int32_t num_accs;
+  uint32_t prefix[kHcMaxPeers + 1];   // records received from sources [0, s)
+  uint64_t acc_off[kHcMaxWords - 1];
+  uint8_t cell_bytes[kHcMaxWords - 1];
+};
+
 struct HcValue {
   const uint8_t* data;
   const uint32_t* mask;
@@ -49,10 +75,12 @@ struct HcScatterParams {
   int32_t log2_parts;        // buckets of this level (per segment)
   int32_t slot_shift;        // bucket = ((slot_hash32(key) & (capacity - 1)) >> slot_shift) & (P - 1)
   uint32_t* status;          // status[6] = 1: a bucket overflowed (skewed keys): the host reruns the call on another path
+  HcPeerIn peer_in;          // level 1 of a merge pass
 };
 
 // accumulator of the slice kernel: where its cell lives in shared memory and how a record word updates it
-enum HcMode : uint8_t { HM_COUNT, HM_ISUM, HM_MINMAX, HM_FSUM64, HM_FSUM32, HM_OTHER };
+enum HcMode : uint8_t { HM_COUNT, HM_ISUM, HM_MINMAX, HM_FSUM64, HM_FSUM32, HM_OTHER,
+                        HM_ADD32 };  // merge of partial counts: the record word is ADDED to a 32-bit cell (peer exchange, final merge)
 struct HcAcc {
   void* cells;               // the accumulator's array in the (dense) table
   uint32_t smem_off;         // byte offset of its cell array in shared memory
@@ -77,6 +105,7 @@ struct HcSliceParams {
   uint32_t* group_slots;     // identity for the dense groups
   unsigned long long* gcount;
   uint64_t max_groups;       // entries the dense arrays can take
+  HcPeerOut peer;
   HcAcc acc[kMaxAccs];
 };
 

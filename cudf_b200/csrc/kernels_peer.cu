@@ -195,7 +195,7 @@ __device__ __forceinline__ void merge_cell(uint8_t op, void* cells, uint64_t slo
   unsigned long long* c64 = reinterpret_cast<unsigned long long*>(cells) + slot;
   unsigned int* c32       = reinterpret_cast<unsigned int*>(cells) + slot;
   switch (op) {
-    case ACC_SUM_I64: case ACC_SUMSQ_I64: atomicAdd(c64, (unsigned long long)v); break;
+    case ACC_SUM_I64: case ACC_SUMSQ_I64: case ACC_SUM_LO32: case ACC_SUM_HI32: atomicAdd(c64, (unsigned long long)v); break;
     case ACC_SUM_F64: case ACC_SUMSQ_F64: atomicAdd(reinterpret_cast<double*>(c64), __longlong_as_double((long long)v)); break;
     case ACC_SUM_F32: case ACC_SUMSQ_F32: atomicAdd(reinterpret_cast<float*>(c32), __uint_as_float((uint32_t)v)); break;
     case ACC_PROD_I64: atomic_mul_i64(c64, (int64_t)v); break;

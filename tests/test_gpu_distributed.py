@@ -378,6 +378,36 @@ def test_high_cardinality_goes_through_the_partitioned_merge(exchange):
     assert abs(sizes[0] - sizes[1]) < 0.05 * sum(sizes)
 
 
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("aggs", [[(0, "sum", 0), (0, "count_valid", 0)],
+                                  [(0, "min", 0), (0, "max", 0)],
+                                  [(0, "mean", 0), (0, "variance", 1)],
+                                  [(0, "sum", 0), (0, "min", 0), (0, "max", 0), (0, "count_all", 0)]], ids=["lean", "minmax", "moments", "five-cells"])
+def test_peer_fused_exchange_and_slice_merge(monkeypatch, world, aggs):
+    """The records-form local build writes every finished slice straight into the owners' regions (no separate scatter pass over
+    the local groups) and the owner merges what it received through the same slice kernels (no HBM hash table, no compaction)."""
+    monkeypatch.setenv("BGB_HC_MERGE_MIN", "1000")
+    nulls = 0.0 if aggs[0][1] == "sum" and len(aggs) == 2 else 0.2
+    shards = int_shards(world, 1_500_000, 700_000, null_frac=nulls, seed=21)
+    # one all-ones key per rank: its group lives in the reserved slot of the slices and travels through hc_finish
+    for k, _ in shards:
+        k[0].data[::100_003] = -1
+    sizes = check_against_oracle(world, shards, aggs, options={"force_path": 7}, exchange="peer", peer_region_bytes=64 << 20)
+    # records of more than three cells do not fit the 32-byte record of the slice kernels: merged in the HBM table
+    want = "bucketed+peer-fused" if len(aggs) == 4 else "bucketed+peer-fused+slices"
+    assert all(LAST[r][1] == want for r in range(world)), LAST
+    assert abs(sizes[0] - sizes[1]) < 0.05 * sum(sizes)
+
+
+def test_peer_slice_merge_after_the_separate_scatter(monkeypatch):
+    """BGB_NO_PEER_FUSE: the local groups are scattered by their own kernel; the merge still runs through the slices."""
+    monkeypatch.setenv("BGB_HC_MERGE_MIN", "1000")
+    monkeypatch.setenv("BGB_NO_PEER_FUSE", "1")
+    shards = int_shards(2, 300_000, 200_000, seed=23)
+    check_against_oracle(2, shards, [(0, "sum", 0), (0, "count_valid", 0)], exchange="peer", peer_region_bytes=64 << 20)
+    assert all(LAST[r][1].endswith("+peer+slices") for r in range(2)), LAST
+
+
 def test_peer_region_grows_after_overflow():
     """A 4 KB region holds 64 records per (source, destination) segment; 1000 groups overflow it on every rank, every rank
     reports BGB_PEER_OVERFLOW in the same step and the communicator re-creates a larger region until the exchange fits."""
