@@ -794,7 +794,7 @@ def run_multi(args, world):
         total_ms = float(t.item())
     ms_per_step = total_ms / steps
     log(f"rank {rank}: {ms_per_step:.1f} ms/step; torch reserved {torch.cuda.memory_reserved(device) / 1e9:.1f} GB, allocated {torch.cuda.memory_allocated(device) / 1e9:.1f} GB, "
-        f"max allocated {torch.cuda.max_memory_allocated(device) / 1e9:.1f} GB")
+        f"max allocated {torch.cuda.max_memory_allocated(device) / 1e9:.1f} GB, allocator retries {torch.cuda.memory_stats(device).get('num_alloc_retries', 0)}")
     n_total = shard_rows * nshards
     value = n_total / (ms_per_step * 1e-3)
 

@@ -42,12 +42,12 @@ struct bgb_groupby {
   bool peer_fused = false;          // ... or wrote them straight into the owner ranks' exchange regions (no local groups at all)
   uint32_t* peer_cursors = nullptr; // records produced per destination by the fused slices
 
-  void* dalloc(size_t bytes)
+  void* dalloc(size_t bytes, bool transient = false)
   {
     if (bytes == 0) bytes = 16;
     void* p = nullptr;
     if (has_alloc) p = alloc.allocate(bytes, (void*)stream, alloc.ctx);
-    else p = pool_alloc_async(bytes, stream);
+    else p = pool_alloc_async(bytes, stream, transient);
     if (p) blocks.push_back({p, bytes});
     return p;
   }
@@ -532,7 +532,7 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, co
   const size_t cur_bytes = up256(sizeof(uint32_t) * ncur);
   const size_t l1_bytes  = up256(rows1 * W * 8 + 64);
   const size_t l2_bytes  = b2 ? up256(rows2 * W * 8 + 64) : 0;
-  uint8_t* arena = (uint8_t*)h->dalloc(cur_bytes + l1_bytes + l2_bytes);
+  uint8_t* arena = (uint8_t*)h->dalloc(cur_bytes + l1_bytes + l2_bytes, /*transient=*/true);
   auto release = [&]() { if (arena) { h->dfree(arena); arena = nullptr; } };
   uint32_t* counters = (uint32_t*)arena;
   uint64_t* L1 = arena ? (uint64_t*)(arena + cur_bytes) : nullptr;
@@ -688,7 +688,7 @@ int run_hc_merge(bgb_groupby* h, int num_sms, const uint8_t* region, uint64_t ca
   const size_t ncur = (size_t)P1 * kHotStride + (b2 ? NB : 0) + 4;
   auto up256 = [](size_t x) { return (x + 255) & ~(size_t)255; };
   const size_t cur_bytes = up256(sizeof(uint32_t) * ncur), l1_bytes = up256(rows1 * W * 8 + 64), l2_bytes = b2 ? up256(rows2 * W * 8 + 64) : 0;
-  uint8_t* arena = (uint8_t*)h->dalloc(cur_bytes + l1_bytes + l2_bytes);
+  uint8_t* arena = (uint8_t*)h->dalloc(cur_bytes + l1_bytes + l2_bytes, /*transient=*/true);
   const uint64_t max_groups = std::min<uint64_t>(h->table.capacity + 1, (uint64_t)N + 1);
   h->group_slots = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
   if (!arena || !h->group_slots) {

@@ -83,7 +83,7 @@ void flush_locked(DeviceCache& c)
 
 }  // namespace
 
-void* pool_alloc_async(size_t bytes, cudaStream_t s)
+void* pool_alloc_async(size_t bytes, cudaStream_t s, bool transient)
 {
   bytes = ((bytes ? bytes : 16) + 255) & ~(size_t)255;
   if (bytes >= ((size_t)64 << 20)) {
@@ -100,7 +100,9 @@ void* pool_alloc_async(size_t bytes, cudaStream_t s)
   auto it = c->free_blocks.find(s);
   if (it != c->free_blocks.end()) {
     // best fit among this stream's freed blocks, with bounded slack so a small request never pins a huge block
-    const size_t slack = bytes + (bytes > (1u << 20) ? bytes / 4 : (1u << 18));
+    // (a transient block: no bound. A 1e9-row call's 38 GB record arena then also serves the 23 GB arena of the fold that follows and
+    // the 6 GB arena of the merge, instead of three blocks that together no longer fit beside the caller's data)
+    const size_t slack = transient ? ~(size_t)0 : bytes + (bytes > (1u << 20) ? bytes / 4 : (1u << 18));
     int best = -1;
     std::vector<FreeBlock>& v = it->second;
     for (int i = 0; i < (int)v.size(); ++i)

@@ -6,7 +6,9 @@
 #include <stddef.h>
 
 namespace bgb {
-void* pool_alloc_async(size_t bytes, cudaStream_t s);   // nullptr on failure (error state cleared)
+// nullptr on failure (error state cleared). transient: scratch that is freed again before the call returns (record buffers):
+// ANY cached block of the stream that is large enough is taken, however much larger -- it is back in the cache within the call
+void* pool_alloc_async(size_t bytes, cudaStream_t s, bool transient = false);
 void pool_free_async(void* p, cudaStream_t s);
 void pool_trim();  // hand every cached block of the current device back to the driver
 void pool_release_stream(cudaStream_t s);  // hand back the blocks cached for stream `s` (call before destroying the stream)
