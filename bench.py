@@ -558,6 +558,7 @@ def main():
     ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"])
     ap.add_argument("--shards", type=int, default=8, help="MG: total number of shards of the job")
     ap.add_argument("--pieces", type=int, default=0, help="MG: pieces every shard is fed as (0 = auto)")
+    ap.add_argument("--fold-rows", type=int, default=0, help="MG: pending partial rows that trigger a fold (0 = auto)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
@@ -731,9 +732,11 @@ def run_multi(args, world):
     if nshards % world != 0:
         raise SystemExit(f"--shards {nshards} must be a multiple of the number of ranks ({world})")
     mine = list(range(rank * nshards // world, (rank + 1) * nshards // world))
-    # one GPU holding all 8 shards (128 GB of 192) has ~60 GB left: a 1e9-row call needs 44 GB of scratch + table, a 2.5e8-row call
-    # 15 GB, and partial tables, their concatenation and the fold need room too: every shard is fed as quarters
-    pieces_per_shard = args.pieces or (4 if world == 1 and shard_rows * nshards > 4_000_000_000 else 1)
+    # one GPU holding all 8 shards (128 GB of its 191) has ~60 GB left for scratch, partial tables and folds: every shard is fed as
+    # halves (a 5e8-row call: 19 GB of record buffers + 5 GB of table). Smaller pieces cost more than they save -- a quarter
+    # shard still meets 9.2e7 of the 1e8 keys, so its call pays the full table and its partial table is as large as a half's
+    # (measured r02: quarters 586-744 ms/step, halves 391 ms/step)
+    pieces_per_shard = args.pieces or (2 if world == 1 and shard_rows * nshards > 4_000_000_000 else 1)
     shards, total_sum, total_rows = [], 0, 0
     for sidx in mine:
         keys, reqs = make_device_inputs("MG", shard_rows, g, 42 + 2 * sidx, device)  # (seed, seed + 1) per shard: key and value streams never collide
@@ -755,7 +758,7 @@ def run_multi(args, world):
         region = max(region, int(2.0 * 20 * g / world) + (8 << 20))
 
     comm = D.TorchComm() if dist is not None else D.SingleComm()   # ONE communicator: its peer-memory context is created once
-    fold_rows = 190_000_000 if world == 1 else 450_000_000          # one GPU holding 128 GB of inputs keeps fewer partial tables pending
+    fold_rows = args.fold_rows or (290_000_000 if world == 1 else 450_000_000)          # one GPU holding 128 GB of inputs keeps fewer partial tables pending
 
     def make_dgb(profile):
         return D.DistributedGroupBy(shards[0][0], options={"profile": profile, "force_path": args.force_path, "fold_rows": fold_rows},
@@ -956,7 +959,7 @@ def run_e2e_multi(args, world, rank, device, dist, host, piece_rows, aggs, n_tot
         torch.cuda.synchronize()
 
     hs = HostShards()
-    dgb = D.DistributedGroupBy(None, options={"force_path": args.force_path, "fold_rows": 190_000_000 if world == 1 else 450_000_000},
+    dgb = D.DistributedGroupBy(None, options={"force_path": args.force_path, "fold_rows": args.fold_rows or (290_000_000 if world == 1 else 450_000_000)},
                                exchange=args.exchange, peer_region_bytes=region, comm=comm)
 
     def step():

@@ -41,6 +41,7 @@ struct bgb_groupby {
   bool dense = false;               // the build wrote the groups densely at [0, G) and filled group_slots itself (kernels_hc.cu)
   bool peer_fused = false;          // ... or wrote them straight into the owner ranks' exchange regions (no local groups at all)
   uint32_t* peer_cursors = nullptr; // records produced per destination by the fused slices
+  uint64_t table_slots = 0;         // entries of table.keys / the accumulator arrays (capacity + 1, or fewer: see build_local)
 
   void* dalloc(size_t bytes, bool transient = false)
   {
@@ -537,7 +538,7 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, co
   uint32_t* counters = (uint32_t*)arena;
   uint64_t* L1 = arena ? (uint64_t*)(arena + cur_bytes) : nullptr;
   uint64_t* L2 = (arena && b2) ? (uint64_t*)(arena + cur_bytes + l1_bytes) : nullptr;
-  const uint64_t max_groups = std::min<uint64_t>(h->table.capacity + 1, (uint64_t)N + 1);
+  const uint64_t max_groups = std::min<uint64_t>(h->table_slots, (uint64_t)N + 1);
   h->group_slots = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
   if (!arena || !h->group_slots) {
     release();
@@ -554,6 +555,7 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, co
   HcSliceParams sp;
   memset(&sp, 0, sizeof sp);
   sp.table = h->table;
+  sp.table.capacity = h->table_slots - 1;  // (the slices use it only as the index of the reserved entry: the LAST allocated one)
   sp.words = W; sp.key_in_low32 = in_low32; sp.vbits_word = vbits_word;
   sp.log2_slice = ls; sp.num_buckets = NB; sp.num_accs = (int)pl.accs.size();
   sp.group_slots = h->group_slots; sp.gcount = gcount; sp.max_groups = max_groups;
@@ -689,7 +691,7 @@ int run_hc_merge(bgb_groupby* h, int num_sms, const uint8_t* region, uint64_t ca
   auto up256 = [](size_t x) { return (x + 255) & ~(size_t)255; };
   const size_t cur_bytes = up256(sizeof(uint32_t) * ncur), l1_bytes = up256(rows1 * W * 8 + 64), l2_bytes = b2 ? up256(rows2 * W * 8 + 64) : 0;
   uint8_t* arena = (uint8_t*)h->dalloc(cur_bytes + l1_bytes + l2_bytes, /*transient=*/true);
-  const uint64_t max_groups = std::min<uint64_t>(h->table.capacity + 1, (uint64_t)N + 1);
+  const uint64_t max_groups = std::min<uint64_t>(h->table_slots, (uint64_t)N + 1);
   h->group_slots = (uint32_t*)h->dalloc(max_groups * sizeof(uint32_t));
   if (!arena || !h->group_slots) {
     if (arena) h->dfree(arena);
@@ -707,6 +709,7 @@ int run_hc_merge(bgb_groupby* h, int num_sms, const uint8_t* region, uint64_t ca
   HcSliceParams sp;
   memset(&sp, 0, sizeof sp);
   sp.table = h->table;
+  sp.table.capacity = h->table_slots - 1;
   sp.words = W; sp.key_in_low32 = 0; sp.vbits_word = -1;
   sp.log2_slice = ls; sp.num_buckets = NB; sp.num_accs = (int)pl.accs.size();
   sp.group_slots = h->group_slots; sp.gcount = gcount; sp.max_groups = max_groups;
@@ -972,10 +975,23 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     if (capacity > cap_max) capacity = cap_max;
   }
 
-  bool skip_tiny = false, no_bucket = false, no_hc = false;
+  bool skip_tiny = false, no_bucket = false, no_hc = false, no_short = false;
+  bool hc_shape = pl.key_words == 1 && pl.accs.size() <= (size_t)kMaxAccs && N >= 1 && N < (1ll << 31) && getenv("BGB_NO_HC") == nullptr;
+  for (const AccPlan& a : pl.accs) hc_shape = hc_shape && !(a.op == ACC_ARGMIN || a.op == ACC_ARGMAX || a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX);
   for (int attempt = 0;; ++attempt) {
     h->table.capacity = capacity;
-    const uint64_t slots = capacity + 1;
+    size_t slot_bytes = 8 * (size_t)pl.key_words;
+    for (const AccPlan& a : pl.accs) slot_bytes += acc_cell_bytes(a.op);
+    // the table will not stay in L2: partition first (measured 3-5x faster than random HBM atomics at 1e8 groups)
+    const bool big = (double)capacity * slot_bytes > 96e6 && N >= (1 << 22);
+    // The records-form path writes its groups DENSELY: the arrays need one entry per possible group (at most one per row) plus the
+    // reserved one, not one per hash slot. That matters when rows repeat little (a fold of partial tables: capacity = 4 x rows).
+    // No other kernel may then touch the arrays: the small-cardinality paths are out of reach at > 70000 estimated groups, and a
+    // records-form attempt that does not complete starts over with full arrays.
+    const bool short_table = !no_short && !no_hc && !no_bucket && hc_shape && (uint64_t)N < capacity &&
+                             (opt.force_path == 7 || (opt.force_path == 0 && big && g_raw > 70000.0));
+    const uint64_t slots = short_table ? (uint64_t)N + 1 : capacity + 1;
+    h->table_slots = slots;
     h->table.keys = (uint64_t*)h->dalloc(slots * 8 * pl.key_words);
     if (!h->table.keys) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "group table keys (%llu slots)", (unsigned long long)slots));
     for (AccPlan& a : pl.accs) {
@@ -987,12 +1003,8 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     std::string path;
     bool done = false, was_hc_attempt = false;
     BuildContext ctx{&pl, h->table, opt, g_raw, max_abs, key_min, key_max, s, &h->prof, num_sms, skip_tiny};
-    FAIL_RC(try_fast_paths(ctx, done, path));
+    if (!short_table) FAIL_RC(try_fast_paths(ctx, done, path));
     if (!done && opt.force_path != 1 && opt.force_path != 2 && opt.force_path != 4) {
-      size_t slot_bytes = 8 * (size_t)pl.key_words;
-      for (const AccPlan& a : pl.accs) slot_bytes += acc_cell_bytes(a.op);
-      // the table will not stay in L2: partition first (measured 3-5x faster than random HBM atomics at 1e8 groups)
-      const bool big = (double)capacity * slot_bytes > 96e6 && N >= (1 << 22);
       // Mid cardinalities (past the shared-memory table, table still L2-sized) stay on the generic kernel: ONE scatter level +
       // slices was measured SLOWER there (1e9 rows: 32 / 27 / 24 ms at 3e4 / 1e5 / 3e5 groups against 19-20 ms, profiles/
       // r01_card_sweep_A9_mid.txt) -- with 64-512 buckets and one CTA per bucket most of the 444 CTA slots stay empty. It would
@@ -1002,6 +1014,13 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
       if ((opt.force_path == 7 || (opt.force_path == 0 && (big || mid))) && !no_bucket) {
         if (!no_hc) FAIL_RC(run_hc(h, num_sms, opt, g_raw, fuse, done));  // records form first; plans it does not take go through the column form
         was_hc_attempt = done;
+        if (!done && short_table) {  // the plan has no records form after all: full arrays, every path open
+          no_short = true;
+          h->dfree(h->table.keys); h->table.keys = nullptr;
+          for (AccPlan& a : pl.accs) { h->dfree(a.cells); a.cells = nullptr; }
+          --attempt;
+          continue;
+        }
         if (!done) FAIL_RC(run_bucketed(h, num_sms, opt, /*one_level_only=*/opt.force_path == 0 && !big, done));
         if (done) path = "bucketed";
       }
@@ -1472,13 +1491,6 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
   h->table.key_words = pl.key_words;
   const uint64_t capacity = next_pow2(std::max<uint64_t>(1024, 2 * total));
   h->table.capacity       = capacity;
-  const uint64_t slots    = capacity + 1;
-  h->table.keys = (uint64_t*)h->dalloc(slots * 8 * pl.key_words);
-  if (!h->table.keys) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "final table keys"));
-  for (AccPlan& a : pl.accs) {
-    a.cells = h->dalloc(slots * acc_cell_bytes(a.op));
-    if (!a.cells) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "final table accumulators"));
-  }
   // The received records are merged like rows of a groupby whose "values" are partial cells: through the records-form slices
   // when the shape fits (one key word, <= 3 accumulators, enough records to fill the machine), else with HBM atomics
   static const bool no_hc_merge = getenv("BGB_NO_HC_MERGE") != nullptr;
@@ -1486,7 +1498,20 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
   if (const char* e = getenv("BGB_HC_MERGE_MIN")) hc_merge_min = (uint64_t)atoll(e);
   bool try_hc = !no_hc_merge && total >= hc_merge_min;
   uint32_t st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  auto free_table = [&]() {
+    if (h->table.keys) { h->dfree(h->table.keys); h->table.keys = nullptr; }
+    for (AccPlan& a : pl.accs) if (a.cells) { h->dfree(a.cells); a.cells = nullptr; }
+  };
   for (;;) {
+    // (the slices write the groups densely: one entry per received record at most, not one per hash slot)
+    const uint64_t slots = try_hc ? total + 1 : capacity + 1;
+    h->table_slots = slots;
+    h->table.keys  = (uint64_t*)h->dalloc(slots * 8 * pl.key_words);
+    if (!h->table.keys) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "final table keys"));
+    for (AccPlan& a : pl.accs) {
+      a.cells = h->dalloc(slots * acc_cell_bytes(a.op));
+      if (!a.cells) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "final table accumulators"));
+    }
     bool merged = false;
     if (try_hc) {
       std::vector<uint32_t> prefix(world + 1, 0);
@@ -1495,6 +1520,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
       FAIL_RC(run_hc_merge(h, num_sms_of_current_device(), peer->buffer + kPeerHeaderBytes + (size_t)parity * peer->region_bytes, cap, world, prefix, acc_off,
                            total, merged));
       h->prof.end();
+      if (!merged) { free_table(); try_hc = false; continue; }  // shape not taken: full-size arrays for the HBM-table merge
     }
     uint32_t* scan_state = nullptr;
     if (!merged) {
@@ -1535,6 +1561,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
     if (scan_state) h->dfree(scan_state);
     if (merged && (st[0] || st[6])) {  // a bucket of the merge overflowed (skewed keys): once more with the HBM-table merge
       h->dfree(h->group_slots); h->group_slots = nullptr;
+      free_table();
       try_hc = false;
       continue;
     }

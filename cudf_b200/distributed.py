@@ -496,19 +496,27 @@ class DistributedGroupBy:
                 out.append(column_from_wire(data, vb, cs[0].type_id, cs[0].scale))
             return out
 
+        def release_caches():
+            """memory pressure: torch's and the library's cached blocks go back to the driver (each allocator then sees the other's)"""
+            torch.cuda.synchronize(device)
+            torch.cuda.empty_cache()
+            _lib.lib().bgb_release_cached_memory()
+
         def fold(tables):
             """several partial tables -> one (concatenate, then ONE merge groupby)"""
-            cols = concat(tables)
+            try:
+                cols = concat(tables)
+            except torch.OutOfMemoryError:
+                release_caches()
+                cols = concat(tables)
             tables.clear()  # the concatenation replaces them
             reqs_m = merge_requests(cols)
             try:
                 fk, fr = GroupBy(Table(cols[:nk]), self._null_handling, options=merge_opts).aggregate(reqs_m)
-            except _lib.CudaError as e:
-                if e.status != 5:  # BGB_OUT_OF_MEMORY: hand torch's and the library's cached blocks back to the driver, once
+            except (_lib.CudaError, torch.OutOfMemoryError) as e:
+                if isinstance(e, _lib.CudaError) and e.status != 5:  # BGB_OUT_OF_MEMORY: once more with both caches emptied
                     raise
-                torch.cuda.synchronize(device)
-                torch.cuda.empty_cache()
-                _lib.lib().bgb_release_cached_memory()
+                release_caches()
                 fk, fr = GroupBy(Table(cols[:nk]), self._null_handling, options=merge_opts).aggregate(reqs_m)
             return list(fk.columns()) + [t.columns()[0] for t in fr]
 
@@ -520,7 +528,13 @@ class DistributedGroupBy:
             local_reqs = [GroupByRequest(r._values, [agg.Aggregation(k) for k in p.partial_kinds]) for r, p in zip(reqs, plans)]
             tok = self._phase("dist_local", device)
             local = GroupBy(keys, self._null_handling, options=self._options)
-            pkeys, presults = local.aggregate(local_reqs)
+            try:
+                pkeys, presults = local.aggregate(local_reqs)
+            except (_lib.CudaError, torch.OutOfMemoryError) as e:
+                if isinstance(e, _lib.CudaError) and e.status != 5:
+                    raise
+                release_caches()
+                pkeys, presults = local.aggregate(local_reqs)
             self._phase_end(tok, device)
             self._local_profile.extend(local.last_profile)
             self.last_path = local.last_path
