@@ -850,6 +850,12 @@ def run_multi(args, world):
         if ps:
             nvlink = {"bytes_out_per_gpu": out_bytes, "peer_scatter_ms": ps, "GBps_out_per_gpu": out_bytes / (ps * 1e-3) / 1e9,
                       "peak_GBps": 900.0, "measured_peer_copy_GBps": 770.0}
+        elif "peer_signal" in prof:
+            # fused exchange: the records leave inside the slice kernel of the last local call (peer stores from its flush), so the
+            # transfer has no kernel of its own to time; the rate below is the floor "bytes / whole slice kernel"
+            sl = prof.get("hc_slices")
+            nvlink = {"bytes_out_per_gpu": out_bytes, "fused_into": "hc_slices", "hc_slices_ms": sl,
+                      "GBps_out_per_gpu_floor": (out_bytes / (sl * 1e-3) / 1e9) if sl else None, "peak_GBps": 900.0, "measured_peer_copy_GBps": 770.0}
     # dominant local kernel against the HBM roofline (per call of the local path: one piece of one shard)
     local = {k: v for k, v in prof.items() if not k.startswith("dist_") and not k.startswith("peer_")}
     calls = len(shards)

@@ -92,11 +92,14 @@ struct AggParams {
   int32_t skip_null_keys;  // null_policy::EXCLUDE and some key column has a mask
   int32_t init_keys;       // init kernel: also reset keys + status (first accumulator chunk)
   const uint32_t* num_rows_dev;  // when set, the row count lives on the device (partitioned copy: rows kept by the scatter)
+  int32_t wide;            // key image wider than 128 bits: table slots hold the ROW NUMBER of the group's first row (find_or_insert_row)
 };
 
 // final (output) operations of the emit kernel
 enum OutOp : uint8_t {
   OUT_KEY,        // unpack key column
+  OUT_KEY_GATHER, // wide keys: the slot holds a row number; the key element is read from the caller's column (a = data, b = mask,
+                  // key_base = offset, acc_op = float class)
   OUT_COPY_I64,   // 8-byte integer cell -> out type (int64 for sums, narrowed ordered image for MIN/MAX)
   OUT_COPY_F64,
   OUT_COPY_F32,

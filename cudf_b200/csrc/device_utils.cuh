@@ -193,6 +193,55 @@ __device__ __forceinline__ uint64_t find_or_insert(const TableDesc& t, uint64_t 
   return kNoSlot;
 }
 
+// ---- keys wider than 128 bits: the table holds ROW NUMBERS (64-bit slots, EMPTY = all ones) and two rows are compared column by
+// column in the caller's key columns -- the reference's own scheme for every key (row hasher + self-comparator over a set of
+// row indices: /root/reference/cpp/src/groupby/hash/compute_groupby.cu:79-104, row_operator/equality.cuh:59-89).
+__device__ __forceinline__ bool row_hash(const AggParams& p, int64_t row, uint64_t& h)
+{
+  h = 0x9E3779B97F4A7C15ull;
+#pragma unroll 1
+  for (int c = 0; c < p.num_key_cols; ++c) {
+    const KeyColDesc& kc = p.kc[c];
+    const int64_t idx    = (int64_t)kc.offset + row;
+    uint64_t v           = 0xA5A5A5A5DEADBEEFull;  // a null element (all nulls are equal: null_equality::EQUAL)
+    if (kc.mask == nullptr || bit_is_set(kc.mask, idx)) v = canon_key_bits(load_raw(kc.data, kc.width, idx), kc.fclass);
+    else if (p.skip_null_keys) return false;
+    h = mix64(h ^ (v + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2)));
+  }
+  return true;
+}
+__device__ __forceinline__ bool rows_equal(const AggParams& p, int64_t r1, int64_t r2)
+{
+#pragma unroll 1
+  for (int c = 0; c < p.num_key_cols; ++c) {
+    const KeyColDesc& kc = p.kc[c];
+    const int64_t i1 = (int64_t)kc.offset + r1, i2 = (int64_t)kc.offset + r2;
+    const bool v1 = kc.mask == nullptr || bit_is_set(kc.mask, i1), v2 = kc.mask == nullptr || bit_is_set(kc.mask, i2);
+    if (v1 != v2) return false;
+    if (v1 && canon_key_bits(load_raw(kc.data, kc.width, i1), kc.fclass) != canon_key_bits(load_raw(kc.data, kc.width, i2), kc.fclass)) return false;
+  }
+  return true;
+}
+// returns the slot of `row`'s key (inserting `row` as the group's representative when the key is new), kNoSlot on overflow
+__device__ __forceinline__ uint64_t find_or_insert_row(const AggParams& p, int64_t row, uint64_t hash)
+{
+  const TableDesc& t = p.table;
+  const uint64_t cap = t.capacity;
+  uint64_t slot = hash & (cap - 1);
+  unsigned long long* keys = reinterpret_cast<unsigned long long*>(t.keys);
+  for (uint32_t probes = 0; probes < kMaxProbes; ++probes) {
+    unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(keys + slot);
+    if (cur == kEmpty) {
+      cur = atomicCAS(keys + slot, (unsigned long long)kEmpty, (unsigned long long)row);
+      if (cur == kEmpty) return slot;
+    }
+    if (cur == (unsigned long long)row || rows_equal(p, (int64_t)cur, row)) return slot;
+    slot = (slot + 1) & (cap - 1);
+  }
+  t.status[0] = 1;
+  return kNoSlot;
+}
+
 // ---- order-preserving unsigned images (so that MIN/MAX are one RED.MIN/MAX.U64 for every type)
 __device__ __forceinline__ uint64_t ordered_image(uint64_t raw, int src)
 {

@@ -133,6 +133,7 @@ void fill_agg_params(const bgb_groupby& h, AggParams& p, size_t acc_begin, size_
   p.num_rows       = pl.num_rows;
   p.num_key_cols   = (int)pl.keys.size();
   p.skip_null_keys = pl.skip_null_keys;
+  p.wide           = pl.wide ? 1 : 0;
   for (size_t c = 0; c < pl.keys.size(); ++c) {
     const KeyPlan& k = pl.keys[c];
     p.kc[c] = KeyColDesc{(const uint8_t*)k.v.data, k.v.null_mask, k.v.offset, k.width, k.fclass, k.shift, k.null_bit};
@@ -875,7 +876,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
   bgb_groupby* h = new bgb_groupby();
   // key images wider than 128 bits are planned too when the call may repack them (the exact value ranges decide below)
   const bool may_repack = !rank_independent && (!options || options->force_path == 0);
-  int rc = make_plan(keys, num_keys, include_null_keys, requests, num_requests, h->plan, rank_independent, may_repack);
+  int rc = make_plan(keys, num_keys, include_null_keys, requests, num_requests, h->plan, rank_independent, /*allow_wide=*/!rank_independent);
   if (rc != BGB_OK) { delete h; return rc; }
   h->stream = (cudaStream_t)stream;
   if (alloc && alloc->allocate && alloc->deallocate) { h->alloc = *alloc; h->has_alloc = true; }
@@ -902,7 +903,14 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     FAIL_RC(try_repack_keys(h, keys, num_keys, include_null_keys, requests, num_requests, repacked));
     tr.mark("repack");
   }
-  if (pl.key_words > 2) FAIL_RC(set_error(BGB_UNSUPPORTED, "packed key wider than 128 bits and the key ranges do not fit 64 bits"));
+  if (pl.key_words > 2) {
+    // no packed image: the table holds the row number of each group's first row and rows are compared in the caller's columns
+    // (the reference's scheme for every key). One-word table of row numbers, generic kernels only.
+    if (opt.force_path != 0 && opt.force_path != 1) FAIL_RC(set_error(BGB_UNSUPPORTED, "force_path %d needs a packed key image of at most 128 bits", opt.force_path));
+    pl.wide         = true;
+    pl.key_words    = 1;
+    opt.force_path  = 1;
+  }
   uint32_t* status = (uint32_t*)h->dalloc(16 * sizeof(uint32_t));
   if (!status) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "status alloc"));
   h->table.status    = status;
@@ -1060,6 +1068,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
       path = "global";
     }
     h->path = path;
+    if (pl.wide) h->path += "+rowkeys";
     // compaction: occupied slots -> dense group list (+ group count)
     const uint64_t max_groups = std::min<uint64_t>(slots, (uint64_t)N);
     uint32_t* scan_state      = nullptr;
@@ -1208,6 +1217,9 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
     d.out = out_keys[i].data; d.out_mask = k.nullable_out ? out_keys[i].null_mask : nullptr; d.null_count = d_nulls + i;
     d.op = OUT_KEY; d.src = type_src(k.v.type_id); d.out_width = k.width; d.shift = k.shift; d.null_bit = k.null_bit;
     d.key_bits = k.bits; d.key_base = k.base;
+    if (pl.wide) {  // gather from the caller's key column at the group's representative row (the columns must still be alive)
+      d.op = OUT_KEY_GATHER; d.a = k.v.data; d.b = k.nullable_out ? k.v.null_mask : nullptr; d.key_base = (uint64_t)(int64_t)k.v.offset; d.acc_op = k.fclass;
+    }
     any_nullable |= k.nullable_out;
     descs.push_back(d);
   }

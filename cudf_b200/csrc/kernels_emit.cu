@@ -153,6 +153,12 @@ __global__ void __launch_bounds__(256) emit_kernel(const __grid_constant__ EmitP
           bits = d.out_width == 8 ? w : (w & ((1ull << (8 * d.out_width)) - 1));
           break;
         }
+        case OUT_KEY_GATHER: {  // k0 = number of the group's representative row
+          const int64_t idx = (int64_t)d.key_base + (int64_t)k0;
+          if (d.b != nullptr) valid = bit_is_set(reinterpret_cast<const uint32_t*>(d.b), idx);
+          bits = valid ? canon_key_bits(load_raw(reinterpret_cast<const uint8_t*>(d.a), d.out_width, idx), d.acc_op) : 0;
+          break;
+        }
         case OUT_COPY_I64: bits = reinterpret_cast<const uint64_t*>(d.a)[slot]; valid = n > 0; break;
         case OUT_COPY_F64: bits = reinterpret_cast<const uint64_t*>(d.a)[slot]; valid = n > 0; break;
         case OUT_COPY_F32: bits = reinterpret_cast<const uint32_t*>(d.a)[slot]; valid = n > 0; break;

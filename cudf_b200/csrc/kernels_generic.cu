@@ -61,9 +61,14 @@ __global__ void __launch_bounds__(256) aggregate_global_kernel(const __grid_cons
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t nrows  = p.num_rows_dev ? (int64_t)*p.num_rows_dev : p.num_rows;
   for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < nrows; row += stride) {
-    uint64_t k0, k1;
-    if (!pack_key(p, row, k0, k1)) continue;
-    const uint64_t slot = find_or_insert(p.table, k0, k1);
+    uint64_t k0, k1, slot;
+    if (p.wide) {  // (warp-uniform) keys of more than 128 bits: slots hold row numbers
+      if (!row_hash(p, row, k0)) continue;
+      slot = find_or_insert_row(p, row, k0);
+    } else {
+      if (!pack_key(p, row, k0, k1)) continue;
+      slot = find_or_insert(p.table, k0, k1);
+    }
     if (slot == kNoSlot) return;
 #pragma unroll 1
     for (int a = 0; a < p.num_accs; ++a) apply_acc(p.acc[a], row, slot);
@@ -88,9 +93,14 @@ __global__ void __launch_bounds__(256) argrow_kernel(const __grid_constant__ Agg
 {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < p.num_rows; row += stride) {
-    uint64_t k0, k1;
-    if (!pack_key(p, row, k0, k1)) continue;
-    const uint64_t slot = find_or_insert(p.table, k0, k1);  // the key is there: pure lookup
+    uint64_t k0, k1, slot;
+    if (p.wide) {
+      if (!row_hash(p, row, k0)) continue;
+      slot = find_or_insert_row(p, row, k0);
+    } else {
+      if (!pack_key(p, row, k0, k1)) continue;
+      slot = find_or_insert(p.table, k0, k1);  // the key is there: pure lookup
+    }
     if (slot == kNoSlot) return;
 #pragma unroll 1
     for (int a = 0; a < p.num_accs; ++a) {
@@ -128,7 +138,8 @@ __global__ void __launch_bounds__(256) estimate_kernel(const __grid_constant__ A
   const int64_t t   = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t row = t * step;
   uint64_t k0 = 0, k1 = 0;
-  const bool live = t < sample_rows && row < p.num_rows && pack_key(p, row, k0, k1);
+  // (wide keys: the 64-bit row hash stands for the key -- the count of distinct hashes is the estimate)
+  const bool live = t < sample_rows && row < p.num_rows && (p.wide ? row_hash(p, row, k0) : pack_key(p, row, k0, k1));
   // per-warp reductions first: one atomic per warp instead of one per sampled row
   unsigned long long kimg = live && p.table.key_words == 1 ? (unsigned long long)(k0 ^ key_flip) : 0ull;
   unsigned long long mag  = 0;

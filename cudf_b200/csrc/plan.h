@@ -53,6 +53,7 @@ struct Plan {
   bool include_null_keys = false;
   bool skip_null_keys = false;
   int key_words = 1;
+  bool wide = false;                    // key image wider than 128 bits: row-number slots, generic kernels only (groupby.cu)
   std::vector<KeyPlan> keys;
   std::vector<ValuePlan> values;
   std::vector<AccPlan> accs;

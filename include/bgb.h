@@ -154,7 +154,12 @@ int32_t bgb_target_type(int32_t values_type_id, int32_t kind);
 
 /* Phase 1: hash rows, aggregate into the group table, compact, count groups.
  * Waits on `stream` once to read *num_groups back (the reference also learns the group count on the host,
- * hash/output_utils.cu:145-147). keys/requests must stay alive until emit. */
+ * hash/output_utils.cu:145-147). keys/requests must stay alive until emit.
+ * Keys: up to 8 fixed-width columns of any total width. Images of at most 128 bits are packed (and range-compressed into one
+ * word when the exact column ranges allow it); wider ones keep the ROW NUMBER of each group's first row in the table and
+ * compare rows in the caller's key columns -- the reference's scheme for every key (hash/compute_groupby.cu:79-104) -- on the
+ * generic kernels only (path "global+rowkeys"; force_path other than 0 / 1 is then BGB_UNSUPPORTED; emit gathers the output keys
+ * from the key columns, which is why they must still be alive). */
 int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys,
                       const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
                       const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups);
@@ -290,11 +295,15 @@ int bgb_finalize_moments(int32_t kind, int32_t ddof, const bgb_column_view* sum,
  * Every rank owns an exchange buffer (bgb_peer_create) that its peers map through CUDA IPC (bgb_peer_export /
  * bgb_peer_attach; the 64-byte handles travel through whatever bootstrap channel the host layer has - torch.distributed
  * all_gather_object in cudf_b200/distributed.py). bgb_groupby_build_peer then (1) aggregates this rank's rows with the
- * single-GPU path, (2) writes one record per local group straight into the OWNER rank's buffer over NVLink (P2P stores;
- * owner = hash2(key) % world, as bgb_partition_by_key_hash), (3) publishes the per-destination counts and the step's
- * epoch with system-scope release stores, (4) waits for every source's epoch, and (5) merges the received records into
- * the final table (SUM of sums, SUM of counts, MIN of mins, MAX of maxes, PRODUCT of products - the merges of
- * cpp/src/groupby/streaming_groupby/merge.cu:30-144) before compaction. The handle it returns is used exactly like
+ * single-GPU path and (2) writes one record per local group straight into the OWNER rank's buffer over NVLink (P2P stores;
+ * owner = hash2(key) % world, as bgb_partition_by_key_hash) -- on the records-form path both happen in ONE kernel: every
+ * table slice a CTA finishes is flushed to its owners from shared memory (path suffix "+peer-fused"), otherwise a scatter
+ * kernel walks the local groups ("+peer") -- (3) publishes the per-destination counts and the step's epoch with system-scope
+ * release stores, (4) waits for every source's epoch, and (5) merges the received records (SUM of sums, SUM of counts, MIN of
+ * mins, MAX of maxes, PRODUCT of products - the merges of cpp/src/groupby/streaming_groupby/merge.cu:30-144): through the same
+ * slice kernels with dense output when the records have one key word and at most three cells ("+slices"), else into an HBM
+ * table that is then compacted. A rank whose step fails tells its peers (BGB_PEER_ABORTED on their side) so that nobody waits
+ * for the timeout. The handle it returns is used exactly like
  * bgb_groupby_build's (result_info / emit / destroy) and holds the groups THIS rank owns; MEAN/M2/VARIANCE/STD are
  * finalised by emit from merged SUM/SUMSQ/COUNT cells, so integer inputs give bit-identical results on any world size.
  * The call is COLLECTIVE: every rank of the context must make it, with the same key/request shapes. Regions are

@@ -112,10 +112,10 @@ def test_forced_paths_keep_the_caller_layout():
     assert path == "global", path
 
 
-def test_three_wide_columns_whose_ranges_do_not_fit_are_unsupported():
-    import cudf_b200 as cb
+def test_three_wide_columns_whose_ranges_do_not_fit_take_the_row_number_table():
+    # 192 bits of key whose ranges need 189: no packed image; the table then holds row numbers (tests/test_gpu_wide_keys.py)
     rng = np.random.default_rng(48)
     ks = [H(rng.integers(-(1 << 62), 1 << 62, N).astype(np.int64)) for _ in range(3)]
     v = H(rng.integers(-9, 9, N).astype(np.int64))
-    with pytest.raises(cb.UnsupportedError):
-        gpu_util.run_gpu(ks, [v], [(0, "sum", 1)])
+    G, path = _check(ks, [v], [(0, "sum", 1)], name="3 x int64 full range", repacked=False)
+    assert G == N and path == "global+rowkeys", path
