@@ -581,6 +581,17 @@ def _nccl_worker(rank, world, port, outdir):
             cols = [kt.columns()[0].to_numpy()] + [c.to_numpy() for c in rts[0].columns()]
             np.savez(os.path.join(outdir, f"{exchange}_r{rank}.npz"), **{f"d{i}": c[0] for i, c in enumerate(cols)},
                      **{f"v{i}": c[1] for i, c in enumerate(cols)})
+        # the fused exchange (slices write into the other PROCESS's region through the CUDA IPC mapping) + the slice merge
+        os.environ["BGB_HC_MERGE_MIN"] = "1000"
+        keys, values = int_shards(world, 1_500_000, 700_000, seed=21)[rank]
+        dk = [cb.Column.from_numpy(k.data, k.valid, device=f"cuda:{rank}") for k in keys]
+        dv = [cb.Column.from_numpy(v.data, v.valid, device=f"cuda:{rank}") for v in values]
+        dgb = D.DistributedGroupBy(cb.Table(dk), exchange="peer", options={"force_path": 7}, peer_region_bytes=64 << 20)
+        for step in range(2):  # twice: both parities of the double-buffered regions
+            kt, rts = dgb.aggregate([cb.GroupByRequest(dv[0], [agg.sum(), agg.count()])])
+        assert dgb.last_path == "bucketed+peer-fused+slices", dgb.last_path
+        cols = [kt.columns()[0].to_numpy()] + [c.to_numpy() for c in rts[0].columns()]
+        np.savez(os.path.join(outdir, f"fused_r{rank}.npz"), **{f"d{i}": c[0] for i, c in enumerate(cols)}, **{f"v{i}": c[1] for i, c in enumerate(cols)})
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -613,3 +624,12 @@ def test_nccl_two_gpus(tmp_path):
                 np.testing.assert_allclose(d[v], ao[i][0][ao[i][1]], rtol=1e-9, atol=0)
             else:
                 np.testing.assert_array_equal(d[v], ao[i][0][ao[i][1]])
+    keys, values = concat_shards(int_shards(world, 1_500_000, 700_000, seed=21))
+    Go, ko, ao = orc.groupby(keys, values, [(0, "sum", 0), (0, "count_valid", 0)], threads=4)
+    parts = [np.load(tmp_path / f"fused_r{r}.npz") for r in range(world)]
+    k = np.concatenate([p["d0"] for p in parts])
+    order = np.argsort(k, kind="stable")
+    assert len(k) == Go
+    np.testing.assert_array_equal(k[order], ko[0][0])
+    for i in range(2):
+        np.testing.assert_array_equal(np.concatenate([p[f"d{i + 1}"] for p in parts])[order], ao[i][0])
