@@ -1141,6 +1141,7 @@ extern "C" int bgb_groupby_build(const bgb_column_view* keys, int32_t num_keys, 
                                  const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
                                  const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups)
 {
+  NvtxRange nvtx_call("bgb_groupby_build");
   return build_local(keys, num_keys, include_null_keys, requests, num_requests, stream, alloc, options, out_handle, num_groups);
 }
 
@@ -1174,6 +1175,7 @@ extern "C" const char* bgb_groupby_path(const bgb_groupby* h) { return h ? h->pa
 
 extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bgb_mutable_column* out_results, void* stream)
 {
+  NvtxRange nvtx_call("bgb_groupby_emit");
   if (!h) return set_error(BGB_INVALID_ARGUMENT, "null handle");
   const Plan& pl = h->plan;
   const std::vector<KeyPlan>& ekeys = h->emit_keys.empty() ? pl.keys : h->emit_keys;  // repacked: the caller's columns
@@ -1370,6 +1372,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
                                       const bgb_request* requests, int32_t num_requests, void* stream, const bgb_allocator* alloc,
                                       const bgb_options* options, bgb_groupby** out_handle, int32_t* num_groups)
 {
+  NvtxRange nvtx_call("bgb_groupby_build_peer");
   if (!peer) return set_error(BGB_INVALID_ARGUMENT, "null peer context");
   for (int r = 0; r < peer->world; ++r)
     if (!peer->peer_buffer[r]) return set_error(BGB_INVALID_ARGUMENT, "rank %d is not attached", r);
@@ -1703,6 +1706,7 @@ static int stream_fold(bgb_stream* st, const TableDesc& src, const uint32_t* src
 
 extern "C" int bgb_stream_aggregate(bgb_stream* st, const bgb_column_view* columns, int32_t num_columns, void* stream, const bgb_options* options)
 {
+  NvtxRange nvtx_call("bgb_stream_aggregate");
   if (!st || (num_columns > 0 && !columns)) return set_error(BGB_INVALID_ARGUMENT, "null argument");
   if (st->invalidated) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: the object was invalidated by a failed aggregate() / merge() and cannot be used");
   std::vector<bgb_column_view> keys;
@@ -1769,6 +1773,7 @@ extern "C" int bgb_stream_aggregate(bgb_stream* st, const bgb_column_view* colum
 
 extern "C" int bgb_stream_merge(bgb_stream* st, const bgb_stream* other, void* stream)
 {
+  NvtxRange nvtx_call("bgb_stream_merge");
   if (!st || !other) return set_error(BGB_INVALID_ARGUMENT, "null argument");
   if (st->invalidated) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: the object was invalidated by a failed aggregate() / merge() and cannot be used");
   if (other->invalidated) return set_error(BGB_INVALID_ARGUMENT, "streaming groupby: the other object was invalidated by a failed aggregate() / merge()");
@@ -1797,6 +1802,7 @@ extern "C" int bgb_stream_distinct_keys(const bgb_stream* st, int32_t* out)
 
 extern "C" int bgb_stream_finalize(const bgb_stream* st, void* stream, bgb_groupby** out_handle, int32_t* num_groups)
 {
+  NvtxRange nvtx_call("bgb_stream_finalize");
   if (!st || !out_handle || !num_groups) return set_error(BGB_INVALID_ARGUMENT, "null argument");
   *out_handle = nullptr;
   *num_groups = 0;

@@ -11,6 +11,7 @@
 
 #include "errors.h"
 #include "plan.h"
+#include "nvtx.h"
 #include "pool.h"
 
 using namespace bgb;
@@ -130,6 +131,7 @@ extern "C" int bgb_groupby_host(const bgb_column_view* host_keys, int32_t num_ke
                                 const bgb_request* host_requests, int32_t num_requests, const bgb_options* options,
                                 int32_t* num_groups, bgb_host_column** out_keys, bgb_host_column** out_results, int32_t* num_results)
 {
+  bgb::NvtxRange nvtx_call("bgb_groupby_host");
   if (!num_groups || !out_keys || !out_results || !num_results) return set_error(BGB_INVALID_ARGUMENT, "null output pointer");
   *num_groups = 0; *out_keys = nullptr; *out_results = nullptr; *num_results = 0;
   if (num_keys <= 0 || !host_keys) return set_error(BGB_INVALID_ARGUMENT, "groupby needs at least one key column");

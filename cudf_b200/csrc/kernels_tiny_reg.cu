@@ -9,6 +9,8 @@
 // a CTA that meets more than G keys raises status[3] and the host takes another path.
 // Reference counterpart: the replicated shared-memory accumulators for low cardinalities,
 // /root/reference/cpp/src/groupby/hash/compute_shared_memory_aggs.cu:260-353.
+#include <algorithm>
+
 #include "device_utils.cuh"
 #include "kernels_tiny.h"
 
@@ -125,7 +127,10 @@ __device__ __forceinline__ void tile_loads(const RegParams& p, int64_t wb, int l
   }
 }
 
-template <int G, int NC, bool SQ, bool F64, int W>
+// MASKS: some key or value column carries a null mask (else every validity test, null counter and zeroing select is compiled
+// out: they were ~40 % of the instructions of the mask-free Q1 shape). K32: the packed key image fits 32 bits (one compare per
+// cached group key instead of two).
+template <int G, int NC, bool SQ, bool F64, int W, bool MASKS, bool K32>
 __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant__ RegParams p)
 {
   constexpr int KCMAX = W == 8 ? 1 : W == 4 ? 2 : 4;  // the packed key image is at most 64 bits
@@ -156,10 +161,10 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
   }
   bool abort_seen = false;
   bool any_vmask  = false;
+  if (MASKS) {
 #pragma unroll
-  for (int c = 0; c < NC; ++c) any_vmask |= p.vmask[c] != nullptr;
-  bool any_mask = any_vmask;
-  for (int c = 0; c < p.a.num_key_cols; ++c) any_mask |= p.a.kc[c].mask != nullptr;
+    for (int c = 0; c < NC; ++c) any_vmask |= p.vmask[c] != nullptr;
+  }
 
   const int64_t n      = p.a.num_rows;
   const int lane       = threadIdx.x & 31;
@@ -173,10 +178,9 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
     uint64_t kr[kPairs][KCMAX][2], val[NC][kPairs][2];
     uint32_t km[kPairs][KCMAX], vm[NC][kPairs];
     if (wb + kWarpTile <= n) {  // warp-uniform; only the last tile takes the guarded element loads
-      if (any_mask) tile_loads<NC, W, KCMAX, true, true>(p, wb, lane, n, kr, km, val, vm);
-      else tile_loads<NC, W, KCMAX, true, false>(p, wb, lane, n, kr, km, val, vm);
+      tile_loads<NC, W, KCMAX, true, MASKS>(p, wb, lane, n, kr, km, val, vm);
     } else {
-      tile_loads<NC, W, KCMAX, false, true>(p, wb, lane, n, kr, km, val, vm);
+      tile_loads<NC, W, KCMAX, false, MASKS>(p, wb, lane, n, kr, km, val, vm);
     }
     // ---- phase 2: packed key images and validity bits
     uint64_t img[kPairs][2];
@@ -192,8 +196,8 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
           const KeyColDesc& kc = p.a.kc[c];
           uint64_t e0, e1;
           split_pair<W>(kr[j][c], e0, e1);
-          const uint32_t kv = km[j][c] & 3u;
-          if (kv != 3u) {
+          const uint32_t kv = MASKS ? (km[j][c] & 3u) : 3u;
+          if (MASKS && kv != 3u) {
             if (p.a.skip_null_keys) ok[j] &= kv;  // EXCLUDE: the row is dropped
             else {                                 // INCLUDE: the null flag is part of the key, value bits stay zero
               if (!(kv & 1u)) { e0 = 0; img[j][0] |= 1ull << kc.null_bit; }
@@ -204,8 +208,10 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
           img[j][1] |= e1 << kc.shift;
         }
       }
+      if (MASKS) {
 #pragma unroll
-      for (int c = 0; c < NC; ++c) ok[j] |= (vm[c][j] & 3u) << (2 * c + 2);
+        for (int c = 0; c < NC; ++c) ok[j] |= (vm[c][j] & 3u) << (2 * c + 2);
+      }
     }
     // ---- rows into the register accumulators
 #pragma unroll
@@ -216,7 +222,7 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
         const unsigned long long k = img[j][h];
         int gid = -1;
 #pragma unroll
-        for (int g = 0; g < G; ++g) gid = (gk[g] == k) ? g : gid;
+        for (int g = 0; g < G; ++g) gid = (K32 ? (uint32_t)gk[g] == (uint32_t)k : gk[g] == k) ? g : gid;  // (K32: unused gk[] are all ones in the low word too)
         if (k == kEmpty) gid = -1;  // the all-ones image equals the 'unused' marker of gk[]: never a cached group (-> abort below)
         if (usable && gid < 0) {  // first rows only: learn the key, then refresh the cached group keys
           gid = (k == kEmpty) ? -2 : reg_insert_key(k, s_dict_key, s_dict_gid, s_group_key, &s_groups, G);
@@ -233,7 +239,7 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
           vz[c] = A::from_bits(val[c][j][h]);
-          if (any_vmask && !((ok[j] >> (2 * c + 2 + h)) & 1u)) vz[c] = (T)0;  // null source skipped (device_aggregators.cuh:434-436)
+          if (MASKS && any_vmask && !((ok[j] >> (2 * c + 2 + h)) & 1u)) vz[c] = (T)0;  // null source skipped (device_aggregators.cuh:434-436)
         }
 #pragma unroll
         for (int g = 0; g < G; ++g) {
@@ -246,7 +252,7 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
             if (SQ) sq[g][c] += vg * vg;
           }
         }
-        if (any_vmask) {  // warp-uniform: columns without a mask never pay for null counting
+        if (MASKS && any_vmask) {  // warp-uniform: columns without a mask never pay for null counting
 #pragma unroll
           for (int c = 0; c < NC; ++c) {
             const bool is_null = !((ok[j] >> (2 * c + 2 + h)) & 1u);
@@ -316,17 +322,34 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
   }
 }
 
-template <int G, int NC, bool SQ, bool F64, int W>
-cudaError_t launch_w(const RegParams& rp, int num_sms, cudaStream_t s)
+template <int G, int NC, bool SQ, bool F64, int W, bool MASKS, bool K32>
+cudaError_t launch_wmk(const RegParams& rp, int num_sms, cudaStream_t s)
 {
   int per_sm = 1;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, agg_tiny_reg_kernel<G, NC, SQ, F64, W>, kRT, 0);
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, agg_tiny_reg_kernel<G, NC, SQ, F64, W, MASKS, K32>, kRT, 0);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   const int64_t tiles = (rp.a.num_rows + (int64_t)kWarpTile * (kRT / 32) - 1) / ((int64_t)kWarpTile * (kRT / 32));
   const int64_t grid  = tiles < (int64_t)num_sms * per_sm ? tiles : (int64_t)num_sms * per_sm;
-  agg_tiny_reg_kernel<G, NC, SQ, F64, W><<<(int)grid, kRT, 0, s>>>(rp);
+  agg_tiny_reg_kernel<G, NC, SQ, F64, W, MASKS, K32><<<(int)grid, kRT, 0, s>>>(rp);
   return note_launch();
+}
+
+template <int G, int NC, bool SQ, bool F64, int W>
+cudaError_t launch_w(const RegParams& rp, int num_sms, cudaStream_t s)
+{
+  bool masks = false;
+  int key_bits = 0;
+  for (int c = 0; c < rp.a.num_key_cols; ++c) {
+    masks |= rp.a.kc[c].mask != nullptr;
+    key_bits = std::max(key_bits, std::max((int)rp.a.kc[c].shift + 8 * rp.a.kc[c].width, (int)rp.a.kc[c].null_bit + 1));
+  }
+  for (int c = 0; c < NC; ++c) masks |= rp.vmask[c] != nullptr;
+  // (the all-ones image of a 32-bit-or-narrower key cannot occur when the image has fewer than 32 bits; at exactly 32 it could
+  //  alias the 'unused' marker in the low word, so K32 wants strictly fewer)
+  const bool k32 = W < 8 && key_bits < 32;
+  if (masks) return launch_wmk<G, NC, SQ, F64, W, true, false>(rp, num_sms, s);
+  return k32 ? launch_wmk<G, NC, SQ, F64, W, false, true>(rp, num_sms, s) : launch_wmk<G, NC, SQ, F64, W, false, false>(rp, num_sms, s);
 }
 
 template <int G, int NC, bool SQ, bool F64>

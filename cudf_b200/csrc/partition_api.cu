@@ -9,6 +9,7 @@
 #include "device_utils.cuh"
 #include "kernels_partition.h"
 #include "plan.h"
+#include "nvtx.h"
 #include "pool.h"
 
 using namespace bgb;
@@ -151,6 +152,7 @@ extern "C" int bgb_bytes_to_bitmask(const uint8_t* valid_bytes, int64_t n, uint3
 extern "C" int bgb_partition_by_key_hash(const bgb_column_view* keys, int32_t num_keys, const bgb_column_view* cols, int32_t num_cols,
                                          int32_t num_parts, bgb_mutable_column* out_cols, int32_t* part_offsets_host, void* stream)
 {
+  bgb::NvtxRange nvtx_call("bgb_partition_by_key_hash");
   if (num_parts < 1 || num_parts > 4096) return set_error(BGB_INVALID_ARGUMENT, "num_parts must be in [1, 4096]");
   if (num_cols < 0 || num_cols > kMaxPartValues || (num_cols > 0 && (!cols || !out_cols)))
     return set_error(BGB_INVALID_ARGUMENT, "between 0 and %d columns can be permuted in one call", kMaxPartValues);
@@ -249,6 +251,7 @@ extern "C" int bgb_hash_partition(const bgb_column_view* input, int32_t num_cols
                                   int32_t num_partitions, int32_t hash_function, uint32_t seed, bgb_mutable_column* out_cols,
                                   int32_t* offsets_host, void* stream)
 {
+  bgb::NvtxRange nvtx_call("bgb_hash_partition");
   if (hash_function != BGB_HASH_IDENTITY && hash_function != BGB_HASH_MURMUR3)
     return set_error(BGB_INVALID_ARGUMENT, "Unsupported hash function in hash_partition");
   if (num_cols < 0 || num_hash_cols < 0 || (num_cols > 0 && !input) || (num_hash_cols > 0 && !columns_to_hash))

@@ -6,6 +6,8 @@
 #include <mutex>
 #include <vector>
 
+#include "nvtx.h"
+
 namespace bgb {
 
 // Events are recycled per device: cudaEventCreate/Destroy cost several microseconds each, and a profiled call brackets
@@ -40,15 +42,23 @@ struct Profiler {
   cudaStream_t stream = nullptr;
   int dev = -1;
 
+  bool ranged = false;  // an NVTX range of a kernel phase is open
+
   void begin(const char* name)
   {
+    nvtx_push(name);
+    ranged = true;
     if (!on) return;
     if (dev < 0) cudaGetDevice(&dev);
     Entry p{name, EventPool::get().acquire(dev), EventPool::get().acquire(dev), -1.f};
     cudaEventRecord(p.e0, stream);
     entries.push_back(p);
   }
-  void end() { if (on && !entries.empty()) cudaEventRecord(entries.back().e1, stream); }
+  void end()
+  {
+    if (ranged) { nvtx_pop(); ranged = false; }
+    if (on && !entries.empty()) cudaEventRecord(entries.back().e1, stream);
+  }
   void resolve()  // call after the stream has been synchronised
   {
     for (Entry& p : entries)
@@ -57,7 +67,7 @@ struct Profiler {
         EventPool::get().release(dev, p.e0); EventPool::get().release(dev, p.e1); p.e0 = p.e1 = nullptr;
       }
   }
-  ~Profiler() { for (Entry& p : entries) if (p.e0) { EventPool::get().release(dev, p.e0); EventPool::get().release(dev, p.e1); } }
+  ~Profiler() { if (ranged) nvtx_pop(); for (Entry& p : entries) if (p.e0) { EventPool::get().release(dev, p.e0); EventPool::get().release(dev, p.e1); } }
 };
 
 }  // namespace bgb
