@@ -18,7 +18,7 @@ namespace bgb {
 namespace {
 
 constexpr int kRT        = 128;  // threads per CTA (111-183 registers per thread: 2-4 CTAs per SM)
-constexpr int kPairs     = 2;    // row pairs per lane per iteration (warp tile = 128 rows). Measured on Q1: 4 pairs 6.7 ms (186 registers, 8 warps/SM), 2 pairs 4.6 ms, 1 pair 5.6 ms
+constexpr int kPairs     = 2;    // row pairs per lane per iteration (warp tile = 128 rows). Measured on Q1 (r02, mask-free specialisation): 2 pairs 2.81 ms (120 registers), 4 pairs 3.11 ms (144)
 constexpr int kWarpTile  = 64 * kPairs;
 constexpr int kDictSlots = 64;
 
@@ -127,10 +127,83 @@ __device__ __forceinline__ void tile_loads(const RegParams& p, int64_t wb, int l
   }
 }
 
+// A full tile of the mask-free shape with a key image of fewer than 32 bits in NK columns of W bytes (BASELINE configs[3]: two int8
+// keys): ~55 instructions per row instead of ~105 for the general body below (ncu r02: per-column uniform predicates for up to
+// four key columns, 64-bit image assembly, 64-bit row-range tests and the gid select chain were half of the instruction stream).
+// A row's group is found as G 32-bit compares that ARE the select predicates of the accumulate step; a row that hits no cached
+// group key goes through the CAS dictionary (first rows of a CTA only).
+template <int G, int NC, bool SQ, bool F64, int W, int NK>
+__device__ __forceinline__ void lean_tile(const RegParams& p, int64_t wb, int lane, unsigned long long (&gk)[G],
+                                          typename Arith<F64>::T (&sum)[G][NC], typename Arith<F64>::T (&sq)[G][NC], int (&cnt_all)[G],
+                                          bool& abort_seen, unsigned long long* s_dict_key, int* s_dict_gid, unsigned long long* s_group_key,
+                                          int* s_groups)
+{
+  using A = Arith<F64>;
+  using T = typename A::T;
+  static_assert(W == 1 || W == 2, "pairs of 1- or 2-byte key elements");
+  uint32_t kraw[kPairs][NK];
+  uint64_t val[NC][kPairs][2];
+#pragma unroll
+  for (int j = 0; j < kPairs; ++j) {
+    const int64_t row = wb + 64 * j + 2 * lane;
+#pragma unroll
+    for (int c = 0; c < NK; ++c) {
+      const KeyColDesc& kc = p.a.kc[c];
+      const int64_t idx    = (int64_t)kc.offset + row;
+      kraw[j][c] = W == 1 ? (uint32_t)__ldg(reinterpret_cast<const uint16_t*>(kc.data + idx)) : __ldg(reinterpret_cast<const uint32_t*>(kc.data + 2 * idx));
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.vdata[c] + 8 * ((int64_t)p.voffset[c] + row)));
+      val[c][j][0]  = (uint64_t)v.x | ((uint64_t)v.y << 32);
+      val[c][j][1]  = (uint64_t)v.z | ((uint64_t)v.w << 32);
+    }
+  }
+  uint32_t gk32[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) gk32[g] = (uint32_t)gk[g];  // (unused entries are all ones: no image of fewer than 32 bits equals them)
+#pragma unroll
+  for (int j = 0; j < kPairs; ++j) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      uint32_t img = 0;
+#pragma unroll
+      for (int c = 0; c < NK; ++c) img |= ((kraw[j][c] >> (8 * W * h)) & ((1u << (8 * W)) - 1)) << p.a.kc[c].shift;
+      bool hit[G];
+      bool any = false;
+#pragma unroll
+      for (int g = 0; g < G; ++g) { hit[g] = img == gk32[g]; any |= hit[g]; }
+      if (!any) {  // first rows of the CTA: learn the key, refresh the cached group keys
+        const int gid = reg_insert_key((uint64_t)img, s_dict_key, s_dict_gid, s_group_key, s_groups, G);
+        if (gid < 0) abort_seen = true;
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          gk[g]   = *reinterpret_cast<volatile unsigned long long*>(&s_group_key[g]);
+          gk32[g] = (uint32_t)gk[g];
+          hit[g]  = gid == g;
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        const T v = A::from_bits(val[c][j][h]);
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          const T vg = hit[g] ? v : (T)0;  // select on the INPUT, unconditional adds (see the general body)
+          sum[g][c] += vg;
+          if (SQ) sq[g][c] += vg * vg;
+        }
+      }
+#pragma unroll
+      for (int g = 0; g < G; ++g) cnt_all[g] += hit[g] ? 1 : 0;
+    }
+  }
+}
+
 // MASKS: some key or value column carries a null mask (else every validity test, null counter and zeroing select is compiled
 // out: they were ~40 % of the instructions of the mask-free Q1 shape). K32: the packed key image fits 32 bits (one compare per
 // cached group key instead of two).
-template <int G, int NC, bool SQ, bool F64, int W, bool MASKS, bool K32>
+// NK > 0 (implies !MASKS, K32, W <= 2): exactly NK key columns -- full tiles run lean_tile, only the last tile the general body.
+template <int G, int NC, bool SQ, bool F64, int W, bool MASKS, bool K32, int NK>
 __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant__ RegParams p)
 {
   constexpr int KCMAX = W == 8 ? 1 : W == 4 ? 2 : 4;  // the packed key image is at most 64 bits
@@ -175,6 +248,12 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
     //      earlier forms decoded each key right after its load, or kept each load behind its own uniform branch, and
     //      ncu showed eight serialised long-scoreboard stalls per tile (12-15 ms on Q1). Lane l owns the row pairs
     //      {wb + 64 j + 2 l, +1}; a pair of W-byte keys is one 2W-byte load, a pair of 8-byte values one LDG.128.
+    if constexpr (NK > 0 && W <= 2) {
+      if (wb + kWarpTile <= n) {
+        lean_tile<G, NC, SQ, F64, W, NK>(p, wb, lane, gk, sum, sq, cnt_all, abort_seen, s_dict_key, s_dict_gid, s_group_key, &s_groups);
+        continue;
+      }
+    }
     uint64_t kr[kPairs][KCMAX][2], val[NC][kPairs][2];
     uint32_t km[kPairs][KCMAX], vm[NC][kPairs];
     if (wb + kWarpTile <= n) {  // warp-uniform; only the last tile takes the guarded element loads
@@ -322,16 +401,16 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
   }
 }
 
-template <int G, int NC, bool SQ, bool F64, int W, bool MASKS, bool K32>
+template <int G, int NC, bool SQ, bool F64, int W, bool MASKS, bool K32, int NK = 0>
 cudaError_t launch_wmk(const RegParams& rp, int num_sms, cudaStream_t s)
 {
   int per_sm = 1;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, agg_tiny_reg_kernel<G, NC, SQ, F64, W, MASKS, K32>, kRT, 0);
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, agg_tiny_reg_kernel<G, NC, SQ, F64, W, MASKS, K32, NK>, kRT, 0);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   const int64_t tiles = (rp.a.num_rows + (int64_t)kWarpTile * (kRT / 32) - 1) / ((int64_t)kWarpTile * (kRT / 32));
   const int64_t grid  = tiles < (int64_t)num_sms * per_sm ? tiles : (int64_t)num_sms * per_sm;
-  agg_tiny_reg_kernel<G, NC, SQ, F64, W, MASKS, K32><<<(int)grid, kRT, 0, s>>>(rp);
+  agg_tiny_reg_kernel<G, NC, SQ, F64, W, MASKS, K32, NK><<<(int)grid, kRT, 0, s>>>(rp);
   return note_launch();
 }
 
@@ -347,9 +426,17 @@ cudaError_t launch_w(const RegParams& rp, int num_sms, cudaStream_t s)
   for (int c = 0; c < NC; ++c) masks |= rp.vmask[c] != nullptr;
   // (the all-ones image of a 32-bit-or-narrower key cannot occur when the image has fewer than 32 bits; at exactly 32 it could
   //  alias the 'unused' marker in the low word, so K32 wants strictly fewer)
-  const bool k32 = W < 8 && key_bits < 32;
+  const bool k32 = W <= 2 && key_bits < 32;
   if (masks) return launch_wmk<G, NC, SQ, F64, W, true, false>(rp, num_sms, s);
-  return k32 ? launch_wmk<G, NC, SQ, F64, W, false, true>(rp, num_sms, s) : launch_wmk<G, NC, SQ, F64, W, false, false>(rp, num_sms, s);
+  if constexpr (W == 1) {
+    if (k32 && rp.a.num_key_cols == 1) return launch_wmk<G, NC, SQ, F64, W, false, true, 1>(rp, num_sms, s);
+    if (k32 && rp.a.num_key_cols == 2) return launch_wmk<G, NC, SQ, F64, W, false, true, 2>(rp, num_sms, s);
+    if (k32 && rp.a.num_key_cols == 3) return launch_wmk<G, NC, SQ, F64, W, false, true, 3>(rp, num_sms, s);
+  }
+  if constexpr (W == 2) {
+    if (k32 && rp.a.num_key_cols == 1) return launch_wmk<G, NC, SQ, F64, W, false, true, 1>(rp, num_sms, s);
+  }
+  return launch_wmk<G, NC, SQ, F64, W, false, false>(rp, num_sms, s);
 }
 
 template <int G, int NC, bool SQ, bool F64>
