@@ -132,17 +132,14 @@ __device__ __forceinline__ void tile_loads(const RegParams& p, int64_t wb, int l
 // four key columns, 64-bit image assembly, 64-bit row-range tests and the gid select chain were half of the instruction stream).
 // A row's group is found as G 32-bit compares that ARE the select predicates of the accumulate step; a row that hits no cached
 // group key goes through the CAS dictionary (first rows of a CTA only).
-template <int G, int NC, bool SQ, bool F64, int W, int NK>
-__device__ __forceinline__ void lean_tile(const RegParams& p, int64_t wb, int lane, unsigned long long (&gk)[G],
-                                          typename Arith<F64>::T (&sum)[G][NC], typename Arith<F64>::T (&sq)[G][NC], int (&cnt_all)[G],
-                                          bool& abort_seen, unsigned long long* s_dict_key, int* s_dict_gid, unsigned long long* s_group_key,
-                                          int* s_groups)
+template <int NC, int NK> struct LeanRaw {
+  uint32_t k[kPairs][NK];
+  uint4 v[NC][kPairs];
+};
+template <int NC, int W, int NK>
+__device__ __forceinline__ void lean_load(const RegParams& p, int64_t wb, int lane, LeanRaw<NC, NK>& r)
 {
-  using A = Arith<F64>;
-  using T = typename A::T;
   static_assert(W == 1 || W == 2, "pairs of 1- or 2-byte key elements");
-  uint32_t kraw[kPairs][NK];
-  uint64_t val[NC][kPairs][2];
 #pragma unroll
   for (int j = 0; j < kPairs; ++j) {
     const int64_t row = wb + 64 * j + 2 * lane;
@@ -150,51 +147,96 @@ __device__ __forceinline__ void lean_tile(const RegParams& p, int64_t wb, int la
     for (int c = 0; c < NK; ++c) {
       const KeyColDesc& kc = p.a.kc[c];
       const int64_t idx    = (int64_t)kc.offset + row;
-      kraw[j][c] = W == 1 ? (uint32_t)__ldg(reinterpret_cast<const uint16_t*>(kc.data + idx)) : __ldg(reinterpret_cast<const uint32_t*>(kc.data + 2 * idx));
+      r.k[j][c] = W == 1 ? (uint32_t)__ldg(reinterpret_cast<const uint16_t*>(kc.data + idx)) : __ldg(reinterpret_cast<const uint32_t*>(kc.data + 2 * idx));
     }
 #pragma unroll
-    for (int c = 0; c < NC; ++c) {
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.vdata[c] + 8 * ((int64_t)p.voffset[c] + row)));
-      val[c][j][0]  = (uint64_t)v.x | ((uint64_t)v.y << 32);
-      val[c][j][1]  = (uint64_t)v.z | ((uint64_t)v.w << 32);
-    }
+    for (int c = 0; c < NC; ++c) r.v[c][j] = __ldg(reinterpret_cast<const uint4*>(p.vdata[c] + 8 * ((int64_t)p.voffset[c] + row)));
   }
+}
+template <int G, int NC, bool SQ, bool F64, int W, int NK>
+__device__ __forceinline__ void lean_compute(const RegParams& p, const LeanRaw<NC, NK>& r, unsigned long long (&gk)[G],
+                                             typename Arith<F64>::T (&sum)[G][NC], typename Arith<F64>::T (&sq)[G][NC], int (&cnt_all)[G],
+                                             bool& abort_seen, unsigned long long* s_dict_key, int* s_dict_gid, unsigned long long* s_group_key,
+                                             int* s_groups)
+{
+  using A = Arith<F64>;
+  using T = typename A::T;
   uint32_t gk32[G];
 #pragma unroll
   for (int g = 0; g < G; ++g) gk32[g] = (uint32_t)gk[g];  // (unused entries are all ones: no image of fewer than 32 bits equals them)
+  uint32_t img[kPairs][2];
+  bool miss = false;
 #pragma unroll
   for (int j = 0; j < kPairs; ++j) {
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      uint32_t img = 0;
+      uint32_t m = 0;
 #pragma unroll
-      for (int c = 0; c < NK; ++c) img |= ((kraw[j][c] >> (8 * W * h)) & ((1u << (8 * W)) - 1)) << p.a.kc[c].shift;
-      bool hit[G];
+      for (int c = 0; c < NK; ++c) m |= ((r.k[j][c] >> (8 * W * h)) & ((1u << (8 * W)) - 1)) << p.a.kc[c].shift;
+      img[j][h] = m;
       bool any = false;
 #pragma unroll
-      for (int g = 0; g < G; ++g) { hit[g] = img == gk32[g]; any |= hit[g]; }
-      if (!any) {  // first rows of the CTA: learn the key, refresh the cached group keys
-        const int gid = reg_insert_key((uint64_t)img, s_dict_key, s_dict_gid, s_group_key, s_groups, G);
+      for (int g = 0; g < G; ++g) any |= m == gk32[g];
+      miss |= !any;
+    }
+  }
+  // Warp-uniform split. Steady state: every row of the tile hits a cached group key, and the G compares of a row ARE the select
+  // predicates of its accumulate step. A tile with a new key (first rows of a CTA) takes the second body, where a learning branch
+  // assigns the group: there the compiler keeps the hits as 0/1 integers (+8 instructions per row), which is why it is kept apart.
+  if (!__any_sync(0xffffffffu, miss)) {
+#pragma unroll
+    for (int j = 0; j < kPairs; ++j) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        bool hit[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) hit[g] = img[j][h] == gk32[g];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          const uint4 q = r.v[c][j];
+          const T v = A::from_bits(h == 0 ? ((uint64_t)q.x | ((uint64_t)q.y << 32)) : ((uint64_t)q.z | ((uint64_t)q.w << 32)));
+#pragma unroll
+          for (int g = 0; g < G; ++g) {
+            const T vg = hit[g] ? v : (T)0;  // select on the INPUT, unconditional adds (see the general body)
+            sum[g][c] += vg;
+            if (SQ) sq[g][c] += vg * vg;
+          }
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) cnt_all[g] += hit[g] ? 1 : 0;
+      }
+    }
+    return;
+  }
+#pragma unroll
+  for (int j = 0; j < kPairs; ++j) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      int gid = -1;
+#pragma unroll
+      for (int g = 0; g < G; ++g) gid = img[j][h] == gk32[g] ? g : gid;
+      if (gid < 0) {  // learn the key, refresh the cached group keys
+        gid = reg_insert_key((uint64_t)img[j][h], s_dict_key, s_dict_gid, s_group_key, s_groups, G);
         if (gid < 0) abort_seen = true;
 #pragma unroll
         for (int g = 0; g < G; ++g) {
           gk[g]   = *reinterpret_cast<volatile unsigned long long*>(&s_group_key[g]);
           gk32[g] = (uint32_t)gk[g];
-          hit[g]  = gid == g;
         }
       }
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
-        const T v = A::from_bits(val[c][j][h]);
+        const uint4 q = r.v[c][j];
+        const T v = A::from_bits(h == 0 ? ((uint64_t)q.x | ((uint64_t)q.y << 32)) : ((uint64_t)q.z | ((uint64_t)q.w << 32)));
 #pragma unroll
         for (int g = 0; g < G; ++g) {
-          const T vg = hit[g] ? v : (T)0;  // select on the INPUT, unconditional adds (see the general body)
+          const T vg = gid == g ? v : (T)0;
           sum[g][c] += vg;
           if (SQ) sq[g][c] += vg * vg;
         }
       }
 #pragma unroll
-      for (int g = 0; g < G; ++g) cnt_all[g] += hit[g] ? 1 : 0;
+      for (int g = 0; g < G; ++g) cnt_all[g] += gid == g ? 1 : 0;
     }
   }
 }
@@ -243,17 +285,26 @@ __global__ void __launch_bounds__(kRT) agg_tiny_reg_kernel(const __grid_constant
   const int lane       = threadIdx.x & 31;
   const int64_t warp0  = (int64_t)blockIdx.x * (kRT / 32) + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * (kRT / 32);
-  for (int64_t wb = warp0 * kWarpTile; wb < n; wb += nwarps * kWarpTile) {
+  int64_t wb_first = warp0 * kWarpTile;
+  if constexpr (NK > 0 && W <= 2) {
+    // full tiles, software-pipelined: the loads of the warp's NEXT tile are in flight while this one is accumulated (the kernel was
+    // latency-bound at 16 warps per SM with one tile of loads per warp: 48 % of the cycles had no eligible warp)
+    LeanRaw<NC, NK> cur, nxt;
+    bool have = wb_first + kWarpTile <= n;
+    if (have) lean_load<NC, W, NK>(p, wb_first, lane, cur);
+    while (have) {
+      const int64_t wn  = wb_first + nwarps * kWarpTile;
+      const bool have_n = wn + kWarpTile <= n;
+      if (have_n) lean_load<NC, W, NK>(p, wn, lane, nxt);
+      lean_compute<G, NC, SQ, F64, W, NK>(p, cur, gk, sum, sq, cnt_all, abort_seen, s_dict_key, s_dict_gid, s_group_key, &s_groups);
+      cur = nxt; wb_first = wn; have = have_n;
+    }
+  }
+  for (int64_t wb = wb_first; wb < n; wb += nwarps * kWarpTile) {
     // ---- phase 1: every load of the tile is issued before anything is decoded, in ONE basic block (tile_loads): the
     //      earlier forms decoded each key right after its load, or kept each load behind its own uniform branch, and
     //      ncu showed eight serialised long-scoreboard stalls per tile (12-15 ms on Q1). Lane l owns the row pairs
     //      {wb + 64 j + 2 l, +1}; a pair of W-byte keys is one 2W-byte load, a pair of 8-byte values one LDG.128.
-    if constexpr (NK > 0 && W <= 2) {
-      if (wb + kWarpTile <= n) {
-        lean_tile<G, NC, SQ, F64, W, NK>(p, wb, lane, gk, sum, sq, cnt_all, abort_seen, s_dict_key, s_dict_gid, s_group_key, &s_groups);
-        continue;
-      }
-    }
     uint64_t kr[kPairs][KCMAX][2], val[NC][kPairs][2];
     uint32_t km[kPairs][KCMAX], vm[NC][kPairs];
     if (wb + kWarpTile <= n) {  // warp-uniform; only the last tile takes the guarded element loads
