@@ -109,6 +109,8 @@ def lib():
     L.bgb_free_host_result.restype = None
     L.bgb_groupby_profile.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_float)]
     L.bgb_kernel_launches.restype = C.c_int64
+    L.bgb_set_estimate_speculation.argtypes = [C.c_int32]
+    L.bgb_set_estimate_speculation.restype = C.c_int32
     L.bgb_partition_by_key_hash.argtypes = [C.POINTER(ColumnView), C.c_int32, C.POINTER(ColumnView), C.c_int32, C.c_int32,
                                             C.POINTER(MutableColumn), C.POINTER(C.c_int32), C.c_void_p]
     L.bgb_hash_partition.argtypes = [C.POINTER(ColumnView), C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32, C.c_uint32,
