@@ -621,7 +621,6 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, co
       }
       if (acc.value_col >= 0) { d.word = (uint8_t)(1 + acc.value_col); d.src = pl.values[acc.value_col].src; d.vbit = (int16_t)vbit[acc.value_col]; }
       else { d.word = 0; d.src = S_I32; d.vbit = -1; }
-      if ((acc.op == ACC_SUM_F64 || acc.op == ACC_SUMSQ_F64) && d.src == S_F64) d.mode = HM_FSUM64;  // (the record word IS the double)
     }
   if (fused) {
     bgb_peer* peer = fuse->peer;
@@ -772,7 +771,7 @@ int run_hc_merge(bgb_groupby* h, int num_sms, const uint8_t* region, uint64_t ca
         case ACC_COUNT_VALID: case ACC_COUNT_ALL: d.mode = HM_ADD32; d.op = acc.op; d.src = S_U32; break;
         case ACC_SUM_I64: case ACC_SUMSQ_I64: case ACC_SUM_LO32: case ACC_SUM_HI32: d.mode = HM_ISUM; d.op = ACC_SUM_I64; d.src = S_I64; break;
         case ACC_MIN: case ACC_MAX: d.mode = HM_MINMAX; d.op = acc.op; d.src = S_U64; break;   // cells are order images already
-        case ACC_SUM_F64: case ACC_SUMSQ_F64: d.mode = HM_FSUM64; d.op = ACC_SUM_F64; d.src = S_F64; break;
+        case ACC_SUM_F64: case ACC_SUMSQ_F64: d.mode = HM_OTHER; d.op = ACC_SUM_F64; d.src = S_F64; break;
         case ACC_SUM_F32: case ACC_SUMSQ_F32: d.mode = HM_OTHER; d.op = ACC_SUM_F32; d.src = S_F32; break;
         case ACC_PROD_I64: d.mode = HM_OTHER; d.op = ACC_PROD_I64; d.src = S_I64; break;
         case ACC_PROD_F64: d.mode = HM_OTHER; d.op = ACC_PROD_F64; d.src = S_F64; break;

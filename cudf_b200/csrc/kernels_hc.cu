@@ -605,66 +605,15 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
             }
           }
         } else if (acc.mode == HM_MINMAX) {
-          // shared memory has no 64-bit MIN/MAX: load, and CAS only when the row improves the extremum (explicit shared-space
-          // addresses: through a generic pointer the compiler emits address-space tests around every atomic)
           const bool is_min = acc.op == ACC_MIN;
           const int src     = acc.src;
-          unsigned long long v[U], cv[U];
-          uint32_t todo = 0;
-#pragma unroll
-          for (int j = 0; j < U; ++j) {
-            v[j] = 0; cv[j] = 0;
-            if (!((on >> j) & 1u)) continue;
-            v[j]  = ordered_image(pick_word<W>(rec[j], acc.word), src);
-            cv[j] = lds64v(a_cells + slot[j] * 8);
-            if (is_min ? v[j] < cv[j] : v[j] > cv[j]) todo |= 1u << j;
-          }
-          while (todo) {  // (rare after a group's first rows: the expected number of improvements is H(rows per group))
-            const int j = __ffs(todo) - 1;
-            unsigned long long mine = v[0], seen = cv[0];
-            uint32_t sl = slot[0];
-#pragma unroll
-            for (int x = 1; x < U; ++x) if (j == x) { mine = v[x]; seen = cv[x]; sl = slot[x]; }
-            const unsigned long long got = atoms_cas64(a_cells + sl * 8, seen, mine);
-            const bool again = got != seen && (is_min ? mine < got : mine > got);  // lost the race and still better: once more
-#pragma unroll
-            for (int x = 0; x < U; ++x) if (j == x) cv[x] = got;
-            if (!again) todo &= todo - 1;
-          }
-        } else if (acc.mode == HM_FSUM64) {
-          // float64 SUM / SUM_OF_SQUARES: shared memory has no FP64 add -- load + add + CAS, all loads first, retries (two rows of
-          // one group in flight) one at a time
-          const bool sqr = acc.op == ACC_SUMSQ_F64;
-          double v[U];
-          unsigned long long cv[U];
-          uint32_t todo = 0;
-#pragma unroll
-          for (int j = 0; j < U; ++j) {
-            v[j] = 0.0; cv[j] = 0;
-            if (!((on >> j) & 1u)) continue;
-            const double x = __longlong_as_double((long long)pick_word<W>(rec[j], acc.word));
-            v[j]  = sqr ? x * x : x;
-            cv[j] = lds64v(a_cells + slot[j] * 8);
-          }
+          unsigned long long* c = reinterpret_cast<unsigned long long*>(smem + acc.smem_off);
 #pragma unroll
           for (int j = 0; j < U; ++j) {
             if (!((on >> j) & 1u)) continue;
-            const unsigned long long nv  = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)cv[j]) + v[j]);
-            const unsigned long long got = atoms_cas64(a_cells + slot[j] * 8, cv[j], nv);
-            if (got != cv[j]) { cv[j] = got; todo |= 1u << j; }
-          }
-          while (todo) {
-            const int j = __ffs(todo) - 1;
-            double add = v[0];
-            unsigned long long seen = cv[0];
-            uint32_t sl = slot[0];
-#pragma unroll
-            for (int x = 1; x < U; ++x) if (j == x) { add = v[x]; seen = cv[x]; sl = slot[x]; }
-            const unsigned long long nv  = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)seen) + add);
-            const unsigned long long got = atoms_cas64(a_cells + sl * 8, seen, nv);
-#pragma unroll
-            for (int x = 0; x < U; ++x) if (j == x) cv[x] = got;
-            if (got == seen) todo &= todo - 1;
+            const unsigned long long v   = ordered_image(pick_word<W>(rec[j], acc.word), src);
+            const unsigned long long cv  = *reinterpret_cast<volatile unsigned long long*>(c + slot[j]);
+            if (is_min) { if (v < cv) atomicMin(c + slot[j], v); } else { if (v > cv) atomicMax(c + slot[j], v); }
           }
         } else {
           void* cells = smem + acc.smem_off;
