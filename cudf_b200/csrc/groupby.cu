@@ -110,7 +110,8 @@ namespace {
 // ---- speculation on the cardinality estimate: ONE host synchronisation per call.
 // The estimate only picks the table capacity and the kernel family; no path's correctness depends on it (a table that fills sets
 // the overflow flag and the call is repeated, a tiny-kernel abort reruns, keys outside a direct-address range bypass). A call whose
-// SHAPE (row count, column types and masks, aggregations, options, device) was seen before therefore starts on the previous
+// SHAPE (row count, KEY COLUMN ADDRESSES, column types and masks, aggregations, options, device) was seen before -- the same table
+// queried again, or the next batch landing in the same buffers -- therefore starts on the previous
 // estimate while a fresh first-stage sample runs beside the kernels; its result is read back with the final status words and, when
 // it disagrees with the remembered one, the entry is dropped and the next call estimates synchronously again. BGB_NO_SPECULATE=1
 // turns this off.
@@ -140,7 +141,7 @@ uint64_t shape_signature(const Plan& pl, const bgb_options& opt)
   add((uint64_t)dev);
   add(pl.include_null_keys);
   add(pl.keys.size());
-  for (const KeyPlan& k : pl.keys) { add((uint64_t)k.v.type_id); add(k.v.null_mask != nullptr); }
+  for (const KeyPlan& k : pl.keys) { add((uint64_t)k.v.type_id); add(k.v.null_mask != nullptr); add((uint64_t)(uintptr_t)k.v.data); add((uint64_t)(int64_t)k.v.offset); }
   add(pl.values.size());
   for (const ValuePlan& v : pl.values) { add((uint64_t)v.v.type_id); add(v.v.null_mask != nullptr); }
   add(pl.accs.size());

@@ -144,7 +144,8 @@ typedef struct bgb_groupby bgb_groupby; /* opaque handle between build and emit 
 
 /* The cardinality estimate of bgb_groupby_build (a 65 536-row sample, read back on the host) only chooses the table size and the
  * kernel family -- no result depends on it. With speculation ON (the default; BGB_NO_SPECULATE=1 in the environment turns it off) a
- * call whose SHAPE (row count, column types and masks, aggregations, options, device) was seen before starts on the remembered
+ * call whose SHAPE (row count, key column addresses, column types and masks, aggregations, options, device) was seen before --
+ * the same table queried again, or the next batch landing in the same buffers -- starts on the remembered
  * estimate while a fresh sample runs beside the kernels, so the call synchronises with the host ONCE (the group count) instead of
  * twice; a fresh sample that disagrees with the remembered one drops it, and the next call of that shape estimates synchronously.
  * The price: which kernel family a call takes can depend on the calls before it. Returns the previous setting; a call also forgets
