@@ -547,11 +547,21 @@ class DistributedGroupBy:
                 pending = [fold(pending)]
                 pending_rows = pending[0][0].size
                 self._phase_end(tok, device)
-        if len(pending) > 1:
+        if len(pending) > 1 and self._comm.world == 1:
             tok = self._phase("dist_fold", device)
             pending = [fold(pending)]
             self._phase_end(tok, device)
-        running = pending[0]
+        if len(pending) > 1:
+            # several ranks: the exchange step's local build IS a fold (a groupby of partial rows with the merge kinds), so the
+            # pending tables go into it concatenated instead of being folded first and re-aggregated there (one pass less)
+            try:
+                running = concat(pending)
+            except torch.OutOfMemoryError:
+                release_caches()
+                running = concat(pending)
+            pending.clear()
+        else:
+            running = pending[0]
 
         if self._comm.world == 1:
             # one rank: the folded table already holds every group once -- nothing to exchange, nothing to merge
