@@ -80,6 +80,7 @@ struct bgb_peer {
   uint32_t epoch = 0;
   uint64_t timeout_ns = 20ull * 1000 * 1000 * 1000;
   bool poisoned = false;                 // a wait timed out or the abort signal could not be sent: epochs may differ between ranks
+  double merge_ratio = 1.0;              // groups per received record in the last step's merge (sizes the next merge's slices)
 };
 
 // record layout of the peer exchange inside a region: key word arrays, then one array per accumulator, each world * cap entries
@@ -1606,8 +1607,18 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
   if (!status) FAIL_RC(set_error(BGB_OUT_OF_MEMORY, "status alloc"));
   h->table.status    = status;
   h->table.key_words = pl.key_words;
-  const uint64_t capacity = next_pow2(std::max<uint64_t>(1024, 2 * total));
-  h->table.capacity       = capacity;
+  // Table size of the merge. Every record could be a group of its own (shards with disjoint keys), and then 2 x records slots are
+  // needed; when every rank saw every key (the usual case) there are `world` records per group and slices sized for the records
+  // are 4-8x too sparse -- the slice kernel's per-bucket work (clearing and scanning 4096 slots) then outweighs its rows (5.05 ms
+  // for 1e8 records at N=8). The distinct count is not known before the merge, so the size follows the LAST step's ratio of groups
+  // to records (first step: the safe size); slices that fill anyway set the overflow flag and the merge reruns at the safe size.
+  const uint64_t cap_safe = next_pow2(std::max<uint64_t>(1024, 2 * total));
+  uint64_t max_got = 0;
+  for (int r = 0; r < world; ++r) max_got = std::max<uint64_t>(max_got, got[r]);
+  const double want_groups = std::max((double)max_got, peer->merge_ratio * 1.25 * (double)total);
+  const uint64_t cap_adapt = std::min<uint64_t>(cap_safe, next_pow2((uint64_t)std::max(1024.0, 2.0 * want_groups)));
+  bool adaptive     = cap_adapt < cap_safe;
+  uint64_t capacity = cap_safe;
   // The received records are merged like rows of a groupby whose "values" are partial cells: through the records-form slices
   // when the shape fits (one key word, <= 3 accumulators, enough records to fill the machine), else with HBM atomics
   static const bool no_hc_merge = getenv("BGB_NO_HC_MERGE") != nullptr;
@@ -1620,6 +1631,8 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
     for (AccPlan& a : pl.accs) if (a.cells) { h->dfree(a.cells); a.cells = nullptr; }
   };
   for (;;) {
+    capacity          = (try_hc && adaptive) ? cap_adapt : cap_safe;
+    h->table.capacity = capacity;
     // (the slices write the groups densely: one entry per received record at most, not one per hash slot)
     const uint64_t slots = try_hc ? total + 1 : capacity + 1;
     h->table_slots = slots;
@@ -1676,10 +1689,13 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
     tr.mark("final sync");
     h->prof.resolve();
     if (scan_state) h->dfree(scan_state);
-    if (merged && (st[0] || st[6])) {  // a bucket of the merge overflowed (skewed keys): once more with the HBM-table merge
+    if (merged && (st[0] || st[6])) {
+      // slices or buckets of the merge filled: more groups per record than the last step had -> the safe size; skewed keys at the
+      // safe size -> the HBM-table merge
       h->dfree(h->group_slots); h->group_slots = nullptr;
       free_table();
-      try_hc = false;
+      if (adaptive) { adaptive = false; peer->merge_ratio = 1.0; }
+      else try_hc = false;
       continue;
     }
     h->dense = merged;
@@ -1690,6 +1706,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
 #undef FAIL_RC
   tr.flush("build_peer");
   h->num_groups = (int32_t)st[1];
+  if (total > 0) peer->merge_ratio = std::min(1.0, (double)st[1] / (double)total);
   h->path += h->peer_fused ? "+peer-fused" : "+peer";       // how the records travelled
   if (h->dense) h->path += "+slices";                        // how they were merged (else: HBM-table atomics + compaction)
   *num_groups = h->num_groups;

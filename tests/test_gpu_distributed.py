@@ -460,6 +460,63 @@ def test_peer_two_steps_reuse_the_context():
         np.testing.assert_array_equal(gc[order], np.bincount(inv))
 
 
+def test_peer_merge_size_follows_the_last_step_and_survives_a_wrong_guess(monkeypatch):
+    """The slices of the merge are sized from the previous step's groups-per-record ratio (groupby.cu: merge_ratio). Steps 0-1: every
+    rank sees every key (ratio 1/world, the second step runs on small slices); step 2: the ranks' key sets are DISJOINT (one group
+    per record: the small slices fill, the overflow flag reruns the merge at the safe size); step 3: shared keys again."""
+    monkeypatch.setenv("BGB_HC_MERGE_MIN", "1000")
+    # sized so that step 2 MUST overflow: steps 0-1 leave a ratio of ~0.27 groups per record, which sizes step 2's slices for ~1.05e6
+    # slots while its ~1.47e6 records per rank are all distinct
+    world, n, K = 4, 4_000_000, 1_600_000
+    shared = _Shared(world)
+    comms = [ThreadComm(shared, r) for r in range(world)]
+    out, errors = {}, []
+
+    def keys_of(step, rank):
+        rng = np.random.default_rng(77 * step + rank)
+        if step == 2:
+            return rng.integers(0, K, n).astype(np.int64) * world + rank  # disjoint over the ranks
+        return rng.integers(0, K, n).astype(np.int64)
+
+    def work(rank):
+        try:
+            with torch.cuda.stream(torch.cuda.Stream()):
+                for step in range(4):
+                    k = keys_of(step, rank)
+                    v = np.random.default_rng(5 + step + 10 * rank).integers(-5, 5, n).astype(np.int64)
+                    dgb = D.DistributedGroupBy(cb.Table([cb.Column.from_numpy(k)]), comm=comms[rank], exchange="peer", peer_region_bytes=64 << 20,
+                                               options={"force_path": 7})
+                    kt, rts = dgb.aggregate([cb.GroupByRequest(cb.Column.from_numpy(v), [agg.sum(), agg.count()])])
+                    torch.cuda.current_stream().synchronize()
+                    assert dgb.last_path == "bucketed+peer-fused+slices", dgb.last_path
+                    out[(step, rank)] = (k, v, kt.columns()[0].to_numpy()[0], rts[0].columns()[0].to_numpy()[0], rts[0].columns()[1].to_numpy()[0])
+        except BaseException as e:  # noqa: BLE001
+            errors.append(e)
+            shared.barrier.abort()
+
+    threads = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for c in shared.ctxs:
+        if c is not None:
+            c.close()
+    if errors:
+        raise errors[0]
+    for step in range(4):
+        k = np.concatenate([out[(step, r)][0] for r in range(world)])
+        v = np.concatenate([out[(step, r)][1] for r in range(world)])
+        gk = np.concatenate([out[(step, r)][2] for r in range(world)])
+        gs = np.concatenate([out[(step, r)][3] for r in range(world)])
+        gc = np.concatenate([out[(step, r)][4] for r in range(world)])
+        order = np.argsort(gk)
+        uk, inv = np.unique(k, return_inverse=True)
+        np.testing.assert_array_equal(gk[order], uk)
+        np.testing.assert_array_equal(gs[order], np.bincount(inv, weights=v).astype(np.int64))
+        np.testing.assert_array_equal(gc[order], np.bincount(inv))
+
+
 def test_peer_rank_failure_is_broadcast_and_the_context_survives():
     """One rank fails before it can scatter (its value column is shorter than its keys: cudf::logic_error, groupby.cu:186-229): it
     still signals -- with the abort word -- so the other rank returns BGB_PEER_ABORTED in the SAME step instead of spinning until
