@@ -5,6 +5,8 @@ Mirrors the parts of pylibcudf.Column / pylibcudf.Table the groupby path needs
 """
 from __future__ import annotations
 
+import ctypes as C
+
 import numpy as np
 import torch
 
@@ -106,7 +108,20 @@ class Column:
             valid = bits[self.offset:self.offset + n].astype(bool)
         return host, valid
 
+    @staticmethod
+    def dictionary(indices: "Column", keys: "Column", mask: torch.Tensor | None = None, null_count: int = 0) -> "Column":
+        """cudf dictionary column (cudf/dictionary/dictionary_column_view.hpp): row r holds keys[indices[r]]; the parent carries the
+        null mask. Served as a VALUE column of a groupby request; results are typed by `keys`."""
+        c = Column(torch.empty(0, dtype=torch.int32, device=indices.data.device), mask, null_count, TypeId.DICTIONARY32, 0, indices.size)
+        c.children = [indices, keys]
+        return c
+
     def view(self) -> _lib.ColumnView:
+        if self.type_id == TypeId.DICTIONARY32:
+            # `data` = host array of the two child views, kept alive by this Column
+            self._child_views = (_lib.ColumnView * 2)(self.children[0].view(), self.children[1].view())
+            return _lib.ColumnView(self.type_id, self.scale, self.size, self.null_count, self.offset, 0,
+                                   C.cast(self._child_views, C.c_void_p).value, self.mask.data_ptr() if self.mask is not None else None)
         return _lib.ColumnView(self.type_id, self.scale, self.size, self.null_count, self.offset, 0,
                                self.data.data_ptr() if self.data.numel() else None,
                                self.mask.data_ptr() if self.mask is not None else None)

@@ -69,7 +69,8 @@ struct AccDesc {
   uint8_t src;            // Src
   uint8_t op;             // AccOp
   uint8_t byte_mask;      // mask points at one validity BYTE per row (partitioned copies) instead of a bitmask
-  uint8_t pad;
+  uint8_t idx_width;      // dict != nullptr: bytes of one dictionary index (`data` holds the indices)
+  const uint8_t* dict;    // DICTIONARY32 values: the dictionary (keys child); the element of row r is dict[data[r]]
   void* cells;            // capacity+1 cells
   const void* aux;        // ACC_ARGROW_*: the MIN / MAX cells of the same value column
 };

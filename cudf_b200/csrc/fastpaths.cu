@@ -215,7 +215,7 @@ static bool tiny_plan(const Plan& pl, TinyParams& tp)
                            c.offset == pl.values[value_col].v.offset && c.src == pl.values[value_col].src))
         return j;
     }
-    if (tp.num_cols == kTinyMaxCols) return -1;
+    if (tp.num_cols == kTinyPlanCols) return -1;
     TinyCol& c = tp.cols[tp.num_cols];
     c.acc_sum = c.acc_sumsq = c.acc_min = c.acc_max = c.acc_count = -1;
     c.sum_op = ACC_SUM_I64;
@@ -261,7 +261,10 @@ static int run_tiny_path(const BuildContext& ctx, TinyParams& tp, bool allow_sme
   }
   tp.a.table = ctx.table; tp.a.init_keys = 1; tp.a.num_accs = (int)pl.accs.size();
   for (size_t i = 0; i < pl.accs.size(); ++i) { tp.a.acc[i].op = pl.accs[i].op; tp.a.acc[i].cells = pl.accs[i].cells; }
-  const bool use_reg = ctx.opt.force_path != 5 && tiny_reg_eligible(tp) && (ctx.opt.force_path == 6 || ctx.g_raw <= 8.5);
+  TinyParams subs[kTinyPlanCols];
+  const bool few     = ctx.opt.force_path == 6 || ctx.g_raw <= 8.5;
+  const int nsub     = (ctx.opt.force_path != 5 && few) ? tiny_reg_split(tp, subs) : 0;
+  const bool use_reg = ctx.opt.force_path != 5 && few && (nsub > 0 || tiny_reg_eligible(tp));
   if (!use_reg && ctx.opt.force_path == 6) return set_error(BGB_UNSUPPORTED, "force_path 6: this shape is not served by the register-resident tiny kernel");
   if (!use_reg && !allow_smem_variant) return BGB_OK;
   done = true;
@@ -271,10 +274,12 @@ static int run_tiny_path(const BuildContext& ctx, TinyParams& tp, bool allow_sme
   if (rc) return rc;
   // at most 8 groups and a shape the register kernel serves: accumulators live in registers (force_path 6 insists on it,
   // 5 on the shared-memory variant)
-  if (ctx.opt.force_path != 5 && tiny_reg_eligible(tp) && (ctx.opt.force_path == 6 || ctx.g_raw <= 8.5)) {
+  if (use_reg) {
     used_reg = true;
+    const int gcap = ctx.g_raw <= 4.5 && ctx.opt.force_path != 6 ? 4 : 8;
     ctx.prof->begin("aggregate_tiny_reg");
-    rc = check_cuda(launch_aggregate_tiny_reg(tp, ctx.g_raw <= 4.5 && ctx.opt.force_path != 6 ? 4 : 8, ctx.num_sms, ctx.stream), "aggregate_tiny_reg");
+    if (nsub == 0) rc = check_cuda(launch_aggregate_tiny_reg(tp, gcap, ctx.num_sms, ctx.stream), "aggregate_tiny_reg");
+    for (int i = 0; i < nsub && !rc; ++i) rc = check_cuda(launch_aggregate_tiny_reg(subs[i], gcap, ctx.num_sms, ctx.stream), "aggregate_tiny_reg");
     ctx.prof->end();
     return rc;
   }
@@ -295,7 +300,7 @@ int try_fast_paths(const BuildContext& ctx, bool& done, std::string& path)
     if (tiny_plan(pl, tp)) {
       const int cap = (int)std::min<size_t>(60, (200 * 1024) / ((size_t)tp.cells * kTinyThreads * 8));
       // (the register variant holds 8 groups whatever the cell count; run_tiny_path picks it when the shape allows)
-      const bool smem_ok = cap >= 2 && (force_tiny || cap >= ctx.g_raw + 1);
+      const bool smem_ok = tp.num_cols <= kTinyMaxCols && cap >= 2 && (force_tiny || cap >= ctx.g_raw + 1);
       if (smem_ok || (ctx.g_raw <= 8.5 && ctx.opt.force_path != 5)) {
         tp.group_cap = cap;
         bool used_reg = false;

@@ -191,6 +191,7 @@ void fill_agg_params(const bgb_groupby& h, AggParams& p, size_t acc_begin, size_
     if (ap.value_col >= 0) {
       const ValuePlan& v = pl.values[ap.value_col];
       d.data = (const uint8_t*)v.v.data; d.mask = v.v.null_mask; d.offset = v.v.offset; d.src = v.src;
+      d.dict = v.dict; d.idx_width = v.idx_width;
     } else { d.data = nullptr; d.mask = nullptr; d.offset = 0; d.src = S_I32; }
     d.op    = ap.op;
     d.cells = ap.cells;
@@ -949,6 +950,12 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     FAIL_RC(try_repack_keys(h, keys, num_keys, include_null_keys, requests, num_requests, repacked));
     tr.mark("repack");
   }
+  if (pl.has_dict) {
+    // dictionary values: the element of a row is keys[indices[row]]; only the generic kernels read values through that indirection
+    // (the reference keeps dictionaries off its shared-memory path too, hash/compute_single_pass_aggs.cu:18-21)
+    if (opt.force_path != 0 && opt.force_path != 1) FAIL_RC(set_error(BGB_UNSUPPORTED, "force_path %d does not serve dictionary values", opt.force_path));
+    opt.force_path = 1;
+  }
   if (pl.key_words > 2) {
     // no packed image: the table holds the row number of each group's first row and rows are compared in the caller's columns
     // (the reference's scheme for every key). One-word table of row numbers, generic kernels only.
@@ -984,7 +991,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     AggParams ep;
     fill_agg_params(*h, ep, 0, 0);
     const SmemEligibility se = smem_eligibility(pl);
-    if (se.ok && se.sum_acc >= 0) {  // also sample the magnitude of the SUM inputs
+    if (se.ok && se.sum_acc >= 0 && !pl.has_dict) {  // also sample the magnitude of the SUM inputs
       const ValuePlan& v = pl.values[se.value_col];
       ep.num_accs = 1;
       ep.acc[0].data = (const uint8_t*)v.v.data; ep.acc[0].mask = v.v.null_mask; ep.acc[0].offset = v.v.offset; ep.acc[0].src = v.src;

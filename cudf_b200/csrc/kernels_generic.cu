@@ -48,7 +48,10 @@ __device__ __forceinline__ void apply_acc(const AccDesc& a, int64_t row, uint64_
     if (!valid) return;
   }
   if (a.op == ACC_COUNT_VALID) { atomicAdd(reinterpret_cast<int*>(a.cells) + slot, 1); return; }
-  apply_value(a.op, a.src, a.cells, slot, load_raw(a.data, src_width(a.src), idx), row);
+  uint64_t raw;
+  if (a.dict != nullptr) raw = load_raw(a.dict, src_width(a.src), (int64_t)load_raw(a.data, a.idx_width, idx));  // keys[indices[row]]
+  else raw = load_raw(a.data, src_width(a.src), idx);
+  apply_value(a.op, a.src, a.cells, slot, raw, row);
 }
 
 // ------------------------------------------------------------------ fused hash + probe + aggregate (HBM table)
@@ -108,7 +111,9 @@ __global__ void __launch_bounds__(256) argrow_kernel(const __grid_constant__ Agg
       if (d.op != ACC_ARGROW_MIN && d.op != ACC_ARGROW_MAX) continue;
       const int64_t idx = (int64_t)d.offset + row;
       if (d.mask != nullptr && !bit_is_set(d.mask, idx)) continue;
-      const uint64_t img = ordered_image(load_raw(d.data, src_width(d.src), idx), d.src);
+      const uint64_t raw = d.dict != nullptr ? load_raw(d.dict, src_width(d.src), (int64_t)load_raw(d.data, d.idx_width, idx))
+                                             : load_raw(d.data, src_width(d.src), idx);
+      const uint64_t img = ordered_image(raw, d.src);
       if (img == reinterpret_cast<const uint64_t*>(d.aux)[slot]) atomicMin(reinterpret_cast<unsigned int*>(d.cells) + slot, (unsigned int)row);
     }
   }

@@ -541,6 +541,31 @@ bool tiny_reg_eligible(const TinyParams& tp)
   return real >= 1;
 }
 
+int tiny_reg_split(const TinyParams& tp, TinyParams* out)
+{
+  if (tiny_reg_eligible(tp)) return 0;  // one launch does it
+  int n = 0;
+  bool used[kTinyPlanCols] = {};
+  int pseudo = -1;
+  for (int j = 0; j < tp.num_cols; ++j) if (tp.cols[j].data == nullptr) { pseudo = j; used[j] = true; }
+  for (int j = 0; j < tp.num_cols; ++j) {
+    if (used[j]) continue;
+    TinyParams& sub = out[n];
+    sub          = tp;
+    sub.num_cols = 0;
+    auto cls = [&](const TinyCol& c) { return c.sum_op == ACC_SUM_F64 ? 1 : (c.src == S_I64 || c.src == S_U64) ? 0 : -2; };
+    sub.cols[sub.num_cols++] = tp.cols[j];
+    used[j] = true;
+    for (int k = j + 1; k < tp.num_cols; ++k)  // a partner of the same arithmetic class
+      if (!used[k] && cls(tp.cols[k]) == cls(tp.cols[j])) { sub.cols[sub.num_cols++] = tp.cols[k]; used[k] = true; break; }
+    if (n == 0 && pseudo >= 0) sub.cols[sub.num_cols++] = tp.cols[pseudo];  // COUNT_ALL rides with the first launch
+    if (!tiny_reg_eligible(sub)) return 0;
+    ++n;
+  }
+  if (n == 0 && pseudo >= 0) return 0;  // (COUNT_ALL alone: the register kernel wants a value column)
+  return n;
+}
+
 cudaError_t launch_aggregate_tiny_reg(const TinyParams& tp, int group_cap, int num_sms, cudaStream_t s)
 {
   if (tp.a.num_rows == 0) return cudaSuccess;

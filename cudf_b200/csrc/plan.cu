@@ -110,6 +110,35 @@ static bool same_column(const bgb_column_view& a, const bgb_column_view& b)
   return a.data == b.data && a.null_mask == b.null_mask && a.offset == b.offset && a.size == b.size && a.type_id == b.type_id;
 }
 
+// DICTIONARY32 values are aggregated as their KEYS' type (hash/groupby.cu:118-120, output_utils.cu:66): the view's `data` is a HOST
+// array of two child views {indices, keys}. Resolves the request's values into the view the kernels read (the indices, under the
+// parent's offset and null mask, typed like the keys) + the dictionary. Non-dictionary columns pass through.
+struct ResolvedValues { bgb_column_view v; const uint8_t* dict; uint8_t idx_width; int rc; };
+static ResolvedValues resolve_values(const bgb_column_view& in, int r)
+{
+  ResolvedValues out{in, nullptr, 0, BGB_OK};
+  if (in.type_id != BGB_DICTIONARY32) return out;
+  const bgb_column_view* ch = static_cast<const bgb_column_view*>(in.data);
+  if (ch == nullptr) { out.rc = set_error(BGB_INVALID_ARGUMENT, "request %d: a DICTIONARY32 view needs data = {indices, keys} child views", r); return out; }
+  const bgb_column_view &idx = ch[0], &keys = ch[1];
+  const int iw = type_width(idx.type_id), kw = type_width(keys.type_id);
+  const bool idx_int = idx.type_id == BGB_INT8 || idx.type_id == BGB_INT16 || idx.type_id == BGB_INT32 || idx.type_id == BGB_UINT8 ||
+                       idx.type_id == BGB_UINT16 || idx.type_id == BGB_UINT32;
+  if (!idx_int || iw == 0 || kw == 0 || keys.type_id == BGB_DICTIONARY32) {
+    out.rc = set_error(BGB_UNSUPPORTED, "request %d: dictionary with index type %d / key type %d is not served by the hash path", r, idx.type_id, keys.type_id);
+    return out;
+  }
+  if (idx.size < in.offset + in.size) { out.rc = set_error(BGB_INVALID_ARGUMENT, "request %d: dictionary indices shorter than the column", r); return out; }
+  out.v.type_id = keys.type_id;
+  out.v.scale   = keys.scale;
+  out.v.data    = idx.data;
+  out.v.offset  = in.offset + idx.offset;  // (the parent's mask is indexed by in.offset: see mask_shift below -- children carry offset 0 in cudf)
+  out.dict      = static_cast<const uint8_t*>(keys.data) + (size_t)keys.offset * kw;
+  out.idx_width = (uint8_t)iw;
+  if (idx.offset != 0 && in.null_mask != nullptr) out.rc = set_error(BGB_UNSUPPORTED, "request %d: dictionary indices child with its own offset under a null mask", r);
+  return out;
+}
+
 int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_null_keys, const bgb_request* requests,
               int32_t num_requests, Plan& plan, bool rank_independent, bool allow_wide)
 {
@@ -126,8 +155,12 @@ int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_nul
       return set_error(BGB_INVALID_ARGUMENT, "Size mismatch between request values and groupby keys.");
   for (int r = 0; r < num_requests; ++r)
     for (int a = 0; a < requests[r].num_aggregations; ++a)
-      if (target_type(requests[r].values.type_id, requests[r].aggregations[a].kind) == -1)
-        return set_error(BGB_INVALID_ARGUMENT, "Invalid type/aggregation combination.");
+      {
+        int32_t vt = requests[r].values.type_id;
+        if (vt == BGB_DICTIONARY32 && requests[r].values.data != nullptr) vt = static_cast<const bgb_column_view*>(requests[r].values.data)[1].type_id;
+        if (target_type(vt, requests[r].aggregations[a].kind) == -1)
+          return set_error(BGB_INVALID_ARGUMENT, "Invalid type/aggregation combination.");
+      }
 
   // ---- what this library's hash path serves (everything else: BGB_UNSUPPORTED -> caller's sort fallback)
   if (num_keys > kMaxKeyCols) return set_error(BGB_UNSUPPORTED, "more than %d key columns", kMaxKeyCols);
@@ -165,18 +198,25 @@ int make_plan(const bgb_column_view* keys, int32_t num_keys, int32_t include_nul
 
   // ---- value columns, accumulators, output recipes
   for (int r = 0; r < num_requests; ++r) {
-    const bgb_request& rq = requests[r];
+    bgb_request rq = requests[r];
     plan.request_first_out.push_back((int)plan.outs.size());
     plan.request_num_aggs.push_back(rq.num_aggregations);
     if (rq.num_aggregations == 0) continue;
+    const ResolvedValues rv = resolve_values(rq.values, r);
+    if (rv.rc != BGB_OK) return rv.rc;
+    if (rv.dict != nullptr && rank_independent) return set_error(BGB_UNSUPPORTED, "request %d: dictionary values on a distributed / streaming table", r);
+    rq.values = rv.v;  // (from here on: the column the kernels read)
     const uint8_t src = type_src(rq.values.type_id);
     if (src == S_BAD) return set_error(BGB_UNSUPPORTED, "request %d: value type %d not served by the hash path", r, rq.values.type_id);
     int vc = -1;
     for (size_t i = 0; i < plan.values.size(); ++i)
-      if (same_column(plan.values[i].v, rq.values)) { vc = (int)i; break; }
+      if (same_column(plan.values[i].v, rq.values) && plan.values[i].dict == rv.dict) { vc = (int)i; break; }
     if (vc < 0) {
       ValuePlan vp;
       vp.v         = rq.values;
+      vp.dict      = rv.dict;
+      vp.idx_width = rv.idx_width;
+      if (rv.dict != nullptr) plan.has_dict = true;
       vp.src       = src;
       // rank_independent: another rank's shard of this column may hold nulls, and every rank must lay out the same cells
       vp.has_nulls = rank_independent || (rq.values.null_count > 0 && rq.values.null_mask != nullptr);

@@ -23,7 +23,9 @@ struct KeyPlan {
 };
 
 struct ValuePlan {
-  bgb_column_view v;
+  bgb_column_view v;      // DICTIONARY32 values: the view of the INDICES child under the parent's offset / mask, typed like the KEYS child
+  const uint8_t* dict = nullptr;  // DICTIONARY32: first element of the keys child (the dictionary), else nullptr
+  uint8_t idx_width   = 0;        // DICTIONARY32: bytes of one index
   uint8_t src;
   bool has_nulls;   // column_view::has_nulls() == null_count > 0
   bool has_mask;    // nullable()
@@ -53,6 +55,7 @@ struct Plan {
   bool include_null_keys = false;
   bool skip_null_keys = false;
   int key_words = 1;
+  bool has_dict = false;                // some value column is a dictionary: generic kernels only (the element is keys[indices[row]])
   bool wide = false;                    // key image wider than 128 bits: row-number slots, generic kernels only (groupby.cu)
   std::vector<KeyPlan> keys;
   std::vector<ValuePlan> values;

@@ -78,7 +78,10 @@ typedef struct bgb_column_view {
   int32_t null_count; /* as column_view::null_count(); has_nulls() == null_count > 0 */
   int32_t offset;
   int32_t reserved;
-  const void* data;
+  const void* data;   /* device pointer to the elements. DICTIONARY32 (value columns only): HOST pointer to two child views
+                         {indices, keys} -- cudf::dictionary_column_view::indices() / keys(), dictionary_column_view.hpp; size, offset
+                         and null_mask of THIS view apply to the rows, the element of row r is keys[indices[offset + r]] and every
+                         aggregation is typed by the keys (hash/groupby.cu:118-120, hash/output_utils.cu:66) */
   const uint32_t* null_mask;
 } bgb_column_view;
 
