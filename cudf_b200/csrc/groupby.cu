@@ -515,7 +515,14 @@ int run_bucketed(bgb_groupby* h, int num_sms, const bgb_options& opt, bool one_l
 // table slice with DENSE group output -- no HBM hash table, no compaction pass. `h->table` and the accumulator cells are
 // allocated (capacity + 1 entries each); on success h->group_slots is allocated and filled and h->dense is set.
 // done=false when the plan does not fit (the caller then tries the column-form kernels of kernels_bucket.cu).
-int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, const PeerFuse* fuse, bool& done)
+// what the cardinality sample saw of the key and value ranges (pack32 eligibility); `unknown` when nothing was sampled
+struct HcHints {
+  uint64_t key_min = 1, key_max = 0;  // order-preserving key image (raw ^ key_flip); min > max: unknown
+  uint64_t max_abs = ~0ull;           // largest |value| of the sampled SUM inputs; ~0: unknown
+  bool no_pack32   = false;           // a previous attempt met a row that does not fit
+};
+
+int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, const PeerFuse* fuse, const HcHints& hints, bool& done)
 {
   done = false;
   Plan& pl = h->plan;
@@ -539,9 +546,30 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, co
   int key_bits = 0;
   for (const KeyPlan& k : pl.keys) key_bits = std::max(key_bits, std::max((int)k.shift + 8 * k.width, (int)k.null_bit + 1));
   const bool in_low32 = nvb > 0 && key_bits <= 32;
-  const int W = 1 + (int)pl.values.size() + ((nvb > 0 && !in_low32) ? 1 : 0);
+  int W = 1 + (int)pl.values.size() + ((nvb > 0 && !in_low32) ? 1 : 0);
   if (W > kHcMaxWords || nvb > 32) return BGB_OK;
   const int vbits_word = (nvb > 0 && !in_low32) ? W - 1 : -1;
+  // pack32: ONE integer value column without nulls, SUM / COUNT only, key and values within 32 bits -> 8-byte records {key32, value32}
+  // instead of 16-byte ones: half the bytes of every pass after the first read (1e9 rows: 80 -> 48 GB). The sample only PREDICTS
+  // that everything fits; level 1 checks every row and raises status[7] otherwise (the call then reruns with 16-byte records).
+  bool pack32 = false;
+  static const bool no_pack32_env = getenv("BGB_HC_NO_PACK32") != nullptr;
+  if (!hints.no_pack32 && !no_pack32_env && W == 2 && nvb == 0 && pl.values.size() == 1 && pl.keys.size() == 1 && pl.keys[0].fclass == 0 &&
+      pl.keys[0].v.null_mask == nullptr) {
+    const ValuePlan& v = pl.values[0];
+    const bool int_val = v.src == S_I8 || v.src == S_I16 || v.src == S_I32 || v.src == S_I64 || v.src == S_U8 || v.src == S_U16 || v.src == S_U32 || v.src == S_U64;
+    bool shape = int_val && v.v.null_mask == nullptr;
+    for (const AccPlan& a : pl.accs) shape = shape && (a.op == ACC_SUM_I64 || a.op == ACC_COUNT_VALID || a.op == ACC_COUNT_ALL);
+    const int vw = type_width(v.v.type_id);
+    const bool val_fits = vw < 4 || v.src == S_I32 || (hints.max_abs != ~0ull && hints.max_abs < (1ull << 31));
+    bool key_fits = pl.keys[0].width <= 4;
+    if (!key_fits && hints.key_min <= hints.key_max) {
+      const uint64_t flip = smem_eligibility(pl).key_flip;
+      key_fits = hints.key_min >= flip && (hints.key_max ^ flip) < (1ull << 32) && (hints.key_min ^ flip) <= (hints.key_max ^ flip);
+    }
+    pack32 = shape && val_fits && key_fits;
+  }
+  if (pack32) W = 1;
   int log2cap = 0; while ((1ull << log2cap) < h->table.capacity) ++log2cap;
   auto round16 = [](uint64_t x) { return (x + 15) & ~15ull; };
 
@@ -604,7 +632,7 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, co
   memset(&sp, 0, sizeof sp);
   sp.table = h->table;
   sp.table.capacity = h->table_slots - 1;  // (the slices use it only as the index of the reserved entry: the LAST allocated one)
-  sp.words = W; sp.key_in_low32 = in_low32; sp.vbits_word = vbits_word;
+  sp.words = W; sp.key_in_low32 = in_low32 || pack32; sp.vbits_word = vbits_word; sp.val_hi32 = pack32;
   sp.log2_slice = ls; sp.num_buckets = NB; sp.num_accs = (int)pl.accs.size();
   sp.group_slots = h->group_slots; sp.gcount = gcount; sp.max_groups = max_groups;
   uint32_t off_b = (uint32_t)(8u << ls);
@@ -624,6 +652,7 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, co
       }
       if (acc.value_col >= 0) { d.word = (uint8_t)(1 + acc.value_col); d.src = pl.values[acc.value_col].src; d.vbit = (int16_t)vbit[acc.value_col]; }
       else { d.word = 0; d.src = S_I32; d.vbit = -1; }
+      if (pack32 && acc.value_col >= 0) { d.word = 0; d.src = S_I64; }  // (the value is the sign-extended upper half of word 0: val_hi32)
     }
   if (fused) {
     bgb_peer* peer = fuse->peer;
@@ -652,12 +681,19 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, co
   for (size_t c = 0; c < pl.values.size(); ++c) {
     const ValuePlan& v = pl.values[c];
     const int w = type_width(v.v.type_id);
-    s1.val[c] = HcValue{(const uint8_t*)v.v.data, v.v.null_mask, v.v.offset, w, vbit[c], 0};
+    s1.val[c] = HcValue{(const uint8_t*)v.v.data, v.v.null_mask, v.v.offset, w, vbit[c], (int32_t)v.src};
     tma = tma && ((uintptr_t)v.v.data + (size_t)v.v.offset * w) % 16 == 0;
     if (v.v.null_mask) tma = tma && v.v.offset % 128 == 0 && ((uintptr_t)v.v.null_mask + (size_t)v.v.offset / 8) % 16 == 0;
   }
   static const bool no_tma = getenv("BGB_HC_NO_TMA") != nullptr;
   s1.tma_src = tma && !no_tma;
+  if (pack32 && !s1.tma_src) {  // (only the TMA loader packs: decided before anything was launched that depends on W... see below)
+    release(); h->dfree(h->group_slots); h->group_slots = nullptr;
+    if (h->peer_cursors) { h->dfree(h->peer_cursors); h->peer_cursors = nullptr; }
+    HcHints again = hints; again.no_pack32 = true;
+    return run_hc(h, num_sms, opt, g_est, fuse, again, done);
+  }
+  s1.pack32 = pack32; s1.key_in_low32 = in_low32 || pack32;
   s1.out = L1; s1.cursor = cursor1; s1.cursor_stride = kHotStride; s1.bucket_capacity = (uint32_t)C1;
   s1.log2_parts = b1; s1.slot_shift = log2cap - b1; s1.status = h->table.status;
   h->prof.begin("hc_scatter1");
@@ -1065,7 +1101,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     if (capacity > cap_max) capacity = cap_max;
   }
 
-  bool skip_tiny = false, no_bucket = false, no_hc = false, no_short = false;
+  bool skip_tiny = false, no_bucket = false, no_hc = false, no_short = false, no_pack32 = false;
   bool hc_shape = pl.key_words == 1 && pl.accs.size() <= (size_t)kMaxAccs && N >= 1 && N < (1ll << 31) && getenv("BGB_NO_HC") == nullptr;
   for (const AccPlan& a : pl.accs) hc_shape = hc_shape && !(a.op == ACC_ARGMIN || a.op == ACC_ARGMAX || a.op == ACC_ARGROW_MIN || a.op == ACC_ARGROW_MAX);
   for (int attempt = 0;; ++attempt) {
@@ -1102,7 +1138,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
       static const bool mid_on = getenv("BGB_BUCKET_MID") != nullptr;
       const bool mid = mid_on && !big && N >= (1 << 24) && capacity >= (1u << 16);
       if ((opt.force_path == 7 || (opt.force_path == 0 && (big || mid))) && !no_bucket) {
-        if (!no_hc) FAIL_RC(run_hc(h, num_sms, opt, g_raw, fuse, done));  // records form first; plans it does not take go through the column form
+        if (!no_hc) { HcHints hints; hints.key_min = key_min; hints.key_max = key_max; hints.max_abs = max_abs; hints.no_pack32 = no_pack32; FAIL_RC(run_hc(h, num_sms, opt, g_raw, fuse, hints, done)); }  // records form first; plans it does not take go through the column form
         was_hc_attempt = done;
         if (!done && short_table) {  // the plan has no records form after all: full arrays, every path open
           no_short = true;
@@ -1191,6 +1227,16 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     const bool was_fused = h->peer_fused;
     h->dense = false;  // (a retry below starts from scratch)
     if (getenv("BGB_DEBUG")) fprintf(stderr, "[bgb] path=%s groups=%u overflow=%u bypass_rows=%u flushes=%u\n", path.c_str(), st[1], st[0], st[4], st[5]);
+    if (st[7] != 0 && path == "bucketed" && was_hc_attempt && !no_pack32) {
+      // a key or a value did not fit the 32-bit halves of the packed record (the sample said they would): 16-byte records
+      no_pack32 = true;
+      h->peer_fused = false;
+      h->dfree(h->group_slots); h->group_slots = nullptr;
+      h->dfree(h->table.keys); h->table.keys = nullptr;
+      for (AccPlan& a : pl.accs) { h->dfree(a.cells); a.cells = nullptr; }
+      --attempt;
+      continue;
+    }
     if (st[6] != 0 && path == "bucketed") {
       // skewed keys filled a bucket of the records form (no overflow region there): column form, whose overflow region takes
       // moderate skew; if that fills too: same table size, exact-offset partitioned path

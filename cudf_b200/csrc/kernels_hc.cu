@@ -89,7 +89,8 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
   extern __shared__ __align__(128) unsigned char smem[];
   const uint32_t P = 1u << p.log2_parts, pmask = P - 1;
   unsigned char* stage = smem;                                               // T x W x 8 bytes: records, or raw column tiles
-  uint16_t* s_idx   = reinterpret_cast<uint16_t*>(smem + (size_t)T * W * 8);  // [T] sorted position -> row
+  const int stage_words = (MODE == 1 && p.pack32) ? 2 : W;                    // (pack32: 16 bytes of raw columns become 8-byte records)
+  uint16_t* s_idx   = reinterpret_cast<uint16_t*>(smem + (size_t)T * stage_words * 8);  // [T] sorted position -> row
   uint32_t* s_cnt   = reinterpret_cast<uint32_t*>(s_idx + T);                 // [P]
   uint32_t* s_off   = s_cnt + P;
   uint32_t* s_gbase = s_off + P;
@@ -117,7 +118,7 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
   const int64_t ntiles = MODE == 2 ? (int64_t)p.num_segs * tiles_per_seg : (p.a.num_rows + T - 1) / T;
   uint32_t phase = 0;
   (void)phase;
-  bool overflow = false;
+  bool overflow = false, misfit = false;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     int64_t row0;
     uint32_t nrows, cbase = 0;
@@ -318,7 +319,11 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
               if (p.val[c].vbit >= 0) vb |= (uint32_t)((stage[moff[c] + (r >> 3)] >> (r & 7)) & 1u) << p.val[c].vbit;
             }
           }
-          if (p.key_in_low32) w[0] |= (uint64_t)vb << 32;
+          if (W == 1 && p.pack32) {
+            const int64_t v = raw_to_i64(lds_raw(stage + voff[0], p.val[0].width, r), p.val[0].src);
+            misfit |= (k >> 32) != 0 || v != (int64_t)(int32_t)v;
+            w[0] = (k & 0xffffffffull) | ((uint64_t)(uint32_t)v << 32);
+          } else if (p.key_in_low32) w[0] |= (uint64_t)vb << 32;
           else if (p.vbits_word > 0) {
 #pragma unroll
             for (int x = 1; x < W; ++x) if (p.vbits_word == x) w[x % W] = vb;
@@ -336,13 +341,14 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
     __syncthreads();  // the stage and the counters are free
   }
   if (overflow) p.status[6] = 1;
+  if (misfit) p.status[7] = 1;
 }
 
 template <int W>
 static cudaError_t launch_scatter_w(const HcScatterParams& p, int num_sms, cudaStream_t s)
 {
   const int T = hc_tile_rows(W);
-  const size_t smem = hc_scatter_smem_bytes(W, p.log2_parts);
+  const size_t smem = hc_scatter_smem_bytes((p.level == 1 && p.pack32) ? 2 : W, p.log2_parts);
   int64_t ntiles;
   cudaError_t e;
   if (p.level == 2) {
@@ -551,7 +557,7 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
 #pragma unroll
             for (int j = 0; j < U; ++j) {
               if (!((act >> j) & 1u)) continue;
-              const uint64_t v   = pick_word<W>(rec[j], word);
+              const uint64_t v   = p.val_hi32 ? (uint64_t)(int64_t)(int32_t)(rec[j][0] >> 32) : pick_word<W>(rec[j], word);
               const uint32_t vlo = (uint32_t)v, vhi = (uint32_t)(v >> 32);
               const uint32_t old = atoms_add_ret(a_cells + slot[j] * 8, vlo);
               const uint32_t add = vhi + ((uint32_t)(old + vlo) < old ? 1u : 0u);
@@ -711,7 +717,7 @@ __global__ void hc_init_kernel(const __grid_constant__ HcSliceParams p)
   const uint64_t cap = p.table.capacity;
   if (a == 0) {
     p.table.keys[cap] = kEmpty;
-    p.table.status[0] = 0; p.table.status[1] = 0; p.table.status[2] = 0; p.table.status[3] = 0; p.table.status[6] = 0;
+    p.table.status[0] = 0; p.table.status[1] = 0; p.table.status[2] = 0; p.table.status[3] = 0; p.table.status[6] = 0; p.table.status[7] = 0;
     *p.gcount = 0ull;
   }
   if (a < p.num_accs) {

@@ -51,7 +51,7 @@ struct HcValue {
   int32_t offset;
   int32_t width;   // 1/2/4/8
   int32_t vbit;    // bit in the validity word, -1: no mask
-  int32_t pad;
+  int32_t src;     // Src of the column (pack32: how the raw element is sign-extended)
 };
 
 struct HcScatterParams {
@@ -63,6 +63,8 @@ struct HcScatterParams {
   int32_t words;             // W
   int32_t key_in_low32;      // validity bits ride in the upper half of word 0
   int32_t vbits_word;        // index of the separate validity word, -1: none
+  int32_t pack32;            // level 1, W == 1: the record is {key (low 32 bits), the ONE value column as int32 (high 32 bits)}; a row whose
+                             // key or value does not fit sets status[7] and the host repeats the call with 16-byte records
   const uint64_t* in;        // level 2 input records
   const uint32_t* seg_cursor;
   uint32_t seg_cursor_stride;
@@ -101,6 +103,7 @@ struct HcSliceParams {
   int32_t words;
   int32_t key_in_low32;
   int32_t vbits_word;
+  int32_t val_hi32;          // pack32 records: the value of the (one) value column is the sign-extended upper half of word 0
   int32_t num_accs;
   uint32_t* group_slots;     // identity for the dense groups
   unsigned long long* gcount;
