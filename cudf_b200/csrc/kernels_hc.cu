@@ -76,7 +76,7 @@ int hc_tile_rows(int words) { return words <= 2 ? 4096 : 2048; }
 size_t hc_scatter_smem_bytes(int words, int log2_parts)
 {
   const size_t T = (size_t)hc_tile_rows(words);
-  return T * words * 8 + T * 2 + (size_t)(4u << log2_parts) * 4 + 64;
+  return T * words * 8 + T * 4 + (size_t)(4u << log2_parts) * 4 + 64;
 }
 
 // MODE 0: level 1, generic packer (LDG -> records in the stage); 1: level 1, raw column tiles by TMA; 2: level 2 (records by TMA);
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
   const uint32_t P = 1u << p.log2_parts, pmask = P - 1;
   unsigned char* stage = smem;                                               // T x W x 8 bytes: records, or raw column tiles
   const int stage_words = (MODE == 1 && p.pack32) ? 2 : W;                    // (pack32: 16 bytes of raw columns become 8-byte records)
-  uint16_t* s_idx   = reinterpret_cast<uint16_t*>(smem + (size_t)T * stage_words * 8);  // [T] sorted position -> row
+  uint32_t* s_idx   = reinterpret_cast<uint32_t*>(smem + (size_t)T * stage_words * 8);  // [T] sorted position -> bucket << 16 | row
   uint32_t* s_cnt   = reinterpret_cast<uint32_t*>(s_idx + T);                 // [P]
   uint32_t* s_off   = s_cnt + P;
   uint32_t* s_gbase = s_off + P;
@@ -284,7 +284,7 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
     // ---- C: permutation; the reservations (in flight since B) become run bases
 #pragma unroll
     for (int j = 0; j < R; ++j)
-      if (pr[j] != 0xFFFFFFFFu) s_idx[s_off[pr[j] >> 16] + (pr[j] & 0xffffu)] = (uint16_t)(j * kHcThreads + t);
+      if (pr[j] != 0xFFFFFFFFu) s_idx[s_off[pr[j] >> 16] + (pr[j] & 0xffffu)] = (pr[j] & 0xffff0000u) | (uint32_t)(j * kHcThreads + t);
 #pragma unroll
     for (int x = 0; x < 2; ++x) {
       const uint32_t i = t * cpt + x;
@@ -304,7 +304,8 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
     for (int j = 0; j < R; ++j) {
       const uint32_t i = j * kHcThreads + t;
       if (i < total) {
-        const uint32_t r = s_idx[i];
+        const uint32_t e = s_idx[i];  // (the bucket travels with the row number: no second hash of the key)
+        const uint32_t r = e & 0xffffu, b = e >> 16;
         uint64_t w[W];
         uint64_t k;
         if (MODE == 1) {
@@ -332,9 +333,7 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
           const uint64_t* src = reinterpret_cast<const uint64_t*>(stage) + (size_t)r * W;
 #pragma unroll
           for (int x = 0; x < W; ++x) w[x] = src[x];
-          k = p.key_in_low32 ? (w[0] & 0xffffffffull) : w[0];
         }
-        const uint32_t b = bucket_of(k);
         if (i < s_end[b]) store_rec<W>(p.out + (uint64_t)(s_gbase[b] + i) * W, w);
       }
     }
