@@ -43,6 +43,8 @@ struct bgb_groupby {
   bool dense = false;               // the build wrote the groups densely at [0, G) and filled group_slots itself (kernels_hc.cu)
   bool peer_fused = false;          // ... or wrote them straight into the owner ranks' exchange regions (no local groups at all)
   uint32_t* peer_cursors = nullptr; // records produced per destination by the fused slices
+  bool dense_out = false;           // the finished handle holds its groups densely: group j sits at entry j (the reserved-key group, if any, last)
+  bool reserved_used = false;       // ... and its last group is the reserved entry (index table_slots - 1)
   uint64_t table_slots = 0;         // entries of table.keys / the accumulator arrays (capacity + 1, or fewer: see build_local)
 
   void* dalloc(size_t bytes, bool transient = false)
@@ -1224,7 +1226,7 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
     }
     h->prof.resolve();
     if (scan_state) h->dfree(scan_state);
-    const bool was_fused = h->peer_fused;
+    const bool was_fused = h->peer_fused, was_dense = h->dense;
     h->dense = false;  // (a retry below starts from scratch)
     if (getenv("BGB_DEBUG")) fprintf(stderr, "[bgb] path=%s groups=%u overflow=%u bypass_rows=%u flushes=%u\n", path.c_str(), st[1], st[0], st[4], st[5]);
     if (st[7] != 0 && path == "bucketed" && was_hc_attempt && !no_pack32) {
@@ -1248,7 +1250,11 @@ static int build_local(const bgb_column_view* keys, int32_t num_keys, int32_t in
       --attempt;
       continue;
     }
-    if (st[0] == 0 && st[3] == 0) { h->num_groups = (int32_t)st[1]; h->peer_fused = was_fused; break; }
+    if (st[0] == 0 && st[3] == 0) {
+      h->num_groups = (int32_t)st[1]; h->peer_fused = was_fused;
+      h->dense_out = was_dense; h->reserved_used = st[2] != 0;
+      break;
+    }
     h->peer_fused = false;
     if (st[0] == 0 && st[3] != 0 && !skip_tiny) {
       // the tiny-cardinality kernel met more distinct keys than it has rows for: same table, general path
@@ -1360,6 +1366,39 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
       }
     }
     if (pl.outs[i].nullable && !out_results[i].null_mask) return set_error(BGB_INVALID_ARGUMENT, "out_results[%d] needs a null mask", i);
+  }
+  // Dense handles whose every output is a plain copy of a cell array (the SUM / COUNT shapes over one 8-byte key): device-to-device
+  // copies instead of the gather kernel, whose one-group-per-thread loop keeps ~10 bytes per thread in flight (2.5 TB/s of traffic: 1.75 ms
+  // for 1e8 groups; the copies move the same 4.4 GB in ~0.7 ms)
+  {
+    bool plain = h->dense_out && !pl.wide && h->emit_keys.empty() && nk == 1 && pl.key_words == 1;
+    if (plain) {
+      const KeyPlan& k = ekeys[0];
+      plain = k.width == 8 && k.shift == 0 && k.null_bit < 0 && !k.nullable_out && k.bits == 0 && k.fclass == 0;
+    }
+    for (int i = 0; i < nr && plain; ++i) {
+      const OutPlan& o = pl.outs[i];
+      const bool copy8 = (o.op == OUT_COPY_I64 || o.op == OUT_COPY_F64) && o.out_width == 8 && acc_cell_bytes(pl.accs[o.acc_a].op) == 8;
+      const bool copy4 = o.op == OUT_COUNT && o.out_width == 4;
+      plain = !o.nullable && (copy8 || copy4);
+    }
+    if (plain) {
+      const size_t body = (size_t)G - (h->reserved_used ? 1 : 0), last = h->table_slots - 1;
+      h->prof.begin("emit_copy");
+      auto copy = [&](void* dst, const void* src, size_t w) -> cudaError_t {
+        cudaError_t e = body ? cudaMemcpyAsync(dst, src, body * w, cudaMemcpyDeviceToDevice, s) : cudaSuccess;
+        if (e == cudaSuccess && h->reserved_used)
+          e = cudaMemcpyAsync((uint8_t*)dst + body * w, (const uint8_t*)src + last * w, w, cudaMemcpyDeviceToDevice, s);
+        return e;
+      };
+      cudaError_t e = copy(out_keys[0].data, h->table.keys, 8);
+      for (int i = 0; i < nr && e == cudaSuccess; ++i) {
+        const OutPlan& o = pl.outs[i];
+        e = copy(out_results[i].data, pl.accs[o.acc_a].cells, o.out_width);
+      }
+      h->prof.end();
+      return check_cuda(e, "emit copies");
+    }
   }
   const int total = nk + nr;
   int32_t* d_nulls = (int32_t*)h->dalloc(sizeof(int32_t) * total);
@@ -1759,6 +1798,7 @@ extern "C" int bgb_groupby_build_peer(bgb_peer* peer, const bgb_column_view* key
 #undef FAIL_RC
   tr.flush("build_peer");
   h->num_groups = (int32_t)st[1];
+  h->dense_out = h->dense; h->reserved_used = st[2] != 0;
   if (total > 0) peer->merge_ratio = std::min(1.0, (double)st[1] / (double)total);
   h->path += h->peer_fused ? "+peer-fused" : "+peer";       // how the records travelled
   if (h->dense) h->path += "+slices";                        // how they were merged (else: HBM-table atomics + compaction)
