@@ -1397,6 +1397,10 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
         e = copy(out_results[i].data, pl.accs[o.acc_a].cells, o.out_width);
       }
       h->prof.end();
+      if (h->prof.on && e == cudaSuccess) {  // (profiled calls read the event times: they need the stream drained, like the kernel form)
+        e = cudaStreamSynchronize(s);
+        h->prof.resolve();
+      }
       return check_cuda(e, "emit copies");
     }
   }
