@@ -656,6 +656,20 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, co
       else { d.word = 0; d.src = S_I32; d.vbit = -1; }
       if (pack32 && acc.value_col >= 0) { d.word = 0; d.src = S_I64; }  // (the value is the sign-extended upper half of word 0: val_hi32)
     }
+  {  // the float64-statistics form of the slice kernel (KIND 2)
+    bool stats = pl.accs.size() >= 1 && pl.accs.size() <= 4;
+    int col = -1;
+    for (const AccPlan& acc : pl.accs) {
+      if (acc.op == ACC_COUNT_ALL) continue;
+      const bool op_ok = acc.op == ACC_SUM_F64 || acc.op == ACC_SUMSQ_F64 || acc.op == ACC_MIN || acc.op == ACC_MAX || acc.op == ACC_COUNT_VALID;
+      stats = stats && op_ok && acc.value_col >= 0 && (col < 0 || col == acc.value_col) && pl.values[acc.value_col].src == S_F64;
+      if (acc.value_col >= 0) col = acc.value_col;
+    }
+    if (stats && col >= 0) {
+      sp.f64stats = 1; sp.stat_vbit = vbit[col];
+      for (size_t a = 0; a < pl.accs.size(); ++a) sp.acc[a].word = (uint8_t)(1 + col);  // (COUNT_ALL too: acc[0].word names the column)
+    }
+  }
   if (fused) {
     bgb_peer* peer = fuse->peer;
     uint32_t* cursors = (uint32_t*)h->dalloc(sizeof(uint32_t) * kMaxPeers);

@@ -426,9 +426,14 @@ template <int W> __device__ __noinline__ void hc_reserved_row(const HcSliceParam
 // BASELINE configs[1], [4] and the north-star target): the other accumulator forms are compiled out -- the general kernel's
 // code does not fit the instruction cache well (5 % of its stall samples were instruction fetches) and its descriptor-driven
 // accumulator section cost ~250 of ~930 warp instructions per 128 rows.
-template <int W, int THREADS, bool LEAN>
+// KIND 2 (F64STATS): every accumulator reads ONE float64 value column (one validity bit) and is a float64 SUM / SUM_OF_SQUARES, a MIN,
+// a MAX or a COUNT -- BASELINE configs[2]. The general section below spends ~620 of its 1520 warp instructions per 128 rows on
+// descriptor fetches, per-row `src` switches the compiler does not hoist and an if-chain over the accumulator modes; here the value,
+// its order image and the validity of the U rows are computed once and every accumulator is one uniform switch around U predicated ops.
+template <int W, int THREADS, int KIND>
 __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_constant__ HcSliceParams p)
 {
+  constexpr bool LEAN = KIND == 1;
   constexpr int U = W <= 2 ? 4 : 2;
   extern __shared__ __align__(128) unsigned char smem[];
   const uint32_t S = 1u << p.log2_slice, smask = S - 1;
@@ -539,7 +544,59 @@ __global__ void __launch_bounds__(THREADS, 2) hc_slice_kernel(const __grid_const
         if (++guard > 4 * S + 8) { overflow = true; act &= ~pend; pend = 0; }  // more distinct keys than slots: the host retries bigger
       }
       // ---- accumulators, one at a time over the U rows
-      if (LEAN) {
+      if (KIND == 2) {
+        const int word = p.acc[0].word, vbit = p.stat_vbit;
+        double x[U];
+        unsigned long long img[U];
+        uint32_t valid = act;
+#pragma unroll
+        for (int j = 0; j < U; ++j) {
+          const uint64_t raw = pick_word<W>(rec[j], word);
+          x[j]   = __longlong_as_double((long long)raw);
+          img[j] = (raw >> 63) ? ~raw : (raw | 0x8000000000000000ull);  // ordered_image(raw, S_F64)
+          if (vbit >= 0 && !((vb[j] >> vbit) & 1u)) valid &= ~(1u << j);
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+          if (a >= p.num_accs) break;
+          const HcAcc& acc = p.acc[a];
+          switch (acc.op) {  // (warp-uniform)
+            case ACC_COUNT_ALL: {
+              const uint32_t a_cells = smem_u32(smem + acc.smem_off);
+#pragma unroll
+              for (int j = 0; j < U; ++j) if ((act >> j) & 1u) reds_add(a_cells + slot[j] * 4, 1u);
+              break;
+            }
+            case ACC_COUNT_VALID: {
+              const uint32_t a_cells = smem_u32(smem + acc.smem_off);
+#pragma unroll
+              for (int j = 0; j < U; ++j) if ((valid >> j) & 1u) reds_add(a_cells + slot[j] * 4, 1u);
+              break;
+            }
+            case ACC_SUM_F64: case ACC_SUMSQ_F64: {
+              double* c = reinterpret_cast<double*>(smem + acc.smem_off);
+              const bool sqr = acc.op == ACC_SUMSQ_F64;
+#pragma unroll
+              for (int j = 0; j < U; ++j) if ((valid >> j) & 1u) atomicAdd(c + slot[j], sqr ? x[j] * x[j] : x[j]);
+              break;
+            }
+            case ACC_MIN: {
+              unsigned long long* c = reinterpret_cast<unsigned long long*>(smem + acc.smem_off);
+#pragma unroll
+              for (int j = 0; j < U; ++j)
+                if (((valid >> j) & 1u) && img[j] < *reinterpret_cast<volatile unsigned long long*>(c + slot[j])) atomicMin(c + slot[j], img[j]);
+              break;
+            }
+            default: {  // ACC_MAX
+              unsigned long long* c = reinterpret_cast<unsigned long long*>(smem + acc.smem_off);
+#pragma unroll
+              for (int j = 0; j < U; ++j)
+                if (((valid >> j) & 1u) && img[j] > *reinterpret_cast<volatile unsigned long long*>(c + slot[j])) atomicMax(c + slot[j], img[j]);
+              break;
+            }
+          }
+        }
+      } else if (LEAN) {
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
           if (a >= p.num_accs) break;
@@ -757,9 +814,10 @@ cudaError_t launch_hc_init(const HcSliceParams& p, cudaStream_t s)
   return note_launch();
 }
 
-template <int W, int THREADS, bool LEAN>
+template <int W, int THREADS, int KIND>
 static cudaError_t launch_slices_wtl(const HcSliceParams& p, size_t smem_bytes, int num_sms, cudaStream_t s)
 {
+  constexpr int LEAN = KIND;
   cudaError_t e = cudaFuncSetAttribute(hc_slice_kernel<W, THREADS, LEAN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
   int occ = 0;
@@ -787,13 +845,18 @@ static cudaError_t launch_slices_w(const HcSliceParams& p, size_t smem_bytes, in
   lean = lean && !no_lean;
   const int thr = thr_env ? thr_env : (lean ? 512 : 384);
   if (lean) {
-    if (thr == 256) return launch_slices_wtl<W, 256, true>(p, smem_bytes, num_sms, s);
-    if (thr == 384) return launch_slices_wtl<W, 384, true>(p, smem_bytes, num_sms, s);
-    return launch_slices_wtl<W, 512, true>(p, smem_bytes, num_sms, s);
+    if (thr == 256) return launch_slices_wtl<W, 256, 1>(p, smem_bytes, num_sms, s);
+    if (thr == 384) return launch_slices_wtl<W, 384, 1>(p, smem_bytes, num_sms, s);
+    return launch_slices_wtl<W, 512, 1>(p, smem_bytes, num_sms, s);
   }
-  if (thr == 256) return launch_slices_wtl<W, 256, false>(p, smem_bytes, num_sms, s);
-  if (thr == 512) return launch_slices_wtl<W, 512, false>(p, smem_bytes, num_sms, s);
-  return launch_slices_wtl<W, 384, false>(p, smem_bytes, num_sms, s);
+  if (p.f64stats && !no_lean && W >= 2) {  // (set by the host: one float64 value column, SUM / SUMSQ / MIN / MAX / COUNT over it)
+    if (thr == 256) return launch_slices_wtl<W, 256, 2>(p, smem_bytes, num_sms, s);
+    if (thr == 512) return launch_slices_wtl<W, 512, 2>(p, smem_bytes, num_sms, s);
+    return launch_slices_wtl<W, 384, 2>(p, smem_bytes, num_sms, s);
+  }
+  if (thr == 256) return launch_slices_wtl<W, 256, 0>(p, smem_bytes, num_sms, s);
+  if (thr == 512) return launch_slices_wtl<W, 512, 0>(p, smem_bytes, num_sms, s);
+  return launch_slices_wtl<W, 384, 0>(p, smem_bytes, num_sms, s);
 }
 
 cudaError_t launch_hc_slices(const HcSliceParams& p, size_t smem_bytes, int num_sms, cudaStream_t s)

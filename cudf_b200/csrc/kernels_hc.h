@@ -103,6 +103,8 @@ struct HcSliceParams {
   int32_t words;
   int32_t key_in_low32;
   int32_t vbits_word;
+  int32_t f64stats;          // every accumulator is SUM / SUMSQ / MIN / MAX / COUNT of ONE float64 value column (stat_vbit: its validity bit, -1 none)
+  int32_t stat_vbit;
   int32_t val_hi32;          // pack32 records: the value of the (one) value column is the sign-extended upper half of word 0
   int32_t num_accs;
   uint32_t* group_slots;     // identity for the dense groups
