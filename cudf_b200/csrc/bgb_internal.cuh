@@ -6,6 +6,8 @@
 // Accumulator semantics follow cudf::detail::update_target_element
 // (/root/reference/cpp/include/cudf/detail/aggregation/device_aggregators.cuh:24-160,309-446).
 #pragma once
+#include <mutex>
+#include <unordered_set>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -197,5 +199,38 @@ cudaError_t launch_estimate_cardinality(const AggParams& p, int64_t sample_rows,
 cudaError_t launch_compact(const TableDesc& t, uint32_t* group_slots, uint32_t* scan_state, cudaStream_t s);
 size_t compact_scan_state_bytes(uint64_t capacity);
 cudaError_t launch_emit(const EmitParams& p, cudaStream_t s);
+
+
+// Opt a kernel in to the device's full dynamic shared memory (227 KB minus its static shared memory), once per device. The attribute
+// is per FUNCTION, not per launch: setting it to each launch's own size let two host threads with different sizes race -- thread A
+// lowers it between thread B's set and B's launch, and B's launch fails with cudaErrorInvalidValue (seen with simulated ranks whose
+// merge slices differed in size). Every caller sets the same maximum, so the order of the calls no longer matters.
+inline std::mutex g_smem_optin_mu;
+inline std::unordered_set<unsigned long long> g_smem_optin_done;  // (kernel address, device) pairs already set up
+
+template <typename Kernel>
+inline cudaError_t allow_max_dynamic_smem(Kernel kernel)
+{
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const unsigned long long key = ((unsigned long long)(uintptr_t)reinterpret_cast<const void*>(kernel) << 6) ^ (unsigned long long)(dev & 63);
+  {
+    std::lock_guard<std::mutex> lock(g_smem_optin_mu);
+    if (g_smem_optin_done.count(key)) return cudaSuccess;
+  }
+  int optin = 0;
+  e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (e != cudaSuccess) return e;
+  cudaFuncAttributes fa{};
+  e = cudaFuncGetAttributes(&fa, kernel);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);
+  if (e == cudaSuccess) {
+    std::lock_guard<std::mutex> lock(g_smem_optin_mu);
+    g_smem_optin_done.insert(key);
+  }
+  return e;
+}
 
 }  // namespace bgb

@@ -252,7 +252,7 @@ template <int MODE>
 static cudaError_t launch_scatter_mode(const BucketScatterParams& p, int64_t ntiles, int num_sms, cudaStream_t s)
 {
   const size_t smem = bucket_scatter_smem_bytes(p.log2_parts);
-  cudaError_t e = cudaFuncSetAttribute(bucket_scatter_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = allow_max_dynamic_smem(bucket_scatter_kernel<MODE>);
   if (e != cudaSuccess) return e;
   const int grid = (int)(ntiles < (int64_t)kBCtasPerSm * num_sms ? ntiles : (int64_t)kBCtasPerSm * num_sms);
   bucket_scatter_kernel<MODE><<<grid, kBThreads, smem, s>>>(p);
@@ -576,7 +576,7 @@ __global__ void __launch_bounds__(kAThreads, 3) bucket_aggregate_kernel(const __
 
 cudaError_t launch_bucket_aggregate(const BucketAggParams& p, size_t smem_bytes, cudaStream_t s)
 {
-  cudaError_t e = cudaFuncSetAttribute(bucket_aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  cudaError_t e = allow_max_dynamic_smem(bucket_aggregate_kernel);
   if (e != cudaSuccess) return e;
   bucket_aggregate_kernel<<<p.num_buckets, kAThreads, smem_bytes, s>>>(p);
   return note_launch();

@@ -353,7 +353,7 @@ static cudaError_t launch_scatter_w(const HcScatterParams& p, int num_sms, cudaS
   if (p.level == 2) {
     ntiles = (int64_t)p.num_segs * ((p.seg_capacity + T - 1) / T);
     if (ntiles == 0) return cudaSuccess;
-    e = cudaFuncSetAttribute(hc_scatter_kernel<W, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = allow_max_dynamic_smem(hc_scatter_kernel<W, 2>);
     if (e != cudaSuccess) return e;
     const int grid = (int)(ntiles < 2ll * num_sms ? ntiles : 2ll * num_sms);
     hc_scatter_kernel<W, 2><<<grid, kHcThreads, smem, s>>>(p);
@@ -363,17 +363,17 @@ static cudaError_t launch_scatter_w(const HcScatterParams& p, int num_sms, cudaS
   if (ntiles == 0) return cudaSuccess;
   const int grid = (int)(ntiles < 2ll * num_sms ? ntiles : 2ll * num_sms);
   if (p.peer_in.region != nullptr) {
-    e = cudaFuncSetAttribute(hc_scatter_kernel<W, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = allow_max_dynamic_smem(hc_scatter_kernel<W, 3>);
     if (e != cudaSuccess) return e;
     hc_scatter_kernel<W, 3><<<grid, kHcThreads, smem, s>>>(p);
     return note_launch();
   }
   if (p.tma_src) {
-    e = cudaFuncSetAttribute(hc_scatter_kernel<W, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = allow_max_dynamic_smem(hc_scatter_kernel<W, 1>);
     if (e != cudaSuccess) return e;
     hc_scatter_kernel<W, 1><<<grid, kHcThreads, smem, s>>>(p);
   } else {
-    e = cudaFuncSetAttribute(hc_scatter_kernel<W, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = allow_max_dynamic_smem(hc_scatter_kernel<W, 0>);
     if (e != cudaSuccess) return e;
     hc_scatter_kernel<W, 0><<<grid, kHcThreads, smem, s>>>(p);
   }
@@ -818,7 +818,7 @@ template <int W, int THREADS, int KIND>
 static cudaError_t launch_slices_wtl(const HcSliceParams& p, size_t smem_bytes, int num_sms, cudaStream_t s)
 {
   constexpr int LEAN = KIND;
-  cudaError_t e = cudaFuncSetAttribute(hc_slice_kernel<W, THREADS, LEAN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  cudaError_t e = allow_max_dynamic_smem(hc_slice_kernel<W, THREADS, LEAN>);
   if (e != cudaSuccess) return e;
   int occ = 0;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, hc_slice_kernel<W, THREADS, LEAN>, THREADS, smem_bytes);

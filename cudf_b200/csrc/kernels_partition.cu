@@ -369,7 +369,7 @@ template <int KW, int NV>
 static cudaError_t launch_scatter_fast(const PartParams& p, int num_sms, cudaStream_t s)
 {
   const size_t smem = partition_scatter_smem_bytes(p.log2_parts, 8);
-  cudaError_t e = cudaFuncSetAttribute(partition_scatter_fast_kernel<KW, NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = allow_max_dynamic_smem(partition_scatter_fast_kernel<KW, NV>);
   if (e != cudaSuccess) return e;
   const int64_t tile   = (int64_t)kPThreads * 8;
   const int64_t ntiles = (p.a.num_rows + tile - 1) / tile;
@@ -398,7 +398,7 @@ template <int ROWS>
 static cudaError_t launch_scatter_rows(const PartParams& p, int num_sms, cudaStream_t s)
 {
   const size_t smem = partition_scatter_smem_bytes(p.log2_parts, ROWS);
-  cudaError_t e = cudaFuncSetAttribute(partition_scatter_kernel<ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = allow_max_dynamic_smem(partition_scatter_kernel<ROWS>);
   if (e != cudaSuccess) return e;
   const int64_t tile   = (int64_t)kPThreads * ROWS;
   const int64_t ntiles = (p.a.num_rows + tile - 1) / tile;

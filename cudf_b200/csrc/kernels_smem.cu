@@ -493,7 +493,7 @@ template <int SK, int KEYMODE, int VW, bool DIRECT, bool TMA = false>
 static cudaError_t launch_one(const SmemParams& p, int grid, size_t smem, cudaStream_t s)
 {
   auto kern = agg_smem_kernel<SK, KEYMODE, VW, DIRECT, TMA>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = allow_max_dynamic_smem(kern);
   if (e != cudaSuccess) return e;
   kern<<<grid, kThreads, smem, s>>>(p);
   return note_launch();

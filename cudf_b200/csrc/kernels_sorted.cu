@@ -415,7 +415,7 @@ cudaError_t launch_aggregate_sorted(const SortedParams& p, int num_sms, cudaStre
     default: return cudaErrorInvalidValue;
   }
   const size_t bytes = sorted_smem_bytes(p.groups, p.num_accs, p.num_cols < 1 ? 1 : p.num_cols, p.hashed != 0);
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  cudaError_t e = allow_max_dynamic_smem(kern);
   if (e != cudaSuccess) return e;
   int per_sm = 1;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSortedThreads, bytes);

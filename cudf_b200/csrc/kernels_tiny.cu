@@ -242,7 +242,7 @@ cudaError_t launch_aggregate_tiny(const TinyParams& p, int num_sms, cudaStream_t
 {
   if (p.a.num_rows == 0) return cudaSuccess;
   const size_t smem = tiny_smem_bytes(p.cells, p.group_cap);
-  cudaError_t e = cudaFuncSetAttribute(agg_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = allow_max_dynamic_smem(agg_tiny_kernel);
   if (e != cudaSuccess) return e;
   const int64_t want = (p.a.num_rows + kTinyThreads * kTinyRows - 1) / (kTinyThreads * kTinyRows);
   const int grid     = (int)(want < num_sms ? want : num_sms);

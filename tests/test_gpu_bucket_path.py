@@ -155,3 +155,25 @@ def test_long_buckets_are_walked_in_chunks():
     k2 = (np.arange(n) % 8).astype(np.int64)
     v2 = np.where(np.arange(n) % 2 == 0, np.int64(-32768), np.int64(32767)).astype(np.int64) * np.int64(65537)
     _check([H(k2)], [H(v2)], [(0, "sum", 1), (0, "count_valid", 1)], name="digit extremes", capacity_log2=12, slice_log2=8, expect=None)
+
+
+@pytest.mark.parametrize("what", ["key", "value", "negative-value", "narrow"])
+def test_packed_8_byte_records_and_the_row_that_does_not_fit(what):
+    """SUM / COUNT of one integer column whose sampled key and value ranges fit 32 bits travel as 8-byte records {key32, value32}
+    (groupby.cu: pack32). The sample only predicts: a single row outside the sample whose key or value needs more bits raises
+    status[7] in level 1 and the call reruns with 16-byte records -- same answer either way."""
+    n = 400_000
+    rng = np.random.default_rng(5)
+    k = rng.integers(0, 60_000, n).astype(np.int64)
+    v = rng.integers(-1000, 1001, n).astype(np.int64)
+    odd = 100_001  # (the estimator samples every 6th row of 400 000: row 100 001 is not one of them)
+    if what == "key":
+        k[odd] = (1 << 40) + 5
+    elif what == "value":
+        v[odd] = (1 << 40)
+    elif what == "negative-value":
+        v[odd] = -(1 << 33) - 7
+    elif what == "narrow":
+        v = v.astype(np.int16)  # narrow value types always fit; the sum still promotes to int64
+    G = _check([H(k)], [H(v)], [(0, "sum", 1), (0, "count_valid", 1), (0, "count_all", 1)], name=f"pack32/{what}")
+    assert G == len(np.unique(k))
