@@ -25,6 +25,18 @@ const char* last_error() { return g_msg; }
 static std::atomic<long long> g_launches{0};
 cudaError_t note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); return cudaGetLastError(); }
 long long launches() { return g_launches.load(); }
+int device_sm_count()
+{
+  static std::atomic<int> cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) { cudaGetLastError(); n = 148; }
+    cached[dev].store(n, std::memory_order_relaxed);
+  }
+  return n;
+}
 }  // namespace bgb
 
 extern "C" const char* bgb_last_error(void) { return bgb::last_error(); }

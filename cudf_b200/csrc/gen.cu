@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(256) gen_cat_kernel(int8_t* out, int64_t n, ui
   }
 }
 
-static int grid_for(int64_t n) { int64_t b = (n + 255) / 256; return (int)(b < 148 * 16 ? (b > 0 ? b : 1) : 148 * 16); }
+static int grid_for(int64_t n) { int64_t b = (n + 255) / 256; return (int)(b < device_sm_count() * 16 ? (b > 0 ? b : 1) : device_sm_count() * 16); }
 
 }  // namespace bgb
 

@@ -630,7 +630,7 @@ cudaError_t launch_bucket_overflow(const BucketAggParams& p, cudaStream_t s)
 {
   if (p.ov_capacity == 0) return cudaSuccess;
   const uint32_t want = (p.ov_capacity + 255) / 256;
-  bucket_overflow_kernel<<<want < 148u * 8 ? want : 148u * 8, 256, 0, s>>>(p);
+  bucket_overflow_kernel<<<want < (uint32_t)device_sm_count() * 8 ? want : (uint32_t)device_sm_count() * 8, 256, 0, s>>>(p);
   return note_launch();
 }
 

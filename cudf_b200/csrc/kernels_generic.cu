@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(256) init_table_kernel(const __grid_constant__
 cudaError_t launch_init_table(const AggParams& p, cudaStream_t s)
 {
   uint64_t n = p.table.capacity + 1;
-  int blocks = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
+  int blocks = (int)((n + 255) / 256 < (uint64_t)device_sm_count() * 16 ? (n + 255) / 256 : (uint64_t)device_sm_count() * 16);
   init_table_kernel<<<blocks, 256, 0, s>>>(p);
   return note_launch();
 }
@@ -82,7 +82,7 @@ cudaError_t launch_aggregate_global(const AggParams& p, cudaStream_t s)
 {
   if (p.num_rows == 0) return cudaSuccess;
   int64_t want = (p.num_rows + 255) / 256;
-  int blocks   = (int)(want < 148 * 8 ? want : 148 * 8);
+  int blocks   = (int)(want < device_sm_count() * 8 ? want : device_sm_count() * 8);
   aggregate_global_kernel<<<blocks, 256, 0, s>>>(p);
   return note_launch();
 }
@@ -123,7 +123,7 @@ cudaError_t launch_argrow(const AggParams& p, cudaStream_t s)
 {
   if (p.num_rows == 0) return cudaSuccess;
   int64_t want = (p.num_rows + 255) / 256;
-  argrow_kernel<<<(int)(want < 148 * 8 ? want : 148 * 8), 256, 0, s>>>(p);
+  argrow_kernel<<<(int)(want < device_sm_count() * 8 ? want : device_sm_count() * 8), 256, 0, s>>>(p);
   return note_launch();
 }
 

@@ -132,9 +132,9 @@ cudaError_t launch_peer_scatter(const PeerScatterParams& p, cudaStream_t s)
 {
   if (p.num_groups <= 0) return cudaSuccess;
   uint32_t tile_rows = kSTile;
-  while (tile_rows > (uint32_t)kThreads && (int64_t)p.num_groups < 148ll * 2 * tile_rows) tile_rows /= 2;
+  while (tile_rows > (uint32_t)kThreads && (int64_t)p.num_groups < (int64_t)device_sm_count() * 2 * tile_rows) tile_rows /= 2;
   int64_t blocks = ((int64_t)p.num_groups + tile_rows - 1) / tile_rows;
-  if (blocks > 148 * 6) blocks = 148 * 6;
+  if (blocks > device_sm_count() * 6) blocks = device_sm_count() * 6;
   peer_scatter_kernel<<<(int)blocks, kThreads, 0, s>>>(p, tile_rows);
   return note_launch();
 }
@@ -292,7 +292,7 @@ cudaError_t launch_table_merge(const TableMergeParams& p, cudaStream_t s)
 {
   if (p.num_groups <= 0) return cudaSuccess;
   int64_t blocks = ((int64_t)p.num_groups + kThreads - 1) / kThreads;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > device_sm_count() * 8) blocks = device_sm_count() * 8;
   table_merge_kernel<<<(int)blocks, kThreads, 0, s>>>(p);
   return note_launch();
 }
@@ -302,7 +302,7 @@ cudaError_t launch_peer_merge(const PeerMergeParams& p, cudaStream_t s)
   const uint32_t total = p.prefix[p.world];
   if (total == 0) return cudaSuccess;
   uint32_t blocks = (total + kThreads - 1) / kThreads;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > (uint32_t)device_sm_count() * 8) blocks = (uint32_t)device_sm_count() * 8;
   peer_merge_kernel<<<blocks, kThreads, 0, s>>>(p);
   return note_launch();
 }

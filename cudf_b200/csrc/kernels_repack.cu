@@ -102,13 +102,13 @@ __global__ void __launch_bounds__(kRThreads) repack_pack_kernel(const __grid_con
   }
 }
 
-static int repack_grid(int64_t n) { const int64_t want = (n + kRThreads * 4 - 1) / (kRThreads * 4); return (int)(want < 148 * 16 ? want : 148 * 16); }
+static int repack_grid(int64_t n) { const int64_t want = (n + kRThreads * 4 - 1) / (kRThreads * 4); return (int)(want < device_sm_count() * 16 ? want : device_sm_count() * 16); }
 
 cudaError_t launch_repack_minmax(const RepackParams& p, cudaStream_t s)
 {
   if (p.num_rows == 0) return cudaSuccess;
   const int64_t want = (p.num_rows + kRThreads * 8 - 1) / (kRThreads * 8);
-  const dim3 grid((unsigned)(want < 148 * 8 ? want : 148 * 8), (unsigned)p.num_cols);
+  const dim3 grid((unsigned)(want < device_sm_count() * 8 ? want : device_sm_count() * 8), (unsigned)p.num_cols);
   repack_minmax_kernel<<<grid, kRThreads, 0, s>>>(p);
   return note_launch();
 }

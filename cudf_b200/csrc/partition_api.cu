@@ -139,7 +139,7 @@ extern "C" int bgb_bytes_to_bitmask(const uint8_t* valid_bytes, int64_t n, uint3
   if (!d_cnt) return set_error(BGB_OUT_OF_MEMORY, "null counter");
   cudaMemsetAsync(d_cnt, 0, sizeof(int), s);
   const int64_t want = (n + 255) / 256;
-  bytes_to_bitmask_kernel<<<(int)(want < 148 * 8 ? want : 148 * 8), 256, 0, s>>>(valid_bytes, n, mask_words, d_cnt);
+  bytes_to_bitmask_kernel<<<(int)(want < device_sm_count() * 8 ? want : device_sm_count() * 8), 256, 0, s>>>(valid_bytes, n, mask_words, d_cnt);
   int rc = check_cuda(note_launch(), "bytes_to_bitmask");
   int h = 0;
   if (!rc) rc = check_cuda(cudaMemcpyAsync(&h, d_cnt, sizeof(int), cudaMemcpyDeviceToHost, s), "null count copy");
