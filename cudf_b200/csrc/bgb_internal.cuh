@@ -145,6 +145,8 @@ struct EmitParams {
   int32_t num_groups;
   int32_t num_outs;
   int32_t key_words;
+  int32_t dense;                // group j sits at entry j (no slot list to read), except ...
+  uint32_t last_slot;           // ... the last group when it is the reserved entry: its index (else 0xFFFFFFFF)
 };
 
 // ------------------------------------------------------------------ device helpers shared by kernels

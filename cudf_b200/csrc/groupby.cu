@@ -1460,6 +1460,7 @@ extern "C" int bgb_groupby_emit(bgb_groupby* h, bgb_mutable_column* out_keys, bg
     EmitParams ep;
     memset(&ep, 0, sizeof ep);
     ep.keys = h->table.keys; ep.group_slots = h->group_slots; ep.num_groups = G; ep.key_words = pl.key_words;
+    ep.dense = h->dense_out ? 1 : 0; ep.last_slot = (h->dense_out && h->reserved_used) ? (uint32_t)(h->table_slots - 1) : 0xFFFFFFFFu;
     ep.num_outs = (int)std::min<size_t>(kMaxOuts, descs.size() - b);
     for (int i = 0; i < ep.num_outs; ++i) ep.out[i] = descs[b + i];
     rc = check_cuda(launch_emit(ep, s), "emit");

@@ -133,7 +133,8 @@ __global__ void __launch_bounds__(256) emit_kernel(const __grid_constant__ EmitP
   const int lane    = threadIdx.x & 31;
   uint64_t slot = 0, k0 = 0, k1 = 0;
   if (active) {
-    slot = p.group_slots[j];
+    // dense handles: one dependent load less per thread (the kernel is latency-bound: ~10 bytes per thread in flight)
+    slot = p.dense ? ((p.last_slot != 0xFFFFFFFFu && j == p.num_groups - 1) ? (uint64_t)p.last_slot : (uint64_t)j) : (uint64_t)p.group_slots[j];
     if (p.key_words == 1) k0 = p.keys[slot];
     else { ulonglong2 k = reinterpret_cast<const ulonglong2*>(p.keys)[slot]; k0 = k.x; k1 = k.y; }
     // (the reserved slot's key array entry is EMPTY == the all-ones key it stands for)

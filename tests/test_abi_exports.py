@@ -72,3 +72,36 @@ def test_sum_overflow_target_type_and_eligibility(tid, expect):
         assert rc == 0 and ok.value == 1
     else:
         assert ok.value == 0 or rc != 0
+
+
+def test_eligibility_of_wide_keys_and_dictionary_values_without_gpu():
+    """bgb_can_use_hash_groupby (hash/groupby.cu:115-131) only plans: four int64 key columns (256 bits of key: the row-number table)
+    and a DICTIONARY32 value column (typed by its keys, hash/groupby.cu:118-120) are served; a dictionary of strings, a dictionary
+    without its child views and a ninth key column are not."""
+    from cudf_b200 import _lib
+    L = _lib.lib()
+    INT64, UINT8, FLOAT64, DICT, STRING = 4, 5, 10, 22, 23
+    SUM, MIN = 0, 2
+
+    def can(keys, values, kind):
+        aggs = (_lib.Aggregation * 1)(_lib.Aggregation(kind, 1))
+        reqs = (_lib.Request * 1)(_lib.Request(values, aggs, 1, 0))
+        ok = C.c_int32(-1)
+        rc = L.bgb_can_use_hash_groupby(keys, len(keys), reqs, 1, C.byref(ok))
+        return rc, ok.value
+
+    plain = _lib.ColumnView(INT64, 0, 4, 0, 0, 0, None, None)
+    four = (_lib.ColumnView * 4)(*[_lib.ColumnView(INT64, 0, 4, 0, 0, 0, None, None) for _ in range(4)])
+    assert can(four, plain, SUM) == (0, 1)
+    nine = (_lib.ColumnView * 9)(*[_lib.ColumnView(INT64, 0, 4, 0, 0, 0, None, None) for _ in range(9)])
+    assert can(nine, plain, SUM)[1] == 0
+    one = (_lib.ColumnView * 1)(plain)
+    children = (_lib.ColumnView * 2)(_lib.ColumnView(UINT8, 0, 4, 0, 0, 0, None, None), _lib.ColumnView(FLOAT64, 0, 3, 0, 0, 0, None, None))
+    dcol = _lib.ColumnView(DICT, 0, 4, 0, 0, 0, C.cast(children, C.c_void_p).value, None)
+    assert can(one, dcol, SUM) == (0, 1) and can(one, dcol, MIN) == (0, 1)
+    str_children = (_lib.ColumnView * 2)(_lib.ColumnView(UINT8, 0, 4, 0, 0, 0, None, None), _lib.ColumnView(STRING, 0, 3, 0, 0, 0, None, None))
+    sdict = _lib.ColumnView(DICT, 0, 4, 0, 0, 0, C.cast(str_children, C.c_void_p).value, None)
+    rc, ok = can(one, sdict, MIN)
+    assert ok == 0 or rc != 0
+    rc, ok = can(one, _lib.ColumnView(DICT, 0, 4, 0, 0, 0, None, None), SUM)
+    assert ok == 0 or rc != 0
