@@ -655,6 +655,11 @@ int run_hc(bgb_groupby* h, int num_sms, const bgb_options& opt, double g_est, co
       if (acc.value_col >= 0) { d.word = (uint8_t)(1 + acc.value_col); d.src = pl.values[acc.value_col].src; d.vbit = (int16_t)vbit[acc.value_col]; }
       else { d.word = 0; d.src = S_I32; d.vbit = -1; }
       if (pack32 && acc.value_col >= 0) { d.word = 0; d.src = S_I64; }  // (the value is the sign-extended upper half of word 0: val_hi32)
+      // integer SUMs: the record word is the value as a 64-bit integer whatever the column's width (kernels_hc.cu: record_value;
+      // unsigned and bool columns are zero-extended by the loader) -> the plain 64-bit add of the lean kernel
+      if (d.mode == HM_ISUM && acc.op == ACC_SUM_I64 && acc.value_col >= 0 &&
+          (d.src == S_I8 || d.src == S_I16 || d.src == S_I32 || d.src == S_U8 || d.src == S_U16 || d.src == S_U32))
+        d.src = S_I64;
     }
   {  // the float64-statistics form of the slice kernel (KIND 2)
     bool stats = pl.accs.size() >= 1 && pl.accs.size() <= 4;

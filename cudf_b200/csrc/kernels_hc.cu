@@ -55,6 +55,18 @@ __device__ __forceinline__ uint64_t lds_raw(const unsigned char* tile, int width
   }
 }
 
+// value word of a record: signed 1/2/4-byte integers travel SIGN-EXTENDED, so that a plain SUM over them is the 64-bit add of the
+// lean slice kernel (every other consumer re-truncates the word to the source width first: ordered_image, raw_to_i64)
+__device__ __forceinline__ uint64_t record_value(uint64_t raw, int src)
+{
+  switch (src) {
+    case S_I8: return (uint64_t)(int64_t)(int8_t)raw;
+    case S_I16: return (uint64_t)(int64_t)(int16_t)raw;
+    case S_I32: return (uint64_t)(int64_t)(int32_t)raw;
+    default: return raw;
+  }
+}
+
 template <int W> __device__ __forceinline__ void store_rec(uint64_t* dst, const uint64_t (&w)[W])
 {
   if (W == 1) dst[0] = w[0];
@@ -228,7 +240,7 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
               w[(c + 1) % W] = 0;
               if (c < p.num_vals) {
                 const HcValue& v = p.val[c];
-                w[(c + 1) % W] = load_raw(v.data, v.width, (int64_t)v.offset + row);
+                w[(c + 1) % W] = record_value(load_raw(v.data, v.width, (int64_t)v.offset + row), v.src);
                 if (v.vbit >= 0) vb |= (uint32_t)bit_is_set(v.mask, (int64_t)v.offset + row) << v.vbit;
               }
             }
@@ -316,7 +328,7 @@ __global__ void __launch_bounds__(kHcThreads, 2) hc_scatter_kernel(const __grid_
           for (int c = 0; c < W - 1; ++c) {
             w[(c + 1) % W] = 0;
             if (c < p.num_vals) {
-              w[(c + 1) % W] = lds_raw(stage + voff[c], p.val[c].width, r);
+              w[(c + 1) % W] = record_value(lds_raw(stage + voff[c], p.val[c].width, r), p.val[c].src);
               if (p.val[c].vbit >= 0) vb |= (uint32_t)((stage[moff[c] + (r >> 3)] >> (r & 7)) & 1u) << p.val[c].vbit;
             }
           }
