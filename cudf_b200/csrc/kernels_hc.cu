@@ -846,7 +846,7 @@ static cudaError_t launch_slices_w(const HcSliceParams& p, size_t smem_bytes, in
   // threads per CTA (two CTAs per SM): measured per 1e9 rows on B200 -- SUM + COUNT (lean kernel): 8.4 ms at 512, 9.5 at 384, 9.6 at
   // 256; float64 SUM + MIN + MAX (general kernel, 78 registers): 17.2-17.9 ms whatever the count (its CAS-loop accumulators bound it)
   static const int thr_env = getenv("BGB_HC_SLICE_THREADS") ? atoi(getenv("BGB_HC_SLICE_THREADS")) : 0;
-  bool lean = p.num_accs <= 3 && W <= 2;
+  bool lean = p.num_accs <= 3 && W <= 3;  // (W == 3: key + two value words -- the fold of partial SUM + COUNT tables)
   for (int a = 0; a < p.num_accs; ++a) {
     const HcAcc& acc = p.acc[a];
     const bool count = (acc.mode == HM_COUNT || acc.mode == HM_ADD32) && (acc.vbit < 0 || acc.op == ACC_COUNT_ALL);
