@@ -6,10 +6,11 @@
 //      a raw tile of every source column and mask; level 2: the records); everybody waits on the barrier's phase
 //   A  bucket of every row from the top bits of its table slot, rank inside the bucket by a returning ATOMS.ADD
 //   B  block scan of the <= 1024 bucket counters; ONE global atomicAdd per (tile, bucket) reserves the run in the bucket
-//   C  16-bit permutation: sorted position -> row of the tile (no 16-byte sorted copy: T = 4096 rows fit two CTAs per SM,
-//      which makes a run 256 B at 256 buckets -- measured 6.2 ms per 1e9 rows per level against 7.5 ms with 128 B runs)
-//   D  position i gathers row idx[i] from the stage, assembles the record and stores it at run base + i: consecutive threads
-//      write consecutive 16-byte records
+//   C  permutation, one 32-bit entry per row: sorted position -> bucket << 16 | row of the tile (no sorted copy of the records:
+//      T = 4096 rows fit two CTAs per SM, which makes a run 256 B at 256 buckets -- measured 6.2 ms per 1e9 rows per level
+//      against 7.5 ms with 128 B runs; the bucket rides along so that D does not hash the key again)
+//   D  position i gathers row idx[i] from the stage, assembles the record (level 1 with pack32: {key32, value32} in 8 bytes,
+//      every row checked to fit) and stores it at run base + i: consecutive threads write consecutive records
 // Bucket capacities are fixed (expected rows + margin); a bucket that fills sets status[6] and the host reruns the call on
 // the exact-offset path (kernels_partition.cu) -- skewed keys are the partitioned path's job.
 //
