@@ -2,7 +2,9 @@
 // ARRAY-OF-STRUCTURES records of W 8-byte words -- word 0 the packed key image (validity bits of the value columns in its upper
 // half when the image needs <= 32 bits), one word per value column, optionally a last word of validity bits -- so that a
 // destination run is one contiguous byte range (256 B per bucket and tile at 256 buckets), every tile arrives in shared
-// memory through ONE cp.async.bulk (TMA) per source, and the slice kernel reads a row as one 128-bit load.
+// memory through ONE cp.async.bulk (TMA) per source, and the slice kernel reads a row as one 128-bit load. One integer value column
+// without nulls under SUM / COUNT whose sampled key and value ranges fit 32 bits travels as ONE word {key32, value32} (pack32: every
+// row is checked in level 1, status[7] = 1 reruns the call with two words).
 //   hc_scatter (level 1)  caller's columns -> records in P1 buckets      (TMA raw column tiles, or a generic LDG packer)
 //   hc_scatter (level 2)  records of every level-1 bucket -> P2 buckets  (TMA)
 //   hc_slices             one CTA per final bucket: table slice in shared memory, DENSE group output (no HBM hash table,
