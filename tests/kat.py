@@ -24,8 +24,8 @@ def _arr(vals, dtype):
     return out
 
 
-def load_cases():
-    with open(os.path.join(HERE, "golden", "reference_kat.json")) as f:
+def load_cases(filename="reference_kat.json"):
+    with open(os.path.join(HERE, "golden", filename)) as f:
         doc = json.load(f)
     out = []
     for c in doc["cases"]:

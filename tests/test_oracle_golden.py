@@ -15,6 +15,17 @@ def test_oracle_matches_reference_kat(name, c, kt, vt):
     kat.check(name, G, kout[0], aout[0], exp)
 
 
+ARG_CASES = kat.load_cases("reference_kat_arg.json")
+
+
+@pytest.mark.parametrize("name,c,kt,vt", ARG_CASES, ids=[x[0] for x in ARG_CASES])
+def test_oracle_matches_reference_argmin_argmax_kat(name, c, kt, vt):
+    """argmin_tests.cpp / argmax_tests.cpp: the result is the row number of the group's extremum (int32), null without a valid value"""
+    keys, vals, exp = kat.materialize(c, kt, vt)
+    G, kout, aout = orc.groupby([keys], [vals], [(0, c["agg"], c["ddof"])], include_null_keys=c["include_null_keys"])
+    kat.check(name, G, kout[0], aout[0], exp)
+
+
 @pytest.mark.parametrize("threads", [1, 4])
 def test_oracle_threads_agree_with_numpy(threads):
     rng = np.random.default_rng(7)
